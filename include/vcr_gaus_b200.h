@@ -1,0 +1,211 @@
+/*
+ * vcr_gaus_b200.h — C ABI of libvcr_gaus_b200.so, the sm_100a rasterizer / D-Normal / kNN library.
+ *
+ * This is the drop-in boundary of the hot path.  Every entry point replaces one native interface
+ * of the reference (paths relative to the reference root; DGR = submodules/diff-gaussian-rasterization):
+ *
+ *   vcr_rasterize_forward        <- CudaRasterizer::Rasterizer::forward       DGR/cuda_rasterizer/rasterizer.h:31-59
+ *                                   (called from RasterizeGaussiansCUDA,        DGR/rasterize_points.cu:49-152)
+ *   vcr_rasterize_backward       <- CudaRasterizer::Rasterizer::backward      DGR/cuda_rasterizer/rasterizer.h:137-177
+ *                                   (called from RasterizeGaussiansBackwardCUDA, DGR/rasterize_points.cu:418-529)
+ *   vcr_mark_visible             <- CudaRasterizer::Rasterizer::markVisible   DGR/cuda_rasterizer/rasterizer.h:24-29
+ *   vcr_rasterize_count          <- CudaRasterizer::Rasterizer::forwardCount  DGR/cuda_rasterizer/rasterizer.h:62-86
+ *   vcr_rasterize_visi_acc       <- CudaRasterizer::Rasterizer::forwardVisiAcc DGR/cuda_rasterizer/rasterizer.h (f_count=3)
+ *   vcr_dist2_knn3               <- SimpleKNN::knn                            submodules/simple-knn/simple_knn.h:17
+ *   vcr_dnormal_forward/backward <- tools/normal_utils.py:30-41 + tools/loss_utils.py:122-142 + trainer.py:266-280
+ *                                   (a PyTorch op chain in the reference; one fused kernel each way here)
+ *
+ * Conventions
+ *   - All pointers are DEVICE pointers unless the name ends in _host.  The caller owns all memory;
+ *     the library never frees, and never keeps a pointer past the call.
+ *   - Absent optional inputs are NULL (the reference passes zero-sized tensors whose data_ptr is
+ *     nullptr, DGR/cuda_rasterizer/forward.cu:208,244,302,418).
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream, which is where the
+ *     reference launches everything).
+ *   - Opaque per-view state (geometry / binning / image buffers) is obtained through caller-supplied
+ *     grow callbacks, exactly like the reference's std::function<char*(size_t)> resize lambdas
+ *     (DGR/rasterize_points.cu:28-34, rasterizer.h:32-34).  The byte layout is private to this
+ *     library (documented in DESIGN.md); forward and backward agree on it.
+ *   - Return value: 0 = success, non-zero = error; vcr_last_error() returns a thread-local message.
+ *     Negative num_rendered is never returned.
+ */
+#ifndef VCR_GAUS_B200_H
+#define VCR_GAUS_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VCR_ABI_VERSION 1
+#define VCR_OUT_CHANNELS 10 /* RGB 0-2, depth 3, normal 4-6, alpha 7, semantics 8-9 (DGR auxiliary.h:21-28) */
+#define VCR_NUM_OBJECTS 2   /* DGR cuda_rasterizer/config.h:16 */
+#define VCR_TILE 16         /* DGR cuda_rasterizer/config.h:19-20 */
+
+/* Grow callback: return a device pointer to at least `bytes` bytes (256-byte aligned), valid until the
+ * matching backward call has finished.  `user` is passed through untouched. */
+typedef char* (*vcr_alloc_fn)(void* user, size_t bytes);
+
+int vcr_abi_version(void);
+const char* vcr_last_error(void);
+
+/* Number of key bits used for tile ids (reference: getHigherMsb, DGR/cuda_rasterizer/rasterizer_impl.cu:35-50). */
+uint32_t vcr_higher_msb(uint32_t n);
+
+/* Buffer sizes the grow callbacks will be asked for (exposed for tests and pre-allocation). */
+size_t vcr_geom_bytes(int P);
+size_t vcr_image_bytes(int width, int height);
+size_t vcr_binning_bytes(int num_rendered);
+
+/* Full forward pass of one view.  On success *num_rendered_host receives R (the number of
+ * (Gaussian, tile) instances).  out_color is f32[10,H,W] and radii is i32[P]; both are fully
+ * written (no pre-zeroing needed).  One host synchronisation on `stream` happens inside (to learn
+ * R before sizing the binning buffer), as in the reference (rasterizer_impl.cu:287). */
+int vcr_rasterize_forward(
+    vcr_alloc_fn geometry_buffer, vcr_alloc_fn binning_buffer, vcr_alloc_fn image_buffer, void* alloc_user,
+    int P, int D, int M,
+    const float* background,
+    int width, int height,
+    const float* means3D,
+    const float* shs,
+    const float* colors_precomp,
+    const float* normals_precomp,
+    const float* sh_objs,
+    const float* opacities,
+    const float* scales,
+    float scale_modifier,
+    const float* rotations,
+    const float* cov3D_precomp,
+    const float* viewmatrix,
+    const float* projmatrix,
+    const float* dirs,
+    const float* cam_pos,
+    float tan_fovx, float tan_fovy,
+    int prefiltered,
+    float* out_color,
+    int* radii,
+    const uint8_t* inside,
+    int debug,
+    int* num_rendered_host,
+    void* stream);
+
+/* Backward pass of one view.  Every output gradient array is fully written by the library
+ * (zeros for Gaussians that were not rendered), so the caller may pass uninitialised memory.
+ * `scratch` must hold vcr_backward_scratch_bytes(P) bytes. */
+size_t vcr_backward_scratch_bytes(int P);
+int vcr_rasterize_backward(
+    int P, int D, int M, int R,
+    const float* background,
+    int width, int height,
+    const float* means3D,
+    const float* shs,
+    const float* colors_precomp,
+    const float* normals_precomp,
+    const float* sh_objs,
+    const float* alpha,          /* out_color channel 7 of the forward, f32[H*W] */
+    const float* depth,          /* out_color channel 3 of the forward, f32[H*W] */
+    const float* scales,
+    float scale_modifier,
+    const float* rotations,
+    const float* cov3D_precomp,
+    const float* viewmatrix,
+    const float* projmatrix,
+    const float* dirs,
+    const float* campos,
+    float tan_fovx, float tan_fovy,
+    const int* radii,
+    char* geom_buffer, char* binning_buffer, char* img_buffer,
+    const float* dL_dpix,        /* f32[10,H,W] */
+    float* dL_dmean2D,           /* f32[P,3] */
+    float* dL_dmean2D_densify,   /* f32[P,3] */
+    float* dL_dopacity,          /* f32[P,1] */
+    float* dL_dcolor,            /* f32[P,3] */
+    float* dL_dnormal,           /* f32[P,3] */
+    float* dL_dobjects,          /* f32[P,2] */
+    float* dL_dmean3D,           /* f32[P,3] */
+    float* dL_dcov3D,            /* f32[P,6] */
+    float* dL_dsh,               /* f32[P,M,3] (may be NULL when M == 0) */
+    float* dL_dscale,            /* f32[P,3] */
+    float* dL_drot,              /* f32[P,4] */
+    const uint8_t* inside,
+    char* scratch,
+    int debug,
+    void* stream);
+
+/* present[i] = (view-space z of means3D[i]) > 0.2   (checkFrustum, rasterizer_impl.cu:54-66). */
+int vcr_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                     uint8_t* present, void* stream);
+
+/* f_count = 1: RGB image + per-Gaussian contribution count and summed opacity
+ * (forwardCount / renderCUDA_count, forward.cu:480-603).  The reference's increments are racy
+ * non-atomic read-modify-writes; this library uses atomics, i.e. returns the exact counts. */
+int vcr_rasterize_count(
+    vcr_alloc_fn geometry_buffer, vcr_alloc_fn binning_buffer, vcr_alloc_fn image_buffer, void* alloc_user,
+    int P, int D, int M,
+    const float* background, int width, int height,
+    const float* means3D, const float* shs, const float* colors_precomp, const float* opacities,
+    const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
+    const float* viewmatrix, const float* projmatrix, const float* cam_pos,
+    float tan_fovx, float tan_fovy, int prefiltered,
+    float* out_color /* f32[3,H,W] */, int* gaussians_count /* i32[P] */, float* important_score /* f32[P] */,
+    int* radii, int debug, int* num_rendered_host, void* stream);
+
+/* f_count = 3: mark the first contributing Gaussian of every pixel (forwardVisiAcc /
+ * renderCUDA_visi_acc, forward.cu:735-835). */
+int vcr_rasterize_visi_acc(
+    vcr_alloc_fn geometry_buffer, vcr_alloc_fn binning_buffer, vcr_alloc_fn image_buffer, void* alloc_user,
+    int P, int D, int M,
+    int width, int height,
+    const float* means3D, const float* shs, const float* colors_precomp, const float* opacities,
+    const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
+    const float* viewmatrix, const float* projmatrix, const float* cam_pos,
+    float tan_fovx, float tan_fovy, int prefiltered,
+    int* gaussians_count /* i32[P] */, int* radii, int debug, int* num_rendered_host, void* stream);
+
+/* D-Normal regularizer, fused.  depth f32[H*W]; gt_normal and render_normal f32[H,W,3]
+ * (render_normal is the UN-normalised rasterizer output permuted to HWC, or NULL with exp_t <= 0);
+ * mask u8[H*W] or NULL (all valid); K is fx, fy, cx, cy.  mask_depth_max > 0 additionally masks
+ * pixels with depth >= mask_depth_max (gaussian_renderer/__init__.py:125-131).
+ * forward writes est_normal f32[H,W,3] (may be NULL), per-pixel weight f32[H*W] (may be NULL) and
+ * sums[3] = { sum_M w*|n-g|_1, sum_M w*(1-n.g), |M| } (sums must be zeroed by the caller or pass
+ * zero_sums = 1).  loss = (sums[0] + sums[1]) / sums[2]  (0 if sums[2] == 0).
+ * backward writes dL_ddepth f32[H*W] given dL_dloss (DEVICE scalar, so no host sync is needed between
+ * autograd nodes), the forward's sums and the same inputs; dL_dest_normal is an optional extra upstream
+ * gradient w.r.t. est_normal (e.g. from a consistency or curvature loss). */
+int vcr_dnormal_forward(const float* depth, const float* gt_normal, const float* render_normal,
+                        const uint8_t* mask, int width, int height,
+                        float fx, float fy, float cx, float cy,
+                        float exp_t, float mask_depth_max,
+                        float* est_normal, float* weight, float* sums, int zero_sums, void* stream);
+int vcr_dnormal_backward(const float* depth, const float* gt_normal, const float* render_normal,
+                         const uint8_t* mask, int width, int height,
+                         float fx, float fy, float cx, float cy,
+                         float exp_t, float mask_depth_max,
+                         const float* sums, const float* dL_dloss, const float* dL_dest_normal /* optional f32[H,W,3] */,
+                         float* dL_ddepth, void* stream);
+
+/* distCUDA2: mean squared distance to the 3 nearest neighbours.  scratch must hold
+ * vcr_knn_scratch_bytes(P) bytes. */
+size_t vcr_knn_scratch_bytes(int P);
+int vcr_dist2_knn3(int P, const float* points /* f32[P,3] */, float* mean_dists /* f32[P] */,
+                   char* scratch, void* stream);
+
+/* ---- test/parity accessors: decode the opaque buffers (used by tests/, never by the product path) ---- */
+typedef struct vcr_geom_view {
+    float* depths; uint8_t* clamped; float* means2D; float* xyz_view; float* cov3D;
+    float* conic_opacity; float* rgb; uint32_t* tiles_touched; uint32_t* point_offsets;
+} vcr_geom_view;
+typedef struct vcr_binning_view {
+    uint32_t* point_list; uint64_t* point_list_keys; uint32_t* point_list_unsorted; uint64_t* point_list_keys_unsorted;
+} vcr_binning_view;
+typedef struct vcr_image_view { float* accum_alpha; uint32_t* n_contrib; uint32_t* ranges; } vcr_image_view;
+void vcr_geom_layout(char* chunk, int P, vcr_geom_view* out);
+void vcr_binning_layout(char* chunk, int num_rendered, vcr_binning_view* out);
+void vcr_image_layout(char* chunk, int width, int height, vcr_image_view* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VCR_GAUS_B200_H */

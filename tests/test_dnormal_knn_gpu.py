@@ -1,0 +1,117 @@
+"""GPU parity of the fused D-Normal kernels and distCUDA2 against the CPU oracle, and D-Normal against the reference's
+own PyTorch op chain restated in tests (tools/normal_utils.py:24-41, tools/graphics_utils.py:111-131,
+tools/loss_utils.py:122-142, trainer.py:266-280)."""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from oracle import oracle as O
+from util import rel_l2
+
+pytestmark = pytest.mark.gpu
+
+
+def ref_chain(depth, K, gt_normal, render_normal, mask, exp_t):
+    """The reference op chain, verbatim semantics, in PyTorch (depth [1,H,W] requires grad)."""
+    _, H, W = depth.shape
+    dev = depth.device
+    vx = torch.arange(W, dtype=torch.float32, device=dev).add_(0.5) / (W - 1)
+    vy = torch.arange(H, dtype=torch.float32, device=dev).add_(0.5) / (H - 1)
+    vy, vx = torch.meshgrid(vy, vx, indexing="ij")
+    ndc = torch.stack([vx, vy, depth[0]], dim=-1)
+    inv_scale = torch.tensor([[W - 1, H - 1]], device=dev)
+    cam_z = ndc[..., 2:3]
+    cam_xy = ndc[..., :2] * inv_scale * cam_z
+    cam = torch.cat([cam_xy, cam_z], dim=-1) @ torch.inverse(K.t())
+    dy = torch.gradient(cam, dim=0)[0]
+    dx = torch.gradient(cam, dim=1)[0]
+    est = F.normalize(torch.cross(dx, dy, dim=-1), p=2, dim=-1)
+    rn = F.normalize(render_normal, dim=-1).detach()
+    cos = torch.sum(rn * gt_normal, dim=-1)
+    w = torch.exp((cos - 1) / exp_t) if exp_t > 0 else torch.ones_like(cos)
+    w = w.detach()
+    if mask.sum() == 0:
+        return depth.sum() * 0, est
+    e, g, ww = est[mask], gt_normal[mask], w[mask]
+    l1 = (ww * torch.abs(e - g).sum(dim=-1)).mean()
+    cs = (ww * (1.0 - torch.sum(e * g, dim=-1))).mean()
+    return l1 + cs, est
+
+
+def make_dn_inputs(W, H, seed):
+    g = torch.Generator().manual_seed(seed)
+    yy, xx = torch.meshgrid(torch.linspace(-1, 1, H), torch.linspace(-1, 1, W), indexing="ij")
+    depth = 2.0 + 0.5 * torch.sin(3 * xx) * torch.cos(2 * yy) + 0.3 * xx + 0.02 * torch.randn((H, W), generator=g)
+    gt = F.normalize(torch.randn((H, W, 3), generator=g) * 0.3 + torch.tensor([0.0, 0.0, -1.0]), dim=-1)
+    rn = (gt + 0.2 * torch.randn((H, W, 3), generator=g)) * (0.2 + torch.rand((H, W, 1), generator=g))
+    mask = torch.rand((H, W), generator=g) > 0.2
+    fx, fy = 0.9 * W, 0.95 * W
+    K = torch.tensor([[fx, 0, W / 2], [0, fy, H / 2], [0, 0, 1]], dtype=torch.float32)
+    return depth[None].contiguous(), gt.contiguous(), rn.contiguous(), mask, K
+
+
+@pytest.mark.parametrize("W,H,exp_t,thr", [(97, 61, 0.5, 0.0), (128, 96, 0.0, 2.3), (33, 2, 1.0, 0.0), (1920, 1080, 0.5, 0.0)])
+def test_dnormal_vs_oracle_and_reference_chain(W, H, exp_t, thr):
+    from vcr_dnormal import compute_normals, depth_normal_loss
+    depth, gt, rn, mask, K = make_dn_inputs(W, H, seed=W + H)
+    dev = torch.device("cuda")
+    d = depth.to(dev).requires_grad_(True)
+    loss, est = depth_normal_loss(d, K, gt.to(dev), rn.to(dev), mask.to(dev), exp_t=exp_t, mask_depth_max=thr, return_normal=True)
+    loss.backward()
+    torch.cuda.synchronize()
+    K4 = (float(K[0, 0]), float(K[1, 1]), float(K[0, 2]), float(K[1, 2]))
+    small = W * H <= 200000
+    if small:
+        o = O.dnormal(depth.numpy(), gt.numpy(), rn.numpy(), mask.numpy(), K4, exp_t=exp_t, mask_depth_max=thr)
+        np.testing.assert_allclose(est.detach().cpu().numpy(), o["est_normal"], atol=2e-4)
+        assert abs(float(loss) - o["loss"]) <= 1e-5 * max(1.0, abs(o["loss"]))
+        assert rel_l2(d.grad.cpu().numpy()[0], o["dL_ddepth"]) <= 1e-3
+    # the reference chain on the GPU, same inputs
+    d2 = depth.to(dev).requires_grad_(True)
+    m = mask.to(dev)
+    if thr > 0:
+        m = m & (d2[0].detach() < thr)
+    l2, est2 = ref_chain(d2, K.to(dev), gt.to(dev), rn.to(dev), m, exp_t)
+    l2.backward()
+    assert abs(float(loss) - float(l2)) <= 1e-5 * max(1.0, abs(float(l2)))
+    np.testing.assert_allclose(est.detach().cpu().numpy(), est2.detach().cpu().numpy(), atol=5e-4)
+    assert rel_l2(d.grad.cpu().numpy(), d2.grad.cpu().numpy()) <= 1e-3
+    # compute_normals drop-in
+    e3 = compute_normals(depth.to(dev), K)
+    np.testing.assert_allclose(e3.cpu().numpy(), est2.detach().cpu().numpy(), atol=5e-4)
+
+
+def test_dnormal_empty_mask():
+    from vcr_dnormal import depth_normal_loss
+    depth, gt, rn, mask, K = make_dn_inputs(64, 48, seed=1)
+    dev = torch.device("cuda")
+    d = depth.to(dev).requires_grad_(True)
+    loss = depth_normal_loss(d, K, gt.to(dev), rn.to(dev), torch.zeros_like(mask).to(dev), exp_t=0.5)
+    loss.backward()
+    assert float(loss) == 0.0 and float(d.grad.abs().max()) == 0.0
+
+
+@pytest.mark.parametrize("P", [4, 1000, 20000])
+def test_knn_vs_oracle(P):
+    from simple_knn._C import distCUDA2
+    g = torch.Generator().manual_seed(P)
+    pts = torch.cat([torch.randn((P // 2, 3), generator=g), torch.rand((P - P // 2, 3), generator=g) * 4 - 2])
+    if P >= 1000:
+        pts[10] = pts[11]  # duplicate point: distance 0 is a valid neighbour (only i == idx is excluded)
+    out = distCUDA2(pts.cuda()).cpu().numpy()
+    ref = O.knn3(pts.numpy())
+    np.testing.assert_allclose(out, ref, rtol=1e-5, atol=1e-9)
+
+
+def test_knn_large_property():
+    """1M points: every result must be >= the oracle-checked lower bound 0 and match brute force on a random subset."""
+    from simple_knn._C import distCUDA2
+    P = 1_000_000
+    pts = torch.rand((P, 3), generator=torch.Generator().manual_seed(3)).cuda()
+    out = distCUDA2(pts)
+    sel = torch.randint(0, P, (64,), generator=torch.Generator().manual_seed(4)).cuda()
+    d = torch.cdist(pts[sel].double(), pts.double()) ** 2
+    d[torch.arange(64), sel] = float("inf")
+    ref = d.topk(3, largest=False).values.mean(dim=1).float()
+    np.testing.assert_allclose(out[sel].cpu().numpy(), ref.cpu().numpy(), rtol=1e-4)

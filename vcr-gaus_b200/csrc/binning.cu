@@ -1,0 +1,366 @@
+// binning.cu — Gaussian -> tile instance lists: prefix sum, key duplication, stable LSD radix sort on
+// (tile | depth) keys, per-tile ranges.  All hand-written (no CUB/thrust).
+//
+// Replaces, in the reference (DGR/cuda_rasterizer/rasterizer_impl.cu):
+//   cub::DeviceScan::InclusiveSum            :283      -> preprocess block sums + scan_block_sums_kernel
+//                                                         + the in-block scan inside duplicate_kernel
+//   duplicateWithKeys                        :70-111   -> duplicate_kernel (block-cooperative, coalesced)
+//   cub::DeviceRadixSort::SortPairs          :309-314  -> radix_pass_kernel (one launch per 8-bit digit,
+//                                                         decoupled look-back, warp-match ranking)
+//   cudaMemset + identifyTileRanges          :316-323  -> tile_ranges_kernel
+//
+// Results are bit-identical to the reference by construction: the unsorted arrays have the same
+// element order (Gaussian index ascending, row-major inside the rectangle), and the sort is stable
+// over bits [0, 32+bit), like CUB's.
+#include "common.cuh"
+
+// ------------------------------------------------------------------------------------------------
+// Prefix sum over the per-block totals written by preprocess_kernel (one block, 1024 threads).
+// block_sums[b] becomes the exclusive prefix; num_rendered[0] the grand total.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(1024) scan_block_sums_kernel(uint32_t* __restrict__ block_sums, int nb,
+                                                               uint32_t* __restrict__ num_rendered) {
+    __shared__ uint32_t warp_tot[32];
+    __shared__ uint32_t carry_s;
+    const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+    if (t == 0) carry_s = 0;
+    __syncthreads();
+    for (int base = 0; base < nb; base += 1024) {
+        const int i = base + t;
+        const uint32_t v = i < nb ? block_sums[i] : 0u;
+        uint32_t inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t n = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += n;
+        }
+        if (lane == 31) warp_tot[w] = inc;
+        __syncthreads();
+        if (w == 0) {
+            uint32_t x = warp_tot[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t n = __shfl_up_sync(0xffffffffu, x, o);
+                if (lane >= o) x += n;
+            }
+            warp_tot[lane] = x;  // inclusive over warps
+        }
+        __syncthreads();
+        const uint32_t carry = carry_s;
+        const uint32_t warp_excl = w ? warp_tot[w - 1] : 0u;
+        if (i < nb) block_sums[i] = carry + warp_excl + inc - v;
+        __syncthreads();
+        if (t == 1023) carry_s = carry + warp_excl + inc;
+        __syncthreads();
+    }
+    if (t == 0) num_rendered[0] = carry_s;
+}
+
+int vcr_launch_scan_block_sums(int P, GeomState& g, cudaStream_t s) {
+    const int nb = (P + 255) / 256;
+    scan_block_sums_kernel<<<1, 1024, 0, s>>>(g.block_sums, nb, g.num_rendered);
+    VCR_LAUNCH_CHECK("scan_block_sums_kernel");
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// point_offsets + key duplication + radix digit histograms, one block per 256 Gaussians.
+// The block's instances occupy the contiguous output range [base, base + total); the 256 threads
+// walk that range together (coalesced 8-byte key / 4-byte value stores) and find the owning
+// Gaussian of each slot by binary search in the block's inclusive scan.
+// ------------------------------------------------------------------------------------------------
+#define VCR_MAX_PASSES 8
+__global__ void __launch_bounds__(256) duplicate_kernel(int P, int gx, int gy, const int* __restrict__ radii,
+                                                        const GeomState g, uint64_t* __restrict__ keys_out,
+                                                        uint32_t* __restrict__ vals_out, uint32_t* __restrict__ ghist,
+                                                        int npass, int key_bits) {
+    __shared__ uint32_t incl[256];
+    __shared__ uint32_t s_depth[256];
+    __shared__ int s_x0[256], s_y0[256], s_w[256];
+    __shared__ uint32_t warp_tot[8];
+    __shared__ uint32_t hist[VCR_MAX_PASSES][256];
+    const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+    const int idx = blockIdx.x * 256 + t;
+    for (int k = t; k < npass * 256; k += 256) (&hist[0][0])[k] = 0u;
+
+    uint32_t tiles = 0, dbits = 0;
+    int x0 = 0, y0 = 0, rw = 0;
+    if (idx < P) {
+        tiles = g.tiles_touched[idx];
+        if (tiles > 0) {
+            int2 rmin, rmax;
+            vcr_get_rect(g.means2D[idx], radii[idx], gx, gy, rmin, rmax);
+            x0 = rmin.x; y0 = rmin.y; rw = rmax.x - rmin.x;
+            dbits = __float_as_uint(g.depths[idx]);
+        }
+    }
+    uint32_t inc = tiles;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t n = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += n;
+    }
+    if (lane == 31) warp_tot[w] = inc;
+    __syncthreads();
+    uint32_t wex = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) wex += (k < w) ? warp_tot[k] : 0u;
+    inc += wex;
+    incl[t] = inc;
+    s_depth[t] = dbits; s_x0[t] = x0; s_y0[t] = y0; s_w[t] = rw;
+    const uint32_t base = g.block_sums[blockIdx.x];
+    if (idx < P) g.point_offsets[idx] = base + inc;
+    // depth digits: one histogram update per Gaussian (weight = its instance count)
+    if (tiles > 0) {
+        const int ndepth = npass < 4 ? npass : 4;
+        for (int p = 0; p < ndepth; p++) atomicAdd(&hist[p][(dbits >> (8 * p)) & 255u], tiles);
+    }
+    __syncthreads();
+    const uint32_t total = incl[255];
+    for (uint32_t k = t; k < total; k += 256) {
+        // smallest gi with incl[gi] > k
+        int lo = 0, hi = 255;
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            if (incl[mid] > k) hi = mid; else lo = mid + 1;
+        }
+        const uint32_t start = lo ? incl[lo - 1] : 0u;
+        const uint32_t local = k - start;
+        const int wdt = s_w[lo];
+        const int y = s_y0[lo] + (int)(local / (uint32_t)wdt);
+        const int x = s_x0[lo] + (int)(local % (uint32_t)wdt);
+        const uint32_t tile = (uint32_t)(y * gx + x);
+        keys_out[base + k] = ((uint64_t)tile << 32) | s_depth[lo];
+        vals_out[base + k] = (uint32_t)(blockIdx.x * 256 + lo);
+        for (int p = 4; p < npass; p++) {
+            const int nb = min(8, key_bits - 8 * p);
+            atomicAdd(&hist[p][(tile >> (8 * (p - 4))) & ((1u << nb) - 1u)], 1u);
+        }
+    }
+    __syncthreads();
+    for (int p = 0; p < npass; p++) {
+        const uint32_t c = hist[p][t];
+        if (c) atomicAdd(&ghist[p * 256 + t], c);
+    }
+}
+
+// Exclusive scan of each pass's 256-bin histogram (one block per pass).
+__global__ void __launch_bounds__(256) radix_scan_hist_kernel(uint32_t* __restrict__ ghist) {
+    __shared__ uint32_t warp_tot[8];
+    const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+    uint32_t* h = ghist + blockIdx.x * 256;
+    const uint32_t v = h[t];
+    uint32_t inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t n = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += n;
+    }
+    if (lane == 31) warp_tot[w] = inc;
+    __syncthreads();
+    uint32_t wex = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) wex += (k < w) ? warp_tot[k] : 0u;
+    h[t] = wex + inc - v;
+}
+
+// ------------------------------------------------------------------------------------------------
+// One stable radix pass (<= 8 bits) over R (u64 key, u32 value) pairs.
+//   - tiles of 4096 pairs per 256-thread block, taken in ticket order (forward progress for look-back)
+//   - in-block stable ranks: per-warp running digit counters + __match_any_sync peer masks
+//   - cross-block digit offsets: decoupled look-back on (flag | count) words, one thread per digit
+//   - pairs are first scattered into shared memory in block-sorted order so the global stores are
+//     runs of consecutive addresses per digit
+// ------------------------------------------------------------------------------------------------
+#define RADIX_THREADS 256
+#define RADIX_ITEMS 16
+#define RADIX_TILE (RADIX_THREADS * RADIX_ITEMS)
+#define FLAG_LOCAL 0x40000000u
+#define FLAG_GLOBAL 0x80000000u
+#define FLAG_MASK 0xC0000000u
+#define RADIX_SMEM_BYTES (RADIX_TILE * 8 + RADIX_TILE * 4 + 8 * 256 * 4 + 256 * 4 + 256 * 4 + 64)
+
+__global__ void __launch_bounds__(RADIX_THREADS) radix_pass_kernel(const uint64_t* __restrict__ keys_in,
+                                                                   const uint32_t* __restrict__ vals_in,
+                                                                   uint64_t* __restrict__ keys_out,
+                                                                   uint32_t* __restrict__ vals_out, uint32_t R, int shift,
+                                                                   int nbits, const uint32_t* __restrict__ digit_base,
+                                                                   volatile uint32_t* status, uint32_t* ticket,
+                                                                   uint32_t* err_flag) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint64_t* s_keys = reinterpret_cast<uint64_t*>(smem_raw);
+    uint32_t* s_vals = reinterpret_cast<uint32_t*>(smem_raw + RADIX_TILE * 8);
+    uint32_t* s_whist = s_vals + RADIX_TILE;             // [8][256]
+    uint32_t* s_dstart = s_whist + 8 * 256;              // [256] block-local exclusive digit start
+    uint32_t* s_gbase = s_dstart + 256;                  // [256] global base minus local start
+    uint32_t* s_misc = s_gbase + 256;                    // [16]
+    const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+    const uint32_t mask = (1u << nbits) - 1u;
+
+    if (t == 0) s_misc[0] = atomicAdd(ticket, 1u);
+#pragma unroll
+    for (int k = 0; k < 8; k++) s_whist[w * 256 + lane + 32 * k] = 0u;
+    __syncthreads();
+    const uint32_t bid = s_misc[0];
+    const uint32_t base = bid * RADIX_TILE;
+    const uint32_t n = min((uint32_t)RADIX_TILE, R - base);
+
+    uint64_t key[RADIX_ITEMS];
+    uint32_t val[RADIX_ITEMS];
+    uint32_t rank[RADIX_ITEMS];
+#pragma unroll
+    for (int i = 0; i < RADIX_ITEMS; i++) {
+        const uint32_t li = w * (32 * RADIX_ITEMS) + i * 32 + lane;
+        if (li < n) { key[i] = keys_in[base + li]; val[i] = vals_in[base + li]; }
+        else { key[i] = ~0ull; val[i] = 0u; }
+    }
+    uint32_t* my_hist = s_whist + w * 256;
+#pragma unroll
+    for (int i = 0; i < RADIX_ITEMS; i++) {
+        const uint32_t li = w * (32 * RADIX_ITEMS) + i * 32 + lane;
+        const bool valid = li < n;
+        const uint32_t d = (uint32_t)(key[i] >> shift) & mask;
+        const uint32_t vmask = __ballot_sync(0xffffffffu, valid);
+        const uint32_t peers = __match_any_sync(0xffffffffu, d) & vmask;
+        uint32_t prev = 0;
+        if (valid) prev = my_hist[d];
+        rank[i] = prev + __popc(peers & ((1u << lane) - 1u));
+        __syncwarp();
+        if (valid && lane == (__ffs(peers) - 1)) my_hist[d] = prev + __popc(peers);
+        __syncwarp();
+    }
+    __syncthreads();
+    // thread t owns digit t
+    uint32_t cnt = 0;
+    {
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            const uint32_t c = s_whist[k * 256 + t];
+            s_whist[k * 256 + t] = cnt;  // exclusive over warps
+            cnt += c;
+        }
+    }
+    // publish the block-local count as early as possible
+    volatile uint32_t* my_status = status + (size_t)bid * 256;
+    if (bid == 0) my_status[t] = FLAG_GLOBAL | cnt;
+    else my_status[t] = FLAG_LOCAL | cnt;
+    __threadfence();
+    // block-local exclusive scan over digits
+    uint32_t inc = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t x = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += x;
+    }
+    if (lane == 31) s_misc[1 + w] = inc;
+    __syncthreads();
+    uint32_t wex = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) wex += (k < w) ? s_misc[1 + k] : 0u;
+    const uint32_t dstart = wex + inc - cnt;
+    s_dstart[t] = dstart;
+    // decoupled look-back
+    uint32_t excl = 0;
+    if (bid > 0) {
+        int j = (int)bid - 1;
+        uint32_t spins = 0;
+        while (true) {
+            const uint32_t v = status[(size_t)j * 256 + t];
+            const uint32_t f = v & FLAG_MASK;
+            if (f == 0u) {
+                if (++spins > (1u << 26)) { atomicExch(err_flag, 1u); break; }
+                continue;
+            }
+            excl += v & ~FLAG_MASK;
+            if (f == FLAG_GLOBAL) break;
+            j--;
+        }
+        my_status[t] = FLAG_GLOBAL | (excl + cnt);
+        __threadfence();
+    }
+    s_gbase[t] = digit_base[t] + excl - dstart;
+    __syncthreads();
+    // scatter into shared memory in block-sorted order
+#pragma unroll
+    for (int i = 0; i < RADIX_ITEMS; i++) {
+        const uint32_t li = w * (32 * RADIX_ITEMS) + i * 32 + lane;
+        if (li < n) {
+            const uint32_t d = (uint32_t)(key[i] >> shift) & mask;
+            const uint32_t slot = s_dstart[d] + my_hist[d] + rank[i];
+            s_keys[slot] = key[i];
+            s_vals[slot] = val[i];
+        }
+    }
+    __syncthreads();
+    for (uint32_t sl = t; sl < n; sl += RADIX_THREADS) {
+        const uint64_t k = s_keys[sl];
+        const uint32_t d = (uint32_t)(k >> shift) & mask;
+        const uint32_t pos = s_gbase[d] + sl;
+        keys_out[pos] = k;
+        vals_out[pos] = s_vals[sl];
+    }
+}
+
+int vcr_launch_offsets_and_duplicate(const FwdParams& p, GeomState& g, BinningState& b, int R, int npass, int key_bits,
+                                     cudaStream_t s) {
+    (void)R;
+    VCR_CUDA_TRY(cudaMemsetAsync(b.sort_hist, 0, VCR_MAX_PASSES * 256 * sizeof(uint32_t), s));
+    duplicate_kernel<<<(p.P + 255) / 256, 256, 0, s>>>(p.P, p.gx, p.gy, p.radii, g, b.point_list_keys_unsorted,
+                                                       b.point_list_unsorted, b.sort_hist, npass, key_bits);
+    VCR_LAUNCH_CHECK("duplicate_kernel");
+    return 0;
+}
+
+int vcr_launch_radix_sort(BinningState& b, int R, int key_bits, cudaStream_t s) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        VCR_CUDA_TRY(cudaFuncSetAttribute(radix_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, RADIX_SMEM_BYTES));
+        attr_set = true;
+    }
+    const int npass = (key_bits + 7) / 8;
+    const uint32_t nblocks = ((uint32_t)R + RADIX_TILE - 1) / RADIX_TILE;
+    radix_scan_hist_kernel<<<npass, 256, 0, s>>>(b.sort_hist);
+    VCR_LAUNCH_CHECK("radix_scan_hist_kernel");
+    // status words for all passes + one ticket per pass + error flag, zeroed in one memset
+    const size_t words = (size_t)npass * nblocks * 256 + 16;
+    VCR_CUDA_TRY(cudaMemsetAsync(b.sort_status, 0, words * sizeof(uint32_t), s));
+    uint32_t* tickets = b.sort_status + (size_t)npass * nblocks * 256;
+    const uint64_t* kin = b.point_list_keys_unsorted;
+    const uint32_t* vin = b.point_list_unsorted;
+    for (int pass = 0; pass < npass; pass++) {
+        const bool to_final = ((npass - 1 - pass) % 2) == 0;
+        uint64_t* kout = to_final ? b.point_list_keys : b.alt_keys;
+        uint32_t* vout = to_final ? b.point_list : b.alt_vals;
+        const int nbits = key_bits - 8 * pass < 8 ? key_bits - 8 * pass : 8;
+        radix_pass_kernel<<<nblocks, RADIX_THREADS, RADIX_SMEM_BYTES, s>>>(
+            kin, vin, kout, vout, (uint32_t)R, 8 * pass, nbits, b.sort_hist + pass * 256,
+            b.sort_status + (size_t)pass * nblocks * 256, tickets + pass, tickets + 15);
+        VCR_LAUNCH_CHECK("radix_pass_kernel");
+        kin = kout; vin = vout;
+    }
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Tile ranges (identifyTileRanges, rasterizer_impl.cu:116-138).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) tile_ranges_kernel(uint32_t L, const uint64_t* __restrict__ keys, uint2* __restrict__ ranges) {
+    const uint32_t idx = blockIdx.x * 256u + threadIdx.x;
+    if (idx >= L) return;
+    const uint32_t cur = (uint32_t)(keys[idx] >> 32);
+    if (idx == 0) ranges[cur].x = 0;
+    else {
+        const uint32_t prev = (uint32_t)(keys[idx - 1] >> 32);
+        if (cur != prev) { ranges[prev].y = idx; ranges[cur].x = idx; }
+    }
+    if (idx == L - 1) ranges[cur].y = L;
+}
+
+int vcr_launch_tile_ranges(BinningState& b, ImageState& img, int R, int tiles, cudaStream_t s) {
+    VCR_CUDA_TRY(cudaMemsetAsync(img.ranges, 0, (size_t)tiles * sizeof(uint2), s));
+    if (R > 0) {
+        tile_ranges_kernel<<<((uint32_t)R + 255u) / 256u, 256, 0, s>>>((uint32_t)R, b.point_list_keys, img.ranges);
+        VCR_LAUNCH_CHECK("tile_ranges_kernel");
+    }
+    return 0;
+}

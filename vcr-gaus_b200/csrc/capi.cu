@@ -1,0 +1,307 @@
+// capi.cu — the extern "C" surface declared in include/vcr_gaus_b200.h: argument checking, opaque
+// buffer layouts, and the launch sequences of the forward / backward passes.
+//
+// Host orchestration replaces CudaRasterizer::Rasterizer::forward / backward / markVisible /
+// forwardCount / forwardVisiAcc (reference DGR/cuda_rasterizer/rasterizer_impl.cu:141-153, 199-348,
+// 352-476, 482-626, 782-917).  All launches go to the caller's stream.
+#include "common.cuh"
+#include "../../include/vcr_gaus_b200.h"
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+static thread_local char g_err[512] = "";
+void vcr_set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+// ---------------- layouts ----------------
+template <typename T>
+static inline void carve_one(char*& p, T*& out, size_t count) {
+    p = reinterpret_cast<char*>(vcr_align256(reinterpret_cast<size_t>(p)));
+    out = reinterpret_cast<T*>(p);
+    p += count * sizeof(T);
+}
+GeomState GeomState::carve(char* chunk, int P) {
+    GeomState g;
+    const size_t n = (size_t)P;
+    carve_one(chunk, g.depths, n);
+    carve_one(chunk, g.clamped, 3 * n);
+    carve_one(chunk, g.means2D, n);
+    carve_one(chunk, g.xyz_view, 3 * n);
+    carve_one(chunk, g.cov3D, 6 * n);
+    carve_one(chunk, g.conic_opacity, n);
+    carve_one(chunk, g.rgb, 3 * n);
+    carve_one(chunk, g.tiles_touched, n);
+    carve_one(chunk, g.point_offsets, n);
+    carve_one(chunk, g.block_sums, (n + 255) / 256 + 1);
+    carve_one(chunk, g.num_rendered, (size_t)4);
+    return g;
+}
+size_t GeomState::bytes(int P) {
+    char* base = nullptr;
+    GeomState g = carve(base, P);
+    return reinterpret_cast<size_t>(g.num_rendered + 4) + 256;
+}
+ImageState ImageState::carve(char* chunk, int W, int H) {
+    ImageState s;
+    const size_t N = (size_t)W * H;
+    const size_t tiles = (size_t)((W + VCR_TILE_X - 1) / VCR_TILE_X) * ((H + VCR_TILE_Y - 1) / VCR_TILE_Y);
+    carve_one(chunk, s.accum_alpha, N);
+    carve_one(chunk, s.n_contrib, N);
+    carve_one(chunk, s.ranges, tiles);
+    return s;
+}
+size_t ImageState::bytes(int W, int H) {
+    char* base = nullptr;
+    ImageState s = carve(base, W, H);
+    const size_t tiles = (size_t)((W + VCR_TILE_X - 1) / VCR_TILE_X) * ((H + VCR_TILE_Y - 1) / VCR_TILE_Y);
+    return reinterpret_cast<size_t>(s.ranges + tiles) + 256;
+}
+static inline size_t radix_blocks(size_t R) { return (R + 4095) / 4096; }
+BinningState BinningState::carve(char* chunk, int R) {
+    BinningState b;
+    const size_t n = (size_t)R;
+    carve_one(chunk, b.point_list, n);
+    carve_one(chunk, b.point_list_keys, n);
+    carve_one(chunk, b.point_list_unsorted, n);
+    carve_one(chunk, b.point_list_keys_unsorted, n);
+    carve_one(chunk, b.alt_vals, n);
+    carve_one(chunk, b.alt_keys, n);
+    carve_one(chunk, b.sort_hist, (size_t)8 * 256);
+    carve_one(chunk, b.sort_status, (size_t)8 * radix_blocks(n) * 256 + 16);
+    return b;
+}
+size_t BinningState::bytes(int R) {
+    char* base = nullptr;
+    BinningState b = carve(base, R);
+    return reinterpret_cast<size_t>(b.sort_status + (size_t)8 * radix_blocks((size_t)R) * 256 + 16) + 256;
+}
+
+static uint32_t higher_msb(uint32_t n) {  // rasterizer_impl.cu:35-50
+    uint32_t msb = sizeof(n) * 4, step = msb;
+    while (step > 1) {
+        step /= 2;
+        if (n >> msb) msb += step; else msb -= step;
+    }
+    if (n >> msb) msb++;
+    return msb;
+}
+
+// pinned word the device copy of R is read back through (one per host thread)
+static int read_back_u32x4(const uint32_t* dev, uint32_t out[4], cudaStream_t s) {
+    static thread_local uint32_t* pinned = nullptr;
+    if (!pinned) VCR_CUDA_TRY(cudaHostAlloc(reinterpret_cast<void**>(&pinned), 4 * sizeof(uint32_t), cudaHostAllocDefault));
+    VCR_CUDA_TRY(cudaMemcpyAsync(pinned, dev, 4 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    VCR_CUDA_TRY(cudaStreamSynchronize(s));
+    memcpy(out, pinned, 4 * sizeof(uint32_t));
+    return 0;
+}
+
+static int debug_sync(int debug, cudaStream_t s, const char* what) {  // CHECK_CUDA of the reference (auxiliary.h:181-188)
+    if (!debug) return 0;
+    cudaError_t e = cudaStreamSynchronize(s);
+    if (e != cudaSuccess) { vcr_set_error("[CUDA ERROR] after %s: %s", what, cudaGetErrorString(e)); return 1; }
+    return 0;
+}
+
+// Shared front half of every forward variant: preprocess -> scan -> R -> duplicate -> sort -> ranges.
+static int forward_front(vcr_alloc_fn geometry_buffer, vcr_alloc_fn binning_buffer, vcr_alloc_fn image_buffer, void* user,
+                         FwdParams& p, GeomState& g, BinningState& b, ImageState& img, int debug, int* num_rendered_host,
+                         cudaStream_t s) {
+    if (p.P <= 0) { vcr_set_error("P must be positive (the P == 0 short-circuit lives in the caller)"); return 1; }
+    if (p.W <= 0 || p.H <= 0) { vcr_set_error("bad image size %dx%d", p.W, p.H); return 1; }
+    if (!geometry_buffer || !binning_buffer || !image_buffer) { vcr_set_error("NULL buffer callback"); return 1; }
+    if (!p.means3D || !p.opacities || !p.viewmatrix || !p.projmatrix || !p.radii) { vcr_set_error("NULL required input"); return 1; }
+    if (!p.colors_precomp && !p.shs) { vcr_set_error("either shs or colors_precomp is required"); return 1; }
+    if (!p.cov3D_precomp && (!p.scales || !p.rotations)) { vcr_set_error("either cov3D_precomp or scales+rotations is required"); return 1; }
+    if (!p.colors_precomp && !p.cam_pos) { vcr_set_error("cam_pos is required for SH colours"); return 1; }
+    p.gx = (p.W + VCR_TILE_X - 1) / VCR_TILE_X;
+    p.gy = (p.H + VCR_TILE_Y - 1) / VCR_TILE_Y;
+    p.focal_y = p.H / (2.0f * p.tan_fovy);  // rasterizer_impl.cu:227-228
+    p.focal_x = p.W / (2.0f * p.tan_fovx);
+
+    char* gchunk = geometry_buffer(user, GeomState::bytes(p.P));
+    char* ichunk = image_buffer(user, ImageState::bytes(p.W, p.H));
+    if (!gchunk || !ichunk) { vcr_set_error("buffer callback returned NULL"); return 1; }
+    g = GeomState::carve(gchunk, p.P);
+    img = ImageState::carve(ichunk, p.W, p.H);
+
+    if (vcr_launch_preprocess(p, g, s)) return 1;
+    if (debug_sync(debug, s, "preprocess")) return 1;
+    if (vcr_launch_scan_block_sums(p.P, g, s)) return 1;
+    uint32_t host[4];
+    if (read_back_u32x4(g.num_rendered, host, s)) return 1;
+    if (host[1]) { vcr_set_error("Point is filtered although prefiltered is set. This shouldn't happen!"); return 1; }
+    const int R = (int)host[0];
+    *num_rendered_host = R;
+
+    char* bchunk = binning_buffer(user, BinningState::bytes(R));
+    if (!bchunk) { vcr_set_error("binning buffer callback returned NULL"); return 1; }
+    b = BinningState::carve(bchunk, R);
+    const int tiles = p.gx * p.gy;
+    const int key_bits = 32 + (int)higher_msb((uint32_t)tiles);
+    const int npass = (key_bits + 7) / 8;
+    if (R > 0) {
+        if (vcr_launch_offsets_and_duplicate(p, g, b, R, npass, key_bits, s)) return 1;
+        if (debug_sync(debug, s, "duplicate")) return 1;
+        if (vcr_launch_radix_sort(b, R, key_bits, s)) return 1;
+        if (debug_sync(debug, s, "radix sort")) return 1;
+    }
+    if (vcr_launch_tile_ranges(b, img, R, tiles, s)) return 1;
+    if (debug_sync(debug, s, "tile ranges")) return 1;
+    return 0;
+}
+
+extern "C" {
+
+int vcr_abi_version(void) { return VCR_ABI_VERSION; }
+const char* vcr_last_error(void) { return g_err; }
+uint32_t vcr_higher_msb(uint32_t n) { return higher_msb(n); }
+size_t vcr_geom_bytes(int P) { return GeomState::bytes(P); }
+size_t vcr_image_bytes(int width, int height) { return ImageState::bytes(width, height); }
+size_t vcr_binning_bytes(int num_rendered) { return BinningState::bytes(num_rendered); }
+size_t vcr_backward_scratch_bytes(int P) { return (size_t)P * VCR_ACC_STRIDE * sizeof(float) + 256; }
+
+int vcr_rasterize_forward(vcr_alloc_fn geometry_buffer, vcr_alloc_fn binning_buffer, vcr_alloc_fn image_buffer, void* alloc_user,
+                          int P, int D, int M, const float* background, int width, int height, const float* means3D,
+                          const float* shs, const float* colors_precomp, const float* normals_precomp, const float* sh_objs,
+                          const float* opacities, const float* scales, float scale_modifier, const float* rotations,
+                          const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix, const float* dirs,
+                          const float* cam_pos, float tan_fovx, float tan_fovy, int prefiltered, float* out_color, int* radii,
+                          const uint8_t* inside, int debug, int* num_rendered_host, void* stream) {
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    if (!normals_precomp) { vcr_set_error("normals_precomp is required (the reference kernel dereferences it unconditionally, forward.cu:374)"); return 1; }
+    if (!inside || !background || !out_color || !num_rendered_host) { vcr_set_error("NULL required argument"); return 1; }
+    FwdParams p;
+    memset(&p, 0, sizeof(p));
+    p.P = P; p.D = D; p.M = M; p.W = width; p.H = height;
+    p.means3D = means3D; p.shs = shs; p.colors_precomp = colors_precomp; p.normals = normals_precomp; p.sh_objs = sh_objs;
+    p.opacities = opacities; p.scales = scales; p.scale_modifier = scale_modifier; p.rotations = rotations;
+    p.cov3D_precomp = cov3D_precomp; p.viewmatrix = viewmatrix; p.projmatrix = projmatrix; p.dirs = dirs; p.cam_pos = cam_pos;
+    p.background = background; p.tan_fovx = tan_fovx; p.tan_fovy = tan_fovy; p.prefiltered = prefiltered;
+    p.out_color = out_color; p.radii = radii; p.inside = inside;
+    GeomState g; BinningState b; ImageState img;
+    if (forward_front(geometry_buffer, binning_buffer, image_buffer, alloc_user, p, g, b, img, debug, num_rendered_host, s)) return 1;
+    if (vcr_launch_render_forward(p, g, b, img, s)) return 1;
+    if (debug_sync(debug, s, "render forward")) return 1;
+    return 0;
+}
+
+int vcr_rasterize_backward(int P, int D, int M, int R, const float* background, int width, int height, const float* means3D,
+                           const float* shs, const float* colors_precomp, const float* normals_precomp, const float* sh_objs,
+                           const float* alpha, const float* depth, const float* scales, float scale_modifier,
+                           const float* rotations, const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+                           const float* dirs, const float* campos, float tan_fovx, float tan_fovy, const int* radii,
+                           char* geom_buffer, char* binning_buffer, char* img_buffer, const float* dL_dpix, float* dL_dmean2D,
+                           float* dL_dmean2D_densify, float* dL_dopacity, float* dL_dcolor, float* dL_dnormal, float* dL_dobjects,
+                           float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
+                           const uint8_t* inside, char* scratch, int debug, void* stream) {
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    if (P <= 0) { vcr_set_error("P must be positive"); return 1; }
+    if (!geom_buffer || !binning_buffer || !img_buffer || !scratch) { vcr_set_error("NULL state/scratch buffer"); return 1; }
+    if (!dL_dpix || !dL_dmean2D || !dL_dmean2D_densify || !dL_dopacity || !dL_dcolor || !dL_dnormal || !dL_dobjects ||
+        !dL_dmean3D || !dL_dcov3D || !dL_dscale || !dL_drot || (M > 0 && shs && !dL_dsh)) {
+        vcr_set_error("NULL gradient output");
+        return 1;
+    }
+    if (!normals_precomp || !inside || !radii || !alpha || !depth) { vcr_set_error("NULL required input"); return 1; }
+    BwdParams p;
+    memset(&p, 0, sizeof(p));
+    p.P = P; p.D = D; p.M = M; p.R = R; p.W = width; p.H = height;
+    p.gx = (width + VCR_TILE_X - 1) / VCR_TILE_X; p.gy = (height + VCR_TILE_Y - 1) / VCR_TILE_Y;
+    p.background = background; p.means3D = means3D; p.shs = shs; p.colors_precomp = colors_precomp; p.normals = normals_precomp;
+    p.sh_objs = sh_objs; p.alpha = alpha; p.depth = depth; p.scales = scales; p.scale_modifier = scale_modifier;
+    p.rotations = rotations; p.cov3D_precomp = cov3D_precomp; p.viewmatrix = viewmatrix; p.projmatrix = projmatrix;
+    p.dirs = dirs; p.campos = campos; p.tan_fovx = tan_fovx; p.tan_fovy = tan_fovy;
+    p.focal_y = height / (2.0f * tan_fovy); p.focal_x = width / (2.0f * tan_fovx);
+    p.radii = radii; p.dL_dpix = dL_dpix;
+    p.dL_dmean2D = dL_dmean2D; p.dL_dmean2D_densify = dL_dmean2D_densify; p.dL_dopacity = dL_dopacity; p.dL_dcolor = dL_dcolor;
+    p.dL_dnormal = dL_dnormal; p.dL_dobjects = dL_dobjects; p.dL_dmean3D = dL_dmean3D; p.dL_dcov3D = dL_dcov3D; p.dL_dsh = dL_dsh;
+    p.dL_dscale = dL_dscale; p.dL_drot = dL_drot; p.inside = inside;
+    p.acc = reinterpret_cast<float*>(vcr_align256(reinterpret_cast<size_t>(scratch)));
+    GeomState g = GeomState::carve(geom_buffer, P);
+    BinningState b = BinningState::carve(binning_buffer, R);
+    ImageState img = ImageState::carve(img_buffer, width, height);
+    if (vcr_launch_render_backward(p, g, b, img, s)) return 1;
+    if (debug_sync(debug, s, "render backward")) return 1;
+    if (vcr_launch_preprocess_backward(p, g, s)) return 1;
+    if (debug_sync(debug, s, "preprocess backward")) return 1;
+    return 0;
+}
+
+int vcr_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix, uint8_t* present, void* stream) {
+    (void)projmatrix;  // the reference computes the projection too but only tests view-space z (auxiliary.h:160-166)
+    if (P <= 0) return 0;
+    if (!means3D || !viewmatrix || !present) { vcr_set_error("NULL argument"); return 1; }
+    return vcr_launch_mark_visible(P, means3D, viewmatrix, present, reinterpret_cast<cudaStream_t>(stream));
+}
+
+static int aux_forward(int mode, vcr_alloc_fn geometry_buffer, vcr_alloc_fn binning_buffer, vcr_alloc_fn image_buffer, void* alloc_user,
+                       int P, int D, int M, const float* background, int width, int height, const float* means3D, const float* shs,
+                       const float* colors_precomp, const float* opacities, const float* scales, float scale_modifier,
+                       const float* rotations, const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+                       const float* cam_pos, float tan_fovx, float tan_fovy, int prefiltered, float* out_color,
+                       int* gaussians_count, float* important_score, int* radii, int debug, int* num_rendered_host, cudaStream_t s) {
+    if (!gaussians_count || !num_rendered_host) { vcr_set_error("NULL required argument"); return 1; }
+    FwdParams p;
+    memset(&p, 0, sizeof(p));
+    p.P = P; p.D = D; p.M = M; p.W = width; p.H = height;
+    p.means3D = means3D; p.shs = shs; p.colors_precomp = colors_precomp; p.opacities = opacities; p.scales = scales;
+    p.scale_modifier = scale_modifier; p.rotations = rotations; p.cov3D_precomp = cov3D_precomp; p.viewmatrix = viewmatrix;
+    p.projmatrix = projmatrix; p.cam_pos = cam_pos; p.background = background; p.tan_fovx = tan_fovx; p.tan_fovy = tan_fovy;
+    p.prefiltered = prefiltered; p.out_color = out_color; p.radii = radii;
+    GeomState g; BinningState b; ImageState img;
+    if (forward_front(geometry_buffer, binning_buffer, image_buffer, alloc_user, p, g, b, img, debug, num_rendered_host, s)) return 1;
+    VCR_CUDA_TRY(cudaMemsetAsync(gaussians_count, 0, (size_t)P * sizeof(int), s));
+    if (important_score) VCR_CUDA_TRY(cudaMemsetAsync(important_score, 0, (size_t)P * sizeof(float), s));
+    if (vcr_launch_render_aux(mode, p, g, b, img, gaussians_count, important_score, s)) return 1;
+    if (debug_sync(debug, s, "render aux")) return 1;
+    return 0;
+}
+
+int vcr_rasterize_count(vcr_alloc_fn geometry_buffer, vcr_alloc_fn binning_buffer, vcr_alloc_fn image_buffer, void* alloc_user, int P,
+                        int D, int M, const float* background, int width, int height, const float* means3D, const float* shs,
+                        const float* colors_precomp, const float* opacities, const float* scales, float scale_modifier,
+                        const float* rotations, const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+                        const float* cam_pos, float tan_fovx, float tan_fovy, int prefiltered, float* out_color,
+                        int* gaussians_count, float* important_score, int* radii, int debug, int* num_rendered_host, void* stream) {
+    if (!out_color || !important_score || !background) { vcr_set_error("NULL required argument"); return 1; }
+    return aux_forward(VCR_MODE_COUNT, geometry_buffer, binning_buffer, image_buffer, alloc_user, P, D, M, background, width, height,
+                       means3D, shs, colors_precomp, opacities, scales, scale_modifier, rotations, cov3D_precomp, viewmatrix,
+                       projmatrix, cam_pos, tan_fovx, tan_fovy, prefiltered, out_color, gaussians_count, important_score, radii,
+                       debug, num_rendered_host, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int vcr_rasterize_visi_acc(vcr_alloc_fn geometry_buffer, vcr_alloc_fn binning_buffer, vcr_alloc_fn image_buffer, void* alloc_user,
+                           int P, int D, int M, int width, int height, const float* means3D, const float* shs,
+                           const float* colors_precomp, const float* opacities, const float* scales, float scale_modifier,
+                           const float* rotations, const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+                           const float* cam_pos, float tan_fovx, float tan_fovy, int prefiltered, int* gaussians_count, int* radii,
+                           int debug, int* num_rendered_host, void* stream) {
+    return aux_forward(VCR_MODE_VISI_ACC, geometry_buffer, binning_buffer, image_buffer, alloc_user, P, D, M, nullptr, width, height,
+                       means3D, shs, colors_precomp, opacities, scales, scale_modifier, rotations, cov3D_precomp, viewmatrix,
+                       projmatrix, cam_pos, tan_fovx, tan_fovy, prefiltered, nullptr, gaussians_count, nullptr, radii, debug,
+                       num_rendered_host, reinterpret_cast<cudaStream_t>(stream));
+}
+
+void vcr_geom_layout(char* chunk, int P, vcr_geom_view* out) {
+    GeomState g = GeomState::carve(chunk, P);
+    out->depths = g.depths; out->clamped = g.clamped; out->means2D = reinterpret_cast<float*>(g.means2D);
+    out->xyz_view = g.xyz_view; out->cov3D = g.cov3D; out->conic_opacity = reinterpret_cast<float*>(g.conic_opacity);
+    out->rgb = g.rgb; out->tiles_touched = g.tiles_touched; out->point_offsets = g.point_offsets;
+}
+void vcr_binning_layout(char* chunk, int num_rendered, vcr_binning_view* out) {
+    BinningState b = BinningState::carve(chunk, num_rendered);
+    out->point_list = b.point_list; out->point_list_keys = b.point_list_keys;
+    out->point_list_unsorted = b.point_list_unsorted; out->point_list_keys_unsorted = b.point_list_keys_unsorted;
+}
+void vcr_image_layout(char* chunk, int width, int height, vcr_image_view* out) {
+    ImageState s = ImageState::carve(chunk, width, height);
+    out->accum_alpha = s.accum_alpha; out->n_contrib = s.n_contrib; out->ranges = reinterpret_cast<uint32_t*>(s.ranges);
+}
+
+}  // extern "C"

@@ -1,0 +1,191 @@
+// dnormal.cu — the D-Normal regularizer as one fused kernel per direction.
+//
+// Replaces the PyTorch op chain of the reference (~15 launches + torch.inverse with a host sync, and
+// >= 10 full-image temporaries per view):
+//   depth -> camera points      tools/graphics_utils.py:111-131 (depth2point_cam, ndc_2_cam)
+//   finite differences, cross, normalise   tools/normal_utils.py:24-41 (compute_gradient, compute_normals)
+//   F.normalize of the rendered normal     gaussian_renderer/__init__.py:133-134
+//   mask = cam.mask & depth < extent*thr   gaussian_renderer/__init__.py:125-131
+//   cos_weight, monosdf_normal_loss        tools/loss_utils.py:122-142
+//   masked means + assembly                trainer.py:266-280
+//
+// forward : est_normal (optional), per-pixel confidence weight (optional), and the three sums
+//           { sum_M w*|n-g|_1, sum_M w*(1-n.g), |M| };  loss = (s0 + s1) / s2   (0 when M is empty).
+// backward: dL/ddepth by a 5-point gather — each pixel re-evaluates the loss gradient of the (at most
+//           five) pixels whose normal depends on its depth; no saved intermediates, no atomics.
+//
+// K = [[fx,0,cx],[0,fy,cy],[0,0,1]] so K^-1 [u+.5, v+.5, 1]^T z = ((u+.5-cx)/fx, (v+.5-cy)/fy, 1) z.
+#include "common.cuh"
+
+struct DnParams {
+    const float* depth; const float* gt; const float* rn; const uint8_t* mask;
+    int W, H;
+    float inv_fx, inv_fy, cx, cy, exp_t, mask_depth_max;
+};
+
+__device__ __forceinline__ float3 dn_point(const DnParams& p, int u, int v) {
+    const float z = __ldg(p.depth + (size_t)v * p.W + u);
+    return make_float3(((u + 0.5f) - p.cx) * p.inv_fx * z, ((v + 0.5f) - p.cy) * p.inv_fy * z, z);
+}
+// torch.gradient (spacing 1, edge_order 1): central differences inside, one-sided at the borders.
+__device__ __forceinline__ float3 dn_diff_u(const DnParams& p, int u, int v) {
+    if (p.W == 1) return make_float3(0.f, 0.f, 0.f);
+    const int u0 = max(u - 1, 0), u1 = min(u + 1, p.W - 1);
+    const float s = (u1 - u0 == 2) ? 0.5f : 1.0f;
+    const float3 a = dn_point(p, u0, v), b = dn_point(p, u1, v);
+    return make_float3((b.x - a.x) * s, (b.y - a.y) * s, (b.z - a.z) * s);
+}
+__device__ __forceinline__ float3 dn_diff_v(const DnParams& p, int u, int v) {
+    if (p.H == 1) return make_float3(0.f, 0.f, 0.f);
+    const int v0 = max(v - 1, 0), v1 = min(v + 1, p.H - 1);
+    const float s = (v1 - v0 == 2) ? 0.5f : 1.0f;
+    const float3 a = dn_point(p, u, v0), b = dn_point(p, u, v1);
+    return make_float3((b.x - a.x) * s, (b.y - a.y) * s, (b.z - a.z) * s);
+}
+__device__ __forceinline__ float3 cross3(const float3 a, const float3 b) {
+    return make_float3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
+}
+__device__ __forceinline__ bool dn_masked_in(const DnParams& p, size_t pix) {
+    bool m = p.mask ? (__ldg(p.mask + pix) != 0) : true;
+    if (p.mask_depth_max > 0.f && !(__ldg(p.depth + pix) < p.mask_depth_max)) m = false;
+    return m;
+}
+__device__ __forceinline__ float dn_weight(const DnParams& p, size_t pix, const float3 g) {
+    if (!(p.exp_t > 0.f)) return 1.0f;
+    const float rx = __ldg(p.rn + 3 * pix), ry = __ldg(p.rn + 3 * pix + 1), rz = __ldg(p.rn + 3 * pix + 2);
+    const float rl = fmaxf(sqrtf(rx * rx + ry * ry + rz * rz), 1e-12f);  // F.normalize eps
+    const float cs = (rx * g.x + ry * g.y + rz * g.z) / rl;
+    return expf((cs - 1.0f) / p.exp_t);
+}
+
+__global__ void __launch_bounds__(256) dnormal_forward_kernel(const DnParams p, float* __restrict__ est_normal,
+                                                              float* __restrict__ weight_out, float* __restrict__ sums) {
+    const int u = blockIdx.x * 32 + (threadIdx.x & 31);
+    const int v = blockIdx.y * 8 + (threadIdx.x >> 5);
+    float l1 = 0.f, lc = 0.f, cnt = 0.f;
+    if (u < p.W && v < p.H) {
+        const size_t pix = (size_t)v * p.W + u;
+        const float3 c = cross3(dn_diff_u(p, u, v), dn_diff_v(p, u, v));
+        const float len = sqrtf(c.x * c.x + c.y * c.y + c.z * c.z);
+        const float inv = 1.0f / fmaxf(len, 1e-12f);
+        const float3 n = make_float3(c.x * inv, c.y * inv, c.z * inv);
+        if (est_normal) { est_normal[3 * pix] = n.x; est_normal[3 * pix + 1] = n.y; est_normal[3 * pix + 2] = n.z; }
+        float w = 0.f;
+        if (dn_masked_in(p, pix)) {
+            const float3 g = make_float3(__ldg(p.gt + 3 * pix), __ldg(p.gt + 3 * pix + 1), __ldg(p.gt + 3 * pix + 2));
+            w = dn_weight(p, pix, g);
+            l1 = w * (fabsf(n.x - g.x) + fabsf(n.y - g.y) + fabsf(n.z - g.z));
+            lc = w * (1.0f - (n.x * g.x + n.y * g.y + n.z * g.z));
+            cnt = 1.f;
+        }
+        if (weight_out) weight_out[pix] = w;
+    }
+    __shared__ float red[3][8];
+    l1 = vcr_warp_sum(l1); lc = vcr_warp_sum(lc); cnt = vcr_warp_sum(cnt);
+    if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = l1; red[1][threadIdx.x >> 5] = lc; red[2][threadIdx.x >> 5] = cnt; }
+    __syncthreads();
+    if (threadIdx.x < 3) {
+        float t = 0.f;
+#pragma unroll
+        for (int k = 0; k < 8; k++) t += red[threadIdx.x][k];
+        if (t != 0.f) atomicAdd(sums + threadIdx.x, t);
+    }
+}
+
+// dL/dc at pixel (u,v): loss gradient w.r.t. the un-normalised cross product; also returns dx, dy there.
+__device__ __forceinline__ float3 dn_grad_c(const DnParams& p, int u, int v, float scale, const float* __restrict__ up,
+                                            float3& dxo, float3& dyo) {
+    const size_t pix = (size_t)v * p.W + u;
+    const float3 dx = dn_diff_u(p, u, v), dy = dn_diff_v(p, u, v);
+    dxo = dx; dyo = dy;
+    const float3 c = cross3(dx, dy);
+    const float len = sqrtf(c.x * c.x + c.y * c.y + c.z * c.z);
+    const float den = fmaxf(len, 1e-12f);
+    const float inv = 1.0f / den;
+    const float3 n = make_float3(c.x * inv, c.y * inv, c.z * inv);
+    float3 dn = make_float3(0.f, 0.f, 0.f);
+    if (dn_masked_in(p, pix)) {
+        const float3 g = make_float3(__ldg(p.gt + 3 * pix), __ldg(p.gt + 3 * pix + 1), __ldg(p.gt + 3 * pix + 2));
+        const float w = dn_weight(p, pix, g) * scale;
+        const float ex = n.x - g.x, ey = n.y - g.y, ez = n.z - g.z;
+        dn.x = w * ((float)((ex > 0.f) - (ex < 0.f)) - g.x);
+        dn.y = w * ((float)((ey > 0.f) - (ey < 0.f)) - g.y);
+        dn.z = w * ((float)((ez > 0.f) - (ez < 0.f)) - g.z);
+    }
+    if (up) { dn.x += __ldg(up + 3 * pix); dn.y += __ldg(up + 3 * pix + 1); dn.z += __ldg(up + 3 * pix + 2); }
+    if (len > 1e-12f) {
+        const float d = dn.x * n.x + dn.y * n.y + dn.z * n.z;
+        return make_float3((dn.x - n.x * d) * inv, (dn.y - n.y * d) * inv, (dn.z - n.z * d) * inv);
+    }
+    return make_float3(dn.x * inv, dn.y * inv, dn.z * inv);
+}
+
+__global__ void __launch_bounds__(256) dnormal_backward_kernel(const DnParams p, const float* __restrict__ sums,
+                                                               const float* __restrict__ dL_dloss,
+                                                               const float* __restrict__ dL_dest, float* __restrict__ dL_ddepth) {
+    const int u = blockIdx.x * 32 + (threadIdx.x & 31);
+    const int v = blockIdx.y * 8 + (threadIdx.x >> 5);
+    if (u >= p.W || v >= p.H) return;
+    const float cnt = __ldg(sums + 2);
+    const float scale = cnt > 0.f ? __ldg(dL_dloss) / cnt : 0.f;
+    float3 gX = make_float3(0.f, 0.f, 0.f);
+    // contributions through dx(q): q = (u-1,v) [+s], q = (u+1,v) [-s], q = (u,v) at a border [-1 / +1]
+    // dL/ddx(q) = dy(q) x gc(q);  dL/ddy(q) = gc(q) x dx(q)
+    auto via_dx = [&](int qu, float coef) {
+        float3 dx, dy;
+        const float3 gc = dn_grad_c(p, qu, v, scale, dL_dest, dx, dy);
+        const float3 t = cross3(dy, gc);
+        gX.x += coef * t.x; gX.y += coef * t.y; gX.z += coef * t.z;
+    };
+    auto via_dy = [&](int qv, float coef) {
+        float3 dx, dy;
+        const float3 gc = dn_grad_c(p, u, qv, scale, dL_dest, dx, dy);
+        const float3 t = cross3(gc, dx);
+        gX.x += coef * t.x; gX.y += coef * t.y; gX.z += coef * t.z;
+    };
+    if (p.W > 1) {
+        if (u > 0) { const int q = u - 1; via_dx(q, (q > 0) ? 0.5f : 1.0f); }               // X(p) is the upper sample of q
+        if (u < p.W - 1) { const int q = u + 1; via_dx(q, (q < p.W - 1) ? -0.5f : -1.0f); } // X(p) is the lower sample of q
+        if (u == 0) via_dx(0, -1.0f);
+        if (u == p.W - 1) via_dx(u, 1.0f);
+    }
+    if (p.H > 1) {
+        if (v > 0) { const int q = v - 1; via_dy(q, (q > 0) ? 0.5f : 1.0f); }
+        if (v < p.H - 1) { const int q = v + 1; via_dy(q, (q < p.H - 1) ? -0.5f : -1.0f); }
+        if (v == 0) via_dy(0, -1.0f);
+        if (v == p.H - 1) via_dy(v, 1.0f);
+    }
+    const float ax = ((u + 0.5f) - p.cx) * p.inv_fx, ay = ((v + 0.5f) - p.cy) * p.inv_fy;
+    dL_ddepth[(size_t)v * p.W + u] = gX.x * ax + gX.y * ay + gX.z;
+}
+
+extern "C" {
+
+int vcr_dnormal_forward(const float* depth, const float* gt_normal, const float* render_normal, const uint8_t* mask, int width,
+                        int height, float fx, float fy, float cx, float cy, float exp_t, float mask_depth_max, float* est_normal,
+                        float* weight, float* sums, int zero_sums, void* stream) {
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    if (!depth || !gt_normal || !sums || width <= 0 || height <= 0) { vcr_set_error("dnormal_forward: bad argument"); return 1; }
+    if (exp_t > 0.f && !render_normal) { vcr_set_error("dnormal_forward: render_normal is required when exp_t > 0"); return 1; }
+    DnParams p{depth, gt_normal, render_normal, mask, width, height, 1.0f / fx, 1.0f / fy, cx, cy, exp_t, mask_depth_max};
+    if (zero_sums) VCR_CUDA_TRY(cudaMemsetAsync(sums, 0, 3 * sizeof(float), s));
+    const dim3 grid((width + 31) / 32, (height + 7) / 8);
+    dnormal_forward_kernel<<<grid, 256, 0, s>>>(p, est_normal, weight, sums);
+    VCR_LAUNCH_CHECK("dnormal_forward_kernel");
+    return 0;
+}
+
+int vcr_dnormal_backward(const float* depth, const float* gt_normal, const float* render_normal, const uint8_t* mask, int width,
+                         int height, float fx, float fy, float cx, float cy, float exp_t, float mask_depth_max, const float* sums,
+                         const float* dL_dloss, const float* dL_dest_normal, float* dL_ddepth, void* stream) {
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    if (!depth || !gt_normal || !sums || !dL_dloss || !dL_ddepth || width <= 0 || height <= 0) { vcr_set_error("dnormal_backward: bad argument"); return 1; }
+    if (exp_t > 0.f && !render_normal) { vcr_set_error("dnormal_backward: render_normal is required when exp_t > 0"); return 1; }
+    DnParams p{depth, gt_normal, render_normal, mask, width, height, 1.0f / fx, 1.0f / fy, cx, cy, exp_t, mask_depth_max};
+    const dim3 grid((width + 31) / 32, (height + 7) / 8);
+    dnormal_backward_kernel<<<grid, 256, 0, s>>>(p, sums, dL_dloss, dL_dest_normal, dL_ddepth);
+    VCR_LAUNCH_CHECK("dnormal_backward_kernel");
+    return 0;
+}
+
+}  // extern "C"

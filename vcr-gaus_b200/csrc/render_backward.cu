@@ -1,0 +1,291 @@
+// render_backward.cu — back-to-front replay of the compositing with per-Gaussian gradient accumulation.
+//
+// Replaces renderCUDA<3,2> backward (reference DGR/cuda_rasterizer/backward.cu:422-812).
+//
+// Same tiling as the forward (one 256-thread block per 16x16 tile, one pixel per thread), Gaussians
+// staged in shared memory in reverse list order.  Where the reference issues ~20 atomicAdd per
+// contributing (pixel, Gaussian) pair, this kernel
+//   1. skips a Gaussian for the whole warp when no lane contributes (__any_sync),
+//   2. reduces the 16 main gradient components across the warp with a transposed butterfly
+//      (15 + 1 shuffles instead of 16 x 5), leaving component k on lane k, and
+//   3. lands them with ONE coalesced 64-byte atomic request per (warp, Gaussian) into a per-Gaussian
+//      AoS record (common.cuh ACC_*), from which preprocess_backward reads them back once.
+// The formulas (including the reference's quirks) are kept term by term; only the
+// division by the final weight is replaced by a multiplication with its reciprocal.
+#include "common.cuh"
+
+#define RB_BATCH 256
+
+struct __align__(16) StagedGeoB {
+    float x, y, ca, cb;
+    float cc, op, nx;    // nx: dot(normal, xyz_view) (intersection mode) or view depth
+    uint32_t id_inside;  // (id << 1) | inside
+};
+
+// Transposed warp reduction: every lane passes 16 values; on return lane L (and lane L+16) holds the
+// warp-wide sum of value (L & 15).  8+4+2+1 exchange shuffles + 1 plain butterfly step.
+__device__ __forceinline__ float warp_reduce16_transposed(float (&v)[16], int lane) {
+    {
+        const bool hi = lane & 8;
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            const float send = hi ? v[i] : v[i + 8];
+            const float keep = hi ? v[i + 8] : v[i];
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+        }
+    }
+    {
+        const bool hi = lane & 4;
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const float send = hi ? v[i] : v[i + 4];
+            const float keep = hi ? v[i + 4] : v[i];
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+        }
+    }
+    {
+        const bool hi = lane & 2;
+#pragma unroll
+        for (int i = 0; i < 2; i++) {
+            const float send = hi ? v[i] : v[i + 2];
+            const float keep = hi ? v[i + 2] : v[i];
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+        }
+    }
+    {
+        const bool hi = lane & 1;
+        const float send = hi ? v[0] : v[1];
+        const float keep = hi ? v[1] : v[0];
+        v[0] = keep + __shfl_xor_sync(0xffffffffu, send, 1);
+    }
+    return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 16);
+}
+
+template <bool HAS_DIRS, bool HAS_OBJ>
+__global__ void __launch_bounds__(256) render_backward_kernel(
+    const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H, const float* __restrict__ bg,
+    const float2* __restrict__ means2D, const float* __restrict__ xyz_view, const float4* __restrict__ conic_opacity,
+    const float* __restrict__ colors, const float* __restrict__ depths, const float* __restrict__ normals,
+    const float* __restrict__ objects, const float* __restrict__ dirs, const float* __restrict__ alpha_img,
+    const float* __restrict__ depth_img, const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
+    const float* __restrict__ dL_dpixels, const uint8_t* __restrict__ inside_gs, float* __restrict__ acc) {
+    __shared__ StagedGeoB s_geo[RB_BATCH];
+    __shared__ float4 s_nrm[RB_BATCH];
+    __shared__ float4 s_col[RB_BATCH];
+    __shared__ float4 s_xv[HAS_DIRS ? RB_BATCH : 1];
+    __shared__ float2 s_obj[HAS_OBJ ? RB_BATCH : 1];
+
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int gx = gridDim.x;
+    const uint32_t px = blockIdx.x * VCR_TILE_X + (tid & 15);
+    const uint32_t py = blockIdx.y * VCR_TILE_Y + (tid >> 4);
+    const bool inside = px < (uint32_t)W && py < (uint32_t)H;
+    const size_t HW = (size_t)H * W;
+    const size_t pix_id = (size_t)W * py + px;
+    const float pfx = (float)px, pfy = (float)py;
+
+    const uint2 range = ranges[blockIdx.y * gx + blockIdx.x];
+    const int rounds = (int)((range.y - range.x + RB_BATCH - 1) / RB_BATCH);
+    int toDo = (int)(range.y - range.x);
+
+    const float T_final = inside ? final_Ts[pix_id] : 0.f;
+    float T = T_final;
+    const float inv_weight = inside ? 1.0f / alpha_img[pix_id] : 1.f;
+    const float depth_final = inside ? depth_img[pix_id] : 1.f;
+    uint32_t contributor = (uint32_t)toDo;
+    const uint32_t last_contributor = inside ? n_contrib[pix_id] : 0u;
+
+    float accum_rec[3] = {0.f, 0.f, 0.f}, dL_dpixel[3] = {0.f, 0.f, 0.f};
+    float accum_depth_rec = 0.f, accum_rec2 = 0.f, dL_dpixel_depth = 0.f;
+    float accum_normal_rec[3] = {0.f, 0.f, 0.f}, dL_dpixel_normal[3] = {0.f, 0.f, 0.f};
+    float accum_rec_obj[2] = {0.f, 0.f}, dL_dpixel_obj[2] = {0.f, 0.f};
+    float accum_alpha_rec = 0.f, dL_dalpha = 0.f;
+    float3 dir = make_float3(0.f, 0.f, 1.f);
+    if (inside) {
+#pragma unroll
+        for (int i = 0; i < 3; i++) dL_dpixel[i] = __ldg(dL_dpixels + i * HW + pix_id);
+        dL_dpixel_depth = __ldg(dL_dpixels + VCR_DEPTH_OFFSET * HW + pix_id);
+#pragma unroll
+        for (int i = 0; i < 3; i++) dL_dpixel_normal[i] = __ldg(dL_dpixels + (VCR_NORMAL_OFFSET + i) * HW + pix_id);
+        if (HAS_OBJ) {
+#pragma unroll
+            for (int i = 0; i < 2; i++) dL_dpixel_obj[i] = __ldg(dL_dpixels + (VCR_OBJECT_OFFSET + i) * HW + pix_id);
+        }
+        dL_dalpha = __ldg(dL_dpixels + VCR_ALPHA_OFFSET * HW + pix_id);
+        if (HAS_DIRS) dir = make_float3(__ldg(dirs + pix_id), __ldg(dirs + HW + pix_id), __ldg(dirs + 2 * HW + pix_id));
+    }
+    float bg_dot_dpixel = 0.f;
+#pragma unroll
+    for (int i = 0; i < 3; i++) bg_dot_dpixel += __ldg(bg + i) * dL_dpixel[i];
+
+    float last_alpha = 0.f, last_color[3] = {0.f, 0.f, 0.f}, last_depth = 0.f, last_normal[3] = {0.f, 0.f, 0.f};
+    float last_object[2] = {0.f, 0.f};
+    const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
+
+    for (int i = 0; i < rounds; i++, toDo -= RB_BATCH) {
+        __syncthreads();
+        const uint32_t progress = (uint32_t)i * RB_BATCH + tid;
+        if (range.x + progress < range.y) {
+            const uint32_t id = __ldg(point_list + (range.y - progress - 1));
+            const float2 xy = __ldg(means2D + id);
+            const float4 co = __ldg(conic_opacity + id);
+            const float3 n = make_float3(__ldg(normals + 3 * (size_t)id), __ldg(normals + 3 * (size_t)id + 1),
+                                         __ldg(normals + 3 * (size_t)id + 2));
+            StagedGeoB sg;
+            sg.x = xy.x; sg.y = xy.y; sg.ca = co.x; sg.cb = co.y; sg.cc = co.z; sg.op = co.w;
+            if (HAS_DIRS) {
+                const float3 xv = make_float3(__ldg(xyz_view + 3 * (size_t)id), __ldg(xyz_view + 3 * (size_t)id + 1),
+                                              __ldg(xyz_view + 3 * (size_t)id + 2));
+                sg.nx = n.x * xv.x + n.y * xv.y + n.z * xv.z;
+                s_xv[tid] = make_float4(xv.x, xv.y, xv.z, 0.f);
+            } else {
+                sg.nx = __ldg(depths + id);
+            }
+            sg.id_inside = (id << 1) | (__ldg(inside_gs + id) ? 1u : 0u);
+            s_geo[tid] = sg;
+            s_nrm[tid] = make_float4(n.x, n.y, n.z, 0.f);
+            s_col[tid] = make_float4(__ldg(colors + 3 * (size_t)id), __ldg(colors + 3 * (size_t)id + 1),
+                                     __ldg(colors + 3 * (size_t)id + 2), 0.f);
+            if (HAS_OBJ) s_obj[tid] = make_float2(__ldg(objects + 2 * (size_t)id), __ldg(objects + 2 * (size_t)id + 1));
+        }
+        __syncthreads();
+
+        const int cnt = min(RB_BATCH, toDo);
+        for (int j = 0; j < cnt; j++) {
+            contributor--;
+            const float4 g0 = *reinterpret_cast<const float4*>(&s_geo[j]);
+            const float4 g1 = *reinterpret_cast<const float4*>(&s_geo[j].cc);
+            const float dx = g0.x - pfx, dy = g0.y - pfy;
+            bool contrib = inside && contributor < last_contributor;
+            const float q = __fmaf_rn(__fmul_rn(g0.z, dx), dx, __fmul_rn(__fmul_rn(g1.x, dy), dy));
+            const float power = __fmaf_rn(q, -0.5f, -__fmul_rn(__fmul_rn(g0.w, dx), dy));
+            contrib = contrib && !(power > 0.0f);
+            const float G = expf(power);
+            const float alpha = fminf(0.99f, g1.y * G);
+            contrib = contrib && !(alpha < 1.0f / 255.0f);
+            const float4 nrm = s_nrm[j];
+            float c_d, pro_dot = 1.f;
+            if (HAS_DIRS) {
+                pro_dot = nrm.x * dir.x + nrm.y * dir.y + nrm.z * dir.z;
+                c_d = (g1.z / pro_dot) * dir.z;
+            } else {
+                c_d = g1.z;
+            }
+            contrib = contrib && !(c_d < 0.2f);  // == (double)c_d < 0.2, backward.cu:616
+            if (!__any_sync(0xffffffffu, contrib)) continue;
+
+            float v[16];
+#pragma unroll
+            for (int k = 0; k < 16; k++) v[k] = 0.f;
+            float ex_view_z = 0.f, ex_obj0 = 0.f, ex_obj1 = 0.f;
+            const uint32_t idi = __float_as_uint(g1.w);
+            if (contrib) {
+                T = T / (1.f - alpha);
+                const float aT = alpha * T;
+                float dL_dopa = 0.0f;
+                const float4 col = s_col[j];
+                const float cc[3] = {col.x, col.y, col.z};
+#pragma unroll
+                for (int ch = 0; ch < 3; ch++) {
+                    accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
+                    last_color[ch] = cc[ch];
+                    dL_dopa += (cc[ch] - accum_rec[ch]) * dL_dpixel[ch];
+                    v[ACC_COLOR_R + ch] = aT * dL_dpixel[ch];
+                }
+                if (idi & 1u) {
+                    accum_depth_rec = last_alpha * last_depth + (1.f - last_alpha) * accum_depth_rec;
+                    accum_rec2 = last_alpha + (1.f - last_alpha) * accum_rec2;  // == accum_normal_rec2[ch], same recurrence
+                    dL_dopa += (((c_d - accum_depth_rec) - depth_final * (1 - accum_rec2)) * inv_weight) * dL_dpixel_depth;
+                    const float dL_dd_j = (aT * inv_weight) * dL_dpixel_depth;
+                    float dnd[3] = {0.f, 0.f, 0.f};
+                    if (HAS_DIRS) {  // backward.cu:722-728
+                        const float4 xv = s_xv[j];
+                        const float s = dL_dd_j * dir.z;
+                        const float inv_pd = 1.0f / pro_dot;
+                        const float s2 = s * inv_pd * inv_pd;
+                        dnd[0] = s2 * (pro_dot * xv.x - dir.x * g1.z);
+                        dnd[1] = s2 * (pro_dot * xv.y - dir.y * g1.z);
+                        dnd[2] = s2 * (pro_dot * xv.z - dir.z * g1.z);
+                        const float sv = s * inv_pd;
+                        v[ACC_VIEW_X_OR_DEPTH] = sv * nrm.x;
+                        v[ACC_VIEW_Y] = sv * nrm.y;
+                        ex_view_z = sv * nrm.z;
+                    } else {
+                        v[ACC_VIEW_X_OR_DEPTH] = dL_dd_j;
+                    }
+                    const float nn[3] = {nrm.x, nrm.y, nrm.z};
+#pragma unroll
+                    for (int ch = 0; ch < 3; ch++) {
+                        const float n = nn[ch];
+                        accum_normal_rec[ch] = last_alpha * last_normal[ch] + (1.f - last_alpha) * accum_normal_rec[ch];
+                        last_normal[ch] = n;
+                        // reference quirk: last_normal was just overwritten with n (backward.cu:741-745)
+                        dL_dopa += (((n - accum_normal_rec[ch]) - n * (1 - accum_rec2)) * inv_weight) * dL_dpixel_normal[ch];
+                        v[ACC_NORMAL_X + ch] = (aT * inv_weight) * dL_dpixel_normal[ch] + dnd[ch];
+                    }
+                }
+                if (HAS_OBJ) {
+                    const float2 o2 = s_obj[j];
+                    const float oo[2] = {o2.x, o2.y};
+                    float eo[2];
+#pragma unroll
+                    for (int ch = 0; ch < 2; ch++) {
+                        accum_rec_obj[ch] = last_alpha * last_object[ch] + (1.f - last_alpha) * accum_rec_obj[ch];
+                        last_object[ch] = oo[ch];
+                        dL_dalpha += (oo[ch] - accum_rec_obj[ch]) * dL_dpixel_obj[ch];  // persists across Gaussians (backward.cu:766)
+                        eo[ch] = aT * dL_dpixel_obj[ch];
+                    }
+                    ex_obj0 = eo[0]; ex_obj1 = eo[1];
+                }
+                accum_alpha_rec = last_alpha + (1.f - last_alpha) * accum_alpha_rec;
+                dL_dopa += (1 - accum_alpha_rec) * dL_dalpha;
+                dL_dopa *= T;
+                last_alpha = alpha;
+                last_depth = c_d;
+                dL_dopa += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
+
+                const float dL_dG = g1.y * dL_dopa;
+                const float gdx = G * dx, gdy = G * dy;
+                const float dG_ddelx = -gdx * g0.z - gdy * g0.w;
+                const float dG_ddely = -gdy * g1.x - gdx * g0.w;
+                const float mx = dL_dG * dG_ddelx * ddelx_dx, my = dL_dG * dG_ddely * ddely_dy;
+                v[ACC_MEAN2D_X] = mx; v[ACC_MEAN2D_Y] = my;
+                v[ACC_ABS_X] = fabsf(mx); v[ACC_ABS_Y] = fabsf(my);
+                v[ACC_CONIC_XX] = -0.5f * gdx * dx * dL_dG;
+                v[ACC_CONIC_XY] = -0.5f * gdx * dy * dL_dG;
+                v[ACC_CONIC_YY] = -0.5f * gdy * dy * dL_dG;
+                v[ACC_OPACITY] = G * dL_dopa;
+            }
+            const float red = warp_reduce16_transposed(v, lane);
+            float* rec = acc + (size_t)(idi >> 1) * VCR_ACC_STRIDE;
+            if (lane < 16) atomicAdd(rec + lane, red);
+            if (HAS_DIRS) {
+                const float z = vcr_warp_sum(ex_view_z);
+                if (lane == 16) atomicAdd(rec + ACC_VIEW_Z, z);
+            }
+            if (HAS_OBJ) {
+                const float o0 = vcr_warp_sum(ex_obj0), o1 = vcr_warp_sum(ex_obj1);
+                if (lane == 17) atomicAdd(rec + ACC_OBJ_0, o0);
+                if (lane == 18) atomicAdd(rec + ACC_OBJ_1, o1);
+            }
+        }
+    }
+}
+
+int vcr_launch_render_backward(const BwdParams& p, GeomState& g, BinningState& b, ImageState& img, cudaStream_t s) {
+    VCR_CUDA_TRY(cudaMemsetAsync(p.acc, 0, (size_t)p.P * VCR_ACC_STRIDE * sizeof(float), s));
+    const dim3 grid(p.gx, p.gy, 1);
+    const float* col = p.colors_precomp ? p.colors_precomp : g.rgb;
+#define RB_ARGS img.ranges, b.point_list, p.W, p.H, p.background, g.means2D, g.xyz_view, g.conic_opacity, col, g.depths, \
+                p.normals, p.sh_objs, p.dirs, p.alpha, p.depth, img.accum_alpha, img.n_contrib, p.dL_dpix, p.inside, p.acc
+    if (p.dirs) {
+        if (p.sh_objs) render_backward_kernel<true, true><<<grid, 256, 0, s>>>(RB_ARGS);
+        else render_backward_kernel<true, false><<<grid, 256, 0, s>>>(RB_ARGS);
+    } else {
+        if (p.sh_objs) render_backward_kernel<false, true><<<grid, 256, 0, s>>>(RB_ARGS);
+        else render_backward_kernel<false, false><<<grid, 256, 0, s>>>(RB_ARGS);
+    }
+#undef RB_ARGS
+    VCR_LAUNCH_CHECK("render_backward_kernel");
+    return 0;
+}

@@ -1,0 +1,199 @@
+// render_forward.cu — per-tile front-to-back compositing of colour / depth / normal / alpha / semantics.
+//
+// Replaces renderCUDA<3,2> (reference DGR/cuda_rasterizer/forward.cu:265-478) and, as MODE 1 / 3, the
+// pruning variants renderCUDA_count (:480-603) and renderCUDA_visi_acc (:735-835).
+//
+// One 256-thread block per 16x16 tile, one pixel per thread, FP32 on the CUDA cores (this is not a
+// dense contraction; no tensor cores).  Unlike the reference, everything the inner loop touches is
+// staged in shared memory per batch (the reference reloads normal / colour / semantics from global
+// memory for every contributing pair), the near-plane test is done in FP32 (x <= 0.2 in double is
+// the same predicate as x < 0.2f for a float x — no F2F.F64/DSETP per pair), and n.x_view of the
+// ray/plane intersection is computed once per staged Gaussian instead of once per pixel.
+//
+// The per-pixel arithmetic keeps the reference's operation order so that images are bit-identical to
+// the reference build on identical inputs.
+#include "common.cuh"
+
+#define RF_BATCH 256
+
+struct __align__(16) StagedGeo {  // 32 bytes
+    float x, y;        // pixel-space centre
+    float ca, cb;      // conic xx, xy
+    float cc, op;      // conic yy, opacity
+    float nx;          // dot(normal, xyz_view)  (intersection mode)  |  view depth (plain mode)
+    uint32_t id_inside;  // (id << 1) | inside
+};
+
+template <int MODE, bool HAS_DIRS, bool HAS_OBJ>
+__global__ void __launch_bounds__(256) render_forward_kernel(
+    const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
+    const float2* __restrict__ means2D, const float* __restrict__ xyz_view, const float* __restrict__ features,
+    const float* __restrict__ depths, const float* __restrict__ normals, const float* __restrict__ obj,
+    const float* __restrict__ dirs, const float4* __restrict__ conic_opacity, const uint8_t* __restrict__ inside_gs,
+    const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
+    float* __restrict__ out_color, int* __restrict__ gaussian_count, float* __restrict__ important_score) {
+    __shared__ StagedGeo s_geo[RF_BATCH];
+    __shared__ float4 s_nrm[MODE == 0 ? RF_BATCH : 1];
+    __shared__ float4 s_col[MODE != VCR_MODE_VISI_ACC ? RF_BATCH : 1];
+    __shared__ float2 s_obj[(MODE == 0 && HAS_OBJ) ? RF_BATCH : 1];
+
+    const int tid = threadIdx.x;
+    const int gx = gridDim.x;
+    const uint32_t px = blockIdx.x * VCR_TILE_X + (tid & 15);
+    const uint32_t py = blockIdx.y * VCR_TILE_Y + (tid >> 4);
+    const bool inside = px < (uint32_t)W && py < (uint32_t)H;
+    const size_t HW = (size_t)H * W;
+    const size_t pix_id = (size_t)W * py + px;
+    const float pfx = (float)px, pfy = (float)py;
+    bool done = !inside;
+
+    float3 dir = make_float3(0.f, 0.f, 0.f);
+    if (HAS_DIRS && inside) dir = make_float3(__ldg(dirs + pix_id), __ldg(dirs + HW + pix_id), __ldg(dirs + 2 * HW + pix_id));
+
+    const uint2 range = ranges[blockIdx.y * gx + blockIdx.x];
+    const int rounds = (int)((range.y - range.x + RF_BATCH - 1) / RF_BATCH);
+    int toDo = (int)(range.y - range.x);
+
+    float T = 1.0f;
+    uint32_t contributor = 0, last_contributor = 0;
+    float C[3] = {0.f, 0.f, 0.f};
+    float weight = 1e-10f;  // reference quirk: alpha output starts at 1e-10 (forward.cu:326)
+    float D = 0.f, N[3] = {0.f, 0.f, 0.f}, O[2] = {0.f, 0.f};
+
+    for (int i = 0; i < rounds; i++, toDo -= RF_BATCH) {
+        if (__syncthreads_count(done) == RF_BATCH) break;
+        const uint32_t progress = (uint32_t)i * RF_BATCH + tid;
+        if (range.x + progress < range.y) {
+            const uint32_t id = __ldg(point_list + range.x + progress);
+            const float2 xy = __ldg(means2D + id);
+            const float4 co = __ldg(conic_opacity + id);
+            StagedGeo sg;
+            sg.x = xy.x; sg.y = xy.y; sg.ca = co.x; sg.cb = co.y; sg.cc = co.z; sg.op = co.w;
+            uint32_t ins = 1u;
+            if (MODE == 0) {
+                const float3 n = make_float3(__ldg(normals + 3 * (size_t)id), __ldg(normals + 3 * (size_t)id + 1),
+                                             __ldg(normals + 3 * (size_t)id + 2));
+                s_nrm[tid] = make_float4(n.x, n.y, n.z, 0.f);
+                if (HAS_DIRS) {
+                    const float3 xv = make_float3(__ldg(xyz_view + 3 * (size_t)id), __ldg(xyz_view + 3 * (size_t)id + 1),
+                                                  __ldg(xyz_view + 3 * (size_t)id + 2));
+                    sg.nx = n.x * xv.x + n.y * xv.y + n.z * xv.z;  // dot(n, x) of intersect(), auxiliary.h:262-271
+                } else {
+                    sg.nx = __ldg(depths + id);
+                }
+                ins = __ldg(inside_gs + id) ? 1u : 0u;
+                if (HAS_OBJ) s_obj[tid] = make_float2(__ldg(obj + 2 * (size_t)id), __ldg(obj + 2 * (size_t)id + 1));
+            } else {
+                sg.nx = 0.f;
+            }
+            sg.id_inside = (id << 1) | ins;
+            s_geo[tid] = sg;
+            if (MODE != VCR_MODE_VISI_ACC)
+                s_col[tid] = make_float4(__ldg(features + 3 * (size_t)id), __ldg(features + 3 * (size_t)id + 1),
+                                         __ldg(features + 3 * (size_t)id + 2), 0.f);
+        }
+        __syncthreads();
+
+        const int cnt = min(RF_BATCH, toDo);
+        for (int j = 0; !done && j < cnt; j++) {
+            contributor++;
+            const float4 g0 = *reinterpret_cast<const float4*>(&s_geo[j]);        // x, y, ca, cb
+            const float4 g1 = *reinterpret_cast<const float4*>(&s_geo[j].cc);     // cc, op, nx, id_inside
+            const float dx = g0.x - pfx, dy = g0.y - pfy;
+            // power = -0.5f*(ca*dx*dx + cc*dy*dy) - cb*dx*dy, contracted exactly like the reference build
+            const float q = __fmaf_rn(__fmul_rn(g0.z, dx), dx, __fmul_rn(__fmul_rn(g1.x, dy), dy));
+            const float power = __fmaf_rn(q, -0.5f, -__fmul_rn(__fmul_rn(g0.w, dx), dy));
+            if (power > 0.0f) continue;
+
+            float depth = 0.f;
+            float4 nrm = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (MODE == 0) {
+                nrm = s_nrm[j];
+                if (HAS_DIRS) {
+                    const float t = g1.z / (nrm.x * dir.x + nrm.y * dir.y + nrm.z * dir.z);
+                    depth = t * dir.z;
+                } else {
+                    depth = g1.z;
+                }
+                if (depth < 0.2f) continue;  // == (double)depth <= 0.2, forward.cu:382
+            }
+            const float alpha = fminf(0.99f, g1.y * expf(power));
+            if (alpha < 1.0f / 255.0f) continue;
+            const uint32_t idi = __float_as_uint(g1.w);
+            if (MODE == VCR_MODE_VISI_ACC) {  // first contributor only (forward.cu:809-826)
+                atomicAdd(gaussian_count + (idi >> 1), 1);  // reference: racy ++ (forward.cu:822)
+                done = true;
+                continue;
+            }
+            const float test_T = T * (1 - alpha);
+            if (test_T < 0.0001f) { done = true; continue; }
+            const float4 col = s_col[j];
+            if (MODE == VCR_MODE_COUNT) {
+                // the reference's plain ++ / += race between pixels (forward.cu:575-576); atomics give the exact totals
+                atomicAdd(gaussian_count + (idi >> 1), 1);
+                atomicAdd(important_score + (idi >> 1), g1.y);
+                C[0] += col.x * alpha * T; C[1] += col.y * alpha * T; C[2] += col.z * alpha * T;
+            } else {
+                const float w = alpha * T;
+                C[0] = __fmaf_rn(col.x, w, C[0]); C[1] = __fmaf_rn(col.y, w, C[1]); C[2] = __fmaf_rn(col.z, w, C[2]);
+                if (HAS_OBJ) {
+                    const float2 o = s_obj[j];
+                    O[0] = __fmaf_rn(o.x, w, O[0]); O[1] = __fmaf_rn(o.y, w, O[1]);
+                }
+                weight += w;
+                if (idi & 1u) {
+                    D = __fmaf_rn(depth, w, D);
+                    N[0] = __fmaf_rn(nrm.x, w, N[0]); N[1] = __fmaf_rn(nrm.y, w, N[1]); N[2] = __fmaf_rn(nrm.z, w, N[2]);
+                }
+            }
+            T = test_T;
+            last_contributor = contributor;
+        }
+    }
+
+    if (inside && MODE != VCR_MODE_VISI_ACC) {
+        final_T[pix_id] = T;
+        n_contrib[pix_id] = last_contributor;
+#pragma unroll
+        for (int ch = 0; ch < 3; ch++) out_color[ch * HW + pix_id] = __fmaf_rn(T, __ldg(bg + ch), C[ch]);
+        if (MODE == 0) {
+            out_color[VCR_DEPTH_OFFSET * HW + pix_id] = D / weight;
+            out_color[VCR_ALPHA_OFFSET * HW + pix_id] = weight;
+#pragma unroll
+            for (int ch = 0; ch < 3; ch++) out_color[(VCR_NORMAL_OFFSET + ch) * HW + pix_id] = N[ch] / weight;
+            // the reference leaves the semantic channels at their zero initialisation when there are none
+            out_color[(VCR_OBJECT_OFFSET + 0) * HW + pix_id] = HAS_OBJ ? O[0] : 0.f;
+            out_color[(VCR_OBJECT_OFFSET + 1) * HW + pix_id] = HAS_OBJ ? O[1] : 0.f;
+        }
+    }
+}
+
+int vcr_launch_render_forward(const FwdParams& p, GeomState& g, BinningState& b, ImageState& img, cudaStream_t s) {
+    const dim3 grid(p.gx, p.gy, 1);
+    const float* feat = p.colors_precomp ? p.colors_precomp : g.rgb;
+#define RF_ARGS img.ranges, b.point_list, p.W, p.H, g.means2D, g.xyz_view, feat, g.depths, p.normals, p.sh_objs, p.dirs, \
+                g.conic_opacity, p.inside, p.background, img.accum_alpha, img.n_contrib, p.out_color, nullptr, nullptr
+    if (p.dirs) {
+        if (p.sh_objs) render_forward_kernel<0, true, true><<<grid, 256, 0, s>>>(RF_ARGS);
+        else render_forward_kernel<0, true, false><<<grid, 256, 0, s>>>(RF_ARGS);
+    } else {
+        if (p.sh_objs) render_forward_kernel<0, false, true><<<grid, 256, 0, s>>>(RF_ARGS);
+        else render_forward_kernel<0, false, false><<<grid, 256, 0, s>>>(RF_ARGS);
+    }
+#undef RF_ARGS
+    VCR_LAUNCH_CHECK("render_forward_kernel");
+    return 0;
+}
+
+int vcr_launch_render_aux(int mode, const FwdParams& p, GeomState& g, BinningState& b, ImageState& img,
+                          int* gaussians_count, float* important_score, cudaStream_t s) {
+    const dim3 grid(p.gx, p.gy, 1);
+    const float* feat = p.colors_precomp ? p.colors_precomp : g.rgb;
+#define RA_ARGS img.ranges, b.point_list, p.W, p.H, g.means2D, g.xyz_view, feat, g.depths, nullptr, nullptr, nullptr, \
+                g.conic_opacity, nullptr, p.background, img.accum_alpha, img.n_contrib, p.out_color, gaussians_count, important_score
+    if (mode == VCR_MODE_COUNT) render_forward_kernel<VCR_MODE_COUNT, false, false><<<grid, 256, 0, s>>>(RA_ARGS);
+    else render_forward_kernel<VCR_MODE_VISI_ACC, false, false><<<grid, 256, 0, s>>>(RA_ARGS);
+#undef RA_ARGS
+    VCR_LAUNCH_CHECK("render_aux_kernel");
+    return 0;
+}

@@ -1,0 +1,113 @@
+"""ctypes binding of libvcr_gaus_b200.so (the C ABI declared in include/vcr_gaus_b200.h).
+
+This is the only place the product path touches native code.  There is NO fallback: if the shared
+library has not been built (``make -C vcr-gaus_b200`` or ``__graft_entry__.build()``) importing this
+module raises, and every wrapper raises ``RuntimeError`` with the library's own message when a call
+fails.  PyTorch is used for device memory and streams only.
+"""
+import ctypes
+import os
+from ctypes import POINTER, c_char_p, c_float, c_int, c_size_t, c_uint32, c_void_p
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libvcr_gaus_b200.so")
+if not os.path.exists(LIB_PATH):
+    raise ImportError(
+        f"{LIB_PATH} is missing: build it with `make -C {_HERE}` (or __graft_entry__.build()). "
+        "There is no CPU or PyTorch fallback for the rasterizer."
+    )
+lib = ctypes.CDLL(LIB_PATH)
+
+ALLOC_FN = ctypes.CFUNCTYPE(c_void_p, c_void_p, c_size_t)
+P_ = c_void_p  # every device pointer travels as void*
+
+_raster_common = [c_int, c_int, c_int]  # P, D, M
+
+
+def _sig(name, restype, argtypes):
+    fn = getattr(lib, name)
+    fn.restype = restype
+    fn.argtypes = argtypes
+    return fn
+
+
+vcr_abi_version = _sig("vcr_abi_version", c_int, [])
+vcr_last_error = _sig("vcr_last_error", c_char_p, [])
+vcr_higher_msb = _sig("vcr_higher_msb", c_uint32, [c_uint32])
+vcr_geom_bytes = _sig("vcr_geom_bytes", c_size_t, [c_int])
+vcr_image_bytes = _sig("vcr_image_bytes", c_size_t, [c_int, c_int])
+vcr_binning_bytes = _sig("vcr_binning_bytes", c_size_t, [c_int])
+vcr_backward_scratch_bytes = _sig("vcr_backward_scratch_bytes", c_size_t, [c_int])
+vcr_knn_scratch_bytes = _sig("vcr_knn_scratch_bytes", c_size_t, [c_int])
+
+vcr_rasterize_forward = _sig(
+    "vcr_rasterize_forward", c_int,
+    [ALLOC_FN, ALLOC_FN, ALLOC_FN, c_void_p, c_int, c_int, c_int,
+     P_, c_int, c_int, P_, P_, P_, P_, P_, P_, P_, c_float, P_, P_, P_, P_, P_, P_,
+     c_float, c_float, c_int, P_, P_, P_, c_int, POINTER(c_int), c_void_p])
+
+vcr_rasterize_backward = _sig(
+    "vcr_rasterize_backward", c_int,
+    [c_int, c_int, c_int, c_int, P_, c_int, c_int, P_, P_, P_, P_, P_, P_, P_, P_, c_float, P_, P_, P_, P_, P_, P_,
+     c_float, c_float, P_, P_, P_, P_, P_,
+     P_, P_, P_, P_, P_, P_, P_, P_, P_, P_, P_, P_, P_, c_int, c_void_p])
+
+vcr_mark_visible = _sig("vcr_mark_visible", c_int, [c_int, P_, P_, P_, P_, c_void_p])
+
+vcr_rasterize_count = _sig(
+    "vcr_rasterize_count", c_int,
+    [ALLOC_FN, ALLOC_FN, ALLOC_FN, c_void_p, c_int, c_int, c_int, P_, c_int, c_int,
+     P_, P_, P_, P_, P_, c_float, P_, P_, P_, P_, P_, c_float, c_float, c_int,
+     P_, P_, P_, P_, c_int, POINTER(c_int), c_void_p])
+
+vcr_rasterize_visi_acc = _sig(
+    "vcr_rasterize_visi_acc", c_int,
+    [ALLOC_FN, ALLOC_FN, ALLOC_FN, c_void_p, c_int, c_int, c_int, c_int, c_int,
+     P_, P_, P_, P_, P_, c_float, P_, P_, P_, P_, P_, c_float, c_float, c_int,
+     P_, P_, c_int, POINTER(c_int), c_void_p])
+
+vcr_dnormal_forward = _sig(
+    "vcr_dnormal_forward", c_int,
+    [P_, P_, P_, P_, c_int, c_int, c_float, c_float, c_float, c_float, c_float, c_float, P_, P_, P_, c_int, c_void_p])
+vcr_dnormal_backward = _sig(
+    "vcr_dnormal_backward", c_int,
+    [P_, P_, P_, P_, c_int, c_int, c_float, c_float, c_float, c_float, c_float, c_float, P_, P_, P_, P_, c_void_p])
+vcr_dist2_knn3 = _sig("vcr_dist2_knn3", c_int, [c_int, P_, P_, P_, c_void_p])
+
+
+class GeomView(ctypes.Structure):
+    _fields_ = [(n, c_void_p) for n in ("depths", "clamped", "means2D", "xyz_view", "cov3D", "conic_opacity", "rgb",
+                                        "tiles_touched", "point_offsets")]
+
+
+class BinningView(ctypes.Structure):
+    _fields_ = [(n, c_void_p) for n in ("point_list", "point_list_keys", "point_list_unsorted", "point_list_keys_unsorted")]
+
+
+class ImageView(ctypes.Structure):
+    _fields_ = [(n, c_void_p) for n in ("accum_alpha", "n_contrib", "ranges")]
+
+
+vcr_geom_layout = _sig("vcr_geom_layout", None, [c_void_p, c_int, POINTER(GeomView)])
+vcr_binning_layout = _sig("vcr_binning_layout", None, [c_void_p, c_int, POINTER(BinningView)])
+vcr_image_layout = _sig("vcr_image_layout", None, [c_void_p, c_int, c_int, POINTER(ImageView)])
+
+# every symbol include/vcr_gaus_b200.h declares (tests check the library exports all of them)
+DECLARED_SYMBOLS = [
+    "vcr_abi_version", "vcr_last_error", "vcr_higher_msb", "vcr_geom_bytes", "vcr_image_bytes", "vcr_binning_bytes",
+    "vcr_rasterize_forward", "vcr_backward_scratch_bytes", "vcr_rasterize_backward", "vcr_mark_visible",
+    "vcr_rasterize_count", "vcr_rasterize_visi_acc", "vcr_dnormal_forward", "vcr_dnormal_backward",
+    "vcr_knn_scratch_bytes", "vcr_dist2_knn3", "vcr_geom_layout", "vcr_binning_layout", "vcr_image_layout",
+]
+
+
+def check(status, what):
+    if status != 0:
+        raise RuntimeError(f"{what}: {vcr_last_error().decode(errors='replace')}")
+
+
+def ptr(t):
+    """data_ptr of a tensor, or NULL for None / zero-sized tensors (the reference's convention for absent inputs)."""
+    if t is None or t.numel() == 0:
+        return None
+    return t.data_ptr()
