@@ -192,6 +192,16 @@ size_t vcr_knn_scratch_bytes(int P);
 int vcr_dist2_knn3(int P, const float* points /* f32[P,3] */, float* mean_dists /* f32[P] */,
                    char* scratch, void* stream);
 
+/* ---- measurement hooks (bench.py; no counterpart in the reference, which has no per-kernel timers — SURVEY.md §5) ----
+ * With profiling enabled every kernel launch of this library is bracketed by CUDA events on its own stream.
+ * vcr_profile_read sums the elapsed milliseconds and the number of timed launches per kernel id since the last reset
+ * (it synchronises on the recorded events) and reports the launch counters, which are kept even when profiling is off.
+ * Not thread-safe. */
+int vcr_profile_enable(int enable);
+int vcr_profile_kernel_count(void);
+const char* vcr_profile_kernel_name(int id);
+int vcr_profile_read(float* ms, long long* timed, long long* launches, int reset);
+
 /* ---- test/parity accessors: decode the opaque buffers (used by tests/, never by the product path) ---- */
 typedef struct vcr_geom_view {
     float* depths; uint8_t* clamped; float* means2D; float* xyz_view; float* cov3D;

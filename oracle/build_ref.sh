@@ -30,13 +30,20 @@ print(" ".join("-I" + i for i in inc))
 PY
 )
 TORCH_LIB=$($PY -c "import torch,os;print(os.path.join(os.path.dirname(torch.__file__),'lib'))")
-ARCH="-gencode arch=compute_100,code=sm_100"
+# Device code of the rasterizer is embedded as compute_90 PTX and JIT-compiled for sm_100 by the driver at load time.
+# Reason (DESIGN.md "Reference build"): with nvcc 12.9 and a compute_100 target the NVVM front end deletes the
+# SH->RGB block (and, with some flag sets, everything after in_frustum()) of the reference's forward
+# preprocessCUDA<3> - the emitted PTX/SASS has no store to `rgb`/`clamped` at all, so the reference renders black
+# Gaussians over the background.  The same source compiled for compute_90 (or compute_86) keeps the code.  All other
+# kernels are equivalent between the two targets.  simple-knn is unaffected and is built natively for sm_100.
+ARCH_DGR="-gencode arch=compute_90,code=compute_90"
+ARCH_KNN="-gencode arch=compute_100,code=sm_100"
 COMMON="-O3 -std=c++17 --expt-relaxed-constexpr -Xcompiler -fPIC -include cstdint \
  -DTORCH_API_INCLUDE_EXTENSION_H -D_GLIBCXX_USE_CXX11_ABI=1 -w $TORCH_INC"
 mkdir -p "$OUT/diff_gaussian_rasterization" "$OUT/simple_knn" "$OUT/obj"
 
-build_one () { # name srcdir extra sources...
-  local name=$1 dir=$2 extra=$3; shift 3
+build_one () { # name srcdir arch extra sources...
+  local name=$1 dir=$2 ARCH=$3 extra=$4; shift 4
   local objs=()
   for s in "$@"; do
     local o="$OUT/obj/${name}_$(basename "${s%.*}").o"
@@ -50,8 +57,8 @@ build_one () { # name srcdir extra sources...
        -Xlinker -rpath -Xlinker "$TORCH_LIB"
 }
 
-build_one diff_gaussian_rasterization "$DGR" "-I$DGR/third_party/glm" \
+build_one diff_gaussian_rasterization "$DGR" "$ARCH_DGR" "-I$DGR/third_party/glm" \
   cuda_rasterizer/rasterizer_impl.cu cuda_rasterizer/forward.cu cuda_rasterizer/backward.cu rasterize_points.cu ext.cpp
-build_one simple_knn "$KNN" "" spatial.cu simple_knn.cu ext.cpp
+build_one simple_knn "$KNN" "$ARCH_KNN" "" spatial.cu simple_knn.cu ext.cpp
 rm -rf "$OUT/obj"
 echo "built: $(ls "$OUT"/*/_C.so)"

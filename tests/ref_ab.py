@@ -25,7 +25,7 @@ def load(name="diff_gaussian_rasterization"):
     mod = None
     if os.path.exists(path):
         try:
-            spec = importlib.util.spec_from_file_location("_C", path)
+            spec = importlib.util.spec_from_file_location(f"vcr_ref_{name}._C", path)  # PyInit__C; distinct cache key per module
             mod = importlib.util.module_from_spec(spec)
             spec.loader.exec_module(mod)
         except Exception as ex:  # pragma: no cover

@@ -1,0 +1,96 @@
+"""World-size-2 gloo tests (CPU) of the view-parallel layer: gradient bucket all-reduce and densification statistics.
+
+The check is the property the layer promises: after the exchange every rank holds exactly what ONE
+process would have accumulated by running the `world` views one after the other, the way the reference trainer does
+(trainer.py:339-347, scene/gaussian_model.py:669-671)."""
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PKG = os.path.join(ROOT, "vcr-gaus_b200")
+
+
+def _fake_view_grads(P, view):
+    g = torch.Generator().manual_seed(100 + view)
+    grads = {"means3D": torch.randn((P, 3), generator=g), "shs": torch.randn((P, 16, 3), generator=g),
+             "opacities": torch.randn((P, 1), generator=g), "scales": torch.randn((P, 3), generator=g),
+             "rotations": torch.randn((P, 4), generator=g)}
+    radii = torch.randint(0, 40, (P,), generator=g, dtype=torch.int32) * (torch.rand(P, generator=g) > 0.3)
+    g2d = torch.randn((P, 3), generator=g).abs()
+    return grads, radii.to(torch.int32), g2d
+
+
+def _worker(rank, world, port, P, out_dir):
+    sys.path.insert(0, PKG)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank))
+    import vcr_view_parallel as VP
+    r, w, _ = VP.init_from_env(backend="gloo")
+    assert (r, w) == (rank, world)
+    vp = VP.ViewParallel()
+    tensors = {"means3D": torch.zeros((P, 3)), "shs": torch.zeros((P, 16, 3)), "opacities": torch.zeros((P, 1)),
+               "scales": torch.ones((P, 3)), "rotations": torch.zeros((P, 4))}
+    if rank == 1:  # replicas start different on purpose; broadcast must fix that
+        tensors["means3D"] += 5.0
+    bucket = VP.GaussianBucket(tensors)
+    vp.broadcast_parameters(bucket, src=0)
+    assert bucket.floats_per_gaussian == 59
+    accum, denom, max_r = torch.zeros((P, 1)), torch.zeros((P, 1)), torch.zeros(P)
+    for step in range(2):
+        view = vp.view_for_step(step, n_views=8, seed=1)
+        grads, radii, g2d = _fake_view_grads(P, view)
+        bucket.zero_grad()
+        loss = sum((bucket.params[k] * grads[k]).sum() for k in grads)  # d loss / d param = grads[k]
+        loss.backward()
+        vp.allreduce_gradients(bucket, average=False)
+        vp.reduce_densification_stats(accum, denom, max_r, g2d, radii)
+        torch.save({"view": view, "grad": bucket.grad_flat.clone(), "accum": accum.clone(), "denom": denom.clone(),
+                    "max_r": max_r.clone(), "flat": bucket.flat.clone()}, os.path.join(out_dir, f"r{rank}_s{step}.pt"))
+    dist.destroy_process_group()
+
+
+def test_world2_gloo_matches_sequential(tmp_path):
+    P, world = 257, 2
+    port = 29500 + (os.getpid() % 2000)
+    mp.spawn(_worker, args=(world, port, P, str(tmp_path)), nprocs=world, join=True)
+    accum, denom, max_r = torch.zeros((P, 1)), torch.zeros((P, 1)), torch.zeros(P)
+    seen = set()
+    for step in range(2):
+        r0 = torch.load(tmp_path / f"r0_s{step}.pt")
+        r1 = torch.load(tmp_path / f"r1_s{step}.pt")
+        assert r0["view"] != r1["view"], "ranks must render different views"
+        seen |= {r0["view"], r1["view"]}
+        assert torch.equal(r0["flat"], r1["flat"]), "replicas differ after broadcast"
+        # sequential reference: the same two views on one process
+        total = None
+        for v in (r0["view"], r1["view"]):
+            grads, radii, g2d = _fake_view_grads(P, v)
+            flat = torch.cat([grads[k].reshape(-1) for k in ("means3D", "shs", "opacities", "scales", "rotations")])
+            total = flat if total is None else total + flat
+            vis = radii > 0
+            accum[vis] += torch.norm(g2d[vis, :2], dim=-1, keepdim=True)   # add_densification_stats
+            denom[vis] += 1
+            max_r[vis] = torch.max(max_r[vis], radii[vis].float())          # trainer.py:345
+        for r in (r0, r1):
+            torch.testing.assert_close(r["grad"], total, rtol=1e-6, atol=1e-6)
+            torch.testing.assert_close(r["accum"], accum, rtol=1e-6, atol=1e-6)
+            assert torch.equal(r["denom"], denom) and torch.equal(r["max_r"], max_r)
+    assert len(seen) == 4, "two steps x two ranks must cover four distinct views of the epoch"
+
+
+def test_single_process_is_a_no_op():
+    sys.path.insert(0, PKG)
+    import vcr_view_parallel as VP
+    vp = VP.ViewParallel()
+    assert vp.world == 1 and vp.rank == 0
+    t = {"means3D": torch.randn((5, 3)), "shs": torch.randn((5, 16, 3)), "opacities": torch.rand((5, 1)),
+         "scales": torch.rand((5, 3)), "rotations": torch.randn((5, 4))}
+    b = VP.GaussianBucket(t)
+    (b.params["means3D"].sum() * 2 + b.params["shs"].sum()).backward()
+    assert torch.equal(b.grad_flat[:15], torch.full((15,), 2.0)) and torch.equal(b.grad_flat[15:15 + 240], torch.ones(240))
+    assert vp.allreduce_gradients(b) is None
+    views = [vp.view_for_step(s, 6, seed=0) for s in range(6)]
+    assert sorted(views) == list(range(6))

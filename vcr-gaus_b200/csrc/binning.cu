@@ -58,6 +58,7 @@ __global__ void __launch_bounds__(1024) scan_block_sums_kernel(uint32_t* __restr
 
 int vcr_launch_scan_block_sums(int P, GeomState& g, cudaStream_t s) {
     const int nb = (P + 255) / 256;
+    VcrProfScope prof(VCR_K_SCAN, s);
     scan_block_sums_kernel<<<1, 1024, 0, s>>>(g.block_sums, nb, g.num_rendered);
     VCR_LAUNCH_CHECK("scan_block_sums_kernel");
     return 0;
@@ -304,7 +305,8 @@ __global__ void __launch_bounds__(RADIX_THREADS) radix_pass_kernel(const uint64_
 int vcr_launch_offsets_and_duplicate(const FwdParams& p, GeomState& g, BinningState& b, int R, int npass, int key_bits,
                                      cudaStream_t s) {
     (void)R;
-    VCR_CUDA_TRY(cudaMemsetAsync(b.sort_hist, 0, VCR_MAX_PASSES * 256 * sizeof(uint32_t), s));
+    { VcrProfScope m(VCR_K_MEMSET, s); VCR_CUDA_TRY(cudaMemsetAsync(b.sort_hist, 0, VCR_MAX_PASSES * 256 * sizeof(uint32_t), s)); }
+    VcrProfScope prof(VCR_K_DUPLICATE, s);
     duplicate_kernel<<<(p.P + 255) / 256, 256, 0, s>>>(p.P, p.gx, p.gy, p.radii, g, b.point_list_keys_unsorted,
                                                        b.point_list_unsorted, b.sort_hist, npass, key_bits);
     VCR_LAUNCH_CHECK("duplicate_kernel");
@@ -319,11 +321,11 @@ int vcr_launch_radix_sort(BinningState& b, int R, int key_bits, cudaStream_t s) 
     }
     const int npass = (key_bits + 7) / 8;
     const uint32_t nblocks = ((uint32_t)R + RADIX_TILE - 1) / RADIX_TILE;
-    radix_scan_hist_kernel<<<npass, 256, 0, s>>>(b.sort_hist);
+    { VcrProfScope prof(VCR_K_RADIX_HIST, s); radix_scan_hist_kernel<<<npass, 256, 0, s>>>(b.sort_hist); }
     VCR_LAUNCH_CHECK("radix_scan_hist_kernel");
     // status words for all passes + one ticket per pass + error flag, zeroed in one memset
     const size_t words = (size_t)npass * nblocks * 256 + 16;
-    VCR_CUDA_TRY(cudaMemsetAsync(b.sort_status, 0, words * sizeof(uint32_t), s));
+    { VcrProfScope m(VCR_K_MEMSET, s); VCR_CUDA_TRY(cudaMemsetAsync(b.sort_status, 0, words * sizeof(uint32_t), s)); }
     uint32_t* tickets = b.sort_status + (size_t)npass * nblocks * 256;
     const uint64_t* kin = b.point_list_keys_unsorted;
     const uint32_t* vin = b.point_list_unsorted;
@@ -332,6 +334,7 @@ int vcr_launch_radix_sort(BinningState& b, int R, int key_bits, cudaStream_t s) 
         uint64_t* kout = to_final ? b.point_list_keys : b.alt_keys;
         uint32_t* vout = to_final ? b.point_list : b.alt_vals;
         const int nbits = key_bits - 8 * pass < 8 ? key_bits - 8 * pass : 8;
+        VcrProfScope prof(VCR_K_RADIX_PASS, s);
         radix_pass_kernel<<<nblocks, RADIX_THREADS, RADIX_SMEM_BYTES, s>>>(
             kin, vin, kout, vout, (uint32_t)R, 8 * pass, nbits, b.sort_hist + pass * 256,
             b.sort_status + (size_t)pass * nblocks * 256, tickets + pass, tickets + 15);
@@ -357,8 +360,9 @@ __global__ void __launch_bounds__(256) tile_ranges_kernel(uint32_t L, const uint
 }
 
 int vcr_launch_tile_ranges(BinningState& b, ImageState& img, int R, int tiles, cudaStream_t s) {
-    VCR_CUDA_TRY(cudaMemsetAsync(img.ranges, 0, (size_t)tiles * sizeof(uint2), s));
+    { VcrProfScope m(VCR_K_MEMSET, s); VCR_CUDA_TRY(cudaMemsetAsync(img.ranges, 0, (size_t)tiles * sizeof(uint2), s)); }
     if (R > 0) {
+        VcrProfScope prof(VCR_K_TILE_RANGES, s);
         tile_ranges_kernel<<<((uint32_t)R + 255u) / 256u, 256, 0, s>>>((uint32_t)R, b.point_list_keys, img.ranges);
         VCR_LAUNCH_CHECK("tile_ranges_kernel");
     }

@@ -18,6 +18,32 @@ void vcr_set_error(const char* fmt, ...) {
     va_end(ap);
 }
 
+// ---------------- per-kernel profiling (not thread-safe; meant for bench.py) ----------------
+#include <vector>
+struct ProfRec { int id; cudaEvent_t a, b; };
+static bool g_prof_on = false;
+static std::vector<ProfRec> g_prof_recs;
+static std::vector<cudaEvent_t> g_prof_pool;
+static long long g_launches[VCR_K_COUNT] = {0};
+static const char* kKernelNames[VCR_K_COUNT] = {
+    "preprocess_kernel", "scan_block_sums_kernel", "duplicate_kernel", "radix_scan_hist_kernel", "radix_pass_kernel",
+    "tile_ranges_kernel", "render_forward_kernel", "render_backward_kernel", "preprocess_backward_kernel",
+    "dnormal_forward_kernel", "dnormal_backward_kernel", "render_aux_kernel", "knn_kernels", "mark_visible_kernel", "memset"};
+static cudaEvent_t prof_event() {
+    if (!g_prof_pool.empty()) { cudaEvent_t e = g_prof_pool.back(); g_prof_pool.pop_back(); return e; }
+    cudaEvent_t e; cudaEventCreate(&e); return e;
+}
+VcrProfScope::VcrProfScope(int id_, cudaStream_t s_, int launches) : id(id_), s(s_), slot(-1) {
+    g_launches[id] += launches;
+    if (g_prof_on) {
+        ProfRec r{id, prof_event(), prof_event()};
+        cudaEventRecord(r.a, s);
+        slot = (int)g_prof_recs.size();
+        g_prof_recs.push_back(r);
+    }
+}
+VcrProfScope::~VcrProfScope() { if (slot >= 0) cudaEventRecord(g_prof_recs[slot].b, s); }
+
 // ---------------- layouts ----------------
 template <typename T>
 static inline void carve_one(char*& p, T*& out, size_t count) {
@@ -286,6 +312,26 @@ int vcr_rasterize_visi_acc(vcr_alloc_fn geometry_buffer, vcr_alloc_fn binning_bu
                        means3D, shs, colors_precomp, opacities, scales, scale_modifier, rotations, cov3D_precomp, viewmatrix,
                        projmatrix, cam_pos, tan_fovx, tan_fovy, prefiltered, nullptr, gaussians_count, nullptr, radii, debug,
                        num_rendered_host, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int vcr_profile_enable(int enable) { g_prof_on = enable != 0; return 0; }
+int vcr_profile_kernel_count(void) { return VCR_K_COUNT; }
+const char* vcr_profile_kernel_name(int id) { return (id >= 0 && id < VCR_K_COUNT) ? kKernelNames[id] : ""; }
+int vcr_profile_read(float* ms, long long* timed, long long* launches, int reset) {
+    for (int k = 0; k < VCR_K_COUNT; k++) { if (ms) ms[k] = 0.f; if (timed) timed[k] = 0; if (launches) launches[k] = g_launches[k]; }
+    for (ProfRec& r : g_prof_recs) {
+        VCR_CUDA_TRY(cudaEventSynchronize(r.b));
+        float t = 0.f;
+        VCR_CUDA_TRY(cudaEventElapsedTime(&t, r.a, r.b));
+        if (ms) ms[r.id] += t;
+        if (timed) timed[r.id] += 1;
+    }
+    if (reset) {
+        for (ProfRec& r : g_prof_recs) { g_prof_pool.push_back(r.a); g_prof_pool.push_back(r.b); }
+        g_prof_recs.clear();
+        for (int k = 0; k < VCR_K_COUNT; k++) g_launches[k] = 0;
+    }
+    return 0;
 }
 
 void vcr_geom_layout(char* chunk, int P, vcr_geom_view* out) {

@@ -170,6 +170,7 @@ int vcr_dnormal_forward(const float* depth, const float* gt_normal, const float*
     DnParams p{depth, gt_normal, render_normal, mask, width, height, 1.0f / fx, 1.0f / fy, cx, cy, exp_t, mask_depth_max};
     if (zero_sums) VCR_CUDA_TRY(cudaMemsetAsync(sums, 0, 3 * sizeof(float), s));
     const dim3 grid((width + 31) / 32, (height + 7) / 8);
+    VcrProfScope prof(VCR_K_DNORMAL_FWD, s);
     dnormal_forward_kernel<<<grid, 256, 0, s>>>(p, est_normal, weight, sums);
     VCR_LAUNCH_CHECK("dnormal_forward_kernel");
     return 0;
@@ -183,6 +184,7 @@ int vcr_dnormal_backward(const float* depth, const float* gt_normal, const float
     if (exp_t > 0.f && !render_normal) { vcr_set_error("dnormal_backward: render_normal is required when exp_t > 0"); return 1; }
     DnParams p{depth, gt_normal, render_normal, mask, width, height, 1.0f / fx, 1.0f / fy, cx, cy, exp_t, mask_depth_max};
     const dim3 grid((width + 31) / 32, (height + 7) / 8);
+    VcrProfScope prof(VCR_K_DNORMAL_BWD, s);
     dnormal_backward_kernel<<<grid, 256, 0, s>>>(p, sums, dL_dloss, dL_dest_normal, dL_ddepth);
     VCR_LAUNCH_CHECK("dnormal_backward_kernel");
     return 0;

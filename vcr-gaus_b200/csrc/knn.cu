@@ -195,6 +195,7 @@ extern "C" int vcr_dist2_knn3(int P, const float* points, float* mean_dists, cha
     const int nboxes = (P + KNN_BOX - 1) / KNN_BOX;
     const int blocks = (P + 255) / 256;
 
+    VcrProfScope prof(VCR_K_KNN, s, 5);
     knn_bounds_init_kernel<<<1, 32, 0, s>>>(bounds);
     VCR_LAUNCH_CHECK("knn_bounds_init_kernel");
     knn_bounds_kernel<<<min(blocks, 148 * 8), 256, 0, s>>>(P, points, bounds);

@@ -263,13 +263,15 @@ __global__ void __launch_bounds__(256) mark_visible_kernel(int P, const float* _
 
 int vcr_launch_preprocess(const FwdParams& p, GeomState& g, cudaStream_t s) {
     const int blocks = (p.P + 255) / 256;
-    VCR_CUDA_TRY(cudaMemsetAsync(g.num_rendered, 0, 4 * sizeof(uint32_t), s));
+    { VcrProfScope m(VCR_K_MEMSET, s); VCR_CUDA_TRY(cudaMemsetAsync(g.num_rendered, 0, 4 * sizeof(uint32_t), s)); }
+    VcrProfScope prof(VCR_K_PREPROCESS, s);
     preprocess_kernel<<<blocks, 256, 0, s>>>(p, g);
     VCR_LAUNCH_CHECK("preprocess_kernel");
     return 0;
 }
 
 int vcr_launch_mark_visible(int P, const float* means3D, const float* viewmatrix, uint8_t* present, cudaStream_t s) {
+    VcrProfScope prof(VCR_K_MARK_VISIBLE, s);
     mark_visible_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, means3D, viewmatrix, present);
     VCR_LAUNCH_CHECK("mark_visible_kernel");
     return 0;

@@ -258,6 +258,7 @@ __global__ void __launch_bounds__(256) preprocess_backward_kernel(const BwdParam
 }
 
 int vcr_launch_preprocess_backward(const BwdParams& p, GeomState& g, cudaStream_t s) {
+    VcrProfScope prof(VCR_K_PREPROCESS_BWD, s);
     preprocess_backward_kernel<<<(p.P + 255) / 256, 256, 0, s>>>(p, g);
     VCR_LAUNCH_CHECK("preprocess_backward_kernel");
     return 0;

@@ -273,7 +273,8 @@ __global__ void __launch_bounds__(256) render_backward_kernel(
 }
 
 int vcr_launch_render_backward(const BwdParams& p, GeomState& g, BinningState& b, ImageState& img, cudaStream_t s) {
-    VCR_CUDA_TRY(cudaMemsetAsync(p.acc, 0, (size_t)p.P * VCR_ACC_STRIDE * sizeof(float), s));
+    { VcrProfScope m(VCR_K_MEMSET, s); VCR_CUDA_TRY(cudaMemsetAsync(p.acc, 0, (size_t)p.P * VCR_ACC_STRIDE * sizeof(float), s)); }
+    VcrProfScope prof(VCR_K_RENDER_BWD, s);
     const dim3 grid(p.gx, p.gy, 1);
     const float* col = p.colors_precomp ? p.colors_precomp : g.rgb;
 #define RB_ARGS img.ranges, b.point_list, p.W, p.H, p.background, g.means2D, g.xyz_view, g.conic_opacity, col, g.depths, \

@@ -171,6 +171,7 @@ __global__ void __launch_bounds__(256) render_forward_kernel(
 int vcr_launch_render_forward(const FwdParams& p, GeomState& g, BinningState& b, ImageState& img, cudaStream_t s) {
     const dim3 grid(p.gx, p.gy, 1);
     const float* feat = p.colors_precomp ? p.colors_precomp : g.rgb;
+    VcrProfScope prof(VCR_K_RENDER_FWD, s);
 #define RF_ARGS img.ranges, b.point_list, p.W, p.H, g.means2D, g.xyz_view, feat, g.depths, p.normals, p.sh_objs, p.dirs, \
                 g.conic_opacity, p.inside, p.background, img.accum_alpha, img.n_contrib, p.out_color, nullptr, nullptr
     if (p.dirs) {
@@ -189,6 +190,7 @@ int vcr_launch_render_aux(int mode, const FwdParams& p, GeomState& g, BinningSta
                           int* gaussians_count, float* important_score, cudaStream_t s) {
     const dim3 grid(p.gx, p.gy, 1);
     const float* feat = p.colors_precomp ? p.colors_precomp : g.rgb;
+    VcrProfScope prof(VCR_K_RENDER_AUX, s);
 #define RA_ARGS img.ranges, b.point_list, p.W, p.H, g.means2D, g.xyz_view, feat, g.depths, nullptr, nullptr, nullptr, \
                 g.conic_opacity, nullptr, p.background, img.accum_alpha, img.n_contrib, p.out_color, gaussians_count, important_score
     if (mode == VCR_MODE_COUNT) render_forward_kernel<VCR_MODE_COUNT, false, false><<<grid, 256, 0, s>>>(RA_ARGS);

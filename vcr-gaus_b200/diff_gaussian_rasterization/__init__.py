@@ -17,6 +17,7 @@ import torch.nn as nn
 
 import vcr_native as _n
 
+_LAST_NUM_RENDERED = 0
 NUM_CHANNELS = 3
 NUM_OBJECTS = 2
 OUTPUT_CHANNELS = 3 + 1 + 3 + 1 + NUM_OBJECTS  # DGR/cuda_rasterizer/auxiliary.h:28 with NUM_DIST = NUM_DEPTH2 = 0
@@ -137,6 +138,8 @@ class _RasterizeGaussians(torch.autograd.Function):
             else:
                 _n.check(_n.vcr_rasterize_forward(*args), "rasterize_gaussians")
             num_rendered = n_host.value
+            global _LAST_NUM_RENDERED
+            _LAST_NUM_RENDERED = num_rendered  # bench.py reads this to report R
         geomBuffer, binningBuffer, imgBuffer = bufs.get("geom"), bufs.get("binning"), bufs.get("img")
         ctx.raster_settings = rs
         ctx.num_rendered = num_rendered

@@ -75,6 +75,22 @@ vcr_dnormal_backward = _sig(
 vcr_dist2_knn3 = _sig("vcr_dist2_knn3", c_int, [c_int, P_, P_, P_, c_void_p])
 
 
+vcr_profile_enable = _sig("vcr_profile_enable", c_int, [c_int])
+vcr_profile_kernel_count = _sig("vcr_profile_kernel_count", c_int, [])
+vcr_profile_kernel_name = _sig("vcr_profile_kernel_name", c_char_p, [c_int])
+vcr_profile_read = _sig("vcr_profile_read", c_int, [POINTER(c_float), POINTER(ctypes.c_longlong), POINTER(ctypes.c_longlong), c_int])
+
+
+def profile_read(reset=True):
+    """{kernel name: (total ms over timed launches, timed launches, launches)} since the last reset."""
+    n = vcr_profile_kernel_count()
+    ms = (c_float * n)()
+    timed = (ctypes.c_longlong * n)()
+    launches = (ctypes.c_longlong * n)()
+    check(vcr_profile_read(ms, timed, launches, int(reset)), "profile_read")
+    return {vcr_profile_kernel_name(i).decode(): (float(ms[i]), int(timed[i]), int(launches[i])) for i in range(n)}
+
+
 class GeomView(ctypes.Structure):
     _fields_ = [(n, c_void_p) for n in ("depths", "clamped", "means2D", "xyz_view", "cov3D", "conic_opacity", "rgb",
                                         "tiles_touched", "point_offsets")]
@@ -98,6 +114,7 @@ DECLARED_SYMBOLS = [
     "vcr_rasterize_forward", "vcr_backward_scratch_bytes", "vcr_rasterize_backward", "vcr_mark_visible",
     "vcr_rasterize_count", "vcr_rasterize_visi_acc", "vcr_dnormal_forward", "vcr_dnormal_backward",
     "vcr_knn_scratch_bytes", "vcr_dist2_knn3", "vcr_geom_layout", "vcr_binning_layout", "vcr_image_layout",
+    "vcr_profile_enable", "vcr_profile_kernel_count", "vcr_profile_kernel_name", "vcr_profile_read",
 ]
 
 
