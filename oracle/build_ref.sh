@@ -30,13 +30,14 @@ print(" ".join("-I" + i for i in inc))
 PY
 )
 TORCH_LIB=$($PY -c "import torch,os;print(os.path.join(os.path.dirname(torch.__file__),'lib'))")
-# Device code of the rasterizer is embedded as compute_90 PTX and JIT-compiled for sm_100 by the driver at load time.
-# Reason (DESIGN.md "Reference build"): with nvcc 12.9 and a compute_100 target the NVVM front end deletes the
-# SH->RGB block (and, with some flag sets, everything after in_frustum()) of the reference's forward
-# preprocessCUDA<3> - the emitted PTX/SASS has no store to `rgb`/`clamped` at all, so the reference renders black
-# Gaussians over the background.  The same source compiled for compute_90 (or compute_86) keeps the code.  All other
-# kernels are equivalent between the two targets.  simple-knn is unaffected and is built natively for sm_100.
-ARCH_DGR="-gencode arch=compute_90,code=compute_90"
+# Toolchain note (DESIGN.md "Reference build"): the GLM 1.0.2 vendored by the reference declares the TMin/TMax
+# functors in glm/detail/func_common.inl WITHOUT __host__ __device__ qualifiers.  glm::max(vec3, float) - the clamp at the
+# end of the reference's computeColorFromSH (forward.cu:72) - therefore calls a host-only function from device code;
+# nvcc 12.9 (the only toolchain in this image) treats that as unreachable and silently deletes the three `rgb[...]`
+# stores (and for compute_100 also the `clamped` stores), i.e. the reference renders black Gaussians.  The build
+# compiles against a TEMPORARY copy of the GLM headers (inside the git-ignored build directory, deleted afterwards) in
+# which those two functors get GLM_FUNC_QUALIFIER.  No file of the reference rasterizer itself is changed.
+ARCH_DGR="-gencode arch=compute_100,code=sm_100"
 ARCH_KNN="-gencode arch=compute_100,code=sm_100"
 COMMON="-O3 -std=c++17 --expt-relaxed-constexpr -Xcompiler -fPIC -include cstdint \
  -DTORCH_API_INCLUDE_EXTENSION_H -D_GLIBCXX_USE_CXX11_ABI=1 -w $TORCH_INC"
@@ -57,7 +58,11 @@ build_one () { # name srcdir arch extra sources...
        -Xlinker -rpath -Xlinker "$TORCH_LIB"
 }
 
-build_one diff_gaussian_rasterization "$DGR" "$ARCH_DGR" "-I$DGR/third_party/glm" \
+GLMFIX="$OUT/obj/glm_qualified"
+rm -rf "$GLMFIX" && cp -r "$DGR/third_party/glm" "$GLMFIX"
+sed -i 's/^\(\s*\)T operator()(const T& a, const T& b) { return \(min\|max\)(a, b); }/\1GLM_FUNC_QUALIFIER T operator()(const T\& a, const T\& b) { return \2(a, b); }/' "$GLMFIX/glm/detail/func_common.inl"
+grep -c "GLM_FUNC_QUALIFIER T operator()" "$GLMFIX/glm/detail/func_common.inl" | grep -q 2 || { echo "GLM qualifier shim did not apply" >&2; exit 1; }
+build_one diff_gaussian_rasterization "$DGR" "$ARCH_DGR" "-I$GLMFIX" \
   cuda_rasterizer/rasterizer_impl.cu cuda_rasterizer/forward.cu cuda_rasterizer/backward.cu rasterize_points.cu ext.cpp
 build_one simple_knn "$KNN" "$ARCH_KNN" "" spatial.cu simple_knn.cu ext.cpp
 rm -rf "$OUT/obj"

@@ -61,25 +61,31 @@ def test_dnormal_vs_oracle_and_reference_chain(W, H, exp_t, thr):
     loss.backward()
     torch.cuda.synchronize()
     K4 = (float(K[0, 0]), float(K[1, 1]), float(K[0, 2]), float(K[1, 2]))
-    small = W * H <= 200000
-    if small:
-        o = O.dnormal(depth.numpy(), gt.numpy(), rn.numpy(), mask.numpy(), K4, exp_t=exp_t, mask_depth_max=thr)
-        np.testing.assert_allclose(est.detach().cpu().numpy(), o["est_normal"], atol=2e-4)
-        assert abs(float(loss) - o["loss"]) <= 1e-5 * max(1.0, abs(o["loss"]))
-        assert rel_l2(d.grad.cpu().numpy()[0], o["dL_ddepth"]) <= 1e-3
-    # the reference chain on the GPU, same inputs
+    # 1) against the double-precision CPU oracle (the exact value of the reference formulas)
+    o = O.dnormal(depth.numpy(), gt.numpy(), rn.numpy(), mask.numpy(), K4, exp_t=exp_t, mask_depth_max=thr)
+    np.testing.assert_allclose(est.detach().cpu().numpy(), o["est_normal"], atol=2e-4)
+    assert abs(float(loss.detach()) - o["loss"]) <= 1e-5 * max(1.0, abs(o["loss"]))
+    e_mine = rel_l2(d.grad.cpu().numpy()[0], o["dL_ddepth"])
+    assert e_mine <= 1e-3, f"dL/ddepth vs oracle: {e_mine}"
+    # 2) against the reference op chain in float32 on the GPU, same inputs.  That chain differences float32 camera
+    #    coordinates (X(u+1) - X(u-1) with |X| ~ 1 and a difference ~ 1/fx), so ITS gradient carries relative noise
+    #    ~1e-7 * fx which grows with the image size; its own distance to the exact value is asserted alongside.
     d2 = depth.to(dev).requires_grad_(True)
     m = mask.to(dev)
     if thr > 0:
         m = m & (d2[0].detach() < thr)
     l2, est2 = ref_chain(d2, K.to(dev), gt.to(dev), rn.to(dev), m, exp_t)
     l2.backward()
-    assert abs(float(loss) - float(l2)) <= 1e-5 * max(1.0, abs(float(l2)))
-    np.testing.assert_allclose(est.detach().cpu().numpy(), est2.detach().cpu().numpy(), atol=5e-4)
-    assert rel_l2(d.grad.cpu().numpy(), d2.grad.cpu().numpy()) <= 1e-3
+    assert abs(float(loss.detach()) - float(l2.detach())) <= 1e-5 * max(1.0, abs(float(l2.detach())))
+    np.testing.assert_allclose(est.detach().cpu().numpy(), est2.detach().cpu().numpy(), atol=5e-4 if W < 1000 else 5e-3)
+    e_chain = rel_l2(d2.grad.cpu().numpy()[0], o["dL_ddepth"])
+    e_pair = rel_l2(d.grad.cpu().numpy(), d2.grad.cpu().numpy())
+    print(f"dL/ddepth rel-L2: ours vs exact {e_mine:.2e}, reference chain vs exact {e_chain:.2e}, ours vs chain {e_pair:.2e}")
+    assert e_mine <= e_chain + 1e-6 or e_mine <= 1e-4
+    assert e_pair <= max(1e-3, 2.0 * e_chain)
     # compute_normals drop-in
     e3 = compute_normals(depth.to(dev), K)
-    np.testing.assert_allclose(e3.cpu().numpy(), est2.detach().cpu().numpy(), atol=5e-4)
+    np.testing.assert_allclose(e3.cpu().numpy(), o["est_normal"], atol=2e-4)
 
 
 def test_dnormal_empty_mask():

@@ -23,24 +23,28 @@ struct DnParams {
     float inv_fx, inv_fy, cx, cy, exp_t, mask_depth_max;
 };
 
-__device__ __forceinline__ float3 dn_point(const DnParams& p, int u, int v) {
-    const float z = __ldg(p.depth + (size_t)v * p.W + u);
-    return make_float3(((u + 0.5f) - p.cx) * p.inv_fx * z, ((v + 0.5f) - p.cy) * p.inv_fy * z, z);
-}
 // torch.gradient (spacing 1, edge_order 1): central differences inside, one-sided at the borders.
+// X(u,v) = (a(u) z, b(v) z, z) with a(u) = (u + .5 - cx)/fx, so along u
+//   X(u1) - X(u0) = (a(u0) dz + (u1-u0)/fx z1,  b dz,  dz),  dz = z1 - z0,
+// which avoids the cancellation of subtracting two O(1) coordinates that differ by O(1/fx) (the reference chain
+// differences the float32 coordinates themselves; both agree with the exact value, this form just carries less noise).
 __device__ __forceinline__ float3 dn_diff_u(const DnParams& p, int u, int v) {
     if (p.W == 1) return make_float3(0.f, 0.f, 0.f);
     const int u0 = max(u - 1, 0), u1 = min(u + 1, p.W - 1);
     const float s = (u1 - u0 == 2) ? 0.5f : 1.0f;
-    const float3 a = dn_point(p, u0, v), b = dn_point(p, u1, v);
-    return make_float3((b.x - a.x) * s, (b.y - a.y) * s, (b.z - a.z) * s);
+    const float z0 = __ldg(p.depth + (size_t)v * p.W + u0), z1 = __ldg(p.depth + (size_t)v * p.W + u1);
+    const float dz = z1 - z0;
+    const float a0 = ((u0 + 0.5f) - p.cx) * p.inv_fx, b = ((v + 0.5f) - p.cy) * p.inv_fy;
+    return make_float3((a0 * dz + (float)(u1 - u0) * p.inv_fx * z1) * s, b * dz * s, dz * s);
 }
 __device__ __forceinline__ float3 dn_diff_v(const DnParams& p, int u, int v) {
     if (p.H == 1) return make_float3(0.f, 0.f, 0.f);
     const int v0 = max(v - 1, 0), v1 = min(v + 1, p.H - 1);
     const float s = (v1 - v0 == 2) ? 0.5f : 1.0f;
-    const float3 a = dn_point(p, u, v0), b = dn_point(p, u, v1);
-    return make_float3((b.x - a.x) * s, (b.y - a.y) * s, (b.z - a.z) * s);
+    const float z0 = __ldg(p.depth + (size_t)v0 * p.W + u), z1 = __ldg(p.depth + (size_t)v1 * p.W + u);
+    const float dz = z1 - z0;
+    const float a = ((u + 0.5f) - p.cx) * p.inv_fx, b0 = ((v0 + 0.5f) - p.cy) * p.inv_fy;
+    return make_float3(a * dz * s, (b0 * dz + (float)(v1 - v0) * p.inv_fy * z1) * s, dz * s);
 }
 __device__ __forceinline__ float3 cross3(const float3 a, const float3 b) {
     return make_float3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);

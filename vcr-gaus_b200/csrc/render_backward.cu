@@ -5,7 +5,10 @@
 // Same tiling as the forward (one 256-thread block per 16x16 tile, one pixel per thread), Gaussians
 // staged in shared memory in reverse list order.  Where the reference issues ~20 atomicAdd per
 // contributing (pixel, Gaussian) pair, this kernel
-//   1. skips a Gaussian for the whole warp when no lane contributes (__any_sync),
+//   0. drops, per block and per warp, the tail of the list behind the last contributor of any of its pixels, and
+//      culls (warp, Gaussian) pairs with a conservative footprint box against the warp's 16x2 pixel strip
+//      (8 ballots per 256 staged Gaussians); only candidates enter the per-pixel code,
+//   1. skips a candidate for the whole warp when no lane contributes (__any_sync),
 //   2. reduces the 16 main gradient components across the warp with a transposed butterfly
 //      (15 + 1 shuffles instead of 16 x 5), leaving component k on lane k, and
 //   3. lands them with ONE coalesced 64-byte atomic request per (warp, Gaussian) into a per-Gaussian
@@ -70,10 +73,12 @@ __global__ void __launch_bounds__(256) render_backward_kernel(
     const float* __restrict__ depth_img, const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
     const float* __restrict__ dL_dpixels, const uint8_t* __restrict__ inside_gs, float* __restrict__ acc) {
     __shared__ StagedGeoB s_geo[RB_BATCH];
+    __shared__ float4 s_box[RB_BATCH];
     __shared__ float4 s_nrm[RB_BATCH];
     __shared__ float4 s_col[RB_BATCH];
     __shared__ float4 s_xv[HAS_DIRS ? RB_BATCH : 1];
     __shared__ float2 s_obj[HAS_OBJ ? RB_BATCH : 1];
+    __shared__ uint32_t s_block_last;
 
     const int tid = threadIdx.x, lane = tid & 31;
     const int gx = gridDim.x;
@@ -83,17 +88,27 @@ __global__ void __launch_bounds__(256) render_backward_kernel(
     const size_t HW = (size_t)H * W;
     const size_t pix_id = (size_t)W * py + px;
     const float pfx = (float)px, pfy = (float)py;
+    const float strip_x0 = (float)(blockIdx.x * VCR_TILE_X), strip_x1 = strip_x0 + (float)(VCR_TILE_X - 1);
+    const float strip_y0 = (float)(blockIdx.y * VCR_TILE_Y + 2 * (tid >> 5)), strip_y1 = strip_y0 + 1.0f;
 
     const uint2 range = ranges[blockIdx.y * gx + blockIdx.x];
-    const int rounds = (int)((range.y - range.x + RB_BATCH - 1) / RB_BATCH);
-    int toDo = (int)(range.y - range.x);
+    const uint32_t last_contributor = inside ? n_contrib[pix_id] : 0u;
+    // Entries behind the last contributor of every pixel of the warp / block can never pass `contributor <
+    // last_contributor` (backward.cu:589-591): drop them without staging or evaluating them.
+    const uint32_t warp_last = __reduce_max_sync(0xffffffffu, last_contributor);
+    if (tid == 0) s_block_last = 0u;
+    __syncthreads();
+    if (lane == 0 && warp_last) atomicMax(&s_block_last, warp_last);
+    __syncthreads();
+    const uint32_t block_last = s_block_last;          // <= range.y - range.x
+    const uint32_t list_end = range.x + block_last;    // effective list: [range.x, list_end)
+    const int rounds = (int)((block_last + RB_BATCH - 1) / RB_BATCH);
+    int toDo = (int)block_last;
 
     const float T_final = inside ? final_Ts[pix_id] : 0.f;
     float T = T_final;
     const float inv_weight = inside ? 1.0f / alpha_img[pix_id] : 1.f;
     const float depth_final = inside ? depth_img[pix_id] : 1.f;
-    uint32_t contributor = (uint32_t)toDo;
-    const uint32_t last_contributor = inside ? n_contrib[pix_id] : 0u;
 
     float accum_rec[3] = {0.f, 0.f, 0.f}, dL_dpixel[3] = {0.f, 0.f, 0.f};
     float accum_depth_rec = 0.f, accum_rec2 = 0.f, dL_dpixel_depth = 0.f;
@@ -125,14 +140,15 @@ __global__ void __launch_bounds__(256) render_backward_kernel(
     for (int i = 0; i < rounds; i++, toDo -= RB_BATCH) {
         __syncthreads();
         const uint32_t progress = (uint32_t)i * RB_BATCH + tid;
-        if (range.x + progress < range.y) {
-            const uint32_t id = __ldg(point_list + (range.y - progress - 1));
+        if (range.x + progress < list_end) {
+            const uint32_t id = __ldg(point_list + (list_end - progress - 1));
             const float2 xy = __ldg(means2D + id);
             const float4 co = __ldg(conic_opacity + id);
             const float3 n = make_float3(__ldg(normals + 3 * (size_t)id), __ldg(normals + 3 * (size_t)id + 1),
                                          __ldg(normals + 3 * (size_t)id + 2));
             StagedGeoB sg;
             sg.x = xy.x; sg.y = xy.y; sg.ca = co.x; sg.cb = co.y; sg.cc = co.z; sg.op = co.w;
+            s_box[tid] = vcr_alpha_bbox(xy, co);
             if (HAS_DIRS) {
                 const float3 xv = make_float3(__ldg(xyz_view + 3 * (size_t)id), __ldg(xyz_view + 3 * (size_t)id + 1),
                                               __ldg(xyz_view + 3 * (size_t)id + 2));
@@ -151,122 +167,136 @@ __global__ void __launch_bounds__(256) render_backward_kernel(
         __syncthreads();
 
         const int cnt = min(RB_BATCH, toDo);
-        for (int j = 0; j < cnt; j++) {
-            contributor--;
-            const float4 g0 = *reinterpret_cast<const float4*>(&s_geo[j]);
-            const float4 g1 = *reinterpret_cast<const float4*>(&s_geo[j].cc);
-            const float dx = g0.x - pfx, dy = g0.y - pfy;
-            bool contrib = inside && contributor < last_contributor;
-            const float q = __fmaf_rn(__fmul_rn(g0.z, dx), dx, __fmul_rn(__fmul_rn(g1.x, dy), dy));
-            const float power = __fmaf_rn(q, -0.5f, -__fmul_rn(__fmul_rn(g0.w, dx), dy));
-            contrib = contrib && !(power > 0.0f);
-            const float G = expf(power);
-            const float alpha = fminf(0.99f, g1.y * G);
-            contrib = contrib && !(alpha < 1.0f / 255.0f);
-            const float4 nrm = s_nrm[j];
-            float c_d, pro_dot = 1.f;
-            if (HAS_DIRS) {
-                pro_dot = nrm.x * dir.x + nrm.y * dir.y + nrm.z * dir.z;
-                c_d = (g1.z / pro_dot) * dir.z;
-            } else {
-                c_d = g1.z;
-            }
-            contrib = contrib && !(c_d < 0.2f);  // == (double)c_d < 0.2, backward.cu:616
-            if (!__any_sync(0xffffffffu, contrib)) continue;
-
-            float v[16];
-#pragma unroll
-            for (int k = 0; k < 16; k++) v[k] = 0.f;
-            float ex_view_z = 0.f, ex_obj0 = 0.f, ex_obj1 = 0.f;
-            const uint32_t idi = __float_as_uint(g1.w);
-            if (contrib) {
-                T = T / (1.f - alpha);
-                const float aT = alpha * T;
-                float dL_dopa = 0.0f;
-                const float4 col = s_col[j];
-                const float cc[3] = {col.x, col.y, col.z};
-#pragma unroll
-                for (int ch = 0; ch < 3; ch++) {
-                    accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
-                    last_color[ch] = cc[ch];
-                    dL_dopa += (cc[ch] - accum_rec[ch]) * dL_dpixel[ch];
-                    v[ACC_COLOR_R + ch] = aT * dL_dpixel[ch];
+        // entry j of this batch has list position (contributor index) block_last - 1 - (i*RB_BATCH + j)
+        const int first_pos = (int)block_last - 1 - i * RB_BATCH;
+#pragma unroll 1
+        for (int k = 0; k < RB_BATCH / 32; k++) {
+            if (k * 32 >= cnt) break;
+            const int jj = k * 32 + lane;
+            const float4 bx = s_box[jj];
+            const bool hit = jj < cnt && (uint32_t)(first_pos - jj) < warp_last && bx.x <= strip_x1 && bx.y >= strip_x0 &&
+                             bx.z <= strip_y1 && bx.w >= strip_y0;
+            uint32_t m = __ballot_sync(0xffffffffu, hit);
+            while (m) {
+                const int j = k * 32 + __ffs(m) - 1;
+                m &= m - 1;
+                const uint32_t contributor = (uint32_t)(first_pos - j);
+                const float4 g0 = *reinterpret_cast<const float4*>(&s_geo[j]);
+                const float4 g1 = *reinterpret_cast<const float4*>(&s_geo[j].cc);
+                const float dx = g0.x - pfx, dy = g0.y - pfy;
+                bool contrib = inside && contributor < last_contributor;
+                const float q = __fmaf_rn(__fmul_rn(g0.z, dx), dx, __fmul_rn(__fmul_rn(g1.x, dy), dy));
+                const float power = __fmaf_rn(q, -0.5f, -__fmul_rn(__fmul_rn(g0.w, dx), dy));
+                contrib = contrib && !(power > 0.0f);
+                if (!__any_sync(0xffffffffu, contrib)) continue;
+                const float G = expf(power);
+                const float alpha = fminf(0.99f, g1.y * G);
+                contrib = contrib && !(alpha < 1.0f / 255.0f);
+                const float4 nrm = s_nrm[j];
+                float c_d, pro_dot = 1.f;
+                if (HAS_DIRS) {
+                    pro_dot = nrm.x * dir.x + nrm.y * dir.y + nrm.z * dir.z;
+                    c_d = (g1.z / pro_dot) * dir.z;
+                } else {
+                    c_d = g1.z;
                 }
-                if (idi & 1u) {
-                    accum_depth_rec = last_alpha * last_depth + (1.f - last_alpha) * accum_depth_rec;
-                    accum_rec2 = last_alpha + (1.f - last_alpha) * accum_rec2;  // == accum_normal_rec2[ch], same recurrence
-                    dL_dopa += (((c_d - accum_depth_rec) - depth_final * (1 - accum_rec2)) * inv_weight) * dL_dpixel_depth;
-                    const float dL_dd_j = (aT * inv_weight) * dL_dpixel_depth;
-                    float dnd[3] = {0.f, 0.f, 0.f};
-                    if (HAS_DIRS) {  // backward.cu:722-728
-                        const float4 xv = s_xv[j];
-                        const float s = dL_dd_j * dir.z;
-                        const float inv_pd = 1.0f / pro_dot;
-                        const float s2 = s * inv_pd * inv_pd;
-                        dnd[0] = s2 * (pro_dot * xv.x - dir.x * g1.z);
-                        dnd[1] = s2 * (pro_dot * xv.y - dir.y * g1.z);
-                        dnd[2] = s2 * (pro_dot * xv.z - dir.z * g1.z);
-                        const float sv = s * inv_pd;
-                        v[ACC_VIEW_X_OR_DEPTH] = sv * nrm.x;
-                        v[ACC_VIEW_Y] = sv * nrm.y;
-                        ex_view_z = sv * nrm.z;
-                    } else {
-                        v[ACC_VIEW_X_OR_DEPTH] = dL_dd_j;
-                    }
-                    const float nn[3] = {nrm.x, nrm.y, nrm.z};
+                contrib = contrib && !(c_d < 0.2f);  // == (double)c_d < 0.2, backward.cu:616
+                if (!__any_sync(0xffffffffu, contrib)) continue;
+
+                float v[16];
+#pragma unroll
+                for (int q_ = 0; q_ < 16; q_++) v[q_] = 0.f;
+                float ex_view_z = 0.f, ex_obj0 = 0.f, ex_obj1 = 0.f;
+                const uint32_t idi = __float_as_uint(g1.w);
+                if (contrib) {
+                    T = T / (1.f - alpha);
+                    const float aT = alpha * T;
+                    float dL_dopa = 0.0f;
+                    const float4 col = s_col[j];
+                    const float cc[3] = {col.x, col.y, col.z};
 #pragma unroll
                     for (int ch = 0; ch < 3; ch++) {
-                        const float n = nn[ch];
-                        accum_normal_rec[ch] = last_alpha * last_normal[ch] + (1.f - last_alpha) * accum_normal_rec[ch];
-                        last_normal[ch] = n;
-                        // reference quirk: last_normal was just overwritten with n (backward.cu:741-745)
-                        dL_dopa += (((n - accum_normal_rec[ch]) - n * (1 - accum_rec2)) * inv_weight) * dL_dpixel_normal[ch];
-                        v[ACC_NORMAL_X + ch] = (aT * inv_weight) * dL_dpixel_normal[ch] + dnd[ch];
+                        accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
+                        last_color[ch] = cc[ch];
+                        dL_dopa += (cc[ch] - accum_rec[ch]) * dL_dpixel[ch];
+                        v[ACC_COLOR_R + ch] = aT * dL_dpixel[ch];
                     }
+                    if (idi & 1u) {
+                        accum_depth_rec = last_alpha * last_depth + (1.f - last_alpha) * accum_depth_rec;
+                        accum_rec2 = last_alpha + (1.f - last_alpha) * accum_rec2;  // == accum_normal_rec2[ch], same recurrence
+                        dL_dopa += (((c_d - accum_depth_rec) - depth_final * (1 - accum_rec2)) * inv_weight) * dL_dpixel_depth;
+                        const float dL_dd_j = (aT * inv_weight) * dL_dpixel_depth;
+                        float dnd[3] = {0.f, 0.f, 0.f};
+                        if (HAS_DIRS) {  // backward.cu:722-728
+                            const float4 xv = s_xv[j];
+                            const float s_ = dL_dd_j * dir.z;
+                            const float inv_pd = 1.0f / pro_dot;
+                            const float s2 = s_ * inv_pd * inv_pd;
+                            dnd[0] = s2 * (pro_dot * xv.x - dir.x * g1.z);
+                            dnd[1] = s2 * (pro_dot * xv.y - dir.y * g1.z);
+                            dnd[2] = s2 * (pro_dot * xv.z - dir.z * g1.z);
+                            const float sv = s_ * inv_pd;
+                            v[ACC_VIEW_X_OR_DEPTH] = sv * nrm.x;
+                            v[ACC_VIEW_Y] = sv * nrm.y;
+                            ex_view_z = sv * nrm.z;
+                        } else {
+                            v[ACC_VIEW_X_OR_DEPTH] = dL_dd_j;
+                        }
+                        const float nn[3] = {nrm.x, nrm.y, nrm.z};
+#pragma unroll
+                        for (int ch = 0; ch < 3; ch++) {
+                            const float n = nn[ch];
+                            accum_normal_rec[ch] = last_alpha * last_normal[ch] + (1.f - last_alpha) * accum_normal_rec[ch];
+                            last_normal[ch] = n;
+                            // reference quirk: last_normal was just overwritten with n (backward.cu:741-745)
+                            dL_dopa += (((n - accum_normal_rec[ch]) - n * (1 - accum_rec2)) * inv_weight) * dL_dpixel_normal[ch];
+                            v[ACC_NORMAL_X + ch] = (aT * inv_weight) * dL_dpixel_normal[ch] + dnd[ch];
+                        }
+                    }
+                    if (HAS_OBJ) {
+                        const float2 o2 = s_obj[j];
+                        const float oo[2] = {o2.x, o2.y};
+                        float eo[2];
+#pragma unroll
+                        for (int ch = 0; ch < 2; ch++) {
+                            accum_rec_obj[ch] = last_alpha * last_object[ch] + (1.f - last_alpha) * accum_rec_obj[ch];
+                            last_object[ch] = oo[ch];
+                            dL_dalpha += (oo[ch] - accum_rec_obj[ch]) * dL_dpixel_obj[ch];  // persists across Gaussians (backward.cu:766)
+                            eo[ch] = aT * dL_dpixel_obj[ch];
+                        }
+                        ex_obj0 = eo[0]; ex_obj1 = eo[1];
+                    }
+                    accum_alpha_rec = last_alpha + (1.f - last_alpha) * accum_alpha_rec;
+                    dL_dopa += (1 - accum_alpha_rec) * dL_dalpha;
+                    dL_dopa *= T;
+                    last_alpha = alpha;
+                    last_depth = c_d;
+                    dL_dopa += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
+
+                    const float dL_dG = g1.y * dL_dopa;
+                    const float gdx = G * dx, gdy = G * dy;
+                    const float dG_ddelx = -gdx * g0.z - gdy * g0.w;
+                    const float dG_ddely = -gdy * g1.x - gdx * g0.w;
+                    const float mx = dL_dG * dG_ddelx * ddelx_dx, my = dL_dG * dG_ddely * ddely_dy;
+                    v[ACC_MEAN2D_X] = mx; v[ACC_MEAN2D_Y] = my;
+                    v[ACC_ABS_X] = fabsf(mx); v[ACC_ABS_Y] = fabsf(my);
+                    v[ACC_CONIC_XX] = -0.5f * gdx * dx * dL_dG;
+                    v[ACC_CONIC_XY] = -0.5f * gdx * dy * dL_dG;
+                    v[ACC_CONIC_YY] = -0.5f * gdy * dy * dL_dG;
+                    v[ACC_OPACITY] = G * dL_dopa;
+                }
+                const float red = warp_reduce16_transposed(v, lane);
+                float* rec = acc + (size_t)(idi >> 1) * VCR_ACC_STRIDE;
+                if (lane < 16) atomicAdd(rec + lane, red);
+                if (HAS_DIRS) {
+                    const float z = vcr_warp_sum(ex_view_z);
+                    if (lane == 16) atomicAdd(rec + ACC_VIEW_Z, z);
                 }
                 if (HAS_OBJ) {
-                    const float2 o2 = s_obj[j];
-                    const float oo[2] = {o2.x, o2.y};
-                    float eo[2];
-#pragma unroll
-                    for (int ch = 0; ch < 2; ch++) {
-                        accum_rec_obj[ch] = last_alpha * last_object[ch] + (1.f - last_alpha) * accum_rec_obj[ch];
-                        last_object[ch] = oo[ch];
-                        dL_dalpha += (oo[ch] - accum_rec_obj[ch]) * dL_dpixel_obj[ch];  // persists across Gaussians (backward.cu:766)
-                        eo[ch] = aT * dL_dpixel_obj[ch];
-                    }
-                    ex_obj0 = eo[0]; ex_obj1 = eo[1];
+                    const float o0 = vcr_warp_sum(ex_obj0), o1 = vcr_warp_sum(ex_obj1);
+                    if (lane == 17) atomicAdd(rec + ACC_OBJ_0, o0);
+                    if (lane == 18) atomicAdd(rec + ACC_OBJ_1, o1);
                 }
-                accum_alpha_rec = last_alpha + (1.f - last_alpha) * accum_alpha_rec;
-                dL_dopa += (1 - accum_alpha_rec) * dL_dalpha;
-                dL_dopa *= T;
-                last_alpha = alpha;
-                last_depth = c_d;
-                dL_dopa += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
-
-                const float dL_dG = g1.y * dL_dopa;
-                const float gdx = G * dx, gdy = G * dy;
-                const float dG_ddelx = -gdx * g0.z - gdy * g0.w;
-                const float dG_ddely = -gdy * g1.x - gdx * g0.w;
-                const float mx = dL_dG * dG_ddelx * ddelx_dx, my = dL_dG * dG_ddely * ddely_dy;
-                v[ACC_MEAN2D_X] = mx; v[ACC_MEAN2D_Y] = my;
-                v[ACC_ABS_X] = fabsf(mx); v[ACC_ABS_Y] = fabsf(my);
-                v[ACC_CONIC_XX] = -0.5f * gdx * dx * dL_dG;
-                v[ACC_CONIC_XY] = -0.5f * gdx * dy * dL_dG;
-                v[ACC_CONIC_YY] = -0.5f * gdy * dy * dL_dG;
-                v[ACC_OPACITY] = G * dL_dopa;
-            }
-            const float red = warp_reduce16_transposed(v, lane);
-            float* rec = acc + (size_t)(idi >> 1) * VCR_ACC_STRIDE;
-            if (lane < 16) atomicAdd(rec + lane, red);
-            if (HAS_DIRS) {
-                const float z = vcr_warp_sum(ex_view_z);
-                if (lane == 16) atomicAdd(rec + ACC_VIEW_Z, z);
-            }
-            if (HAS_OBJ) {
-                const float o0 = vcr_warp_sum(ex_obj0), o1 = vcr_warp_sum(ex_obj1);
-                if (lane == 17) atomicAdd(rec + ACC_OBJ_0, o0);
-                if (lane == 18) atomicAdd(rec + ACC_OBJ_1, o1);
             }
         }
     }

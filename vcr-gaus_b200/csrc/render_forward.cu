@@ -25,7 +25,7 @@ struct __align__(16) StagedGeo {  // 32 bytes
 };
 
 template <int MODE, bool HAS_DIRS, bool HAS_OBJ>
-__global__ void __launch_bounds__(256) render_forward_kernel(
+__global__ void __launch_bounds__(256, 4) render_forward_kernel(
     const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
     const float2* __restrict__ means2D, const float* __restrict__ xyz_view, const float* __restrict__ features,
     const float* __restrict__ depths, const float* __restrict__ normals, const float* __restrict__ obj,
@@ -33,11 +33,12 @@ __global__ void __launch_bounds__(256) render_forward_kernel(
     const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
     float* __restrict__ out_color, int* __restrict__ gaussian_count, float* __restrict__ important_score) {
     __shared__ StagedGeo s_geo[RF_BATCH];
+    __shared__ float4 s_box[RF_BATCH];   // conservative {xlo, xhi, ylo, yhi} of the alpha >= 1/255 footprint
     __shared__ float4 s_nrm[MODE == 0 ? RF_BATCH : 1];
     __shared__ float4 s_col[MODE != VCR_MODE_VISI_ACC ? RF_BATCH : 1];
     __shared__ float2 s_obj[(MODE == 0 && HAS_OBJ) ? RF_BATCH : 1];
 
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31;
     const int gx = gridDim.x;
     const uint32_t px = blockIdx.x * VCR_TILE_X + (tid & 15);
     const uint32_t py = blockIdx.y * VCR_TILE_Y + (tid >> 4);
@@ -46,6 +47,9 @@ __global__ void __launch_bounds__(256) render_forward_kernel(
     const size_t pix_id = (size_t)W * py + px;
     const float pfx = (float)px, pfy = (float)py;
     bool done = !inside;
+    // the warp's pixel strip: the full tile width, two rows
+    const float strip_x0 = (float)(blockIdx.x * VCR_TILE_X), strip_x1 = strip_x0 + (float)(VCR_TILE_X - 1);
+    const float strip_y0 = (float)(blockIdx.y * VCR_TILE_Y + 2 * (tid >> 5)), strip_y1 = strip_y0 + 1.0f;
 
     float3 dir = make_float3(0.f, 0.f, 0.f);
     if (HAS_DIRS && inside) dir = make_float3(__ldg(dirs + pix_id), __ldg(dirs + HW + pix_id), __ldg(dirs + 2 * HW + pix_id));
@@ -55,7 +59,7 @@ __global__ void __launch_bounds__(256) render_forward_kernel(
     int toDo = (int)(range.y - range.x);
 
     float T = 1.0f;
-    uint32_t contributor = 0, last_contributor = 0;
+    uint32_t last_contributor = 0;
     float C[3] = {0.f, 0.f, 0.f};
     float weight = 1e-10f;  // reference quirk: alpha output starts at 1e-10 (forward.cu:326)
     float D = 0.f, N[3] = {0.f, 0.f, 0.f}, O[2] = {0.f, 0.f};
@@ -69,6 +73,7 @@ __global__ void __launch_bounds__(256) render_forward_kernel(
             const float4 co = __ldg(conic_opacity + id);
             StagedGeo sg;
             sg.x = xy.x; sg.y = xy.y; sg.ca = co.x; sg.cb = co.y; sg.cc = co.z; sg.op = co.w;
+            s_box[tid] = vcr_alpha_bbox(xy, co);
             uint32_t ins = 1u;
             if (MODE == 0) {
                 const float3 n = make_float3(__ldg(normals + 3 * (size_t)id), __ldg(normals + 3 * (size_t)id + 1),
@@ -95,59 +100,75 @@ __global__ void __launch_bounds__(256) render_forward_kernel(
         __syncthreads();
 
         const int cnt = min(RF_BATCH, toDo);
-        for (int j = 0; !done && j < cnt; j++) {
-            contributor++;
-            const float4 g0 = *reinterpret_cast<const float4*>(&s_geo[j]);        // x, y, ca, cb
-            const float4 g1 = *reinterpret_cast<const float4*>(&s_geo[j].cc);     // cc, op, nx, id_inside
-            const float dx = g0.x - pfx, dy = g0.y - pfy;
-            // power = -0.5f*(ca*dx*dx + cc*dy*dy) - cb*dx*dy, contracted exactly like the reference build
-            const float q = __fmaf_rn(__fmul_rn(g0.z, dx), dx, __fmul_rn(__fmul_rn(g1.x, dy), dy));
-            const float power = __fmaf_rn(q, -0.5f, -__fmul_rn(__fmul_rn(g0.w, dx), dy));
-            if (power > 0.0f) continue;
+        // Warp-level culling: each lane tests 8 staged Gaussians against the warp's 16x2 pixel strip; the ballots
+        // form a 256-bit candidate mask and only candidates enter the per-pixel loop (in list order).
+        if (__all_sync(0xffffffffu, done)) continue;
+        bool warp_done = false;
+#pragma unroll 1
+        for (int k = 0; k < RF_BATCH / 32 && !warp_done; k++) {
+            const int jj = k * 32 + lane;
+            if (k * 32 >= cnt) break;
+            const float4 bx = s_box[jj];
+            const bool hit = jj < cnt && bx.x <= strip_x1 && bx.y >= strip_x0 && bx.z <= strip_y1 && bx.w >= strip_y0;
+            uint32_t m = __ballot_sync(0xffffffffu, hit);
+            while (m) {
+                // m is warp-uniform, so every lane passes here once per candidate: a safe place to vote
+                if (__all_sync(0xffffffffu, done)) { warp_done = true; break; }
+                const int j = k * 32 + __ffs(m) - 1;
+                m &= m - 1;
+                if (done) continue;
+                const float4 g0 = *reinterpret_cast<const float4*>(&s_geo[j]);        // x, y, ca, cb
+                const float4 g1 = *reinterpret_cast<const float4*>(&s_geo[j].cc);     // cc, op, nx, id_inside
+                const float dx = g0.x - pfx, dy = g0.y - pfy;
+                // power = -0.5f*(ca*dx*dx + cc*dy*dy) - cb*dx*dy, contracted exactly like the reference build
+                const float q = __fmaf_rn(__fmul_rn(g0.z, dx), dx, __fmul_rn(__fmul_rn(g1.x, dy), dy));
+                const float power = __fmaf_rn(q, -0.5f, -__fmul_rn(__fmul_rn(g0.w, dx), dy));
+                if (power > 0.0f) continue;
 
-            float depth = 0.f;
-            float4 nrm = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (MODE == 0) {
-                nrm = s_nrm[j];
-                if (HAS_DIRS) {
-                    const float t = g1.z / (nrm.x * dir.x + nrm.y * dir.y + nrm.z * dir.z);
-                    depth = t * dir.z;
+                float depth = 0.f;
+                float4 nrm = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (MODE == 0) {
+                    nrm = s_nrm[j];
+                    if (HAS_DIRS) {
+                        const float t = g1.z / (nrm.x * dir.x + nrm.y * dir.y + nrm.z * dir.z);
+                        depth = t * dir.z;
+                    } else {
+                        depth = g1.z;
+                    }
+                    if (depth < 0.2f) continue;  // == (double)depth <= 0.2, forward.cu:382
+                }
+                const float alpha = fminf(0.99f, g1.y * expf(power));
+                if (alpha < 1.0f / 255.0f) continue;
+                const uint32_t idi = __float_as_uint(g1.w);
+                if (MODE == VCR_MODE_VISI_ACC) {  // first contributor only (forward.cu:809-826)
+                    atomicAdd(gaussian_count + (idi >> 1), 1);  // reference: racy ++ (forward.cu:822)
+                    done = true;
+                    continue;
+                }
+                const float test_T = T * (1 - alpha);
+                if (test_T < 0.0001f) { done = true; continue; }
+                const float4 col = s_col[j];
+                if (MODE == VCR_MODE_COUNT) {
+                    // the reference's plain ++ / += race between pixels (forward.cu:575-576); atomics give the exact totals
+                    atomicAdd(gaussian_count + (idi >> 1), 1);
+                    atomicAdd(important_score + (idi >> 1), g1.y);
+                    C[0] += col.x * alpha * T; C[1] += col.y * alpha * T; C[2] += col.z * alpha * T;
                 } else {
-                    depth = g1.z;
+                    const float w = alpha * T;
+                    C[0] = __fmaf_rn(col.x, w, C[0]); C[1] = __fmaf_rn(col.y, w, C[1]); C[2] = __fmaf_rn(col.z, w, C[2]);
+                    if (HAS_OBJ) {
+                        const float2 o = s_obj[j];
+                        O[0] = __fmaf_rn(o.x, w, O[0]); O[1] = __fmaf_rn(o.y, w, O[1]);
+                    }
+                    weight += w;
+                    if (idi & 1u) {
+                        D = __fmaf_rn(depth, w, D);
+                        N[0] = __fmaf_rn(nrm.x, w, N[0]); N[1] = __fmaf_rn(nrm.y, w, N[1]); N[2] = __fmaf_rn(nrm.z, w, N[2]);
+                    }
                 }
-                if (depth < 0.2f) continue;  // == (double)depth <= 0.2, forward.cu:382
+                T = test_T;
+                last_contributor = (uint32_t)(i * RF_BATCH + j + 1);
             }
-            const float alpha = fminf(0.99f, g1.y * expf(power));
-            if (alpha < 1.0f / 255.0f) continue;
-            const uint32_t idi = __float_as_uint(g1.w);
-            if (MODE == VCR_MODE_VISI_ACC) {  // first contributor only (forward.cu:809-826)
-                atomicAdd(gaussian_count + (idi >> 1), 1);  // reference: racy ++ (forward.cu:822)
-                done = true;
-                continue;
-            }
-            const float test_T = T * (1 - alpha);
-            if (test_T < 0.0001f) { done = true; continue; }
-            const float4 col = s_col[j];
-            if (MODE == VCR_MODE_COUNT) {
-                // the reference's plain ++ / += race between pixels (forward.cu:575-576); atomics give the exact totals
-                atomicAdd(gaussian_count + (idi >> 1), 1);
-                atomicAdd(important_score + (idi >> 1), g1.y);
-                C[0] += col.x * alpha * T; C[1] += col.y * alpha * T; C[2] += col.z * alpha * T;
-            } else {
-                const float w = alpha * T;
-                C[0] = __fmaf_rn(col.x, w, C[0]); C[1] = __fmaf_rn(col.y, w, C[1]); C[2] = __fmaf_rn(col.z, w, C[2]);
-                if (HAS_OBJ) {
-                    const float2 o = s_obj[j];
-                    O[0] = __fmaf_rn(o.x, w, O[0]); O[1] = __fmaf_rn(o.y, w, O[1]);
-                }
-                weight += w;
-                if (idi & 1u) {
-                    D = __fmaf_rn(depth, w, D);
-                    N[0] = __fmaf_rn(nrm.x, w, N[0]); N[1] = __fmaf_rn(nrm.y, w, N[1]); N[2] = __fmaf_rn(nrm.z, w, N[2]);
-                }
-            }
-            T = test_T;
-            last_contributor = contributor;
         }
     }
 
