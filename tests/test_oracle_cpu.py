@@ -1,0 +1,175 @@
+"""Pins the CPU oracle (oracle/vcr_oracle.c) against golden vectors produced by the REFERENCE CUDA rasterizer itself.
+
+tests/golden/ref_*.npz were generated on a B200 by tests/golden/make_golden.py from oracle/_ref (the unmodified
+reference sources compiled by oracle/build_ref.sh) on seeded synthetic inputs; the reference ships no golden vectors
+of its own.  Gates, as in BASELINE.json:
+  * radii, tiles touched, duplicated keys / values, sorted keys / point list, tile ranges: bit-exact
+  * forward maps <= 1e-5 absolute (a CPU cannot reproduce the GPU's MUFU.EX2, so a handful of pixels may flip one of
+    the threshold tests; at most FLIP_FRAC of the values may exceed the tolerance)
+  * gradients <= 1e-3 relative L2
+plus oracle-only checks: finite-difference validation of the hand-derived backward on the terms where the
+reference's backward is the true gradient, and the D-Normal / kNN restatements against plain PyTorch.
+"""
+import glob
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import oracle as O
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+GOLDEN = sorted(glob.glob(os.path.join(HERE, "golden", "ref_*.npz")))
+FLIP_FRAC = 5e-4
+
+
+def rel_l2(a, b):
+    a, b = np.asarray(a, np.float64).ravel(), np.asarray(b, np.float64).ravel()
+    n = np.linalg.norm(b)
+    return float(np.linalg.norm(a - b) / n) if n > 0 else float(np.linalg.norm(a - b))
+
+
+def load(path):
+    z = np.load(path)
+    P, W, H, use_dirs, use_sem, deg, seed = [int(v) for v in z["meta"]]
+    inp = {k[3:]: z[k] for k in z.files if k.startswith("in_")}
+    inp.update(W=W, H=H, sh_degree=deg, tanfovx=float(inp["tanfovx"]), tanfovy=float(inp["tanfovy"]))
+    inp.setdefault("dirs", None)
+    inp.setdefault("semantics", None)
+    return z, inp
+
+
+@pytest.mark.parametrize("path", GOLDEN, ids=[os.path.basename(p) for p in GOLDEN])
+def test_oracle_matches_reference_cuda_golden(path):
+    z, inp = load(path)
+    f = O.rasterize_forward(inp)
+    pre, b = f["pre"], f["binned"]
+    assert np.array_equal(pre["radii"], z["ref_radii"]), "radii"
+    vis = z["ref_radii"] > 0
+    assert np.array_equal(pre["tiles_touched"], z["ref_tiles_touched"])
+    assert b["R"] == int(z["ref_R"])
+    assert np.array_equal(pre["depths"][vis].view(np.uint32), z["ref_depths"][vis].view(np.uint32)), "depth bits"
+    assert np.array_equal(pre["xy"][vis].view(np.uint32), z["ref_xy"][vis].view(np.uint32)), "pixel centre bits"
+    np.testing.assert_allclose(pre["conic_opacity"][vis], z["ref_conic_opacity"][vis], rtol=2e-5, atol=1e-7)
+    np.testing.assert_allclose(pre["cov3D"][vis], z["ref_cov3D"][vis], rtol=2e-5, atol=1e-9)
+    np.testing.assert_allclose(pre["rgb"][vis], z["ref_rgb"][vis], atol=2e-6)
+    assert np.array_equal(b["keys_unsorted"], z["ref_keys_unsorted"]), "duplicated keys"
+    assert np.array_equal(b["vals_unsorted"], z["ref_vals_unsorted"]), "duplicated values"
+    assert np.array_equal(b["keys"], z["ref_keys"]), "sorted keys"
+    assert np.array_equal(b["point_list"], z["ref_point_list"]), "sorted point list"
+    assert np.array_equal(b["ranges"], z["ref_ranges"]), "tile ranges"
+    out, ref = f["out_color"], z["ref_out_color"]
+    solid = ref[7] > 1e-3
+    for name, a, r in (("rgb", out[:3], ref[:3]), ("alpha", out[7], ref[7]), ("sem", out[8:], ref[8:]),
+                       ("depth", out[3][solid], ref[3][solid]), ("normal", out[4:7][:, solid], ref[4:7][:, solid])):
+        bad = np.abs(a - r) > 1e-5 * np.maximum(1.0, np.abs(r))
+        assert bad.mean() <= FLIP_FRAC, f"{name}: {bad.sum()} of {bad.size} values beyond 1e-5 (max {np.abs(a - r).max()})"
+    assert (f["n_contrib"] != z["ref_n_contrib"]).mean() <= FLIP_FRAC
+    # backward, from the REFERENCE's forward state so that a flipped pixel cannot leak into the comparison
+    fref = dict(f, out_color=ref, final_T=z["ref_final_T"], n_contrib=z["ref_n_contrib"])
+    g = O.rasterize_backward(inp, fref, z["dL_dout"])
+    for k in ("dL_dmeans3D", "dL_dmeans2D", "dL_dmeans2D_densify", "dL_dsh", "dL_dnormals", "dL_dopacity", "dL_dscales",
+              "dL_drotations", "dL_dcov3D", "dL_dobjects"):
+        e = rel_l2(g[k], z["ref_" + k])
+        assert e <= 1e-3, f"{k}: relative L2 error {e}"
+    if "ref_dist2" in z.files:
+        np.testing.assert_allclose(O.knn3(inp["means3D"]), z["ref_dist2"], rtol=1e-5, atol=1e-10)
+
+
+def test_golden_vectors_are_present():
+    assert len(GOLDEN) >= 2, "tests/golden/ref_*.npz missing (generate with tests/golden/make_golden.py on a GPU box)"
+
+
+def _tiny_case(seed=0, use_dirs=False):
+    import vcr_synth as S
+    sc = S.make_scene(40, seed=seed, scale0=0.25)
+    cam = S.make_camera(32, 32, idx=1)
+    inp = S.raster_inputs(sc, cam, use_dirs=use_dirs, sh_degree=2)
+    return {k: (v.numpy().astype(np.float64).astype(np.float32) if isinstance(v, torch.Tensor) else v) for k, v in inp.items()}
+
+
+def test_backward_matches_finite_differences_on_colour_and_alpha():
+    """With upstream gradient only on RGB + alpha and every alpha below the 0.99 clamp, the reference's backward is the
+    true gradient of its forward (the quirks of SURVEY §7 sit in the depth/normal terms and the clamp)."""
+    inp = _tiny_case()
+    inp["opacities"] = np.minimum(inp["opacities"], 0.9).astype(np.float32)
+    H = W = 32
+    rng = np.random.default_rng(0)
+    g = np.zeros((10, H, W), np.float32)
+    g[:3] = rng.standard_normal((3, H, W))
+    g[7] = rng.standard_normal((H, W))
+
+    def loss(i):
+        o = O.rasterize_forward(i)["out_color"].astype(np.float64)
+        return float((o[:3] * g[:3]).sum() + (o[7] * g[7]).sum())
+
+    f = O.rasterize_forward(inp)
+    b = O.rasterize_backward(inp, f, g)
+    checked = 0
+    for name, gname, eps in (("opacities", "dL_dopacity", 2e-3), ("means3D", "dL_dmeans3D", 1e-3), ("shs", "dL_dsh", 5e-3),
+                             ("scales", "dL_dscales", 1e-3)):
+        num = np.zeros_like(inp[name], dtype=np.float64)
+        idxs = [tuple(rng.integers(0, s) for s in inp[name].shape) for _ in range(12)]
+        for ix in idxs:
+            p, m = dict(inp), dict(inp)
+            p[name] = inp[name].copy(); m[name] = inp[name].copy()
+            p[name][ix] += eps; m[name][ix] -= eps
+            num[ix] = (loss(p) - loss(m)) / (2 * eps)
+        ana = np.array([b[gname][ix] for ix in idxs], np.float64)
+        fd = np.array([num[ix] for ix in idxs])
+        scale = max(np.abs(ana).max(), 1e-3)
+        ok = np.abs(ana - fd) <= 0.05 * scale + 0.08 * np.abs(fd)   # FP32 forward + threshold tests: loose but telling
+        assert ok.mean() >= 0.75, f"{name}: analytic {ana} vs finite differences {fd}"
+        checked += 1
+    assert checked == 4
+
+
+def test_dnormal_oracle_matches_pytorch_autograd():
+    torch.manual_seed(0)
+    H, W = 23, 31
+    yy, xx = torch.meshgrid(torch.linspace(-1, 1, H), torch.linspace(-1, 1, W), indexing="ij")
+    depth = (2.0 + 0.4 * torch.sin(3 * xx) * torch.cos(2 * yy) + 0.02 * torch.randn(H, W)).double().requires_grad_(True)
+    gt = torch.nn.functional.normalize(torch.randn(H, W, 3).double(), dim=-1)
+    rn = torch.randn(H, W, 3).double()
+    mask = torch.rand(H, W) > 0.25
+    fx, fy, cx, cy = 28.0, 30.0, W / 2, H / 2
+    u = torch.arange(W).double() + 0.5
+    v = torch.arange(H).double() + 0.5
+    X = torch.stack([(u[None, :] - cx) / fx * depth, (v[:, None] - cy) / fy * depth, depth], dim=-1)
+    dy = torch.gradient(X, dim=0)[0]
+    dx = torch.gradient(X, dim=1)[0]
+    est = torch.nn.functional.normalize(torch.cross(dx, dy, dim=-1), dim=-1)
+    w = torch.exp((torch.sum(torch.nn.functional.normalize(rn, dim=-1) * gt, dim=-1) - 1) / 0.5)
+    l = (w[mask] * (est[mask] - gt[mask]).abs().sum(-1)).mean() + (w[mask] * (1 - (est[mask] * gt[mask]).sum(-1))).mean()
+    l.backward()
+    o = O.dnormal(depth.detach().float().numpy(), gt.float().numpy(), rn.float().numpy(), mask.numpy(), (fx, fy, cx, cy), exp_t=0.5)
+    assert abs(o["loss"] - float(l.detach())) < 1e-6
+    np.testing.assert_allclose(o["est_normal"], est.detach().numpy(), atol=1e-6)
+    assert rel_l2(o["dL_ddepth"], depth.grad.numpy()) < 1e-5
+
+
+def test_knn_oracle_matches_cdist():
+    pts = torch.randn(300, 3, generator=torch.Generator().manual_seed(1))
+    d = torch.cdist(pts.double(), pts.double()) ** 2
+    d.fill_diagonal_(float("inf"))
+    ref = d.topk(3, largest=False).values.mean(1).float().numpy()
+    np.testing.assert_allclose(O.knn3(pts.numpy()), ref, rtol=1e-5)
+
+
+def test_preprocess_edge_cases():
+    """Culling rules of preprocessCUDA (forward.cu:194-240): behind the near plane, off-screen, and P = 1."""
+    inp = _tiny_case()
+    V = inp["viewmatrix"]
+    behind = inp["means3D"].copy()
+    # move everything behind the camera: p_view.z = m . V[:,2] + V[3,2] <= 0.2
+    z = behind @ V[:3, 2] + V[3, 2]
+    behind -= np.outer(z + 1.0, V[:3, 2] / np.dot(V[:3, 2], V[:3, 2])).astype(np.float32)
+    f = O.rasterize_forward(dict(inp, means3D=behind))
+    assert f["binned"]["R"] == 0 and (f["pre"]["radii"] == 0).all()
+    np.testing.assert_allclose(f["out_color"][:3], np.broadcast_to(inp["bg"][:, None, None], (3, 32, 32)), atol=1e-7)
+    assert np.allclose(f["out_color"][7], 1e-10)          # alpha starts at 1e-10 (forward.cu:326)
+    assert not O.mark_visible(behind, V).any()
+    one = {k: (v[:1] if isinstance(v, np.ndarray) and v.shape[:1] == (40,) else v) for k, v in inp.items()}
+    f1 = O.rasterize_forward(one)
+    assert f1["pre"]["radii"].shape == (1,)
