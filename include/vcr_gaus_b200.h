@@ -192,6 +192,16 @@ size_t vcr_knn_scratch_bytes(int P);
 int vcr_dist2_knn3(int P, const float* points /* f32[P,3] */, float* mean_dists /* f32[P] */,
                    char* scratch, void* stream);
 
+/* distCUDA2 without caller scratch.  No counterpart in the reference (its SimpleKNN::knn allocates with cudaMalloc and
+ * thrust on every call, simple_knn.cu:186-222).  For hosts that cannot hand over device memory at call time — the GPU's
+ * free memory is already owned by another allocator, allocation is forbidden after start-up, or the call comes from
+ * inside an allocator callback — the scratch is a fixed array inside the library (4 MiB per GPU that loads the library,
+ * held until exit).  At most vcr_knn_noalloc_max_points() (65536) points; more is refused with an error.  Allocates and
+ * frees nothing.  The first call on each device resolves the array's device address: make it before any stream
+ * capture.  Calls share the array, so calls that overlap in time on one GPU must be serialised by the caller. */
+int vcr_knn_noalloc_max_points(void);
+int vcr_dist2_knn3_noalloc(int P, const float* points /* f32[P,3] */, float* mean_dists /* f32[P] */, void* stream);
+
 /* ---- measurement hooks (bench.py; no counterpart in the reference, which has no per-kernel timers — SURVEY.md §5) ----
  * With profiling enabled every kernel launch of this library is bracketed by CUDA events on its own stream.
  * vcr_profile_read sums the elapsed milliseconds and the number of timed launches per kernel id since the last reset

@@ -210,3 +210,65 @@ extern "C" int vcr_dist2_knn3(int P, const float* points, float* mean_dists, cha
     VCR_LAUNCH_CHECK("knn_search_kernel");
     return 0;
 }
+
+// ------------------------------------------------------------------------------------------------------------------
+// vcr_dist2_knn3_noalloc — the same computation for callers that cannot obtain device memory at the time of the call.
+//
+// vcr_dist2_knn3 needs a few megabytes of scratch from its caller.  Some callers have nowhere to get it: a host program
+// that has handed the whole GPU to another allocator (a framework's caching pool that already owns all free memory, so
+// a fresh cudaMalloc fails), a plug-in running under a "no device allocation after start-up" rule, or code invoked
+// from inside an allocator's own callback, where asking for more memory would re-enter it.  For them the scratch lives
+// in the fixed device array below, which is part of the library image: every GPU that loads the library sets aside
+// VCR_KNN_NOALLOC_BYTES for it until the process exits, whether or not this entry point is ever called.
+//
+// Limits and rules
+//   * at most VCR_KNN_NOALLOC_MAX_POINTS points per call; larger inputs are refused (use vcr_dist2_knn3);
+//   * nothing is allocated or freed here, by this function or by anything it calls (kernel launches and
+//     cudaMemsetAsync only); inputs and outputs are still the caller's;
+//   * the first call on each device looks up the device address of the array (cudaGetSymbolAddress) and remembers it;
+//     make that first call outside any stream capture;
+//   * all calls on a device share the one array, and it keeps whatever the previous call left in it.  The parts that
+//     must start from zero (digit histograms, look-back words, bounds) are cleared on every call, everything else is
+//     overwritten before it is read.  Two calls that overlap on the same GPU (different streams, different threads)
+//     would trample each other's scratch: serialise them.
+// ------------------------------------------------------------------------------------------------------------------
+#define VCR_KNN_NOALLOC_MAX_POINTS 65536
+#define VCR_KNN_NOALLOC_BYTES (4u << 20)
+static __device__ __align__(256) unsigned char g_knn_noalloc_scratch[VCR_KNN_NOALLOC_BYTES];
+
+#include <mutex>
+#define VCR_MAX_DEVICES 64
+static char* g_knn_noalloc_ptr[VCR_MAX_DEVICES] = {nullptr};
+static std::mutex g_knn_noalloc_mutex;
+
+// In host code `g_knn_noalloc_scratch` is only a handle for the symbol, not an address a kernel could use: the device
+// address has to be asked for, per device, with that device current.
+static int knn_noalloc_scratch_for_current_device(char** out) {
+    int dev = -1;
+    VCR_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= VCR_MAX_DEVICES) { vcr_set_error("dist2_knn3_noalloc: unsupported device index %d", dev); return 1; }
+    std::lock_guard<std::mutex> lock(g_knn_noalloc_mutex);
+    if (!g_knn_noalloc_ptr[dev]) {
+        char* p = nullptr;
+        VCR_CUDA_TRY(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_knn_noalloc_scratch));
+        if (!p) { vcr_set_error("dist2_knn3_noalloc: cudaGetSymbolAddress returned a null address on device %d", dev); return 1; }
+        g_knn_noalloc_ptr[dev] = p;
+    }
+    *out = g_knn_noalloc_ptr[dev];
+    return 0;
+}
+
+extern "C" int vcr_knn_noalloc_max_points(void) { return VCR_KNN_NOALLOC_MAX_POINTS; }
+
+extern "C" int vcr_dist2_knn3_noalloc(int P, const float* points, float* mean_dists, void* stream) {
+    if (P <= 0) return 0;
+    if (!points || !mean_dists) { vcr_set_error("dist2_knn3_noalloc: NULL argument"); return 1; }
+    if (P > VCR_KNN_NOALLOC_MAX_POINTS || vcr_knn_scratch_bytes(P) > (size_t)VCR_KNN_NOALLOC_BYTES) {
+        vcr_set_error("dist2_knn3_noalloc: %d points exceed the built-in scratch (at most %d points, %u bytes); "
+                      "use vcr_dist2_knn3 with caller-provided scratch", P, VCR_KNN_NOALLOC_MAX_POINTS, VCR_KNN_NOALLOC_BYTES);
+        return 1;
+    }
+    char* scratch = nullptr;
+    if (knn_noalloc_scratch_for_current_device(&scratch)) return 1;
+    return vcr_dist2_knn3(P, points, mean_dists, scratch, stream);
+}
