@@ -50,13 +50,20 @@ __global__ void __launch_bounds__(256) preprocess_backward_kernel(const BwdParam
             a[4 * k] = q.x; a[4 * k + 1] = q.y; a[4 * k + 2] = q.z; a[4 * k + 3] = q.w;
         }
     }
-    // direct outputs of the compositing backward
-    p.dL_dmean2D[3 * i] = a[ACC_MEAN2D_X]; p.dL_dmean2D[3 * i + 1] = a[ACC_MEAN2D_Y]; p.dL_dmean2D[3 * i + 2] = 0.f;
-    p.dL_dmean2D_densify[3 * i] = a[ACC_ABS_X]; p.dL_dmean2D_densify[3 * i + 1] = a[ACC_ABS_Y]; p.dL_dmean2D_densify[3 * i + 2] = 0.f;
-    p.dL_dopacity[i] = a[ACC_OPACITY];
+    // outputs of the compositing backward: raw moments -> the reference's per-Gaussian gradients (common.cuh ACC_*)
+    const float4 co = g.conic_opacity[i];
+    const float half_w = 0.5f * p.W, half_h = 0.5f * p.H;
+    const float g2x = -half_w * co.w * (co.x * a[ACC_MX] + co.y * a[ACC_MY]);
+    const float g2y = -half_h * co.w * (co.z * a[ACC_MY] + co.y * a[ACC_MX]);
+    p.dL_dmean2D[3 * i] = g2x; p.dL_dmean2D[3 * i + 1] = g2y; p.dL_dmean2D[3 * i + 2] = 0.f;
+    p.dL_dmean2D_densify[3 * i] = half_w * fabsf(co.w) * a[ACC_ABS_X];
+    p.dL_dmean2D_densify[3 * i + 1] = half_h * fabsf(co.w) * a[ACC_ABS_Y];
+    p.dL_dmean2D_densify[3 * i + 2] = 0.f;
+    p.dL_dopacity[i] = a[ACC_M0];
 #pragma unroll
     for (int k = 0; k < 3; k++) { p.dL_dcolor[3 * i + k] = a[ACC_COLOR_R + k]; p.dL_dnormal[3 * i + k] = a[ACC_NORMAL_X + k]; }
     p.dL_dobjects[2 * i] = a[ACC_OBJ_0]; p.dL_dobjects[2 * i + 1] = a[ACC_OBJ_1];
+    const float gcx = -0.5f * co.w * a[ACC_MXX], gcy = -0.5f * co.w * a[ACC_MXY], gcz = -0.5f * co.w * a[ACC_MYY];
 
     const float3 mean = make_float3(__ldg(p.means3D + 3 * i), __ldg(p.means3D + 3 * i + 1), __ldg(p.means3D + 3 * i + 2));
     const float* c3 = p.cov3D_precomp ? p.cov3D_precomp + 6 * i : g.cov3D + 6 * i;
@@ -91,7 +98,6 @@ __global__ void __launch_bounds__(256) preprocess_backward_kernel(const BwdParam
     const float ca = s0[0] * T0[0] + s0[1] * T0[1] + s0[2] * T0[2] + 0.3f;
     const float cb = s1[0] * T0[0] + s1[1] * T0[1] + s1[2] * T0[2];
     const float cc = s1[0] * T1[0] + s1[1] * T1[1] + s1[2] * T1[2] + 0.3f;
-    const float gcx = a[ACC_CONIC_XX], gcy = a[ACC_CONIC_XY], gcz = a[ACC_CONIC_YY];
     const float denom = ca * cc - cb * cb;
     float dL_da = 0, dL_db = 0, dL_dc = 0;
     const float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
@@ -135,15 +141,15 @@ __global__ void __launch_bounds__(256) preprocess_backward_kernel(const BwdParam
     const float m_w = 1.0f / (m_hw + 0.0000001f);
     const float mul1 = (Pm[0] * mean.x + Pm[4] * mean.y + Pm[8] * mean.z + Pm[12]) * m_w * m_w;
     const float mul2 = (Pm[1] * mean.x + Pm[5] * mean.y + Pm[9] * mean.z + Pm[13]) * m_w * m_w;
-    const float g2x = a[ACC_MEAN2D_X], g2y = a[ACC_MEAN2D_Y];
     gm[0] += (Pm[0] * m_w - Pm[3] * mul1) * g2x + (Pm[1] * m_w - Pm[3] * mul2) * g2y;
     gm[1] += (Pm[4] * m_w - Pm[7] * mul1) * g2x + (Pm[5] * m_w - Pm[7] * mul2) * g2y;
     gm[2] += (Pm[8] * m_w - Pm[11] * mul1) * g2x + (Pm[9] * m_w - Pm[11] * mul2) * g2y;
     if (p.dirs == nullptr) {
-        const float gd = a[ACC_VIEW_X_OR_DEPTH];
+        const float gd = a[ACC_SV_OR_DEPTH];
         gm[0] += V[2] * gd; gm[1] += V[6] * gd; gm[2] += V[10] * gd;
     } else {
-        const float gvx = a[ACC_VIEW_X_OR_DEPTH], gvy = a[ACC_VIEW_Y], gvz = a[ACC_VIEW_Z];
+        const float sv = a[ACC_SV_OR_DEPTH];
+        const float gvx = sv * __ldg(p.normals + 3 * i), gvy = sv * __ldg(p.normals + 3 * i + 1), gvz = sv * __ldg(p.normals + 3 * i + 2);
         gm[0] += V[0] * gvx + V[1] * gvy + V[2] * gvz;
         gm[1] += V[4] * gvx + V[5] * gvy + V[6] * gvz;
         gm[2] += V[8] * gvx + V[9] * gvy + V[10] * gvz;

@@ -18,6 +18,7 @@
 #include "common.cuh"
 
 #define RB_BATCH 256
+#define RB_SPARSE_LANES 2
 
 struct __align__(16) StagedGeoB {
     float x, y, ca, cb;
@@ -189,27 +190,31 @@ __global__ void __launch_bounds__(256) render_backward_kernel(
                 const float power = __fmaf_rn(q, -0.5f, -__fmul_rn(__fmul_rn(g0.w, dx), dy));
                 contrib = contrib && !(power > 0.0f);
                 if (!__any_sync(0xffffffffu, contrib)) continue;
-                const float G = expf(power);
+                // Fast intrinsics from here on: the backward only has to meet 1e-3 relative L2 (the forward, which must
+                // match the reference bit for bit, keeps expf and IEEE division).
+                const float G = __expf(power);
                 const float alpha = fminf(0.99f, g1.y * G);
                 contrib = contrib && !(alpha < 1.0f / 255.0f);
                 const float4 nrm = s_nrm[j];
-                float c_d, pro_dot = 1.f;
+                float c_d, inv_pd = 1.f;
                 if (HAS_DIRS) {
-                    pro_dot = nrm.x * dir.x + nrm.y * dir.y + nrm.z * dir.z;
-                    c_d = (g1.z / pro_dot) * dir.z;
+                    inv_pd = __fdividef(1.0f, nrm.x * dir.x + nrm.y * dir.y + nrm.z * dir.z);
+                    c_d = (g1.z * inv_pd) * dir.z;
                 } else {
                     c_d = g1.z;
                 }
                 contrib = contrib && !(c_d < 0.2f);  // == (double)c_d < 0.2, backward.cu:616
-                if (!__any_sync(0xffffffffu, contrib)) continue;
+                const uint32_t cmask = __ballot_sync(0xffffffffu, contrib);
+                if (cmask == 0u) continue;
 
                 float v[16];
 #pragma unroll
                 for (int q_ = 0; q_ < 16; q_++) v[q_] = 0.f;
-                float ex_view_z = 0.f, ex_obj0 = 0.f, ex_obj1 = 0.f;
+                float ex_obj1 = 0.f;
                 const uint32_t idi = __float_as_uint(g1.w);
                 if (contrib) {
-                    T = T / (1.f - alpha);
+                    const float inv1ma = __fdividef(1.0f, 1.f - alpha);
+                    T = T * inv1ma;
                     const float aT = alpha * T;
                     float dL_dopa = 0.0f;
                     const float4 col = s_col[j];
@@ -225,22 +230,20 @@ __global__ void __launch_bounds__(256) render_backward_kernel(
                         accum_depth_rec = last_alpha * last_depth + (1.f - last_alpha) * accum_depth_rec;
                         accum_rec2 = last_alpha + (1.f - last_alpha) * accum_rec2;  // == accum_normal_rec2[ch], same recurrence
                         dL_dopa += (((c_d - accum_depth_rec) - depth_final * (1 - accum_rec2)) * inv_weight) * dL_dpixel_depth;
-                        const float dL_dd_j = (aT * inv_weight) * dL_dpixel_depth;
+                        const float aTw = aT * inv_weight;
+                        const float dL_dd_j = aTw * dL_dpixel_depth;
                         float dnd[3] = {0.f, 0.f, 0.f};
                         if (HAS_DIRS) {  // backward.cu:722-728
                             const float4 xv = s_xv[j];
-                            const float s_ = dL_dd_j * dir.z;
-                            const float inv_pd = 1.0f / pro_dot;
-                            const float s2 = s_ * inv_pd * inv_pd;
+                            const float sv = dL_dd_j * dir.z * inv_pd;      // dL/dxyz_view = normal * sum(sv)
+                            const float s2 = sv * inv_pd;
+                            const float pro_dot = nrm.x * dir.x + nrm.y * dir.y + nrm.z * dir.z;
                             dnd[0] = s2 * (pro_dot * xv.x - dir.x * g1.z);
                             dnd[1] = s2 * (pro_dot * xv.y - dir.y * g1.z);
                             dnd[2] = s2 * (pro_dot * xv.z - dir.z * g1.z);
-                            const float sv = s_ * inv_pd;
-                            v[ACC_VIEW_X_OR_DEPTH] = sv * nrm.x;
-                            v[ACC_VIEW_Y] = sv * nrm.y;
-                            ex_view_z = sv * nrm.z;
+                            v[ACC_SV_OR_DEPTH] = sv;
                         } else {
-                            v[ACC_VIEW_X_OR_DEPTH] = dL_dd_j;
+                            v[ACC_SV_OR_DEPTH] = dL_dd_j;
                         }
                         const float nn[3] = {nrm.x, nrm.y, nrm.z};
 #pragma unroll
@@ -250,7 +253,7 @@ __global__ void __launch_bounds__(256) render_backward_kernel(
                             last_normal[ch] = n;
                             // reference quirk: last_normal was just overwritten with n (backward.cu:741-745)
                             dL_dopa += (((n - accum_normal_rec[ch]) - n * (1 - accum_rec2)) * inv_weight) * dL_dpixel_normal[ch];
-                            v[ACC_NORMAL_X + ch] = (aT * inv_weight) * dL_dpixel_normal[ch] + dnd[ch];
+                            v[ACC_NORMAL_X + ch] = aTw * dL_dpixel_normal[ch] + dnd[ch];
                         }
                     }
                     if (HAS_OBJ) {
@@ -264,38 +267,39 @@ __global__ void __launch_bounds__(256) render_backward_kernel(
                             dL_dalpha += (oo[ch] - accum_rec_obj[ch]) * dL_dpixel_obj[ch];  // persists across Gaussians (backward.cu:766)
                             eo[ch] = aT * dL_dpixel_obj[ch];
                         }
-                        ex_obj0 = eo[0]; ex_obj1 = eo[1];
+                        v[ACC_OBJ_0] = eo[0]; ex_obj1 = eo[1];
                     }
                     accum_alpha_rec = last_alpha + (1.f - last_alpha) * accum_alpha_rec;
                     dL_dopa += (1 - accum_alpha_rec) * dL_dalpha;
                     dL_dopa *= T;
                     last_alpha = alpha;
                     last_depth = c_d;
-                    dL_dopa += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
+                    dL_dopa += (-T_final * inv1ma) * bg_dot_dpixel;
 
-                    const float dL_dG = g1.y * dL_dopa;
-                    const float gdx = G * dx, gdy = G * dy;
-                    const float dG_ddelx = -gdx * g0.z - gdy * g0.w;
-                    const float dG_ddely = -gdy * g1.x - gdx * g0.w;
-                    const float mx = dL_dG * dG_ddelx * ddelx_dx, my = dL_dG * dG_ddely * ddely_dy;
-                    v[ACC_MEAN2D_X] = mx; v[ACC_MEAN2D_Y] = my;
-                    v[ACC_ABS_X] = fabsf(mx); v[ACC_ABS_Y] = fabsf(my);
-                    v[ACC_CONIC_XX] = -0.5f * gdx * dx * dL_dG;
-                    v[ACC_CONIC_XY] = -0.5f * gdx * dy * dL_dG;
-                    v[ACC_CONIC_YY] = -0.5f * gdy * dy * dL_dG;
-                    v[ACC_OPACITY] = G * dL_dopa;
+                    // raw moments; the per-Gaussian factors (opacity, conic, 0.5 W) are applied once in preprocess_backward
+                    const float b = G * dL_dopa;
+                    const float bx = b * dx, by = b * dy;
+                    v[ACC_M0] = b; v[ACC_MX] = bx; v[ACC_MY] = by;
+                    v[ACC_MXX] = bx * dx; v[ACC_MXY] = bx * dy; v[ACC_MYY] = by * dy;
+                    v[ACC_ABS_X] = fabsf(bx * g0.z + by * g0.w);
+                    v[ACC_ABS_Y] = fabsf(by * g1.x + bx * g0.w);
+                }
+                float* rec = acc + (size_t)(idi >> 1) * VCR_ACC_STRIDE;
+                if (__popc(cmask) <= RB_SPARSE_LANES) {
+                    // few contributing pixels (footprint edges): cheaper to let each of them issue its own atomics than
+                    // to run the 32-lane reduction
+                    if (contrib) {
+#pragma unroll
+                        for (int q_ = 0; q_ < (HAS_OBJ ? 16 : 15); q_++) atomicAdd(rec + q_, v[q_]);
+                        if (HAS_OBJ) atomicAdd(rec + ACC_OBJ_1, ex_obj1);
+                    }
+                    continue;
                 }
                 const float red = warp_reduce16_transposed(v, lane);
-                float* rec = acc + (size_t)(idi >> 1) * VCR_ACC_STRIDE;
-                if (lane < 16) atomicAdd(rec + lane, red);
-                if (HAS_DIRS) {
-                    const float z = vcr_warp_sum(ex_view_z);
-                    if (lane == 16) atomicAdd(rec + ACC_VIEW_Z, z);
-                }
+                if (lane < (HAS_OBJ ? 16 : 15)) atomicAdd(rec + lane, red);
                 if (HAS_OBJ) {
-                    const float o0 = vcr_warp_sum(ex_obj0), o1 = vcr_warp_sum(ex_obj1);
-                    if (lane == 17) atomicAdd(rec + ACC_OBJ_0, o0);
-                    if (lane == 18) atomicAdd(rec + ACC_OBJ_1, o1);
+                    const float o1 = vcr_warp_sum(ex_obj1);
+                    if (lane == 16) atomicAdd(rec + ACC_OBJ_1, o1);
                 }
             }
         }
