@@ -213,6 +213,8 @@ class Stepper:
         self.h2d_bytes = sum(t.numel() * t.element_size() for t in self.host[0].values())
         self.d2h_bytes = 4
         self.loss_host = torch.zeros(1).pin_memory()
+        self.copy_stream = torch.cuda.Stream(device=dev)
+        self._prefetched = None
         if impl == "reference":
             import ref_ab
             self.C = ref_ab.load()
@@ -224,11 +226,29 @@ class Stepper:
         # normals_precomp depends on the view (flip towards the camera + w2c rotation): precomputed per view on device
         self.normals = [v["inp"]["normals"].to(dev).requires_grad_(True) for v in views]
 
+    def _issue_prefetch(self, i):
+        k = i % len(self.views)
+        with torch.cuda.stream(self.copy_stream):
+            d = {name: t.to(self.dev, non_blocking=True) for name, t in self.host[k].items()}
+            ev = torch.cuda.Event()
+            ev.record(self.copy_stream)
+        # keep the tensors alive on the compute stream's timeline
+        for t in d.values():
+            t.record_stream(torch.cuda.current_stream())
+        self._prefetched = (i, d, ev)
+
     def step(self, i, e2e):
         k = i % len(self.views)
         p = self.bucket.params
         if e2e:
-            d = {name: t.to(self.dev, non_blocking=True) for name, t in self.host[k].items()}
+            # per-view inputs come from pinned host memory every step; like a data loader with prefetch depth 1 the
+            # copy of view i+1 is issued on a side stream while view i is being rendered (the copies stay inside the
+            # timed region, they are just overlapped)
+            if self._prefetched is None or self._prefetched[0] != i:
+                self._issue_prefetch(i)
+            _, d, ev = self._prefetched
+            torch.cuda.current_stream().wait_event(ev)
+            self._issue_prefetch(i + 1)
         else:
             d = self.devv[k]
         cam = d["cam"]
@@ -248,7 +268,8 @@ class Stepper:
             out, radii = self.GR(rs)(means3D=p["means3D"], means2D=means2D, means2D_densify=means2D_densify, shs=p["shs"],
                                      normals_precomp=normals, opacities=p["opacities"], scales=p["scales"],
                                      rotations=p["rotations"], dirs=self.dirs, inside=self.inside)
-        image, depth, normal = out[0:3], out[3:4], out[4:7]
+        # channel split exactly like render() (gaussian_renderer/__init__.py:122-123, 133-134)
+        image, depth, normal, _alpha, _sem = out.split([3, 1, 3, 1, 2], dim=0)
         rn = F.normalize(normal.permute(1, 2, 0), dim=-1)
         gt_n = d["gt_normal"]
         loss = (image - d["gt_image"]).abs().mean()

@@ -15,12 +15,12 @@ static __device__ __constant__ float kC3[7] = {-0.5900435899266435f, 2.890611442
                                                0.3731763325901154f,  -0.4570457994644658f, 1.445305721320277f,
                                                -0.5900435899266435f};
 
-__global__ void __launch_bounds__(256) preprocess_backward_kernel(const BwdParams p, const GeomState g) {
-    const int idx = blockIdx.x * 256 + threadIdx.x;
-    __shared__ float V[16], Pm[16];
-    if (threadIdx.x < 16) V[threadIdx.x] = __ldg(p.viewmatrix + threadIdx.x);
-    else if (threadIdx.x < 32) Pm[threadIdx.x - 16] = __ldg(p.projmatrix + threadIdx.x - 16);
-    __syncthreads();
+// Per-Gaussian work.  With COOP (M == 16) the SH gradient is not written here: the thread leaves its 16 basis values
+// and its 3 clamp-masked colour gradients in shared memory (both pre-zeroed by the caller) and the block writes the
+// [256][16][3] gradient tile with fully coalesced stores afterwards.
+template <bool COOP>
+__device__ __forceinline__ void preprocess_backward_body(const BwdParams& p, const GeomState& g, const int idx, const float* V,
+                                                         const float* Pm, float* s_basis, float* s_gg) {
     if (idx >= p.P) return;
     const size_t i = (size_t)idx;
     const int M = p.M;
@@ -37,7 +37,7 @@ __global__ void __launch_bounds__(256) preprocess_backward_kernel(const BwdParam
         for (int k = 0; k < 6; k++) p.dL_dcov3D[6 * i + k] = 0.f;
 #pragma unroll
         for (int k = 0; k < 4; k++) p.dL_drot[4 * i + k] = 0.f;
-        if (p.dL_dsh) for (int k = 0; k < 3 * M; k++) p.dL_dsh[i * 3 * M + k] = 0.f;
+        if (!COOP && p.dL_dsh) for (int k = 0; k < 3 * M; k++) p.dL_dsh[i * 3 * M + k] = 0.f;
         return;
     }
 
@@ -178,9 +178,16 @@ __global__ void __launch_bounds__(256) preprocess_backward_kernel(const BwdParam
         basis[12] = kC3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy); basis[13] = kC3[4] * x * (4.f * zz - xx - yy);
         basis[14] = kC3[5] * z * (xx - yy); basis[15] = kC3[6] * x * (xx - 3.f * yy);
         const int nact = (D + 1) * (D + 1);
-        for (int k = 0; k < M; k++) {
-            const float bk = (k < nact && k < 16) ? basis[k] : 0.f;
-            gsh[3 * k] = bk * gg[0]; gsh[3 * k + 1] = bk * gg[1]; gsh[3 * k + 2] = bk * gg[2];
+        if (COOP) {
+#pragma unroll
+            for (int k = 0; k < 16; k++) s_basis[threadIdx.x * 17 + k] = k < nact ? basis[k] : 0.f;
+#pragma unroll
+            for (int ch = 0; ch < 3; ch++) s_gg[threadIdx.x * 3 + ch] = gg[ch];
+        } else {
+            for (int k = 0; k < M; k++) {
+                const float bk = (k < nact && k < 16) ? basis[k] : 0.f;
+                gsh[3 * k] = bk * gg[0]; gsh[3 * k + 1] = bk * gg[1]; gsh[3 * k + 2] = bk * gg[2];
+            }
         }
 #pragma unroll
         for (int ch = 0; ch < 3; ch++) {
@@ -213,7 +220,7 @@ __global__ void __launch_bounds__(256) preprocess_backward_kernel(const BwdParam
         gm[0] += ((+sum2 - dox * dox) * ddx - doy * dox * ddy - doz * dox * ddz) * invsum32;
         gm[1] += (-dox * doy * ddx + (sum2 - doy * doy) * ddy - doz * doy * ddz) * invsum32;
         gm[2] += (-dox * doz * ddx - doy * doz * ddy + (sum2 - doz * doz) * ddz) * invsum32;
-    } else if (p.dL_dsh) {
+    } else if (!COOP && p.dL_dsh) {
         for (int k = 0; k < 3 * M; k++) p.dL_dsh[i * 3 * M + k] = 0.f;
     }
     p.dL_dmean3D[3 * i] = gm[0]; p.dL_dmean3D[3 * i + 1] = gm[1]; p.dL_dmean3D[3 * i + 2] = gm[2];
@@ -263,9 +270,50 @@ __global__ void __launch_bounds__(256) preprocess_backward_kernel(const BwdParam
     }
 }
 
+template <bool COOP>
+__global__ void __launch_bounds__(256) preprocess_backward_kernel(const BwdParams p, const GeomState g) {
+    const int idx = blockIdx.x * 256 + threadIdx.x;
+    __shared__ float V[16], Pm[16];
+    __shared__ float s_basis[COOP ? 256 * 17 : 1];  // stride 17: conflict-free per-thread rows
+    __shared__ float s_gg[COOP ? 256 * 3 : 1];
+    if (threadIdx.x < 16) V[threadIdx.x] = __ldg(p.viewmatrix + threadIdx.x);
+    else if (threadIdx.x < 32) Pm[threadIdx.x - 16] = __ldg(p.projmatrix + threadIdx.x - 16);
+    if (COOP) {
+#pragma unroll
+        for (int ch = 0; ch < 3; ch++) s_gg[threadIdx.x * 3 + ch] = 0.f;  // zero colour gradient => zero SH gradient row
+#pragma unroll
+        for (int k = 0; k < 16; k++) s_basis[threadIdx.x * 17 + k] = 0.f;  // (uninitialised shared memory could hold NaNs)
+    }
+    __syncthreads();
+    preprocess_backward_body<COOP>(p, g, idx, V, Pm, s_basis, s_gg);
+    if (COOP) {
+        __syncthreads();
+        // dL_dsh tile of this block: 256 Gaussians x 48 floats = 3072 float4, written as coalesced 16-byte stores
+        const size_t base = (size_t)blockIdx.x * 256 * 48;
+        const size_t total = (size_t)p.P * 48;
+        float4* out4 = reinterpret_cast<float4*>(p.dL_dsh + base);
+#pragma unroll 4
+        for (int r = 0; r < 12; r++) {
+            const int e4 = r * 256 + threadIdx.x;   // float4 index inside the tile
+            const int e = e4 * 4;
+            if (base + e >= total) continue;
+            const int gi = e / 48, k0 = e - gi * 48;
+            float o[4];
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                const int k = k0 + q;                // never crosses a Gaussian: 48 is a multiple of 4
+                o[q] = s_basis[gi * 17 + k / 3] * s_gg[gi * 3 + k % 3];
+            }
+            out4[e4] = make_float4(o[0], o[1], o[2], o[3]);
+        }
+    }
+}
+
 int vcr_launch_preprocess_backward(const BwdParams& p, GeomState& g, cudaStream_t s) {
     VcrProfScope prof(VCR_K_PREPROCESS_BWD, s);
-    preprocess_backward_kernel<<<(p.P + 255) / 256, 256, 0, s>>>(p, g);
+    const bool coop = p.shs != nullptr && p.M == 16 && p.dL_dsh != nullptr;
+    if (coop) preprocess_backward_kernel<true><<<(p.P + 255) / 256, 256, 0, s>>>(p, g);
+    else preprocess_backward_kernel<false><<<(p.P + 255) / 256, 256, 0, s>>>(p, g);
     VCR_LAUNCH_CHECK("preprocess_backward_kernel");
     return 0;
 }
