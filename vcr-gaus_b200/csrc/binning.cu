@@ -314,10 +314,13 @@ int vcr_launch_offsets_and_duplicate(const FwdParams& p, GeomState& g, BinningSt
 }
 
 int vcr_launch_radix_sort(BinningState& b, int R, int key_bits, cudaStream_t s) {
-    static bool attr_set = false;
-    if (!attr_set) {
+    // the opt-in shared-memory size is a per-device function attribute
+    static bool attr_set_dev[64] = {false};
+    int dev_ = 0;
+    VCR_CUDA_TRY(cudaGetDevice(&dev_));
+    if (dev_ >= 0 && dev_ < 64 && !attr_set_dev[dev_]) {
         VCR_CUDA_TRY(cudaFuncSetAttribute(radix_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, RADIX_SMEM_BYTES));
-        attr_set = true;
+        attr_set_dev[dev_] = true;
     }
     const int npass = (key_bits + 7) / 8;
     const uint32_t nblocks = ((uint32_t)R + RADIX_TILE - 1) / RADIX_TILE;

@@ -26,6 +26,15 @@ struct __align__(16) StagedGeoB {
     uint32_t id_inside;  // (id << 1) | inside
 };
 
+template <bool HAS_DIRS>
+struct RbStage {                     // one staging buffer (24 KB with intersection depth, 20 KB without)
+    StagedGeoB geo[RB_BATCH];
+    float4 box[RB_BATCH];            // conservative footprint box {xlo, xhi, ylo, yhi}
+    float4 nrm[RB_BATCH];            // normal.xyz, semantics[0]
+    float4 col[RB_BATCH];            // rgb, semantics[1]
+    float4 xv[HAS_DIRS ? RB_BATCH : 1];  // view-space position (intersection mode)
+};
+
 // Transposed warp reduction: every lane passes 16 values; on return lane L (and lane L+16) holds the
 // warp-wide sum of value (L & 15).  8+4+2+1 exchange shuffles + 1 plain butterfly step.
 __device__ __forceinline__ float warp_reduce16_transposed(float (&v)[16], int lane) {
@@ -73,12 +82,8 @@ __global__ void __launch_bounds__(256) render_backward_kernel(
     const float* __restrict__ objects, const float* __restrict__ dirs, const float* __restrict__ alpha_img,
     const float* __restrict__ depth_img, const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
     const float* __restrict__ dL_dpixels, const uint8_t* __restrict__ inside_gs, float* __restrict__ acc) {
-    __shared__ StagedGeoB s_geo[RB_BATCH];
-    __shared__ float4 s_box[RB_BATCH];
-    __shared__ float4 s_nrm[RB_BATCH];
-    __shared__ float4 s_col[RB_BATCH];
-    __shared__ float4 s_xv[HAS_DIRS ? RB_BATCH : 1];
-    __shared__ float2 s_obj[HAS_OBJ ? RB_BATCH : 1];
+    extern __shared__ __align__(16) unsigned char rb_smem[];
+    RbStage<HAS_DIRS>* s_stage = reinterpret_cast<RbStage<HAS_DIRS>*>(rb_smem);   // [2]: double-buffered staging
     __shared__ uint32_t s_block_last;
 
     const int tid = threadIdx.x, lane = tid & 31;
@@ -138,34 +143,42 @@ __global__ void __launch_bounds__(256) render_backward_kernel(
     float last_object[2] = {0.f, 0.f};
     const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
 
-    for (int i = 0; i < rounds; i++, toDo -= RB_BATCH) {
-        __syncthreads();
-        const uint32_t progress = (uint32_t)i * RB_BATCH + tid;
-        if (range.x + progress < list_end) {
-            const uint32_t id = __ldg(point_list + (list_end - progress - 1));
-            const float2 xy = __ldg(means2D + id);
-            const float4 co = __ldg(conic_opacity + id);
-            const float3 n = make_float3(__ldg(normals + 3 * (size_t)id), __ldg(normals + 3 * (size_t)id + 1),
-                                         __ldg(normals + 3 * (size_t)id + 2));
-            StagedGeoB sg;
-            sg.x = xy.x; sg.y = xy.y; sg.ca = co.x; sg.cb = co.y; sg.cc = co.z; sg.op = co.w;
-            s_box[tid] = vcr_alpha_bbox(xy, co);
-            if (HAS_DIRS) {
-                const float3 xv = make_float3(__ldg(xyz_view + 3 * (size_t)id), __ldg(xyz_view + 3 * (size_t)id + 1),
-                                              __ldg(xyz_view + 3 * (size_t)id + 2));
-                sg.nx = n.x * xv.x + n.y * xv.y + n.z * xv.z;
-                s_xv[tid] = make_float4(xv.x, xv.y, xv.z, 0.f);
-            } else {
-                sg.nx = __ldg(depths + id);
-            }
-            sg.id_inside = (id << 1) | (__ldg(inside_gs + id) ? 1u : 0u);
-            s_geo[tid] = sg;
-            s_nrm[tid] = make_float4(n.x, n.y, n.z, 0.f);
-            s_col[tid] = make_float4(__ldg(colors + 3 * (size_t)id), __ldg(colors + 3 * (size_t)id + 1),
-                                     __ldg(colors + 3 * (size_t)id + 2), 0.f);
-            if (HAS_OBJ) s_obj[tid] = make_float2(__ldg(objects + 2 * (size_t)id), __ldg(objects + 2 * (size_t)id + 1));
+    // gather reversed-list entry (batch, tid) into staging buffer `buf`
+    auto stage = [&](int batch, int buf) {
+        const uint32_t progress = (uint32_t)batch * RB_BATCH + tid;
+        if (range.x + progress >= list_end) return;
+        RbStage<HAS_DIRS>& st = s_stage[buf];
+        const uint32_t id = __ldg(point_list + (list_end - progress - 1));
+        const float2 xy = __ldg(means2D + id);
+        const float4 co = __ldg(conic_opacity + id);
+        const float3 n = make_float3(__ldg(normals + 3 * (size_t)id), __ldg(normals + 3 * (size_t)id + 1),
+                                     __ldg(normals + 3 * (size_t)id + 2));
+        StagedGeoB sg;
+        sg.x = xy.x; sg.y = xy.y; sg.ca = co.x; sg.cb = co.y; sg.cc = co.z; sg.op = co.w;
+        st.box[tid] = vcr_alpha_bbox(xy, co);
+        if (HAS_DIRS) {
+            const float3 xv = make_float3(__ldg(xyz_view + 3 * (size_t)id), __ldg(xyz_view + 3 * (size_t)id + 1),
+                                          __ldg(xyz_view + 3 * (size_t)id + 2));
+            sg.nx = n.x * xv.x + n.y * xv.y + n.z * xv.z;
+            st.xv[tid] = make_float4(xv.x, xv.y, xv.z, 0.f);
+        } else {
+            sg.nx = __ldg(depths + id);
         }
-        __syncthreads();
+        sg.id_inside = (id << 1) | (__ldg(inside_gs + id) ? 1u : 0u);
+        st.geo[tid] = sg;
+        float o0 = 0.f, o1 = 0.f;
+        if (HAS_OBJ) { o0 = __ldg(objects + 2 * (size_t)id); o1 = __ldg(objects + 2 * (size_t)id + 1); }
+        st.nrm[tid] = make_float4(n.x, n.y, n.z, o0);
+        st.col[tid] = make_float4(__ldg(colors + 3 * (size_t)id), __ldg(colors + 3 * (size_t)id + 1),
+                                  __ldg(colors + 3 * (size_t)id + 2), o1);
+    };
+
+    if (rounds > 0) stage(0, 0);
+    __syncthreads();
+    for (int i = 0; i < rounds; i++, toDo -= RB_BATCH) {
+        const int buf = i & 1;
+        if (i + 1 < rounds) stage(i + 1, buf ^ 1);   // overlaps with the replay of batch i
+        const RbStage<HAS_DIRS>& st = s_stage[buf];
 
         const int cnt = min(RB_BATCH, toDo);
         // entry j of this batch has list position (contributor index) block_last - 1 - (i*RB_BATCH + j)
@@ -174,7 +187,7 @@ __global__ void __launch_bounds__(256) render_backward_kernel(
         for (int k = 0; k < RB_BATCH / 32; k++) {
             if (k * 32 >= cnt) break;
             const int jj = k * 32 + lane;
-            const float4 bx = s_box[jj];
+            const float4 bx = st.box[jj];
             const bool hit = jj < cnt && (uint32_t)(first_pos - jj) < warp_last && bx.x <= strip_x1 && bx.y >= strip_x0 &&
                              bx.z <= strip_y1 && bx.w >= strip_y0;
             uint32_t m = __ballot_sync(0xffffffffu, hit);
@@ -182,8 +195,8 @@ __global__ void __launch_bounds__(256) render_backward_kernel(
                 const int j = k * 32 + __ffs(m) - 1;
                 m &= m - 1;
                 const uint32_t contributor = (uint32_t)(first_pos - j);
-                const float4 g0 = *reinterpret_cast<const float4*>(&s_geo[j]);
-                const float4 g1 = *reinterpret_cast<const float4*>(&s_geo[j].cc);
+                const float4 g0 = *reinterpret_cast<const float4*>(&st.geo[j]);
+                const float4 g1 = *reinterpret_cast<const float4*>(&st.geo[j].cc);
                 const float dx = g0.x - pfx, dy = g0.y - pfy;
                 bool contrib = inside && contributor < last_contributor;
                 const float q = __fmaf_rn(__fmul_rn(g0.z, dx), dx, __fmul_rn(__fmul_rn(g1.x, dy), dy));
@@ -195,7 +208,7 @@ __global__ void __launch_bounds__(256) render_backward_kernel(
                 const float G = __expf(power);
                 const float alpha = fminf(0.99f, g1.y * G);
                 contrib = contrib && !(alpha < 1.0f / 255.0f);
-                const float4 nrm = s_nrm[j];
+                const float4 nrm = st.nrm[j];
                 float c_d, inv_pd = 1.f;
                 if (HAS_DIRS) {
                     inv_pd = __fdividef(1.0f, nrm.x * dir.x + nrm.y * dir.y + nrm.z * dir.z);
@@ -217,7 +230,7 @@ __global__ void __launch_bounds__(256) render_backward_kernel(
                     T = T * inv1ma;
                     const float aT = alpha * T;
                     float dL_dopa = 0.0f;
-                    const float4 col = s_col[j];
+                    const float4 col = st.col[j];
                     const float cc[3] = {col.x, col.y, col.z};
 #pragma unroll
                     for (int ch = 0; ch < 3; ch++) {
@@ -234,7 +247,7 @@ __global__ void __launch_bounds__(256) render_backward_kernel(
                         const float dL_dd_j = aTw * dL_dpixel_depth;
                         float dnd[3] = {0.f, 0.f, 0.f};
                         if (HAS_DIRS) {  // backward.cu:722-728
-                            const float4 xv = s_xv[j];
+                            const float4 xv = st.xv[j];
                             const float sv = dL_dd_j * dir.z * inv_pd;      // dL/dxyz_view = normal * sum(sv)
                             const float s2 = sv * inv_pd;
                             const float pro_dot = nrm.x * dir.x + nrm.y * dir.y + nrm.z * dir.z;
@@ -257,8 +270,7 @@ __global__ void __launch_bounds__(256) render_backward_kernel(
                         }
                     }
                     if (HAS_OBJ) {
-                        const float2 o2 = s_obj[j];
-                        const float oo[2] = {o2.x, o2.y};
+                        const float oo[2] = {nrm.w, col.w};
                         float eo[2];
 #pragma unroll
                         for (int ch = 0; ch < 2; ch++) {
@@ -303,6 +315,8 @@ __global__ void __launch_bounds__(256) render_backward_kernel(
                 }
             }
         }
+        // one barrier per batch: publishes batch i+1 and frees buffer `buf` for batch i+2
+        __syncthreads();
     }
 }
 
@@ -313,12 +327,25 @@ int vcr_launch_render_backward(const BwdParams& p, GeomState& g, BinningState& b
     const float* col = p.colors_precomp ? p.colors_precomp : g.rgb;
 #define RB_ARGS img.ranges, b.point_list, p.W, p.H, p.background, g.means2D, g.xyz_view, g.conic_opacity, col, g.depths, \
                 p.normals, p.sh_objs, p.dirs, p.alpha, p.depth, img.accum_alpha, img.n_contrib, p.dL_dpix, p.inside, p.acc
+    // the opt-in shared-memory size is a per-device function attribute
+    static bool attr_set_dev[64] = {false};
+    int dev_ = 0;
+    VCR_CUDA_TRY(cudaGetDevice(&dev_));
+    if (dev_ >= 0 && dev_ < 64 && !attr_set_dev[dev_]) {
+        VCR_CUDA_TRY(cudaFuncSetAttribute(render_backward_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * sizeof(RbStage<true>))));
+        VCR_CUDA_TRY(cudaFuncSetAttribute(render_backward_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * sizeof(RbStage<true>))));
+        VCR_CUDA_TRY(cudaFuncSetAttribute(render_backward_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * sizeof(RbStage<false>))));
+        VCR_CUDA_TRY(cudaFuncSetAttribute(render_backward_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * sizeof(RbStage<false>))));
+        attr_set_dev[dev_] = true;
+    }
     if (p.dirs) {
-        if (p.sh_objs) render_backward_kernel<true, true><<<grid, 256, 0, s>>>(RB_ARGS);
-        else render_backward_kernel<true, false><<<grid, 256, 0, s>>>(RB_ARGS);
+        const size_t sm = 2 * sizeof(RbStage<true>);
+        if (p.sh_objs) render_backward_kernel<true, true><<<grid, 256, sm, s>>>(RB_ARGS);
+        else render_backward_kernel<true, false><<<grid, 256, sm, s>>>(RB_ARGS);
     } else {
-        if (p.sh_objs) render_backward_kernel<false, true><<<grid, 256, 0, s>>>(RB_ARGS);
-        else render_backward_kernel<false, false><<<grid, 256, 0, s>>>(RB_ARGS);
+        const size_t sm = 2 * sizeof(RbStage<false>);
+        if (p.sh_objs) render_backward_kernel<false, true><<<grid, 256, sm, s>>>(RB_ARGS);
+        else render_backward_kernel<false, false><<<grid, 256, sm, s>>>(RB_ARGS);
     }
 #undef RB_ARGS
     VCR_LAUNCH_CHECK("render_backward_kernel");

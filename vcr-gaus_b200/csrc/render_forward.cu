@@ -4,14 +4,17 @@
 // pruning variants renderCUDA_count (:480-603) and renderCUDA_visi_acc (:735-835).
 //
 // One 256-thread block per 16x16 tile, one pixel per thread, FP32 on the CUDA cores (this is not a
-// dense contraction; no tensor cores).  Unlike the reference, everything the inner loop touches is
-// staged in shared memory per batch (the reference reloads normal / colour / semantics from global
-// memory for every contributing pair), the near-plane test is done in FP32 (x <= 0.2 in double is
-// the same predicate as x < 0.2f for a float x — no F2F.F64/DSETP per pair), and n.x_view of the
-// ray/plane intersection is computed once per staged Gaussian instead of once per pixel.
-//
-// The per-pixel arithmetic keeps the reference's operation order so that images are bit-identical to
-// the reference build on identical inputs.
+// dense contraction; no tensor cores).  Differences to the reference, none of which changes a result:
+//   * everything the inner loop touches is staged in shared memory per batch of 256 list entries (the
+//     reference reloads normal / colour / semantics from global memory for every contributing pair);
+//   * staging is double-buffered: batch i+1 is gathered while batch i is composited, one barrier per batch;
+//   * per warp and batch, 8 ballots test the conservative footprint boxes of the 256 staged Gaussians
+//     (vcr_alpha_bbox) against the warp's 16x2 pixel strip, and only candidates enter the per-pixel code;
+//   * the near-plane test is done in FP32 (x <= 0.2 in double is the same predicate as x < 0.2f for a
+//     float x — no F2F.F64/DSETP per pair), and n.x_view of the ray/plane intersection is computed once
+//     per staged Gaussian instead of once per pixel.
+// The per-pixel arithmetic keeps the reference's operation order, so images are bit-identical to the
+// reference build on identical inputs.
 #include "common.cuh"
 
 #define RF_BATCH 256
@@ -24,6 +27,14 @@ struct __align__(16) StagedGeo {  // 32 bytes
     uint32_t id_inside;  // (id << 1) | inside
 };
 
+template <int MODE>
+struct RfStage {                       // one staging buffer
+    StagedGeo geo[RF_BATCH];
+    float4 box[RF_BATCH];              // conservative {xlo, xhi, ylo, yhi} of the alpha >= 1/255 footprint
+    float4 nrm[MODE == 0 ? RF_BATCH : 1];                              // normal.xyz, semantics[0]
+    float4 col[MODE != VCR_MODE_VISI_ACC ? RF_BATCH : 1];              // rgb, semantics[1]
+};
+
 template <int MODE, bool HAS_DIRS, bool HAS_OBJ>
 __global__ void __launch_bounds__(256, 4) render_forward_kernel(
     const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
@@ -32,11 +43,7 @@ __global__ void __launch_bounds__(256, 4) render_forward_kernel(
     const float* __restrict__ dirs, const float4* __restrict__ conic_opacity, const uint8_t* __restrict__ inside_gs,
     const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
     float* __restrict__ out_color, int* __restrict__ gaussian_count, float* __restrict__ important_score) {
-    __shared__ StagedGeo s_geo[RF_BATCH];
-    __shared__ float4 s_box[RF_BATCH];   // conservative {xlo, xhi, ylo, yhi} of the alpha >= 1/255 footprint
-    __shared__ float4 s_nrm[MODE == 0 ? RF_BATCH : 1];
-    __shared__ float4 s_col[MODE != VCR_MODE_VISI_ACC ? RF_BATCH : 1];
-    __shared__ float2 s_obj[(MODE == 0 && HAS_OBJ) ? RF_BATCH : 1];
+    __shared__ RfStage<MODE> s_stage[2];
 
     const int tid = threadIdx.x, lane = tid & 31;
     const int gx = gridDim.x;
@@ -55,8 +62,44 @@ __global__ void __launch_bounds__(256, 4) render_forward_kernel(
     if (HAS_DIRS && inside) dir = make_float3(__ldg(dirs + pix_id), __ldg(dirs + HW + pix_id), __ldg(dirs + 2 * HW + pix_id));
 
     const uint2 range = ranges[blockIdx.y * gx + blockIdx.x];
-    const int rounds = (int)((range.y - range.x + RF_BATCH - 1) / RF_BATCH);
-    int toDo = (int)(range.y - range.x);
+    const int total = (int)(range.y - range.x);
+    const int rounds = (total + RF_BATCH - 1) / RF_BATCH;
+
+    // gather list entry (batch, tid) into staging buffer `buf`
+    auto stage = [&](int batch, int buf) {
+        const uint32_t pos = range.x + (uint32_t)batch * RF_BATCH + tid;
+        if (pos >= range.y) return;
+        RfStage<MODE>& st = s_stage[buf];
+        const uint32_t id = __ldg(point_list + pos);
+        const float2 xy = __ldg(means2D + id);
+        const float4 co = __ldg(conic_opacity + id);
+        StagedGeo sg;
+        sg.x = xy.x; sg.y = xy.y; sg.ca = co.x; sg.cb = co.y; sg.cc = co.z; sg.op = co.w;
+        st.box[tid] = vcr_alpha_bbox(xy, co);
+        uint32_t ins = 1u;
+        float o0 = 0.f, o1 = 0.f;
+        if (MODE == 0) {
+            const float3 n = make_float3(__ldg(normals + 3 * (size_t)id), __ldg(normals + 3 * (size_t)id + 1),
+                                         __ldg(normals + 3 * (size_t)id + 2));
+            if (HAS_DIRS) {
+                const float3 xv = make_float3(__ldg(xyz_view + 3 * (size_t)id), __ldg(xyz_view + 3 * (size_t)id + 1),
+                                              __ldg(xyz_view + 3 * (size_t)id + 2));
+                sg.nx = n.x * xv.x + n.y * xv.y + n.z * xv.z;  // dot(n, x) of intersect(), auxiliary.h:262-271
+            } else {
+                sg.nx = __ldg(depths + id);
+            }
+            ins = __ldg(inside_gs + id) ? 1u : 0u;
+            if (HAS_OBJ) { o0 = __ldg(obj + 2 * (size_t)id); o1 = __ldg(obj + 2 * (size_t)id + 1); }
+            st.nrm[tid] = make_float4(n.x, n.y, n.z, o0);
+        } else {
+            sg.nx = 0.f;
+        }
+        sg.id_inside = (id << 1) | ins;
+        st.geo[tid] = sg;
+        if (MODE != VCR_MODE_VISI_ACC)
+            st.col[tid] = make_float4(__ldg(features + 3 * (size_t)id), __ldg(features + 3 * (size_t)id + 1),
+                                      __ldg(features + 3 * (size_t)id + 2), o1);
+    };
 
     float T = 1.0f;
     uint32_t last_contributor = 0;
@@ -64,51 +107,21 @@ __global__ void __launch_bounds__(256, 4) render_forward_kernel(
     float weight = 1e-10f;  // reference quirk: alpha output starts at 1e-10 (forward.cu:326)
     float D = 0.f, N[3] = {0.f, 0.f, 0.f}, O[2] = {0.f, 0.f};
 
-    for (int i = 0; i < rounds; i++, toDo -= RF_BATCH) {
-        if (__syncthreads_count(done) == RF_BATCH) break;
-        const uint32_t progress = (uint32_t)i * RF_BATCH + tid;
-        if (range.x + progress < range.y) {
-            const uint32_t id = __ldg(point_list + range.x + progress);
-            const float2 xy = __ldg(means2D + id);
-            const float4 co = __ldg(conic_opacity + id);
-            StagedGeo sg;
-            sg.x = xy.x; sg.y = xy.y; sg.ca = co.x; sg.cb = co.y; sg.cc = co.z; sg.op = co.w;
-            s_box[tid] = vcr_alpha_bbox(xy, co);
-            uint32_t ins = 1u;
-            if (MODE == 0) {
-                const float3 n = make_float3(__ldg(normals + 3 * (size_t)id), __ldg(normals + 3 * (size_t)id + 1),
-                                             __ldg(normals + 3 * (size_t)id + 2));
-                s_nrm[tid] = make_float4(n.x, n.y, n.z, 0.f);
-                if (HAS_DIRS) {
-                    const float3 xv = make_float3(__ldg(xyz_view + 3 * (size_t)id), __ldg(xyz_view + 3 * (size_t)id + 1),
-                                                  __ldg(xyz_view + 3 * (size_t)id + 2));
-                    sg.nx = n.x * xv.x + n.y * xv.y + n.z * xv.z;  // dot(n, x) of intersect(), auxiliary.h:262-271
-                } else {
-                    sg.nx = __ldg(depths + id);
-                }
-                ins = __ldg(inside_gs + id) ? 1u : 0u;
-                if (HAS_OBJ) s_obj[tid] = make_float2(__ldg(obj + 2 * (size_t)id), __ldg(obj + 2 * (size_t)id + 1));
-            } else {
-                sg.nx = 0.f;
-            }
-            sg.id_inside = (id << 1) | ins;
-            s_geo[tid] = sg;
-            if (MODE != VCR_MODE_VISI_ACC)
-                s_col[tid] = make_float4(__ldg(features + 3 * (size_t)id), __ldg(features + 3 * (size_t)id + 1),
-                                         __ldg(features + 3 * (size_t)id + 2), 0.f);
-        }
-        __syncthreads();
-
-        const int cnt = min(RF_BATCH, toDo);
+    if (rounds > 0) stage(0, 0);
+    __syncthreads();
+    for (int i = 0; i < rounds; i++) {
+        const int buf = i & 1;
+        if (i + 1 < rounds) stage(i + 1, buf ^ 1);   // overlaps with compositing batch i
+        const RfStage<MODE>& st = s_stage[buf];
+        const int cnt = min(RF_BATCH, total - i * RF_BATCH);
         // Warp-level culling: each lane tests 8 staged Gaussians against the warp's 16x2 pixel strip; the ballots
-        // form a 256-bit candidate mask and only candidates enter the per-pixel loop (in list order).
-        if (__all_sync(0xffffffffu, done)) continue;
-        bool warp_done = false;
+        // form the candidate masks and only candidates enter the per-pixel loop (in list order).
+        bool warp_done = __all_sync(0xffffffffu, done);
 #pragma unroll 1
         for (int k = 0; k < RF_BATCH / 32 && !warp_done; k++) {
-            const int jj = k * 32 + lane;
             if (k * 32 >= cnt) break;
-            const float4 bx = s_box[jj];
+            const int jj = k * 32 + lane;
+            const float4 bx = st.box[jj];
             const bool hit = jj < cnt && bx.x <= strip_x1 && bx.y >= strip_x0 && bx.z <= strip_y1 && bx.w >= strip_y0;
             uint32_t m = __ballot_sync(0xffffffffu, hit);
             while (m) {
@@ -117,18 +130,21 @@ __global__ void __launch_bounds__(256, 4) render_forward_kernel(
                 const int j = k * 32 + __ffs(m) - 1;
                 m &= m - 1;
                 if (done) continue;
-                const float4 g0 = *reinterpret_cast<const float4*>(&s_geo[j]);        // x, y, ca, cb
-                const float4 g1 = *reinterpret_cast<const float4*>(&s_geo[j].cc);     // cc, op, nx, id_inside
+                const float4 g0 = *reinterpret_cast<const float4*>(&st.geo[j]);        // x, y, ca, cb
+                const float4 g1 = *reinterpret_cast<const float4*>(&st.geo[j].cc);     // cc, op, nx, id_inside
                 const float dx = g0.x - pfx, dy = g0.y - pfy;
                 // power = -0.5f*(ca*dx*dx + cc*dy*dy) - cb*dx*dy, contracted exactly like the reference build
                 const float q = __fmaf_rn(__fmul_rn(g0.z, dx), dx, __fmul_rn(__fmul_rn(g1.x, dy), dy));
                 const float power = __fmaf_rn(q, -0.5f, -__fmul_rn(__fmul_rn(g0.w, dx), dy));
                 if (power > 0.0f) continue;
-
+                // the reference tests depth before alpha (forward.cu:382-391); both are side-effect-free `continue`s,
+                // so alpha goes first here: most rejected pairs fail it, and it spares them the IEEE division
+                const float alpha = fminf(0.99f, g1.y * expf(power));
+                if (alpha < 1.0f / 255.0f) continue;
                 float depth = 0.f;
                 float4 nrm = make_float4(0.f, 0.f, 0.f, 0.f);
                 if (MODE == 0) {
-                    nrm = s_nrm[j];
+                    nrm = st.nrm[j];
                     if (HAS_DIRS) {
                         const float t = g1.z / (nrm.x * dir.x + nrm.y * dir.y + nrm.z * dir.z);
                         depth = t * dir.z;
@@ -137,8 +153,6 @@ __global__ void __launch_bounds__(256, 4) render_forward_kernel(
                     }
                     if (depth < 0.2f) continue;  // == (double)depth <= 0.2, forward.cu:382
                 }
-                const float alpha = fminf(0.99f, g1.y * expf(power));
-                if (alpha < 1.0f / 255.0f) continue;
                 const uint32_t idi = __float_as_uint(g1.w);
                 if (MODE == VCR_MODE_VISI_ACC) {  // first contributor only (forward.cu:809-826)
                     atomicAdd(gaussian_count + (idi >> 1), 1);  // reference: racy ++ (forward.cu:822)
@@ -147,7 +161,7 @@ __global__ void __launch_bounds__(256, 4) render_forward_kernel(
                 }
                 const float test_T = T * (1 - alpha);
                 if (test_T < 0.0001f) { done = true; continue; }
-                const float4 col = s_col[j];
+                const float4 col = st.col[j];
                 if (MODE == VCR_MODE_COUNT) {
                     // the reference's plain ++ / += race between pixels (forward.cu:575-576); atomics give the exact totals
                     atomicAdd(gaussian_count + (idi >> 1), 1);
@@ -156,10 +170,7 @@ __global__ void __launch_bounds__(256, 4) render_forward_kernel(
                 } else {
                     const float w = alpha * T;
                     C[0] = __fmaf_rn(col.x, w, C[0]); C[1] = __fmaf_rn(col.y, w, C[1]); C[2] = __fmaf_rn(col.z, w, C[2]);
-                    if (HAS_OBJ) {
-                        const float2 o = s_obj[j];
-                        O[0] = __fmaf_rn(o.x, w, O[0]); O[1] = __fmaf_rn(o.y, w, O[1]);
-                    }
+                    if (HAS_OBJ) { O[0] = __fmaf_rn(nrm.w, w, O[0]); O[1] = __fmaf_rn(col.w, w, O[1]); }
                     weight += w;
                     if (idi & 1u) {
                         D = __fmaf_rn(depth, w, D);
@@ -170,6 +181,8 @@ __global__ void __launch_bounds__(256, 4) render_forward_kernel(
                 last_contributor = (uint32_t)(i * RF_BATCH + j + 1);
             }
         }
+        // one barrier per batch: publishes batch i+1, frees buffer `buf` for batch i+2, and votes on completion
+        if (__syncthreads_and(done)) break;
     }
 
     if (inside && MODE != VCR_MODE_VISI_ACC) {
