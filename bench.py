@@ -209,6 +209,7 @@ class Stepper:
         self.dirs = inp0["dirs"].to(dev)
         self.K = views[0]["cam"].intr.to(dev)
         self.K_host = views[0]["cam"].intr
+        self.K4 = (float(self.K_host[0, 0]), float(self.K_host[1, 1]), float(self.K_host[0, 2]), float(self.K_host[1, 2]))
         self.tanx, self.tany = inp0["tanfovx"], inp0["tanfovy"]
         self.h2d_bytes = sum(t.numel() * t.element_size() for t in self.host[0].values())
         self.d2h_bytes = 4
@@ -268,19 +269,18 @@ class Stepper:
             out, radii = self.GR(rs)(means3D=p["means3D"], means2D=means2D, means2D_densify=means2D_densify, shs=p["shs"],
                                      normals_precomp=normals, opacities=p["opacities"], scales=p["scales"],
                                      rotations=p["rotations"], dirs=self.dirs, inside=self.inside)
-        # channel split exactly like render() (gaussian_renderer/__init__.py:122-123, 133-134)
-        image, depth, normal, _alpha, _sem = out.split([3, 1, 3, 1, 2], dim=0)
-        rn = F.normalize(normal.permute(1, 2, 0), dim=-1)
         gt_n = d["gt_normal"]
-        loss = (image - d["gt_image"]).abs().mean()
-        loss = loss + LAMBDA_MONO * ((rn - gt_n).abs().sum(-1).mean() + (1.0 - (rn * gt_n).sum(-1)).mean())
         if self.impl == "reference":
+            # channel split exactly like render() (gaussian_renderer/__init__.py:122-123, 133-134), losses as in trainer.py
+            image, depth, normal, _alpha, _sem = out.split([3, 1, 3, 1, 2], dim=0)
+            rn = F.normalize(normal.permute(1, 2, 0), dim=-1)
+            loss = (image - d["gt_image"]).abs().mean()
+            loss = loss + LAMBDA_MONO * ((rn - gt_n).abs().sum(-1).mean() + (1.0 - (rn * gt_n).sum(-1)).mean())
             loss = loss + LAMBDA_DN * ref_dnormal_chain(depth, self.K, gt_n, rn, EXP_T)
         else:
-            from vcr_dnormal import depth_normal_loss
-            loss = loss + LAMBDA_DN * depth_normal_loss(depth, (float(self.K_host[0, 0]), float(self.K_host[1, 1]),
-                                                               float(self.K_host[0, 2]), float(self.K_host[1, 2])),
-                                                        gt_n, normal.permute(1, 2, 0), None, exp_t=EXP_T)
+            # the same three terms through this repository's public loss API (one fused kernel per direction)
+            from vcr_dnormal import view_loss
+            loss = view_loss(out, d["gt_image"], gt_n, self.K4, w_l1=1.0, w_mono=LAMBDA_MONO, w_dn=LAMBDA_DN, exp_t=EXP_T)
         self.bucket.zero_grad()
         normals.grad = None
         loss.backward()

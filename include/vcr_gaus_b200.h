@@ -186,6 +186,23 @@ int vcr_dnormal_backward(const float* depth, const float* gt_normal, const float
                          const float* sums, const float* dL_dloss, const float* dL_dest_normal /* optional f32[H,W,3] */,
                          float* dL_ddepth, void* stream);
 
+/* Fused per-view image loss on the rasterizer's output map (outmap f32[10,H,W], planes as in vcr_rasterize_forward):
+ *   loss = w_l1 * mean|RGB - gt_image| + w_mono * monosdf_normal_loss(normalize(normal planes), gt_normal)
+ *        + w_dn * D-Normal(depth plane, gt_normal, confidence from the normal planes)
+ * i.e. l1_loss (tools/loss_utils.py:22-23, trainer.py:236), the mono-normal term (trainer.py:261-264 with
+ * gaussian_renderer/__init__.py:133-134) and the depth-normal term (trainer.py:266-280), ~60 PyTorch launches per view in
+ * the reference, as one kernel per direction.  gt_image f32[3,H,W], gt_normal f32[H,W,3], mask u8[H*W] or NULL.
+ * forward fills sums[8] (zeroed inside): { sum|dRGB|, sum|rn-g|_1, sum(1-rn.g), sum_M w|n-g|_1, sum_M w(1-n.g), |M|, -, - };
+ * loss = w_l1*s0/(3N) + w_mono*(s1+s2)/N + w_dn*(s3+s4)/s5 (the last term 0 when s5 == 0).
+ * backward writes dL/d outmap f32[10,H,W] in full, given dL_dloss (DEVICE scalar) and the forward's sums. */
+int vcr_view_loss_forward(const float* outmap, const float* gt_image, const float* gt_normal, const uint8_t* mask,
+                          int width, int height, float fx, float fy, float cx, float cy, float exp_t, float mask_depth_max,
+                          float* sums, void* stream);
+int vcr_view_loss_backward(const float* outmap, const float* gt_image, const float* gt_normal, const uint8_t* mask,
+                           int width, int height, float fx, float fy, float cx, float cy, float exp_t, float mask_depth_max,
+                           const float* sums, const float* dL_dloss, float w_l1, float w_mono, float w_dn,
+                           float* dL_doutmap, void* stream);
+
 /* distCUDA2: mean squared distance to the 3 nearest neighbours.  scratch must hold
  * vcr_knn_scratch_bytes(P) bytes. */
 size_t vcr_knn_scratch_bytes(int P);

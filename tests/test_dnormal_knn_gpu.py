@@ -16,8 +16,8 @@ def ref_chain(depth, K, gt_normal, render_normal, mask, exp_t):
     """The reference op chain, verbatim semantics, in PyTorch (depth [1,H,W] requires grad)."""
     _, H, W = depth.shape
     dev = depth.device
-    vx = torch.arange(W, dtype=torch.float32, device=dev).add_(0.5) / (W - 1)
-    vy = torch.arange(H, dtype=torch.float32, device=dev).add_(0.5) / (H - 1)
+    vx = torch.arange(W, dtype=depth.dtype, device=dev).add_(0.5) / (W - 1)
+    vy = torch.arange(H, dtype=depth.dtype, device=dev).add_(0.5) / (H - 1)
     vy, vx = torch.meshgrid(vy, vx, indexing="ij")
     ndc = torch.stack([vx, vy, depth[0]], dim=-1)
     inv_scale = torch.tensor([[W - 1, H - 1]], device=dev)
@@ -121,3 +121,40 @@ def test_knn_large_property():
     d[torch.arange(64), sel] = float("inf")
     ref = d.topk(3, largest=False).values.mean(dim=1).float()
     np.testing.assert_allclose(out[sel].cpu().numpy(), ref.cpu().numpy(), rtol=1e-4)
+
+
+@pytest.mark.parametrize("W,H,use_mask", [(96, 64, True), (161, 87, False)])
+def test_fused_view_loss_matches_the_pytorch_composition(W, H, use_mask):
+    """vcr_view_loss (L1 + mono-normal + D-Normal in one kernel per direction) against the same loss composed from
+    PyTorch ops in float64 the way trainer.py does it (l1_loss, F.normalize, monosdf_normal_loss, cos_weight, masks)."""
+    from vcr_dnormal import view_loss
+    dev = torch.device("cuda")
+    depth, gt_n, rn_raw, mask, K = make_dn_inputs(W, H, seed=5 * W + H)
+    g = torch.Generator().manual_seed(W)
+    out = torch.zeros((10, H, W))
+    out[0:3] = torch.rand((3, H, W), generator=g)
+    out[3] = depth[0]
+    out[4:7] = rn_raw.permute(2, 0, 1)
+    out[7] = torch.rand((H, W), generator=g)
+    gt_img = torch.rand((3, H, W), generator=g)
+    w_l1, w_mono, w_dn, exp_t = 0.8, 0.05, 0.015, 0.5
+    o32 = out.to(dev).requires_grad_(True)
+    loss, sums = view_loss(o32, gt_img.to(dev), gt_n.to(dev), K, mask=mask.to(dev) if use_mask else None, w_l1=w_l1, w_mono=w_mono,
+                           w_dn=w_dn, exp_t=exp_t, return_terms=True)
+    loss.backward()
+    # float64 composition
+    o = out.double().to(dev).requires_grad_(True)
+    image, d, normal = o[0:3], o[3:4], o[4:7]
+    rn = F.normalize(normal.permute(1, 2, 0), dim=-1)
+    gn = gt_n.double().to(dev)
+    l1 = (image - gt_img.double().to(dev)).abs().mean()
+    mono = (rn - gn).abs().sum(-1).mean() + (1.0 - (rn * gn).sum(-1)).mean()
+    m = mask.to(dev) if use_mask else torch.ones((H, W), dtype=torch.bool, device=dev)
+    dn, _ = ref_chain(d, K.double().to(dev), gn, rn.detach(), m, exp_t)
+    ref = w_l1 * l1 + w_mono * mono + w_dn * dn
+    ref.backward()
+    assert abs(float(loss.detach()) - float(ref.detach())) <= 1e-5 * max(1.0, abs(float(ref.detach())))
+    for sl, name in ((slice(0, 3), "rgb"), (slice(3, 4), "depth"), (slice(4, 7), "normal")):
+        e = rel_l2(o32.grad[sl].cpu().numpy(), o.grad[sl].cpu().numpy())
+        assert e <= 1e-3, f"{name}: relative L2 error {e}"
+    assert float(o32.grad[7:].abs().max()) == 0.0

@@ -21,6 +21,7 @@ struct DnParams {
     const float* depth; const float* gt; const float* rn; const uint8_t* mask;
     int W, H;
     float inv_fx, inv_fy, cx, cy, exp_t, mask_depth_max;
+    size_t rn_ps, rn_cs;   // element strides of the rendered normal: per pixel / per channel (HWC: 3,1 ; CHW planes: 1,H*W)
 };
 
 // torch.gradient (spacing 1, edge_order 1): central differences inside, one-sided at the borders.
@@ -56,7 +57,7 @@ __device__ __forceinline__ bool dn_masked_in(const DnParams& p, size_t pix) {
 }
 __device__ __forceinline__ float dn_weight(const DnParams& p, size_t pix, const float3 g) {
     if (!(p.exp_t > 0.f)) return 1.0f;
-    const float rx = __ldg(p.rn + 3 * pix), ry = __ldg(p.rn + 3 * pix + 1), rz = __ldg(p.rn + 3 * pix + 2);
+    const float rx = __ldg(p.rn + p.rn_ps * pix), ry = __ldg(p.rn + p.rn_ps * pix + p.rn_cs), rz = __ldg(p.rn + p.rn_ps * pix + 2 * p.rn_cs);
     const float rl = fmaxf(sqrtf(rx * rx + ry * ry + rz * rz), 1e-12f);  // F.normalize eps
     const float cs = (rx * g.x + ry * g.y + rz * g.z) / rl;
     return expf((cs - 1.0f) / p.exp_t);
@@ -163,7 +164,158 @@ __global__ void __launch_bounds__(256) dnormal_backward_kernel(const DnParams p,
     dL_ddepth[(size_t)v * p.W + u] = gX.x * ax + gX.y * ay + gX.z;
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// Fused per-view image loss: everything trainer.py computes from the rasterizer's output map in image space, except
+// SSIM, in one kernel per direction:
+//   l1          = mean |render - gt_image|                                   tools/loss_utils.py l1_loss, trainer.py:236
+//   mono_normal = monosdf_normal_loss(normalize(render_normal), gt_normal)    trainer.py:261-264, loss_utils.py:122-132
+//   depth_normal (D-Normal, as above)                                         trainer.py:266-280
+// forward : sums[6] = { sum |dRGB|, sum |rn-g|_1, sum (1 - rn.g), sum_M w|n-g|_1, sum_M w(1-n.g), |M| }
+//           loss = w_l1 s0/(3N) + w_mono (s1+s2)/N + w_dn (s3+s4)/s5
+// backward: dL/d outmap [10,H,W] written in full (zeros in the alpha / semantic planes).
+// ------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) view_loss_forward_kernel(const DnParams p, const float* __restrict__ out,
+                                                                const float* __restrict__ gt_image, float* __restrict__ sums) {
+    const int u = blockIdx.x * 32 + (threadIdx.x & 31);
+    const int v = blockIdx.y * 8 + (threadIdx.x >> 5);
+    const size_t HW = (size_t)p.W * p.H;
+    float acc[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (u < p.W && v < p.H) {
+        const size_t pix = (size_t)v * p.W + u;
+#pragma unroll
+        for (int c = 0; c < 3; c++) acc[0] += fabsf(__ldg(out + c * HW + pix) - __ldg(gt_image + c * HW + pix));
+        const float3 g = make_float3(__ldg(p.gt + 3 * pix), __ldg(p.gt + 3 * pix + 1), __ldg(p.gt + 3 * pix + 2));
+        const float rx = __ldg(p.rn + pix), ry = __ldg(p.rn + HW + pix), rz = __ldg(p.rn + 2 * HW + pix);
+        const float rinv = 1.0f / fmaxf(sqrtf(rx * rx + ry * ry + rz * rz), 1e-12f);
+        const float3 rn = make_float3(rx * rinv, ry * rinv, rz * rinv);
+        const float rcos = rn.x * g.x + rn.y * g.y + rn.z * g.z;
+        acc[1] = fabsf(rn.x - g.x) + fabsf(rn.y - g.y) + fabsf(rn.z - g.z);
+        acc[2] = 1.0f - rcos;
+        if (dn_masked_in(p, pix)) {
+            const float3 c = cross3(dn_diff_u(p, u, v), dn_diff_v(p, u, v));
+            const float inv = 1.0f / fmaxf(sqrtf(c.x * c.x + c.y * c.y + c.z * c.z), 1e-12f);
+            const float3 n = make_float3(c.x * inv, c.y * inv, c.z * inv);
+            const float w = p.exp_t > 0.f ? expf((rcos - 1.0f) / p.exp_t) : 1.0f;
+            acc[3] = w * (fabsf(n.x - g.x) + fabsf(n.y - g.y) + fabsf(n.z - g.z));
+            acc[4] = w * (1.0f - (n.x * g.x + n.y * g.y + n.z * g.z));
+            acc[5] = 1.f;
+        }
+    }
+    __shared__ float red[6][8];
+#pragma unroll
+    for (int k = 0; k < 6; k++) {
+        const float t = vcr_warp_sum(acc[k]);
+        if ((threadIdx.x & 31) == 0) red[k][threadIdx.x >> 5] = t;
+    }
+    __syncthreads();
+    if (threadIdx.x < 6) {
+        float t = 0.f;
+#pragma unroll
+        for (int k = 0; k < 8; k++) t += red[threadIdx.x][k];
+        if (t != 0.f) atomicAdd(sums + threadIdx.x, t);
+    }
+}
+
+__global__ void __launch_bounds__(256) view_loss_backward_kernel(const DnParams p, const float* __restrict__ out,
+                                                                 const float* __restrict__ gt_image, const float* __restrict__ sums,
+                                                                 const float* __restrict__ dL_dloss, float w_l1, float w_mono,
+                                                                 float w_dn, float* __restrict__ dL_dout) {
+    const int u = blockIdx.x * 32 + (threadIdx.x & 31);
+    const int v = blockIdx.y * 8 + (threadIdx.x >> 5);
+    if (u >= p.W || v >= p.H) return;
+    const size_t HW = (size_t)p.W * p.H;
+    const size_t pix = (size_t)v * p.W + u;
+    const float gl = __ldg(dL_dloss);
+    const float cnt = __ldg(sums + 5);
+    const float a_l1 = gl * w_l1 / (3.0f * (float)HW), a_mono = gl * w_mono / (float)HW;
+    const float a_dn = cnt > 0.f ? gl * w_dn / cnt : 0.f;
+    // RGB: d|x|/dx = sign(x)
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+        const float e = __ldg(out + c * HW + pix) - __ldg(gt_image + c * HW + pix);
+        dL_dout[c * HW + pix] = a_l1 * (float)((e > 0.f) - (e < 0.f));
+    }
+    // rendered normal: gradient of |rn-g|_1 + 1 - rn.g through rn = n / max(|n|, eps)
+    {
+        const float3 g = make_float3(__ldg(p.gt + 3 * pix), __ldg(p.gt + 3 * pix + 1), __ldg(p.gt + 3 * pix + 2));
+        const float rx = __ldg(p.rn + pix), ry = __ldg(p.rn + HW + pix), rz = __ldg(p.rn + 2 * HW + pix);
+        const float len = sqrtf(rx * rx + ry * ry + rz * rz);
+        const float rinv = 1.0f / fmaxf(len, 1e-12f);
+        const float3 rn = make_float3(rx * rinv, ry * rinv, rz * rinv);
+        const float ex = rn.x - g.x, ey = rn.y - g.y, ez = rn.z - g.z;
+        float3 d = make_float3(a_mono * ((float)((ex > 0.f) - (ex < 0.f)) - g.x), a_mono * ((float)((ey > 0.f) - (ey < 0.f)) - g.y),
+                               a_mono * ((float)((ez > 0.f) - (ez < 0.f)) - g.z));
+        if (len > 1e-12f) {
+            const float dd = d.x * rn.x + d.y * rn.y + d.z * rn.z;
+            d = make_float3((d.x - rn.x * dd) * rinv, (d.y - rn.y * dd) * rinv, (d.z - rn.z * dd) * rinv);
+        } else {
+            d = make_float3(d.x * rinv, d.y * rinv, d.z * rinv);
+        }
+        dL_dout[4 * HW + pix] = d.x; dL_dout[5 * HW + pix] = d.y; dL_dout[6 * HW + pix] = d.z;
+    }
+    // depth: the D-Normal 5-point gather (same as dnormal_backward_kernel)
+    float3 gX = make_float3(0.f, 0.f, 0.f);
+    auto via_dx = [&](int qu, float coef) {
+        float3 dx, dy;
+        const float3 gc = dn_grad_c(p, qu, v, a_dn, nullptr, dx, dy);
+        const float3 t = cross3(dy, gc);
+        gX.x += coef * t.x; gX.y += coef * t.y; gX.z += coef * t.z;
+    };
+    auto via_dy = [&](int qv, float coef) {
+        float3 dx, dy;
+        const float3 gc = dn_grad_c(p, u, qv, a_dn, nullptr, dx, dy);
+        const float3 t = cross3(gc, dx);
+        gX.x += coef * t.x; gX.y += coef * t.y; gX.z += coef * t.z;
+    };
+    if (a_dn != 0.f) {
+        if (p.W > 1) {
+            if (u > 0) { const int q = u - 1; via_dx(q, (q > 0) ? 0.5f : 1.0f); }
+            if (u < p.W - 1) { const int q = u + 1; via_dx(q, (q < p.W - 1) ? -0.5f : -1.0f); }
+            if (u == 0) via_dx(0, -1.0f);
+            if (u == p.W - 1) via_dx(u, 1.0f);
+        }
+        if (p.H > 1) {
+            if (v > 0) { const int q = v - 1; via_dy(q, (q > 0) ? 0.5f : 1.0f); }
+            if (v < p.H - 1) { const int q = v + 1; via_dy(q, (q < p.H - 1) ? -0.5f : -1.0f); }
+            if (v == 0) via_dy(0, -1.0f);
+            if (v == p.H - 1) via_dy(v, 1.0f);
+        }
+    }
+    const float ax = ((u + 0.5f) - p.cx) * p.inv_fx, ay = ((v + 0.5f) - p.cy) * p.inv_fy;
+    dL_dout[3 * HW + pix] = gX.x * ax + gX.y * ay + gX.z;
+    dL_dout[7 * HW + pix] = 0.f; dL_dout[8 * HW + pix] = 0.f; dL_dout[9 * HW + pix] = 0.f;
+}
+
 extern "C" {
+
+int vcr_view_loss_forward(const float* outmap, const float* gt_image, const float* gt_normal, const uint8_t* mask, int width,
+                          int height, float fx, float fy, float cx, float cy, float exp_t, float mask_depth_max, float* sums,
+                          void* stream) {
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    if (!outmap || !gt_image || !gt_normal || !sums || width <= 0 || height <= 0) { vcr_set_error("view_loss_forward: bad argument"); return 1; }
+    const size_t HW = (size_t)width * height;
+    DnParams p{outmap + 3 * HW, gt_normal, outmap + 4 * HW, mask, width, height, 1.0f / fx, 1.0f / fy, cx, cy, exp_t, mask_depth_max, 1, HW};
+    { VcrProfScope m(VCR_K_MEMSET, s); VCR_CUDA_TRY(cudaMemsetAsync(sums, 0, 8 * sizeof(float), s)); }
+    const dim3 grid((width + 31) / 32, (height + 7) / 8);
+    VcrProfScope prof(VCR_K_DNORMAL_FWD, s);
+    view_loss_forward_kernel<<<grid, 256, 0, s>>>(p, outmap, gt_image, sums);
+    VCR_LAUNCH_CHECK("view_loss_forward_kernel");
+    return 0;
+}
+
+int vcr_view_loss_backward(const float* outmap, const float* gt_image, const float* gt_normal, const uint8_t* mask, int width,
+                           int height, float fx, float fy, float cx, float cy, float exp_t, float mask_depth_max, const float* sums,
+                           const float* dL_dloss, float w_l1, float w_mono, float w_dn, float* dL_doutmap, void* stream) {
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    if (!outmap || !gt_image || !gt_normal || !sums || !dL_dloss || !dL_doutmap || width <= 0 || height <= 0) { vcr_set_error("view_loss_backward: bad argument"); return 1; }
+    const size_t HW = (size_t)width * height;
+    DnParams p{outmap + 3 * HW, gt_normal, outmap + 4 * HW, mask, width, height, 1.0f / fx, 1.0f / fy, cx, cy, exp_t, mask_depth_max, 1, HW};
+    const dim3 grid((width + 31) / 32, (height + 7) / 8);
+    VcrProfScope prof(VCR_K_DNORMAL_BWD, s);
+    view_loss_backward_kernel<<<grid, 256, 0, s>>>(p, outmap, gt_image, sums, dL_dloss, w_l1, w_mono, w_dn, dL_doutmap);
+    VCR_LAUNCH_CHECK("view_loss_backward_kernel");
+    return 0;
+}
 
 int vcr_dnormal_forward(const float* depth, const float* gt_normal, const float* render_normal, const uint8_t* mask, int width,
                         int height, float fx, float fy, float cx, float cy, float exp_t, float mask_depth_max, float* est_normal,
@@ -171,7 +323,7 @@ int vcr_dnormal_forward(const float* depth, const float* gt_normal, const float*
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
     if (!depth || !gt_normal || !sums || width <= 0 || height <= 0) { vcr_set_error("dnormal_forward: bad argument"); return 1; }
     if (exp_t > 0.f && !render_normal) { vcr_set_error("dnormal_forward: render_normal is required when exp_t > 0"); return 1; }
-    DnParams p{depth, gt_normal, render_normal, mask, width, height, 1.0f / fx, 1.0f / fy, cx, cy, exp_t, mask_depth_max};
+    DnParams p{depth, gt_normal, render_normal, mask, width, height, 1.0f / fx, 1.0f / fy, cx, cy, exp_t, mask_depth_max, 3, 1};
     if (zero_sums) VCR_CUDA_TRY(cudaMemsetAsync(sums, 0, 3 * sizeof(float), s));
     const dim3 grid((width + 31) / 32, (height + 7) / 8);
     VcrProfScope prof(VCR_K_DNORMAL_FWD, s);
@@ -186,7 +338,7 @@ int vcr_dnormal_backward(const float* depth, const float* gt_normal, const float
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
     if (!depth || !gt_normal || !sums || !dL_dloss || !dL_ddepth || width <= 0 || height <= 0) { vcr_set_error("dnormal_backward: bad argument"); return 1; }
     if (exp_t > 0.f && !render_normal) { vcr_set_error("dnormal_backward: render_normal is required when exp_t > 0"); return 1; }
-    DnParams p{depth, gt_normal, render_normal, mask, width, height, 1.0f / fx, 1.0f / fy, cx, cy, exp_t, mask_depth_max};
+    DnParams p{depth, gt_normal, render_normal, mask, width, height, 1.0f / fx, 1.0f / fy, cx, cy, exp_t, mask_depth_max, 3, 1};
     const dim3 grid((width + 31) / 32, (height + 7) / 8);
     VcrProfScope prof(VCR_K_DNORMAL_BWD, s);
     dnormal_backward_kernel<<<grid, 256, 0, s>>>(p, sums, dL_dloss, dL_dest_normal, dL_ddepth);

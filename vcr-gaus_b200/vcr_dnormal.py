@@ -89,3 +89,53 @@ def compute_normals(depth_map, K):
     none_mask = torch.zeros((H, W), dtype=torch.uint8, device=depth_map.device)  # empty mask: loss part is identically 0
     _, est = _DNormal.apply(depth_map, dummy, None, none_mask, _intr(K), 0.0, 0.0, True)
     return est
+
+
+class _ViewLoss(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, outmap, gt_image, gt_normal, mask, intr, exp_t, mask_depth_max, w_l1, w_mono, w_dn):
+        if not outmap.is_cuda:
+            raise RuntimeError("view_loss (B200 build) needs CUDA tensors; there is no CPU fallback")
+        C, H, W = outmap.shape
+        if C != 10:
+            raise RuntimeError("view_loss expects the rasterizer's [10,H,W] output map")
+        o = outmap.contiguous()
+        gi = gt_image.contiguous().to(torch.float32)
+        gn = gt_normal.contiguous().to(torch.float32)
+        m = mask.contiguous().to(torch.uint8) if mask is not None else None
+        fx, fy, cx, cy = intr
+        sums = torch.empty(8, dtype=torch.float32, device=o.device)
+        _n.check(_n.vcr_view_loss_forward(o.data_ptr(), gi.data_ptr(), gn.data_ptr(), _n.ptr(m), W, H, fx, fy, cx, cy,
+                                          float(exp_t), float(mask_depth_max), sums.data_ptr(), _stream()), "view_loss_forward")
+        ctx.save_for_backward(o, gi, gn, m if m is not None else torch.empty(0, dtype=torch.uint8, device=o.device), sums)
+        ctx.meta = (W, H, fx, fy, cx, cy, float(exp_t), float(mask_depth_max), float(w_l1), float(w_mono), float(w_dn))
+        N = float(H * W)
+        dn = torch.where(sums[5] > 0, (sums[3] + sums[4]) / torch.clamp(sums[5], min=1.0), torch.zeros_like(sums[5]))
+        loss = w_l1 * sums[0] / (3.0 * N) + w_mono * (sums[1] + sums[2]) / N + w_dn * dn
+        ctx.mark_non_differentiable(sums)
+        return loss, sums
+
+    @staticmethod
+    def backward(ctx, g_loss, _g_sums):
+        o, gi, gn, m, sums = ctx.saved_tensors
+        W, H, fx, fy, cx, cy, exp_t, mdm, w_l1, w_mono, w_dn = ctx.meta
+        gl = g_loss.contiguous().to(torch.float32).reshape(1)
+        g_out = torch.empty_like(o)
+        _n.check(_n.vcr_view_loss_backward(o.data_ptr(), gi.data_ptr(), gn.data_ptr(), _n.ptr(m), W, H, fx, fy, cx, cy, exp_t, mdm,
+                                           sums.data_ptr(), gl.data_ptr(), w_l1, w_mono, w_dn, g_out.data_ptr(), _stream()),
+                 "view_loss_backward")
+        return g_out, None, None, None, None, None, None, None, None, None
+
+
+def view_loss(outmap, gt_image, gt_normal, intr, mask=None, w_l1=1.0, w_mono=0.0, w_dn=0.0, exp_t=0.0, mask_depth_max=0.0,
+              return_terms=False):
+    """All image-space loss terms of one training view (except SSIM) from the rasterizer's [10,H,W] output map, fused:
+
+        w_l1 * l1_loss(render, gt_image)                                   (trainer.py:236, tools/loss_utils.py:22-23)
+      + w_mono * monosdf_normal_loss(normalize(render_normal), gt_normal)  (trainer.py:261-264)
+      + w_dn * depth-normal loss with confidence weights                   (trainer.py:266-280)
+
+    gt_image [3,H,W], gt_normal [H,W,3], intr = 3x3 K or (fx,fy,cx,cy), mask bool/uint8 [H,W] (D-Normal term only).
+    Returns the scalar loss; with return_terms also the raw sums (see include/vcr_gaus_b200.h) for logging."""
+    loss, sums = _ViewLoss.apply(outmap, gt_image, gt_normal, mask, _intr(intr), exp_t, mask_depth_max, w_l1, w_mono, w_dn)
+    return (loss, sums) if return_terms else loss

@@ -72,6 +72,13 @@ vcr_dnormal_forward = _sig(
 vcr_dnormal_backward = _sig(
     "vcr_dnormal_backward", c_int,
     [P_, P_, P_, P_, c_int, c_int, c_float, c_float, c_float, c_float, c_float, c_float, P_, P_, P_, P_, c_void_p])
+vcr_view_loss_forward = _sig(
+    "vcr_view_loss_forward", c_int,
+    [P_, P_, P_, P_, c_int, c_int, c_float, c_float, c_float, c_float, c_float, c_float, P_, c_void_p])
+vcr_view_loss_backward = _sig(
+    "vcr_view_loss_backward", c_int,
+    [P_, P_, P_, P_, c_int, c_int, c_float, c_float, c_float, c_float, c_float, c_float, P_, P_, c_float, c_float, c_float, P_,
+     c_void_p])
 vcr_dist2_knn3 = _sig("vcr_dist2_knn3", c_int, [c_int, P_, P_, P_, c_void_p])
 vcr_knn_noalloc_max_points = _sig("vcr_knn_noalloc_max_points", c_int, [])
 vcr_dist2_knn3_noalloc = _sig("vcr_dist2_knn3_noalloc", c_int, [c_int, P_, P_, c_void_p])
@@ -116,7 +123,7 @@ DECLARED_SYMBOLS = [
     "vcr_rasterize_forward", "vcr_backward_scratch_bytes", "vcr_rasterize_backward", "vcr_mark_visible",
     "vcr_rasterize_count", "vcr_rasterize_visi_acc", "vcr_dnormal_forward", "vcr_dnormal_backward",
     "vcr_knn_scratch_bytes", "vcr_dist2_knn3", "vcr_geom_layout", "vcr_binning_layout", "vcr_image_layout",
-    "vcr_knn_noalloc_max_points", "vcr_dist2_knn3_noalloc",
+    "vcr_knn_noalloc_max_points", "vcr_dist2_knn3_noalloc", "vcr_view_loss_forward", "vcr_view_loss_backward",
     "vcr_profile_enable", "vcr_profile_kernel_count", "vcr_profile_kernel_name", "vcr_profile_read",
 ]
 
