@@ -177,11 +177,11 @@ class RefRasterFn(torch.autograd.Function):
         return None, g3d, gsh, gnrm, gop, gsc, grot, None, None, None
 
 
-def clone_params(scene, dev):
+def clone_params(scene, dev, direct=False):
     import vcr_view_parallel as VP
     tensors = dict(means3D=scene.means3D.to(dev), shs=scene.shs.to(dev), opacities=scene.opacities.to(dev),
                    scales=scene.scales.to(dev), rotations=scene.rotations.to(dev))
-    return VP.GaussianBucket(tensors, device=dev)
+    return VP.GaussianBucket(tensors, device=dev, direct=direct)
 
 
 class Stepper:
@@ -283,9 +283,10 @@ class Stepper:
             loss = view_loss(out, d["gt_image"], gt_n, self.K4, w_l1=1.0, w_mono=LAMBDA_MONO, w_dn=LAMBDA_DN, exp_t=EXP_T)
         self.bucket.zero_grad()
         normals.grad = None
-        loss.backward()
+        # mean over ranks = SUM all-reduce of gradients of loss / world (no separate division pass over the bucket)
+        (loss / self.vp.world if self.vp.world > 1 else loss).backward()
         if self.vp.world > 1:
-            self.vp.allreduce_gradients(self.bucket, average=True)
+            self.vp.allreduce_gradients(self.bucket, average=False)
             if means2D_densify is not None:
                 self.vp.reduce_densification_stats(self.xyz_gradient_accum, self.denom, self.max_radii2D,
                                                    means2D_densify.grad, radii)
@@ -366,23 +367,28 @@ def main():
             if rank == 0:
                 print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/_C.so (reference CUDA build) not present on this box"}))
             return
-    bucket = clone_params(scene, dev)
+    bucket = clone_params(scene, dev, direct=(impl == "ours"))
     stepper = Stepper(args, impl, bucket, views, dev, vp)
 
     import vcr_native as N
     prof = (impl == "ours") and not args.no_profile
-    # ---- device-resident timing (`value`) ----
+    # ---- device-resident timing (`value`): K steps, launch counters on, per-kernel event brackets OFF ----
     if impl == "ours":
-        N.profile_read(reset=True)
-        N.vcr_profile_enable(1 if prof else 0)
+        N.vcr_profile_enable(0)
     for i in range(args.warmup):
         stepper.step(i, False)
     torch.cuda.synchronize(dev)
     if impl == "ours":
         N.profile_read(reset=True)
     ms, clocks = timed_region(stepper, args.steps, 0, False, dev, world, sample_clocks=True)
-    kern = N.profile_read(reset=True) if impl == "ours" else {}
-    if impl == "ours":
+    counts = N.profile_read(reset=True) if impl == "ours" else {}
+    # ---- the same K steps once more with every kernel of the library bracketed by CUDA events on its stream ----
+    # (the brackets cost ~5-10 % of a step, so they are kept out of `value`; `ms_per_step_with_kernel_events` reports it)
+    kern, ms_prof = {}, None
+    if prof:
+        N.vcr_profile_enable(1)
+        ms_prof, _ = timed_region(stepper, args.steps, 1, False, dev, world)
+        kern = N.profile_read(reset=True)
         N.vcr_profile_enable(0)
     # ---- end-to-end timing (`e2e`): per-view inputs from pinned host memory, loss read back ----
     ms_e2e, _ = timed_region(stepper, args.steps, min(args.warmup, 3), True, dev, world)
@@ -422,7 +428,7 @@ def main():
     peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
     stats = scene_stats(stepper, args)
     per_kernel = kernel_table(kern, stats, args, hbm_peak)
-    launches = sum(v[2] for k, v in kern.items() if k != "memset")
+    launches = sum(v[2] for k, v in counts.items() if k != "memset")
     out["gpu_launches"] = launches
     if per_kernel:
         dom = max(per_kernel, key=lambda r: r["ms_per_step"])
@@ -431,6 +437,7 @@ def main():
                            "algorithmic_bytes_per_launch": dom["bytes_per_launch"],
                            "note": "compositing kernels are FP32-issue / atomic bound, not HBM bound (DESIGN.md); the HBM fraction is reported as the contract asks"}
         out["kernels"] = per_kernel
+        out["ms_per_step_with_kernel_events"] = ms_prof / args.steps if ms_prof else None
     out["scene"] = stats
     if not args.no_cpu_baseline and world == 1:
         vps, dt, R = cpu_oracle_views_per_s(args, views[0])

@@ -14,7 +14,7 @@ def main(impl):
     dev = torch.device("cuda", 0); torch.cuda.set_device(dev)
     vp = VP.ViewParallel()
     scene, views = bench.build_workload(args, 0, 1)
-    bucket = bench.clone_params(scene, dev)
+    bucket = bench.clone_params(scene, dev, direct=(impl == "ours"))
     st = bench.Stepper(args, impl, bucket, views, dev, vp)
     for i in range(4): st.step(i, False)
     torch.cuda.synchronize()

@@ -173,28 +173,29 @@ __global__ void __launch_bounds__(256) radix_scan_hist_kernel(uint32_t* __restri
 //   - pairs are first scattered into shared memory in block-sorted order so the global stores are
 //     runs of consecutive addresses per digit
 // ------------------------------------------------------------------------------------------------
-#define RADIX_THREADS 256
-#define RADIX_ITEMS 16
+#define RADIX_THREADS 512
+#define RADIX_WARPS (RADIX_THREADS / 32)
+#define RADIX_ITEMS 8
 #define RADIX_TILE (RADIX_THREADS * RADIX_ITEMS)
 #define FLAG_LOCAL 0x40000000u
 #define FLAG_GLOBAL 0x80000000u
 #define FLAG_MASK 0xC0000000u
-#define RADIX_SMEM_BYTES (RADIX_TILE * 8 + RADIX_TILE * 4 + 8 * 256 * 4 + 256 * 4 + 256 * 4 + 64)
+#define RADIX_SMEM_BYTES (RADIX_TILE * 8 + RADIX_TILE * 4 + RADIX_WARPS * 256 * 4 + 256 * 4 + 256 * 4 + 128)
 
-__global__ void __launch_bounds__(RADIX_THREADS) radix_pass_kernel(const uint64_t* __restrict__ keys_in,
-                                                                   const uint32_t* __restrict__ vals_in,
-                                                                   uint64_t* __restrict__ keys_out,
-                                                                   uint32_t* __restrict__ vals_out, uint32_t R, int shift,
-                                                                   int nbits, const uint32_t* __restrict__ digit_base,
-                                                                   volatile uint32_t* status, uint32_t* ticket,
-                                                                   uint32_t* err_flag) {
+__global__ void __launch_bounds__(RADIX_THREADS, 2) radix_pass_kernel(const uint64_t* __restrict__ keys_in,
+                                                                      const uint32_t* __restrict__ vals_in,
+                                                                      uint64_t* __restrict__ keys_out,
+                                                                      uint32_t* __restrict__ vals_out, uint32_t R, int shift,
+                                                                      int nbits, const uint32_t* __restrict__ digit_base,
+                                                                      volatile uint32_t* status, uint32_t* ticket,
+                                                                      uint32_t* err_flag) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint64_t* s_keys = reinterpret_cast<uint64_t*>(smem_raw);
     uint32_t* s_vals = reinterpret_cast<uint32_t*>(smem_raw + RADIX_TILE * 8);
-    uint32_t* s_whist = s_vals + RADIX_TILE;             // [8][256]
-    uint32_t* s_dstart = s_whist + 8 * 256;              // [256] block-local exclusive digit start
+    uint32_t* s_whist = s_vals + RADIX_TILE;             // [RADIX_WARPS][256] per-warp running digit counters
+    uint32_t* s_dstart = s_whist + RADIX_WARPS * 256;    // [256] block-local exclusive digit start
     uint32_t* s_gbase = s_dstart + 256;                  // [256] global base minus local start
-    uint32_t* s_misc = s_gbase + 256;                    // [16]
+    uint32_t* s_misc = s_gbase + 256;                    // [32]
     const int t = threadIdx.x, lane = t & 31, w = t >> 5;
     const uint32_t mask = (1u << nbits) - 1u;
 
@@ -231,55 +232,55 @@ __global__ void __launch_bounds__(RADIX_THREADS) radix_pass_kernel(const uint64_
         __syncwarp();
     }
     __syncthreads();
-    // thread t owns digit t
-    uint32_t cnt = 0;
-    {
+    // threads 0..255 own one digit each
+    uint32_t cnt = 0, inc = 0;
+    volatile uint32_t* my_status = status + (size_t)bid * 256;
+    if (t < 256) {
 #pragma unroll
-        for (int k = 0; k < 8; k++) {
+        for (int k = 0; k < RADIX_WARPS; k++) {
             const uint32_t c = s_whist[k * 256 + t];
             s_whist[k * 256 + t] = cnt;  // exclusive over warps
             cnt += c;
         }
-    }
-    // publish the block-local count as early as possible
-    volatile uint32_t* my_status = status + (size_t)bid * 256;
-    if (bid == 0) my_status[t] = FLAG_GLOBAL | cnt;
-    else my_status[t] = FLAG_LOCAL | cnt;
-    __threadfence();
-    // block-local exclusive scan over digits
-    uint32_t inc = cnt;
+        // Publish the block-local count as early as possible.  Flag and count share one 32-bit word, so no fence is
+        // needed: a reader either sees the old word (keeps polling) or the complete new one.
+        my_status[t] = (bid == 0 ? FLAG_GLOBAL : FLAG_LOCAL) | cnt;
+        // block-local exclusive scan over digits (8 warps)
+        inc = cnt;
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const uint32_t x = __shfl_up_sync(0xffffffffu, inc, o);
-        if (lane >= o) inc += x;
-    }
-    if (lane == 31) s_misc[1 + w] = inc;
-    __syncthreads();
-    uint32_t wex = 0;
-#pragma unroll
-    for (int k = 0; k < 8; k++) wex += (k < w) ? s_misc[1 + k] : 0u;
-    const uint32_t dstart = wex + inc - cnt;
-    s_dstart[t] = dstart;
-    // decoupled look-back
-    uint32_t excl = 0;
-    if (bid > 0) {
-        int j = (int)bid - 1;
-        uint32_t spins = 0;
-        while (true) {
-            const uint32_t v = status[(size_t)j * 256 + t];
-            const uint32_t f = v & FLAG_MASK;
-            if (f == 0u) {
-                if (++spins > (1u << 26)) { atomicExch(err_flag, 1u); break; }
-                continue;
-            }
-            excl += v & ~FLAG_MASK;
-            if (f == FLAG_GLOBAL) break;
-            j--;
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t x = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += x;
         }
-        my_status[t] = FLAG_GLOBAL | (excl + cnt);
-        __threadfence();
+        if (lane == 31) s_misc[1 + w] = inc;
     }
-    s_gbase[t] = digit_base[t] + excl - dstart;
+    __syncthreads();
+    if (t < 256) {
+        uint32_t wex = 0;
+#pragma unroll
+        for (int k = 0; k < 8; k++) wex += (k < w) ? s_misc[1 + k] : 0u;
+        const uint32_t dstart = wex + inc - cnt;
+        s_dstart[t] = dstart;
+        // decoupled look-back
+        uint32_t excl = 0;
+        if (bid > 0) {
+            int j = (int)bid - 1;
+            uint32_t spins = 0;
+            while (true) {
+                const uint32_t v = status[(size_t)j * 256 + t];
+                const uint32_t f = v & FLAG_MASK;
+                if (f == 0u) {
+                    if (++spins > (1u << 26)) { atomicExch(err_flag, 1u); break; }
+                    continue;
+                }
+                excl += v & ~FLAG_MASK;
+                if (f == FLAG_GLOBAL) break;
+                j--;
+            }
+            my_status[t] = FLAG_GLOBAL | (excl + cnt);
+        }
+        s_gbase[t] = digit_base[t] + excl - dstart;
+    }
     __syncthreads();
     // scatter into shared memory in block-sorted order
 #pragma unroll

@@ -143,6 +143,10 @@ class _RasterizeGaussians(torch.autograd.Function):
         geomBuffer, binningBuffer, imgBuffer = bufs.get("geom"), bufs.get("binning"), bufs.get("img")
         ctx.raster_settings = rs
         ctx.num_rendered = num_rendered
+        # Optional zero-copy gradient destinations (vcr_view_parallel.GaussianBucket): a parameter may carry a
+        # `_vcr_grad_out` tensor; the backward kernel then writes that gradient straight into it (every element is
+        # written) and autograd adopts a view of it as `.grad` instead of allocating + accumulating.
+        ctx.grad_out = tuple(getattr(t, "_vcr_grad_out", None) for t in (means3D, sh, opacities, scales, rotations))
         depth, alpha = outmap[3:4], outmap[7:8]
         ctx.save_for_backward(colors_precomp, normals_precomp, semantics_precomp, means3D, scales, rotations, cov3Ds_precomp,
                               radii, sh, geomBuffer, binningBuffer, imgBuffer, alpha, depth, dirs, inside)
@@ -159,17 +163,23 @@ class _RasterizeGaussians(torch.autograd.Function):
         H, W = grad_color.shape[1], grad_color.shape[2]
         M = sh.shape[1] if sh.numel() != 0 else 0
         f = dict(dtype=torch.float32, device=device)
+        def dest(i, shape):
+            buf = ctx.grad_out[i] if hasattr(ctx, "grad_out") else None
+            if buf is not None and buf.is_cuda and buf.dtype == torch.float32 and buf.is_contiguous() and tuple(buf.shape) == tuple(shape):
+                return buf.view(shape)   # a fresh view: autograd can adopt it without a copy
+            return torch.empty(shape, **f)
+
         g_means2D = torch.empty((P, 3), **f)
         g_means2D_densify = torch.empty((P, 3), **f)
         g_colors = torch.empty((P, NUM_CHANNELS), **f)
         g_normals = torch.empty((P, 3), **f)
         g_objects = torch.empty((P, NUM_OBJECTS), **f)
-        g_opacity = torch.empty((P, 1), **f)
-        g_means3D = torch.empty((P, 3), **f)
+        g_opacity = dest(2, (P, 1))
+        g_means3D = dest(0, (P, 3))
         g_cov3D = torch.empty((P, 6), **f)
-        g_sh = torch.empty((P, M, 3), **f)
-        g_scales = torch.empty((P, 3), **f)
-        g_rot = torch.empty((P, 4), **f)
+        g_sh = dest(1, (P, M, 3))
+        g_scales = dest(3, (P, 3))
+        g_rot = dest(4, (P, 4))
         if P != 0:
             scratch = torch.empty(int(_n.vcr_backward_scratch_bytes(P)), dtype=torch.uint8, device=device)
             bg, view, proj, campos = _settings_tensors(rs, device)

@@ -44,7 +44,11 @@ class GaussianBucket:
     `params[name]` are views into `flat`; their `.grad` are views into `grad_flat`, so autograd accumulates straight
     into the bucket and the gradient exchange is a single collective with no packing copy."""
 
-    def __init__(self, tensors: Dict[str, torch.Tensor], device=None):
+    def __init__(self, tensors: Dict[str, torch.Tensor], device=None, direct: bool = False):
+        """direct=True: the rasterizer's backward writes each parameter gradient straight into `grad_flat` (through the
+        `_vcr_grad_out` hook of diff_gaussian_rasterization) and autograd adopts views of it as `.grad` — no per-step
+        memset of the bucket and no accumulate pass.  The price: exactly one backward per `zero_grad()`."""
+        self.direct = direct
         P = tensors["means3D"].shape[0]
         self.P = P
         self.layout = []
@@ -62,11 +66,18 @@ class GaussianBucket:
         for name, o, n, shape in self.layout:
             self.flat[o:o + n].copy_(tensors[name].reshape(-1))
             p = self.flat[o:o + n].view(shape).requires_grad_(True)
-            p.grad = self.grad_flat[o:o + n].view(shape)
+            if direct:
+                p._vcr_grad_out = self.grad_flat[o:o + n].view(shape)
+            else:
+                p.grad = self.grad_flat[o:o + n].view(shape)
             self.params[name] = p
 
     def zero_grad(self):
-        self.grad_flat.zero_()
+        if self.direct:
+            for p in self.params.values():
+                p.grad = None     # the next backward overwrites every element of grad_flat
+        else:
+            self.grad_flat.zero_()
 
     @property
     def floats_per_gaussian(self):
