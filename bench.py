@@ -47,8 +47,8 @@ METRIC = "train views/s (fwd+bwd rasterize + D-Normal loss; 1M Gaussians, 1920x1
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "reference-cpu"])
     ap.add_argument("--gaussians", type=int, default=1_000_000)
     ap.add_argument("--width", type=int, default=1920)
@@ -102,7 +102,7 @@ class ClockSampler(threading.Thread):
                         self.reasons.add(name)
             except Exception:
                 pass
-            time.sleep(0.05)
+            time.sleep(0.2)   # the recipe's -lms 200; NVML queries contend with CUDA launches for the driver lock
 
     def stop(self):
         self._stop_evt.set()

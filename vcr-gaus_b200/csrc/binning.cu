@@ -363,12 +363,45 @@ __global__ void __launch_bounds__(256) tile_ranges_kernel(uint32_t L, const uint
     if (idx == L - 1) ranges[cur].y = L;
 }
 
+// Block schedule for the compositing kernels: tile ids ordered by list length, longest first (coarse: by
+// floor(log2(length)), arbitrary inside a bucket).  Per-tile list lengths are extremely skewed (median tens, maximum
+// tens of thousands of entries), and thread blocks are dispatched in index order, so without this the longest tiles
+// can start last and run alone at the end of the kernel.  One block; counting sort over 33 buckets.
+__global__ void __launch_bounds__(1024) tile_order_kernel(const uint2* __restrict__ ranges, int tiles, uint32_t* __restrict__ order) {
+    __shared__ uint32_t cnt[33];
+    __shared__ uint32_t start[33];
+    const int t = threadIdx.x;
+    if (t < 33) cnt[t] = 0u;
+    __syncthreads();
+    for (int i = t; i < tiles; i += 1024) {
+        const uint2 r = ranges[i];
+        const uint32_t n = r.y - r.x;
+        atomicAdd(&cnt[n ? 32 - __clz(n) : 0], 1u);     // bucket 0: empty tiles, bucket k: 2^(k-1) <= n < 2^k
+    }
+    __syncthreads();
+    if (t == 0) {
+        uint32_t acc = 0;
+        for (int b = 32; b >= 0; b--) { start[b] = acc; acc += cnt[b]; }   // longest first
+    }
+    __syncthreads();
+    for (int i = t; i < tiles; i += 1024) {
+        const uint2 r = ranges[i];
+        const uint32_t n = r.y - r.x;
+        order[atomicAdd(&start[n ? 32 - __clz(n) : 0], 1u)] = (uint32_t)i;
+    }
+}
+
 int vcr_launch_tile_ranges(BinningState& b, ImageState& img, int R, int tiles, cudaStream_t s) {
     { VcrProfScope m(VCR_K_MEMSET, s); VCR_CUDA_TRY(cudaMemsetAsync(img.ranges, 0, (size_t)tiles * sizeof(uint2), s)); }
     if (R > 0) {
         VcrProfScope prof(VCR_K_TILE_RANGES, s);
         tile_ranges_kernel<<<((uint32_t)R + 255u) / 256u, 256, 0, s>>>((uint32_t)R, b.point_list_keys, img.ranges);
         VCR_LAUNCH_CHECK("tile_ranges_kernel");
+    }
+    {
+        VcrProfScope prof(VCR_K_TILE_RANGES, s);
+        tile_order_kernel<<<1, 1024, 0, s>>>(img.ranges, tiles, img.tile_order);
+        VCR_LAUNCH_CHECK("tile_order_kernel");
     }
     return 0;
 }

@@ -79,13 +79,14 @@ ImageState ImageState::carve(char* chunk, int W, int H) {
     carve_one(chunk, s.accum_alpha, N);
     carve_one(chunk, s.n_contrib, N);
     carve_one(chunk, s.ranges, tiles);
+    carve_one(chunk, s.tile_order, tiles);
     return s;
 }
 size_t ImageState::bytes(int W, int H) {
     char* base = nullptr;
     ImageState s = carve(base, W, H);
     const size_t tiles = (size_t)((W + VCR_TILE_X - 1) / VCR_TILE_X) * ((H + VCR_TILE_Y - 1) / VCR_TILE_Y);
-    return reinterpret_cast<size_t>(s.ranges + tiles) + 256;
+    return reinterpret_cast<size_t>(s.tile_order + tiles) + 256;
 }
 static inline size_t radix_blocks(size_t R) { return (R + 4095) / 4096; }
 BinningState BinningState::carve(char* chunk, int R) {

@@ -76,7 +76,7 @@ __device__ __forceinline__ float warp_reduce16_transposed(float (&v)[16], int la
 
 template <bool HAS_DIRS, bool HAS_OBJ>
 __global__ void __launch_bounds__(256) render_backward_kernel(
-    const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H, const float* __restrict__ bg,
+    const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order, int gx, const uint32_t* __restrict__ point_list, int W, int H, const float* __restrict__ bg,
     const float2* __restrict__ means2D, const float* __restrict__ xyz_view, const float4* __restrict__ conic_opacity,
     const float* __restrict__ colors, const float* __restrict__ depths, const float* __restrict__ normals,
     const float* __restrict__ objects, const float* __restrict__ dirs, const float* __restrict__ alpha_img,
@@ -87,17 +87,18 @@ __global__ void __launch_bounds__(256) render_backward_kernel(
     __shared__ uint32_t s_block_last;
 
     const int tid = threadIdx.x, lane = tid & 31;
-    const int gx = gridDim.x;
-    const uint32_t px = blockIdx.x * VCR_TILE_X + (tid & 15);
-    const uint32_t py = blockIdx.y * VCR_TILE_Y + (tid >> 4);
+    const uint32_t tile = __ldg(tile_order + blockIdx.x);      // blocks take tiles longest-list first
+    const uint32_t tile_x = tile % (uint32_t)gx, tile_y = tile / (uint32_t)gx;
+    const uint32_t px = tile_x * VCR_TILE_X + (tid & 15);
+    const uint32_t py = tile_y * VCR_TILE_Y + (tid >> 4);
     const bool inside = px < (uint32_t)W && py < (uint32_t)H;
     const size_t HW = (size_t)H * W;
     const size_t pix_id = (size_t)W * py + px;
     const float pfx = (float)px, pfy = (float)py;
-    const float strip_x0 = (float)(blockIdx.x * VCR_TILE_X), strip_x1 = strip_x0 + (float)(VCR_TILE_X - 1);
-    const float strip_y0 = (float)(blockIdx.y * VCR_TILE_Y + 2 * (tid >> 5)), strip_y1 = strip_y0 + 1.0f;
+    const float strip_x0 = (float)(tile_x * VCR_TILE_X), strip_x1 = strip_x0 + (float)(VCR_TILE_X - 1);
+    const float strip_y0 = (float)(tile_y * VCR_TILE_Y + 2 * (tid >> 5)), strip_y1 = strip_y0 + 1.0f;
 
-    const uint2 range = ranges[blockIdx.y * gx + blockIdx.x];
+    const uint2 range = ranges[tile];
     const uint32_t last_contributor = inside ? n_contrib[pix_id] : 0u;
     // Entries behind the last contributor of every pixel of the warp / block can never pass `contributor <
     // last_contributor` (backward.cu:589-591): drop them without staging or evaluating them.
@@ -323,9 +324,9 @@ __global__ void __launch_bounds__(256) render_backward_kernel(
 int vcr_launch_render_backward(const BwdParams& p, GeomState& g, BinningState& b, ImageState& img, cudaStream_t s) {
     { VcrProfScope m(VCR_K_MEMSET, s); VCR_CUDA_TRY(cudaMemsetAsync(p.acc, 0, (size_t)p.P * VCR_ACC_STRIDE * sizeof(float), s)); }
     VcrProfScope prof(VCR_K_RENDER_BWD, s);
-    const dim3 grid(p.gx, p.gy, 1);
+    const dim3 grid(p.gx * p.gy, 1, 1);
     const float* col = p.colors_precomp ? p.colors_precomp : g.rgb;
-#define RB_ARGS img.ranges, b.point_list, p.W, p.H, p.background, g.means2D, g.xyz_view, g.conic_opacity, col, g.depths, \
+#define RB_ARGS img.ranges, img.tile_order, p.gx, b.point_list, p.W, p.H, p.background, g.means2D, g.xyz_view, g.conic_opacity, col, g.depths, \
                 p.normals, p.sh_objs, p.dirs, p.alpha, p.depth, img.accum_alpha, img.n_contrib, p.dL_dpix, p.inside, p.acc
     // the opt-in shared-memory size is a per-device function attribute
     static bool attr_set_dev[64] = {false};

@@ -37,7 +37,7 @@ struct RfStage {                       // one staging buffer
 
 template <int MODE, bool HAS_DIRS, bool HAS_OBJ>
 __global__ void __launch_bounds__(256, 4) render_forward_kernel(
-    const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
+    const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order, int gx, const uint32_t* __restrict__ point_list, int W, int H,
     const float2* __restrict__ means2D, const float* __restrict__ xyz_view, const float* __restrict__ features,
     const float* __restrict__ depths, const float* __restrict__ normals, const float* __restrict__ obj,
     const float* __restrict__ dirs, const float4* __restrict__ conic_opacity, const uint8_t* __restrict__ inside_gs,
@@ -46,22 +46,23 @@ __global__ void __launch_bounds__(256, 4) render_forward_kernel(
     __shared__ RfStage<MODE> s_stage[2];
 
     const int tid = threadIdx.x, lane = tid & 31;
-    const int gx = gridDim.x;
-    const uint32_t px = blockIdx.x * VCR_TILE_X + (tid & 15);
-    const uint32_t py = blockIdx.y * VCR_TILE_Y + (tid >> 4);
+    const uint32_t tile = __ldg(tile_order + blockIdx.x);      // blocks take tiles longest-list first
+    const uint32_t tile_x = tile % (uint32_t)gx, tile_y = tile / (uint32_t)gx;
+    const uint32_t px = tile_x * VCR_TILE_X + (tid & 15);
+    const uint32_t py = tile_y * VCR_TILE_Y + (tid >> 4);
     const bool inside = px < (uint32_t)W && py < (uint32_t)H;
     const size_t HW = (size_t)H * W;
     const size_t pix_id = (size_t)W * py + px;
     const float pfx = (float)px, pfy = (float)py;
     bool done = !inside;
     // the warp's pixel strip: the full tile width, two rows
-    const float strip_x0 = (float)(blockIdx.x * VCR_TILE_X), strip_x1 = strip_x0 + (float)(VCR_TILE_X - 1);
-    const float strip_y0 = (float)(blockIdx.y * VCR_TILE_Y + 2 * (tid >> 5)), strip_y1 = strip_y0 + 1.0f;
+    const float strip_x0 = (float)(tile_x * VCR_TILE_X), strip_x1 = strip_x0 + (float)(VCR_TILE_X - 1);
+    const float strip_y0 = (float)(tile_y * VCR_TILE_Y + 2 * (tid >> 5)), strip_y1 = strip_y0 + 1.0f;
 
     float3 dir = make_float3(0.f, 0.f, 0.f);
     if (HAS_DIRS && inside) dir = make_float3(__ldg(dirs + pix_id), __ldg(dirs + HW + pix_id), __ldg(dirs + 2 * HW + pix_id));
 
-    const uint2 range = ranges[blockIdx.y * gx + blockIdx.x];
+    const uint2 range = ranges[tile];
     const int total = (int)(range.y - range.x);
     const int rounds = (total + RF_BATCH - 1) / RF_BATCH;
 
@@ -203,10 +204,10 @@ __global__ void __launch_bounds__(256, 4) render_forward_kernel(
 }
 
 int vcr_launch_render_forward(const FwdParams& p, GeomState& g, BinningState& b, ImageState& img, cudaStream_t s) {
-    const dim3 grid(p.gx, p.gy, 1);
+    const dim3 grid(p.gx * p.gy, 1, 1);
     const float* feat = p.colors_precomp ? p.colors_precomp : g.rgb;
     VcrProfScope prof(VCR_K_RENDER_FWD, s);
-#define RF_ARGS img.ranges, b.point_list, p.W, p.H, g.means2D, g.xyz_view, feat, g.depths, p.normals, p.sh_objs, p.dirs, \
+#define RF_ARGS img.ranges, img.tile_order, p.gx, b.point_list, p.W, p.H, g.means2D, g.xyz_view, feat, g.depths, p.normals, p.sh_objs, p.dirs, \
                 g.conic_opacity, p.inside, p.background, img.accum_alpha, img.n_contrib, p.out_color, nullptr, nullptr
     if (p.dirs) {
         if (p.sh_objs) render_forward_kernel<0, true, true><<<grid, 256, 0, s>>>(RF_ARGS);
@@ -222,10 +223,10 @@ int vcr_launch_render_forward(const FwdParams& p, GeomState& g, BinningState& b,
 
 int vcr_launch_render_aux(int mode, const FwdParams& p, GeomState& g, BinningState& b, ImageState& img,
                           int* gaussians_count, float* important_score, cudaStream_t s) {
-    const dim3 grid(p.gx, p.gy, 1);
+    const dim3 grid(p.gx * p.gy, 1, 1);
     const float* feat = p.colors_precomp ? p.colors_precomp : g.rgb;
     VcrProfScope prof(VCR_K_RENDER_AUX, s);
-#define RA_ARGS img.ranges, b.point_list, p.W, p.H, g.means2D, g.xyz_view, feat, g.depths, nullptr, nullptr, nullptr, \
+#define RA_ARGS img.ranges, img.tile_order, p.gx, b.point_list, p.W, p.H, g.means2D, g.xyz_view, feat, g.depths, nullptr, nullptr, nullptr, \
                 g.conic_opacity, nullptr, p.background, img.accum_alpha, img.n_contrib, p.out_color, gaussians_count, important_score
     if (mode == VCR_MODE_COUNT) render_forward_kernel<VCR_MODE_COUNT, false, false><<<grid, 256, 0, s>>>(RA_ARGS);
     else render_forward_kernel<VCR_MODE_VISI_ACC, false, false><<<grid, 256, 0, s>>>(RA_ARGS);

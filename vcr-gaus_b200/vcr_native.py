@@ -10,7 +10,8 @@ import os
 from ctypes import POINTER, c_char_p, c_float, c_int, c_size_t, c_uint32, c_void_p
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libvcr_gaus_b200.so")
+# VCR_GAUS_LIB lets a developer A/B a differently tuned build of the SAME library; it is not a fallback.
+LIB_PATH = os.environ.get("VCR_GAUS_LIB") or os.path.join(_HERE, "libvcr_gaus_b200.so")
 if not os.path.exists(LIB_PATH):
     raise ImportError(
         f"{LIB_PATH} is missing: build it with `make -C {_HERE}` (or __graft_entry__.build()). "
