@@ -61,55 +61,57 @@ def parse():
 
 
 # ------------------------------------------------------------------------------------------------------------------
-class ClockSampler(threading.Thread):
-    """Samples SM clock and throttle reasons through NVML while the timed region runs."""
+class ClockSampler:
+    """SM clock and throttle reasons DURING the timed region, through NVML from the benchmarking thread itself.
+
+    Polling from a side thread or from an `nvidia-smi -lms` process was tried first and dropped: NVML queries contend
+    with this process's CUDA launches for the driver lock and inflated a 90 ms timed region by tens of milliseconds
+    (up to 10x with 50 ms polling); even from this thread an uncached query costs 3-10 ms of host time (tools/nvml_probe.py).
+    So one sample is taken per timed region: right after the last launch and the closing event have been enqueued, while
+    the GPU is still executing the last timed step."""
 
     def __init__(self, index):
-        super().__init__(daemon=True)
-        self.index = index
-        self.samples, self.reasons, self.max_mhz = [], set(), None
-        self._stop_evt = threading.Event()
-        self.ok = False
+        self.samples, self.reasons, self.max_mhz, self.ok = [], set(), None, False
         try:
             import pynvml
             pynvml.nvmlInit()
             self.nv = pynvml
-            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            try:
+                uuid = str(torch.cuda.get_device_properties(index).uuid)
+                self.h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid) if not uuid.startswith("GPU-") else uuid)
+            except Exception:
+                self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
             self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.names = {
+                getattr(pynvml, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
+                getattr(pynvml, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+                getattr(pynvml, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+                getattr(pynvml, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
+            }
             self.ok = True
         except Exception:  # pragma: no cover
             self.ok = False
 
-    def run(self):
+    def sample(self):
         if not self.ok:
             return
         nv = self.nv
-        names = {
-            getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
-            getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
-            getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
-            getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
-        }
-        while not self._stop_evt.is_set():
+        try:
+            self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
             try:
-                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
-                try:
-                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
-                except Exception:
-                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
-                for bit, name in names.items():
-                    if r & bit:
-                        self.reasons.add(name)
+                r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
             except Exception:
-                pass
-            time.sleep(0.2)   # the recipe's -lms 200; NVML queries contend with CUDA launches for the driver lock
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+            for bit, name in self.names.items():
+                if r & bit:
+                    self.reasons.add(name)
+        except Exception:
+            pass
 
-    def stop(self):
-        self._stop_evt.set()
-        if self.ok:
-            self.join(timeout=2)
+    def result(self):
         s = sorted(self.samples)
-        return {"sm_mhz": (s[len(s) // 2] if s else None), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+        return {"sm_mhz": (s[len(s) // 2] if s else None), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
 
 
 # ------------------------------------------------------------------------------------------------------------------
@@ -301,21 +303,21 @@ def timed_region(stepper, steps, warmup, e2e, dev, world, sample_clocks=False):
     torch.cuda.synchronize(dev)
     if world > 1:
         dist.barrier()
-    sampler = None
-    if sample_clocks:
-        sampler = ClockSampler(dev.index or 0)
-        sampler.start()
+    sampler = ClockSampler(dev.index or 0) if sample_clocks else None
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize(dev)
     ev0.record()
     for i in range(steps):
         stepper.step(warmup + i, e2e)
     ev1.record()
+    if sampler:
+        sampler.sample()          # the GPU is still executing the last timed step(s); ev1 is already enqueued, so the
+                                  # 3-10 ms an (uncached) NVML query can take on the host does not enter the measurement
     torch.cuda.synchronize(dev)
     if world > 1:
         dist.barrier()
     ms = ev0.elapsed_time(ev1)
-    clocks = sampler.stop() if sampler else None
+    clocks = sampler.result() if sampler else None
     if world > 1:
         t = torch.tensor([ms], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -375,7 +377,9 @@ def main():
     # ---- device-resident timing (`value`): K steps, launch counters on, per-kernel event brackets OFF ----
     if impl == "ours":
         N.vcr_profile_enable(0)
-    for i in range(args.warmup):
+    # warm-up: W steps, but at least three passes over the view set, so that the caching allocator has seen every
+    # per-view buffer size (the binning buffer depends on R) and no cudaMalloc lands in the timed region
+    for i in range(max(args.warmup, 3 * len(views))):
         stepper.step(i, False)
     torch.cuda.synchronize(dev)
     if impl == "ours":
