@@ -288,10 +288,17 @@ class Stepper:
         # mean over ranks = SUM all-reduce of gradients of loss / world (no separate division pass over the bucket)
         (loss / self.vp.world if self.vp.world > 1 else loss).backward()
         if self.vp.world > 1:
-            self.vp.allreduce_gradients(self.bucket, average=False)
-            if means2D_densify is not None:
-                self.vp.reduce_densification_stats(self.xyz_gradient_accum, self.denom, self.max_radii2D,
-                                                   means2D_densify.grad, radii)
+            skip = os.environ.get("VCR_BENCH_SKIP", "")   # diagnosis only: "grads", "stats" or "grads,stats"
+            if "grads" not in skip:
+                self.vp.allreduce_gradients(self.bucket, average=False)
+            if means2D_densify is not None and "stats" not in skip:
+                # densification statistics: local per view, combined across ranks every 100 steps (the reference
+                # densifies every 100 iterations, trainer.py:357-370)
+                self.vp.accumulate_densification_stats(self.xyz_gradient_accum, self.denom, self.max_radii2D,
+                                                       means2D_densify.grad, radii)
+                if (i + 1) % 100 == 0:
+                    self.vp.sync_densification_stats(self.xyz_gradient_accum, self.denom, self.max_radii2D)
+                    self.xyz_gradient_accum.zero_(); self.denom.zero_(); self.max_radii2D.zero_()
         if e2e:
             self.loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
         return loss
@@ -379,7 +386,8 @@ def main():
         N.vcr_profile_enable(0)
     # warm-up: W steps, but at least three passes over the view set, so that the caching allocator has seen every
     # per-view buffer size (the binning buffer depends on R) and no cudaMalloc lands in the timed region
-    for i in range(max(args.warmup, 3 * len(views))):
+    # ... and long enough (a fixed count, identical on every rank) for clocks and power state to settle under load
+    for i in range(max(args.warmup, 3 * len(views), 200 if impl == "ours" else 60)):
         stepper.step(i, False)
     torch.cuda.synchronize(dev)
     if impl == "ours":

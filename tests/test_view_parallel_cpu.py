@@ -39,6 +39,7 @@ def _worker(rank, world, port, P, out_dir):
     vp.broadcast_parameters(bucket, src=0)
     assert bucket.floats_per_gaussian == 59
     accum, denom, max_r = torch.zeros((P, 1)), torch.zeros((P, 1)), torch.zeros(P)
+    lazy = [torch.zeros((P, 1)), torch.zeros((P, 1)), torch.zeros(P)]   # local accumulation, combined once at the end
     for step in range(2):
         view = vp.view_for_step(step, n_views=8, seed=1)
         grads, radii, g2d = _fake_view_grads(P, view)
@@ -47,8 +48,11 @@ def _worker(rank, world, port, P, out_dir):
         loss.backward()
         vp.allreduce_gradients(bucket, average=False)
         vp.reduce_densification_stats(accum, denom, max_r, g2d, radii)
+        vp.accumulate_densification_stats(lazy[0], lazy[1], lazy[2], g2d, radii)
         torch.save({"view": view, "grad": bucket.grad_flat.clone(), "accum": accum.clone(), "denom": denom.clone(),
                     "max_r": max_r.clone(), "flat": bucket.flat.clone()}, os.path.join(out_dir, f"r{rank}_s{step}.pt"))
+    vp.sync_densification_stats(*lazy)
+    torch.save({"accum": lazy[0], "denom": lazy[1], "max_r": lazy[2]}, os.path.join(out_dir, f"r{rank}_lazy.pt"))
     dist.destroy_process_group()
 
 
@@ -79,6 +83,11 @@ def test_world2_gloo_matches_sequential(tmp_path):
             torch.testing.assert_close(r["accum"], accum, rtol=1e-6, atol=1e-6)
             assert torch.equal(r["denom"], denom) and torch.equal(r["max_r"], max_r)
     assert len(seen) == 4, "two steps x two ranks must cover four distinct views of the epoch"
+    # the lazily combined statistics (local accumulation + one sync) equal the per-step ones and the sequential ones
+    for r in (0, 1):
+        lz = torch.load(tmp_path / f"r{r}_lazy.pt")
+        torch.testing.assert_close(lz["accum"], accum, rtol=1e-6, atol=1e-6)
+        assert torch.equal(lz["denom"], denom) and torch.equal(lz["max_r"], max_r)
 
 
 def test_single_process_is_a_no_op():

@@ -6,9 +6,10 @@ rank renders a different view; the only exchange is
 
   * one all-reduce(SUM) over a single flat gradient bucket holding every per-Gaussian gradient
     (xyz 3, SH 48, opacity 1, scaling 3, rotation 4 = 59 floats per Gaussian at SH degree 3), and
-  * the densification statistics of scene/gaussian_model.py:669-671 and trainer.py:345:
-    all-reduce(SUM) of [ |grad means2D_densify| * visible, visible ] and all-reduce(MAX) of radii * visible,
-    which reproduces exactly what `world` sequential iterations of the reference would have accumulated.
+  * the densification statistics of scene/gaussian_model.py:669-671 and trainer.py:345, accumulated locally per view
+    and combined only when the model densifies: all-reduce(SUM) of [ sum |grad means2D_densify| * visible, sum visible ]
+    and all-reduce(MAX) of max_radii2D, which reproduces exactly what one process would have accumulated over the
+    same views.
 
 Backends: "nccl" on GPUs (NVLink 5 / NVSwitch), "gloo" on CPU for the tests.  No collective is issued at world size 1.
 """
@@ -111,9 +112,35 @@ class ViewParallel:
             bucket.grad_flat.div_(self.world)
         return work
 
+    def accumulate_densification_stats(self, xyz_gradient_accum, denom, max_radii2D, grad_means2D_densify, radii):
+        """Per view, LOCAL: add_densification_stats (scene/gaussian_model.py:669-671) + the max_radii2D update
+        (trainer.py:345).  No communication: sums and maxima commute, and the statistics are only read when the model
+        densifies (every 100 iterations, trainer.py:357-370), so the ranks are combined there, once, by
+        sync_densification_stats().  Tensors are updated in place; shapes [P,1], [P,1], [P]."""
+        visible = radii > 0
+        xyz_gradient_accum.add_((torch.norm(grad_means2D_densify[:, :2], dim=-1) * visible).unsqueeze(1))
+        denom.add_(visible.unsqueeze(1).to(denom.dtype))
+        max_radii2D.copy_(torch.max(max_radii2D, torch.where(visible, radii, torch.zeros_like(radii)).to(max_radii2D.dtype)))
+
+    def sync_densification_stats(self, xyz_gradient_accum, denom, max_radii2D):
+        """Combine the per-rank statistics right before densify/prune: all-reduce(SUM) of the two accumulators and
+        all-reduce(MAX) of max_radii2D.  Afterwards every rank holds exactly what ONE process would have accumulated over
+        the same views, and the accumulators must then be reset on every rank (the reference zeroes them in
+        densification_postfix, scene/gaussian_model.py).  Call it with freshly reset local accumulators between
+        densification rounds, i.e. each rank's tensors must contain only its own views since the last sync."""
+        if self.world == 1:
+            return
+        packed = torch.cat([xyz_gradient_accum.reshape(-1), denom.reshape(-1)])
+        dist.all_reduce(packed, op=dist.ReduceOp.SUM, group=self.group)
+        n = xyz_gradient_accum.numel()
+        xyz_gradient_accum.copy_(packed[:n].view_as(xyz_gradient_accum))
+        denom.copy_(packed[n:].view_as(denom))
+        dist.all_reduce(max_radii2D, op=dist.ReduceOp.MAX, group=self.group)
+
     def reduce_densification_stats(self, xyz_gradient_accum, denom, max_radii2D, grad_means2D_densify, radii):
-        """add_densification_stats (scene/gaussian_model.py:669-671) + the max_radii2D update (trainer.py:345),
-        summed / maxed over the views of all ranks.  Tensors are updated in place; shapes [P,1], [P,1], [P]."""
+        """Per-step variant (one SUM and one MAX all-reduce every view): accumulate this view on every rank and combine
+        immediately.  Same result as accumulate_... + sync_..., at the cost of two small collectives per step; kept for
+        callers that read the statistics every iteration."""
         visible = radii > 0
         packed = torch.zeros((radii.shape[0], 2), dtype=torch.float32, device=radii.device)
         packed[:, 0] = torch.norm(grad_means2D_densify[:, :2], dim=-1) * visible
