@@ -179,11 +179,19 @@ class RefRasterFn(torch.autograd.Function):
         return None, g3d, gsh, gnrm, gop, gsc, grot, None, None, None
 
 
-def clone_params(scene, dev, direct=False):
+def clone_params(scene, dev, direct=False, vp=None):
+    """Parameters + flat gradient bucket.  With a ViewParallel layer at N > 1 the bucket is placed in symmetric memory so
+    that the gradient exchange can go through the NVSwitch multicast kernel (VCR_BENCH_TRANSPORT=nccl forces NCCL)."""
     import vcr_view_parallel as VP
     tensors = dict(means3D=scene.means3D.to(dev), shs=scene.shs.to(dev), opacities=scene.opacities.to(dev),
                    scales=scene.scales.to(dev), rotations=scene.rotations.to(dev))
-    return VP.GaussianBucket(tensors, device=dev, direct=direct)
+    store = None
+    if vp is not None and vp.world > 1 and direct and os.environ.get("VCR_BENCH_TRANSPORT", "multimem") == "multimem":
+        # (symmetric storage is also fine for NCCL, so it is allocated whenever the multicast kernel may be chosen)
+        store = vp.symmetric_gradient_storage(VP.GaussianBucket.numel_for(tensors), dev)
+    b = VP.GaussianBucket(tensors, device=dev, direct=direct, grad_storage=store)
+    b.transport = "multimem" if store is not None else "nccl"
+    return b
 
 
 class Stepper:
@@ -218,6 +226,23 @@ class Stepper:
         self.loss_host = torch.zeros(1).pin_memory()
         self.copy_stream = torch.cuda.Stream(device=dev)
         self._prefetched = None
+        self.diag_events = None
+        self.view_cost = [0.0] * len(views)      # R of each local view, measured during the first warm-up pass
+        self.order = list(range(len(views)))
+        self.skip = os.environ.get("VCR_BENCH_SKIP", "")   # diagnosis only: "grads", "stats" or "grads,stats"
+        # N > 1: pipeline the gradient all-reduce with the per-Gaussian backward stage in this many ranges (0 = one
+        # all-reduce after the backward)
+        # (measured: no gain from the pipelining at 2 or 8 GPUs — the exchange slows the overlapped launches down by as much
+        # as it hides — so the default is one exchange after the backward)
+        self.chunks = int(os.environ.get("VCR_BENCH_CHUNKS", "0")) if (impl == "ours" and vp.world > 1) else 0
+        self.exchange_ms = {}
+        if impl == "ours" and vp.world > 1:
+            self.exchange_ms = vp.pick_transport(bucket)          # NCCL or the multicast kernel, whichever is faster here
+            forced = os.environ.get("VCR_BENCH_TRANSPORT")
+            if forced in ("nccl", "multimem") and (forced == "nccl" or bucket.transport == "multimem"):
+                vp.transport = forced
+        if self.chunks > 0 and "grads" not in self.skip:
+            vp.overlap_gradients(bucket, n_chunks=self.chunks, transport=vp.transport)
         if impl == "reference":
             import ref_ab
             self.C = ref_ab.load()
@@ -229,8 +254,17 @@ class Stepper:
         # normals_precomp depends on the view (flip towards the camera + w2c rotation): precomputed per view on device
         self.normals = [v["inp"]["normals"].to(dev).requires_grad_(True) for v in views]
 
+    def note_view_cost(self, i):
+        """Warm-up bookkeeping: remember the number of (tile, Gaussian) instances R of local view i (what a trainer knows
+        from the previous epoch).  After the last view, N > 1: order the local shard by cost so that step k takes every
+        rank's k-th cheapest view — the ranks of one step then finish together instead of waiting for the slowest view
+        (ViewParallel.cost_ordered_shard)."""
+        self.view_cost[i] = float(last_num_rendered())
+        if i == len(self.views) - 1 and self.vp.world > 1 and self.impl == "ours" and os.environ.get("VCR_BENCH_BALANCE", "1") == "1":
+            self.order = self.vp.cost_ordered_shard(self.view_cost, seed=0)
+
     def _issue_prefetch(self, i):
-        k = i % len(self.views)
+        k = self.order[i % len(self.views)]
         with torch.cuda.stream(self.copy_stream):
             d = {name: t.to(self.dev, non_blocking=True) for name, t in self.host[k].items()}
             ev = torch.cuda.Event()
@@ -241,7 +275,7 @@ class Stepper:
         self._prefetched = (i, d, ev)
 
     def step(self, i, e2e):
-        k = i % len(self.views)
+        k = self.order[i % len(self.views)]
         p = self.bucket.params
         if e2e:
             # per-view inputs come from pinned host memory every step; like a data loader with prefetch depth 1 the
@@ -280,38 +314,55 @@ class Stepper:
             loss = loss + LAMBDA_MONO * ((rn - gt_n).abs().sum(-1).mean() + (1.0 - (rn * gt_n).sum(-1)).mean())
             loss = loss + LAMBDA_DN * ref_dnormal_chain(depth, self.K, gt_n, rn, EXP_T)
         else:
-            # the same three terms through this repository's public loss API (one fused kernel per direction)
+            # the same three terms through this repository's public loss API (one fused kernel per direction).  Mean over
+            # ranks = SUM all-reduce of the gradients of loss / world: the 1/world goes into the loss weights, so there is
+            # neither a division pass over the bucket nor an extra scaling kernel
             from vcr_dnormal import view_loss
-            loss = view_loss(out, d["gt_image"], gt_n, self.K4, w_l1=1.0, w_mono=LAMBDA_MONO, w_dn=LAMBDA_DN, exp_t=EXP_T)
+            sc = 1.0 / self.vp.world
+            loss = view_loss(out, d["gt_image"], gt_n, self.K4, w_l1=sc, w_mono=LAMBDA_MONO * sc, w_dn=LAMBDA_DN * sc, exp_t=EXP_T)
         self.bucket.zero_grad()
         normals.grad = None
-        # mean over ranks = SUM all-reduce of gradients of loss / world (no separate division pass over the bucket)
-        (loss / self.vp.world if self.vp.world > 1 else loss).backward()
-        if self.vp.world > 1:
-            skip = os.environ.get("VCR_BENCH_SKIP", "")   # diagnosis only: "grads", "stats" or "grads,stats"
-            if "grads" not in skip:
+        ev = self.diag_events
+        if ev is not None:
+            e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+            ev.append(e)
+            e[0].record()
+        if self.impl == "reference" and self.vp.world > 1:
+            (loss / self.vp.world).backward()
+        else:
+            loss.backward()     # ours, N > 1: the chunk hook queues the gradient exchange range by range during this call
+        if ev is not None:
+            e[1].record()
+        skip = self.skip
+        if self.vp.world > 1 and "grads" not in skip:
+            if self.chunks > 0:
+                self.vp.finish_gradients(self.bucket)
+            else:
                 self.vp.allreduce_gradients(self.bucket, average=False)
-            if means2D_densify is not None and "stats" not in skip:
-                # densification statistics: local per view, combined across ranks every 100 steps (the reference
-                # densifies every 100 iterations, trainer.py:357-370)
-                self.vp.accumulate_densification_stats(self.xyz_gradient_accum, self.denom, self.max_radii2D,
-                                                       means2D_densify.grad, radii)
-                if (i + 1) % 100 == 0:
-                    self.vp.sync_densification_stats(self.xyz_gradient_accum, self.denom, self.max_radii2D)
-                    self.xyz_gradient_accum.zero_(); self.denom.zero_(); self.max_radii2D.zero_()
+        if ev is not None:
+            e[2].record()
+        if means2D_densify is not None and "stats" not in skip:
+            # densification statistics (trainer.py:345-347), every view at every N: one fused local pass; the ranks are
+            # combined every 100 steps (the reference densifies every 100 iterations, trainer.py:357-370)
+            self.vp.accumulate_densification_stats(self.xyz_gradient_accum, self.denom, self.max_radii2D,
+                                                   means2D_densify.grad, radii)
+            if (i + 1) % 100 == 0:
+                self.vp.sync_densification_stats(self.xyz_gradient_accum, self.denom, self.max_radii2D)
+                self.xyz_gradient_accum.zero_(); self.denom.zero_(); self.max_radii2D.zero_()
         if e2e:
             self.loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
         return loss
 
 
-def timed_region(stepper, steps, warmup, e2e, dev, world, sample_clocks=False):
+def timed_region(stepper, steps, warmup, e2e, dev, world, sampler=None):
+    """`sampler`: a ClockSampler built BEFORE the warm-up (NVML initialisation takes tens of milliseconds of host time; done
+    between the warm-up and the first timed step it lets the GPU fall idle and the first timed steps run at ramping clocks)."""
     for i in range(warmup):
         stepper.step(i, e2e)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize(dev)
     if world > 1:
         dist.barrier()
-    sampler = ClockSampler(dev.index or 0) if sample_clocks else None
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize(dev)
     ev0.record()
     for i in range(steps):
@@ -347,8 +398,25 @@ def cpu_oracle_views_per_s(args, view, repeat=1):
     return 1.0 / dt, dt, f["binned"]["R"]
 
 
+_JSON_FD = None
+
+
+def emit(obj):
+    """The ONE JSON line goes to the process's real stdout; everything else written to fd 1 during the run (NCCL prints its
+    version banner there) has been redirected to stderr."""
+    line = (json.dumps(obj) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(line.decode()); sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, line)
+
+
 def main():
+    global _JSON_FD
     args = parse()
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
     import vcr_view_parallel as VP
     rank, world, local = VP.init_from_env()
     if args.impl == "reference-cpu":
@@ -356,7 +424,7 @@ def main():
             scene, views = build_workload(args, 0, 1)
             vps, dt, R = cpu_oracle_views_per_s(args, views[0])
             cores = os.cpu_count()
-            print(json.dumps({
+            emit(({
                 "impl": "reference", "metric": METRIC, "value": vps, "unit": "views/s", "n_gpus": 0, "steps": 1, "warmup": 0,
                 "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
                 "data": "synthetic", "config": {"workload": f"{args.gaussians} Gaussians, {args.width}x{args.height}, SH3, dirs; CPU oracle port"},
@@ -374,9 +442,9 @@ def main():
         import ref_ab
         if ref_ab.load() is None:
             if rank == 0:
-                print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/_C.so (reference CUDA build) not present on this box"}))
+                emit(({"impl": "reference", "unavailable": "oracle/_ref/_C.so (reference CUDA build) not present on this box"}))
             return
-    bucket = clone_params(scene, dev, direct=(impl == "ours"))
+    bucket = clone_params(scene, dev, direct=(impl == "ours"), vp=vp)
     stepper = Stepper(args, impl, bucket, views, dev, vp)
 
     import vcr_native as N
@@ -387,12 +455,15 @@ def main():
     # warm-up: W steps, but at least three passes over the view set, so that the caching allocator has seen every
     # per-view buffer size (the binning buffer depends on R) and no cudaMalloc lands in the timed region
     # ... and long enough (a fixed count, identical on every rank) for clocks and power state to settle under load
-    for i in range(max(args.warmup, 3 * len(views), 200 if impl == "ours" else 60)):
+    sampler = ClockSampler(dev.index or 0)
+    n_warm = max(args.warmup, 3 * len(views), 200 if impl == "ours" else 60)
+    for i in range(n_warm):
         stepper.step(i, False)
-    torch.cuda.synchronize(dev)
+        if i < len(views):
+            stepper.note_view_cost(i)
     if impl == "ours":
         N.profile_read(reset=True)
-    ms, clocks = timed_region(stepper, args.steps, 0, False, dev, world, sample_clocks=True)
+    ms, clocks = timed_region(stepper, args.steps, 0, False, dev, world, sampler=sampler)
     counts = N.profile_read(reset=True) if impl == "ours" else {}
     # ---- the same K steps once more with every kernel of the library bracketed by CUDA events on its stream ----
     # (the brackets cost ~5-10 % of a step, so they are kept out of `value`; `ms_per_step_with_kernel_events` reports it)
@@ -404,6 +475,8 @@ def main():
         N.vcr_profile_enable(0)
     # ---- end-to-end timing (`e2e`): per-view inputs from pinned host memory, loss read back ----
     ms_e2e, _ = timed_region(stepper, args.steps, min(args.warmup, 3), True, dev, world)
+    if os.environ.get("VCR_BENCH_DIAG"):
+        diagnose(stepper, args, dev, rank, world)
     views_per_s = world * args.steps / (ms / 1e3)
     e2e_vps = world * args.steps / (ms_e2e / 1e3)
 
@@ -415,10 +488,15 @@ def main():
         "data": "synthetic",
         "config": {"workload": f"{args.gaussians} Gaussians (SH degree 3), {args.width}x{args.height}, {args.views} views/rank cycled, "
                                f"ray/plane-intersection depth, loss = L1 + mono-normal + D-Normal; rasterize fwd+bwd per view",
-                   "parallelism": f"view-parallel x{world} (replicated Gaussians, NCCL all-reduce of the flat gradient bucket)" if world > 1 else "single GPU",
+                   "parallelism": (f"view-parallel x{world} (replicated Gaussians, all-reduce of the flat gradient bucket via "
+                                   + ("own NVSwitch-multicast kernel" if vp.transport == "multimem" else "NCCL")
+                                   + (f", pipelined with the backward in {stepper.chunks} Gaussian ranges)" if stepper.chunks else ")"))
+                   if world > 1 else "single GPU",
                    "l2": "working set per step (parameters + gradients + per-view state > 600 MB) exceeds the 126 MB L2; views rotate every step",
                    "not_in_step": "SSIM, Adam (outside the hot path, SURVEY.md 8f)"},
         "clocks": clocks,
+        "exchange": ({"chosen": vp.transport, "ms_per_236MB_bucket": stepper.exchange_ms, "view_order": "cost-ordered shard" if stepper.order != list(range(len(views))) else "as listed"}
+                     if world > 1 and impl == "ours" else None),
         "e2e": {"value": e2e_vps, "unit": "views/s", "h2d_bytes_per_step": stepper.h2d_bytes, "d2h_bytes_per_step": stepper.d2h_bytes,
                 "ms_per_step": ms_e2e / args.steps},
     }
@@ -428,7 +506,7 @@ def main():
         out["cpu_baseline"] = {"value": None, "unit": "views/s", "cores": 0, "kind": "reference",
                                "sample": "not a CPU run: the reference's implementation of this path is CUDA-only; this arm is its CUDA rasterizer on this GPU"}
         out["gpu_launches"] = 0
-        print(json.dumps(out))
+        emit(out)
         return
     # ---- roofline of the dominant kernel + per-kernel table ----
     peaks = {}
@@ -455,7 +533,41 @@ def main():
         vps, dt, R = cpu_oracle_views_per_s(args, views[0])
         out["cpu_baseline"] = {"value": vps, "unit": "views/s", "cores": os.cpu_count(), "kind": "port",
                                "sample": f"one full {args.width}x{args.height} view of the same scene, rasterize fwd+bwd, CPU oracle with OpenMP ({dt:.1f} s)"}
-    print(json.dumps(out))
+    emit(out)
+
+
+def diagnose(stepper, args, dev, rank, world):
+    """VCR_BENCH_DIAG=1: per-rank split of a step into [start of backward -> gradients written] and [-> exchange done],
+    plus the whole step, over 40 steps (printed to stderr by rank 0; not part of the bench line)."""
+    n = 40
+    stepper.diag_events = []
+    marks = [torch.cuda.Event(enable_timing=True) for _ in range(n + 1)]
+    torch.cuda.synchronize(dev)
+    if world > 1:
+        dist.barrier()
+    for i in range(n):
+        marks[i].record()
+        stepper.step(1000 + i, False)
+    marks[n].record()
+    torch.cuda.synchronize(dev)
+    ev, stepper.diag_events = stepper.diag_events, None
+    step = [marks[i].elapsed_time(marks[i + 1]) for i in range(n)]
+    bwd = [e[0].elapsed_time(e[1]) for e in ev]
+    comm = [e[1].elapsed_time(e[2]) for e in ev]
+    fwd = [marks[i].elapsed_time(ev[i][0]) for i in range(n)]
+    t = torch.tensor([step, fwd, bwd, comm], device=dev)
+    if world > 1:
+        allt = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(allt, t)
+    else:
+        allt = [t]
+    if rank == 0:
+        a = torch.stack(allt).cpu()            # [world, 4, n]
+        names = ["step", "fwd+loss", "bwd", "exchange_tail"]
+        rep = {nm: {"mean_per_rank": [round(float(x), 3) for x in a[:, k].mean(dim=1)],
+                    "mean_of_max_over_ranks": round(float(a[:, k].max(dim=0).values.mean()), 3),
+                    "mean_of_min_over_ranks": round(float(a[:, k].min(dim=0).values.mean()), 3)} for k, nm in enumerate(names)}
+        print("DIAG " + json.dumps(rep), file=sys.stderr, flush=True)
 
 
 def scene_stats(stepper, args):
@@ -504,6 +616,7 @@ def kernel_table(kern, st, args, hbm_peak):
         "preprocess_backward_kernel": (92 + 571) * Pv,
         "dnormal_forward_kernel": 29 * N,
         "dnormal_backward_kernel": 33 * N,
+        "densify_stats_kernel": 16 * P + 24 * Pv,
     }
     rows = []
     for name, (ms, timed, launches) in kern.items():

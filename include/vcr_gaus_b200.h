@@ -134,7 +134,79 @@ int vcr_rasterize_backward(
     int debug,
     void* stream);
 
-/* present[i] = (view-space z of means3D[i]) > 0.2   (checkFrustum, rasterizer_impl.cu:54-66). */
+/* The same backward with its last, per-Gaussian stage (computeCov2DCUDA + preprocessCUDA of the backward,
+ * DGR/cuda_rasterizer/backward.cu:144-419) split into `n_chunks` launches over consecutive ranges of Gaussians
+ * (range starts are multiples of 256).  Right after the launch of chunk c has been enqueued on `stream`, the library
+ * calls chunk_enqueued(chunk_user, c, first_gaussian, n_gaussians) on the calling host thread: rows
+ * [first_gaussian, first_gaussian + n_gaussians) of every gradient output are final once the work enqueued so far has
+ * run.  A view-parallel caller queues the all-reduce of those rows from the callback (ordered after `stream`), so the
+ * exchange of chunk c overlaps the computation of chunk c+1 ("overlappable with bwd preprocess").
+ * n_chunks <= 1 with a NULL callback is exactly vcr_rasterize_backward.  The reference has no counterpart: it is
+ * single-GPU (tools/distributed.py is never called). */
+typedef void (*vcr_chunk_fn)(void* user, int chunk, int first_gaussian, int n_gaussians);
+int vcr_rasterize_backward_chunked(
+    int P, int D, int M, int R,
+    const float* background,
+    int width, int height,
+    const float* means3D,
+    const float* shs,
+    const float* colors_precomp,
+    const float* normals_precomp,
+    const float* sh_objs,
+    const float* alpha,
+    const float* depth,
+    const float* scales,
+    float scale_modifier,
+    const float* rotations,
+    const float* cov3D_precomp,
+    const float* viewmatrix,
+    const float* projmatrix,
+    const float* dirs,
+    const float* campos,
+    float tan_fovx, float tan_fovy,
+    const int* radii,
+    char* geom_buffer, char* binning_buffer, char* img_buffer,
+    const float* dL_dpix,
+    float* dL_dmean2D,
+    float* dL_dmean2D_densify,
+    float* dL_dopacity,
+    float* dL_dcolor,
+    float* dL_dnormal,
+    float* dL_dobjects,
+    float* dL_dmean3D,
+    float* dL_dcov3D,
+    float* dL_dsh,
+    float* dL_dscale,
+    float* dL_drot,
+    const uint8_t* inside,
+    char* scratch,
+    int debug,
+    void* stream,
+    int n_chunks,
+    vcr_chunk_fn chunk_enqueued,
+    void* chunk_user);
+
+/* Per-view densification statistics, in place, for Gaussians with radii > 0:
+ *   xyz_gradient_accum[i] += |grad_means2D_densify[i, 0:2]|;  denom[i] += 1     (scene/gaussian_model.py:669-671)
+ *   max_radii2D[i] = max(max_radii2D[i], radii[i])                              (trainer.py:345)
+ * One pass instead of the reference's three boolean-mask-indexed PyTorch updates.  All arrays f32[P] except radii i32[P]
+ * and grad_means2D_densify f32[P,3]. */
+int vcr_densify_stats_accumulate(int P, const float* grad_means2D_densify, const int* radii, float* xyz_gradient_accum,
+                                 float* denom, float* max_radii2D, void* stream);
+
+/* Gradient exchange of the view-parallel layer through the NVSwitch (the reference is single-GPU and
+ * has no counterpart).  `multicast_base` is the multicast mapping (NVLink SHARP, e.g. torch symmetric memory's
+ * multicast_ptr) of a float buffer that every rank holds at the same offset.  For each of the n_ranges (<= 8) float
+ * ranges [first_float_host[i], +n_floats_host[i]) this rank reduces its 1/world share with multimem.ld_reduce (the sum is
+ * formed inside the switch) and writes it to every rank with multimem.st: a two-shot all-reduce(SUM) in ONE launch, S
+ * bytes in and S bytes out per GPU.  The range arrays are HOST arrays, consumed before the call returns.  `blocks` <= 0
+ * picks 74.  The launch waits for nobody: the caller must order it after every rank has written the ranges and
+ * order consumers after every rank's launch has completed (symmetric-memory barrier on `stream`, see
+ * vcr_view_parallel.py).  All ranks must pass identical ranges. */
+int vcr_multimem_allreduce_sum(void* multicast_base, int n_ranges, const long long* first_float_host,
+                               const long long* n_floats_host, int rank, int world, int blocks, void* stream);
+
+/* present[i] = (view-space z of means3D[i]) > 0.2  (checkFrustum, rasterizer_impl.cu:54-66). */
 int vcr_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
                      uint8_t* present, void* stream);
 

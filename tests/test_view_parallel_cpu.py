@@ -52,6 +52,21 @@ def _worker(rank, world, port, P, out_dir):
         torch.save({"view": view, "grad": bucket.grad_flat.clone(), "accum": accum.clone(), "denom": denom.clone(),
                     "max_r": max_r.clone(), "flat": bucket.flat.clone()}, os.path.join(out_dir, f"r{rank}_s{step}.pt"))
     vp.sync_densification_stats(*lazy)
+    # chunk-pipelined exchange: the rasterizer's backward calls the hook once per Gaussian range; here the hook is driven
+    # by hand over ragged ranges, with the gradient rows of a range written just before its call
+    dbucket = VP.GaussianBucket(tensors, direct=True)
+    vp.overlap_gradients(dbucket, n_chunks=3)
+    n_chunks, hook = dbucket.params["means3D"]._vcr_chunk_hook
+    grads, _, _ = _fake_view_grads(P, 40 + rank)
+    bounds = [0, 100, 101, P]
+    for c in range(n_chunks):
+        a, b = bounds[c], bounds[c + 1]
+        for name, off, n, shape in dbucket.layout:
+            per = n // P
+            dbucket.grad_flat[off + a * per: off + b * per] = grads[name].reshape(-1)[a * per: b * per]
+        hook(c, a, b - a)
+    assert vp.finish_gradients(dbucket) == n_chunks
+    torch.save({"grad": dbucket.grad_flat.clone()}, os.path.join(out_dir, f"r{rank}_chunked.pt"))
     torch.save({"accum": lazy[0], "denom": lazy[1], "max_r": lazy[2]}, os.path.join(out_dir, f"r{rank}_lazy.pt"))
     dist.destroy_process_group()
 
@@ -82,6 +97,10 @@ def test_world2_gloo_matches_sequential(tmp_path):
             torch.testing.assert_close(r["grad"], total, rtol=1e-6, atol=1e-6)
             torch.testing.assert_close(r["accum"], accum, rtol=1e-6, atol=1e-6)
             assert torch.equal(r["denom"], denom) and torch.equal(r["max_r"], max_r)
+    total = sum(torch.cat([_fake_view_grads(P, 40 + r)[0][k].reshape(-1) for k in ("means3D", "shs", "opacities", "scales", "rotations")])
+                for r in (0, 1))
+    for r in (0, 1):
+        torch.testing.assert_close(torch.load(tmp_path / f"r{r}_chunked.pt")["grad"], total, rtol=1e-6, atol=1e-6)
     assert len(seen) == 4, "two steps x two ranks must cover four distinct views of the epoch"
     # the lazily combined statistics (local accumulation + one sync) equal the per-step ones and the sequential ones
     for r in (0, 1):

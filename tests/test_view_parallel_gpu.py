@@ -1,0 +1,91 @@
+"""GPU tests of the view-parallel pieces that run on one GPU: the chunked backward (vcr_rasterize_backward_chunked, the hook
+the gradient exchange is pipelined through) and the fused densification-statistics pass."""
+import numpy as np
+import pytest
+import torch
+
+from util import CudaRun, make_case, rel_l2, settings_from
+
+pytestmark = pytest.mark.gpu
+
+
+def test_chunked_backward_equals_single_launch():
+    """The per-Gaussian backward stage in 5 launches writes the same gradients as in one, straight into the flat bucket,
+    and reports consecutive ranges starting at multiples of 256 that cover every Gaussian."""
+    import vcr_view_parallel as VP
+    from diff_gaussian_rasterization import GaussianRasterizer
+    P, W, H = 3000, 320, 200                      # 12 blocks of 256 -> ragged split into 5 ranges, last block partial
+    inp, _, _ = make_case(P, W, H, seed=3, use_dirs=True, use_sem=False)
+    dev = torch.device("cuda")
+    g = torch.Generator().manual_seed(5)
+    dL = torch.randn((10, H, W), generator=g)
+
+    plain = CudaRun(inp)
+    ref = plain.backward(dL)
+
+    tensors = {k: inp[k].to(dev) for k in ("means3D", "shs", "opacities", "scales", "rotations")}
+    bucket = VP.GaussianBucket(tensors, device=dev, direct=True)
+    bucket.grad_flat.fill_(float("nan"))          # every element must be overwritten
+    calls = []
+    bucket.params["means3D"]._vcr_chunk_hook = (5, lambda c, first, count: calls.append((c, first, count)))
+    p = bucket.params
+    normals = inp["normals"].to(dev).requires_grad_(True)
+    out, radii = GaussianRasterizer(settings_from(inp, dev))(
+        means3D=p["means3D"], means2D=torch.zeros_like(p["means3D"], requires_grad=True), shs=p["shs"], normals_precomp=normals,
+        opacities=p["opacities"], scales=p["scales"], rotations=p["rotations"], dirs=inp["dirs"].to(dev))
+    out.backward(dL.to(dev))
+    torch.cuda.synchronize()
+
+    assert [c for c, _, _ in calls] == [0, 1, 2, 3, 4]
+    assert calls[0][1] == 0 and all(first % 256 == 0 for _, first, _ in calls)
+    assert all(calls[i][1] + calls[i][2] == calls[i + 1][1] for i in range(4)) and calls[-1][1] + calls[-1][2] == P
+    assert p["means3D"].grad.data_ptr() == bucket.grad_flat.data_ptr(), "gradient was not written in place"
+    assert torch.isfinite(bucket.grad_flat).all()
+    names = dict(means3D="dL_dmeans3D", shs="dL_dsh", opacities="dL_dopacity", scales="dL_dscales", rotations="dL_drotations")
+    for name, off, n, shape in bucket.layout:
+        got = bucket.grad_flat[off:off + n].view(shape).cpu().numpy()
+        # two runs of the compositing backward differ by float-atomic ordering only
+        assert rel_l2(got, ref[names[name]]) <= 1e-5, name
+    assert rel_l2(normals.grad.cpu().numpy(), ref["dL_dnormals"]) <= 1e-5
+
+
+def test_chunk_hook_exception_surfaces():
+    import vcr_view_parallel as VP
+    from diff_gaussian_rasterization import GaussianRasterizer
+    inp, _, _ = make_case(600, 96, 64, seed=1)
+    dev = torch.device("cuda")
+    bucket = VP.GaussianBucket({k: inp[k].to(dev) for k in ("means3D", "shs", "opacities", "scales", "rotations")}, device=dev, direct=True)
+
+    def boom(c, first, count):
+        raise KeyError("from the hook")
+    bucket.params["means3D"]._vcr_chunk_hook = (2, boom)
+    p = bucket.params
+    out, _ = GaussianRasterizer(settings_from(inp, dev))(
+        means3D=p["means3D"], means2D=None, shs=p["shs"], normals_precomp=inp["normals"].to(dev), opacities=p["opacities"],
+        scales=p["scales"], rotations=p["rotations"], dirs=inp["dirs"].to(dev))
+    with pytest.raises(KeyError):
+        out.sum().backward()
+    torch.cuda.synchronize()
+
+
+def test_densify_stats_kernel_matches_reference_updates():
+    """vcr_densify_stats_accumulate == trainer.py:345 + scene/gaussian_model.py:669-671, two views in a row."""
+    import vcr_view_parallel as VP
+    vp = VP.ViewParallel()
+    P = 100_003
+    dev = torch.device("cuda")
+    g = torch.Generator().manual_seed(11)
+    accum, denom, max_r = torch.zeros((P, 1), device=dev), torch.zeros((P, 1), device=dev), torch.zeros(P, device=dev)
+    e_accum, e_denom, e_max = accum.clone(), denom.clone(), max_r.clone()
+    for _ in range(2):
+        grad = torch.randn((P, 3), generator=g).to(dev)
+        radii = (torch.randint(0, 60, (P,), generator=g, dtype=torch.int32) * (torch.rand(P, generator=g) > 0.4)).to(torch.int32).to(dev)
+        vp.accumulate_densification_stats(accum, denom, max_r, grad, radii)
+        vis = radii > 0                                                           # the reference's three updates
+        e_max[vis] = torch.max(e_max[vis], radii[vis].float())
+        e_accum[vis] += torch.norm(grad[vis, :2], dim=-1, keepdim=True)
+        e_denom[vis] += 1
+    torch.cuda.synchronize()
+    assert torch.equal(denom, e_denom) and torch.equal(max_r, e_max)
+    torch.testing.assert_close(accum, e_accum, rtol=1e-6, atol=1e-7)              # sqrt(x*x+y*y): contraction may differ by 1 ulp
+    assert float(denom.max()) == 2.0 and float((denom == 0).sum()) > 0

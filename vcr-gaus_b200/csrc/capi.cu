@@ -28,7 +28,7 @@ static long long g_launches[VCR_K_COUNT] = {0};
 static const char* kKernelNames[VCR_K_COUNT] = {
     "preprocess_kernel", "scan_block_sums_kernel", "duplicate_kernel", "radix_scan_hist_kernel", "radix_pass_kernel",
     "tile_ranges_kernel", "render_forward_kernel", "render_backward_kernel", "preprocess_backward_kernel",
-    "dnormal_forward_kernel", "dnormal_backward_kernel", "render_aux_kernel", "knn_kernels", "mark_visible_kernel", "memset"};
+    "dnormal_forward_kernel", "dnormal_backward_kernel", "render_aux_kernel", "knn_kernels", "mark_visible_kernel", "memset", "densify_stats_kernel", "multimem_allreduce_kernel"};
 static cudaEvent_t prof_event() {
     if (!g_prof_pool.empty()) { cudaEvent_t e = g_prof_pool.back(); g_prof_pool.pop_back(); return e; }
     cudaEvent_t e; cudaEventCreate(&e); return e;
@@ -218,7 +218,7 @@ int vcr_rasterize_forward(vcr_alloc_fn geometry_buffer, vcr_alloc_fn binning_buf
     return 0;
 }
 
-int vcr_rasterize_backward(int P, int D, int M, int R, const float* background, int width, int height, const float* means3D,
+int vcr_rasterize_backward_chunked(int P, int D, int M, int R, const float* background, int width, int height, const float* means3D,
                            const float* shs, const float* colors_precomp, const float* normals_precomp, const float* sh_objs,
                            const float* alpha, const float* depth, const float* scales, float scale_modifier,
                            const float* rotations, const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
@@ -226,7 +226,8 @@ int vcr_rasterize_backward(int P, int D, int M, int R, const float* background, 
                            char* geom_buffer, char* binning_buffer, char* img_buffer, const float* dL_dpix, float* dL_dmean2D,
                            float* dL_dmean2D_densify, float* dL_dopacity, float* dL_dcolor, float* dL_dnormal, float* dL_dobjects,
                            float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
-                           const uint8_t* inside, char* scratch, int debug, void* stream) {
+                           const uint8_t* inside, char* scratch, int debug, void* stream, int n_chunks,
+                           vcr_chunk_fn chunk_enqueued, void* chunk_user) {
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
     if (P <= 0) { vcr_set_error("P must be positive"); return 1; }
     if (!geom_buffer || !binning_buffer || !img_buffer || !scratch) { vcr_set_error("NULL state/scratch buffer"); return 1; }
@@ -255,9 +256,58 @@ int vcr_rasterize_backward(int P, int D, int M, int R, const float* background, 
     ImageState img = ImageState::carve(img_buffer, width, height);
     if (vcr_launch_render_backward(p, g, b, img, s)) return 1;
     if (debug_sync(debug, s, "render backward")) return 1;
-    if (vcr_launch_preprocess_backward(p, g, s)) return 1;
+    // The per-Gaussian stage runs as n_chunks launches over consecutive ranges (multiples of 256 Gaussians).  After each
+    // launch the caller is told which rows of the gradient outputs that launch completes, so it can queue the exchange of
+    // those rows (an all-reduce ordered after this stream's work so far) while the next range is still being computed.
+    if (n_chunks < 1) n_chunks = 1;
+    const int blocks = (P + 255) / 256;
+    if (n_chunks > blocks) n_chunks = blocks;
+    for (int c = 0; c < n_chunks; c++) {
+        const int b0 = (int)((long long)blocks * c / n_chunks), b1 = (int)((long long)blocks * (c + 1) / n_chunks);
+        const int first = b0 * 256, count = (b1 * 256 < P ? b1 * 256 : P) - first;
+        if (vcr_launch_preprocess_backward(p, g, first, count, s)) return 1;
+        if (chunk_enqueued) chunk_enqueued(chunk_user, c, first, count);
+    }
     if (debug_sync(debug, s, "preprocess backward")) return 1;
     return 0;
+}
+
+int vcr_rasterize_backward(int P, int D, int M, int R, const float* background, int width, int height, const float* means3D,
+                           const float* shs, const float* colors_precomp, const float* normals_precomp, const float* sh_objs,
+                           const float* alpha, const float* depth, const float* scales, float scale_modifier,
+                           const float* rotations, const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+                           const float* dirs, const float* campos, float tan_fovx, float tan_fovy, const int* radii,
+                           char* geom_buffer, char* binning_buffer, char* img_buffer, const float* dL_dpix, float* dL_dmean2D,
+                           float* dL_dmean2D_densify, float* dL_dopacity, float* dL_dcolor, float* dL_dnormal, float* dL_dobjects,
+                           float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
+                           const uint8_t* inside, char* scratch, int debug, void* stream) {
+    return vcr_rasterize_backward_chunked(P, D, M, R, background, width, height, means3D, shs, colors_precomp, normals_precomp, sh_objs,
+                                          alpha, depth, scales, scale_modifier, rotations, cov3D_precomp, viewmatrix, projmatrix, dirs,
+                                          campos, tan_fovx, tan_fovy, radii, geom_buffer, binning_buffer, img_buffer, dL_dpix,
+                                          dL_dmean2D, dL_dmean2D_densify, dL_dopacity, dL_dcolor, dL_dnormal, dL_dobjects, dL_dmean3D,
+                                          dL_dcov3D, dL_dsh, dL_dscale, dL_drot, inside, scratch, debug, stream, 1, nullptr, nullptr);
+}
+
+int vcr_multimem_allreduce_sum(void* multicast_base, int n_ranges, const long long* first_float_host,
+                               const long long* n_floats_host, int rank, int world, int blocks, void* stream) {
+    if (!multicast_base) { vcr_set_error("NULL multicast address (no NVLink multicast mapping for this buffer)"); return 1; }
+    if (n_ranges < 0 || n_ranges > 8) { vcr_set_error("at most 8 ranges per launch"); return 1; }
+    if (world < 1 || rank < 0 || rank >= world) { vcr_set_error("bad rank / world"); return 1; }
+    if (n_ranges == 0) return 0;
+    if (!first_float_host || !n_floats_host) { vcr_set_error("NULL range arrays"); return 1; }
+    for (int i = 0; i < n_ranges; i++)
+        if (first_float_host[i] < 0 || n_floats_host[i] < 0) { vcr_set_error("negative range"); return 1; }
+    if (blocks <= 0) blocks = 74;   // 2.4 MB in flight already saturates the links; half the SMs stay free (tools/mm_bench.py)
+    return vcr_launch_multimem_allreduce(static_cast<float*>(multicast_base), n_ranges, first_float_host, n_floats_host, rank, world,
+                                         blocks, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int vcr_densify_stats_accumulate(int P, const float* grad_means2D_densify, const int* radii, float* xyz_gradient_accum,
+                                 float* denom, float* max_radii2D, void* stream) {
+    if (P <= 0) return 0;
+    if (!grad_means2D_densify || !radii || !xyz_gradient_accum || !denom || !max_radii2D) { vcr_set_error("NULL argument"); return 1; }
+    return vcr_launch_densify_stats(P, grad_means2D_densify, radii, xyz_gradient_accum, denom, max_radii2D,
+                                    reinterpret_cast<cudaStream_t>(stream));
 }
 
 int vcr_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix, uint8_t* present, void* stream) {

@@ -271,8 +271,9 @@ __device__ __forceinline__ void preprocess_backward_body(const BwdParams& p, con
 }
 
 template <bool COOP>
-__global__ void __launch_bounds__(256) preprocess_backward_kernel(const BwdParams p, const GeomState g) {
-    const int idx = blockIdx.x * 256 + threadIdx.x;
+__global__ void __launch_bounds__(256) preprocess_backward_kernel(const BwdParams p, const GeomState g, const int first_block) {
+    const int block = first_block + (int)blockIdx.x;        // a launch covers blocks [first_block, first_block + gridDim.x)
+    const int idx = block * 256 + threadIdx.x;
     __shared__ float V[16], Pm[16];
     __shared__ float s_basis[COOP ? 256 * 17 : 1];  // stride 17: conflict-free per-thread rows
     __shared__ float s_gg[COOP ? 256 * 3 : 1];
@@ -289,7 +290,7 @@ __global__ void __launch_bounds__(256) preprocess_backward_kernel(const BwdParam
     if (COOP) {
         __syncthreads();
         // dL_dsh tile of this block: 256 Gaussians x 48 floats = 3072 float4, written as coalesced 16-byte stores
-        const size_t base = (size_t)blockIdx.x * 256 * 48;
+        const size_t base = (size_t)block * 256 * 48;
         const size_t total = (size_t)p.P * 48;
         float4* out4 = reinterpret_cast<float4*>(p.dL_dsh + base);
 #pragma unroll 4
@@ -309,11 +310,14 @@ __global__ void __launch_bounds__(256) preprocess_backward_kernel(const BwdParam
     }
 }
 
-int vcr_launch_preprocess_backward(const BwdParams& p, GeomState& g, cudaStream_t s) {
+int vcr_launch_preprocess_backward(const BwdParams& p, GeomState& g, int first_gaussian, int n_gaussians, cudaStream_t s) {
+    // Gaussians [first_gaussian, first_gaussian + n_gaussians); first_gaussian must be a multiple of 256 (one block's worth)
+    if (n_gaussians <= 0) return 0;
     VcrProfScope prof(VCR_K_PREPROCESS_BWD, s);
     const bool coop = p.shs != nullptr && p.M == 16 && p.dL_dsh != nullptr;
-    if (coop) preprocess_backward_kernel<true><<<(p.P + 255) / 256, 256, 0, s>>>(p, g);
-    else preprocess_backward_kernel<false><<<(p.P + 255) / 256, 256, 0, s>>>(p, g);
+    const int first_block = first_gaussian / 256, blocks = (n_gaussians + 255) / 256;
+    if (coop) preprocess_backward_kernel<true><<<blocks, 256, 0, s>>>(p, g, first_block);
+    else preprocess_backward_kernel<false><<<blocks, 256, 0, s>>>(p, g, first_block);
     VCR_LAUNCH_CHECK("preprocess_backward_kernel");
     return 0;
 }

@@ -147,6 +147,9 @@ class _RasterizeGaussians(torch.autograd.Function):
         # `_vcr_grad_out` tensor; the backward kernel then writes that gradient straight into it (every element is
         # written) and autograd adopts a view of it as `.grad` instead of allocating + accumulating.
         ctx.grad_out = tuple(getattr(t, "_vcr_grad_out", None) for t in (means3D, sh, opacities, scales, rotations))
+        # Optional chunk hook (vcr_view_parallel.ViewParallel.overlap_gradients): `means3D._vcr_chunk_hook = (n_chunks, fn)`
+        # makes the backward run its per-Gaussian stage in n_chunks launches and call fn(chunk, first, count) after each.
+        ctx.chunk_hook = getattr(means3D, "_vcr_chunk_hook", None)
         depth, alpha = outmap[3:4], outmap[7:8]
         ctx.save_for_backward(colors_precomp, normals_precomp, semantics_precomp, means3D, scales, rotations, cov3Ds_precomp,
                               radii, sh, geomBuffer, binningBuffer, imgBuffer, alpha, depth, dirs, inside)
@@ -205,6 +208,18 @@ class _RasterizeGaussians(torch.autograd.Function):
                     torch.save(cpu_args, "snapshot_bw.dump")
                     print("\nAn error occured in backward. Writing snapshot_bw.dump for debugging.\n")
                     raise ex
+            elif getattr(ctx, "chunk_hook", None) is not None:
+                n_chunks, hook = ctx.chunk_hook
+                failure = []
+                def _cb(_user, chunk, first, count):
+                    try:
+                        hook(chunk, first, count)
+                    except BaseException as ex:      # exceptions cannot cross the C frame; re-raised below
+                        failure.append(ex)
+                cb = _n.CHUNK_FN(_cb)
+                _n.check(_n.vcr_rasterize_backward_chunked(*args, int(n_chunks), cb, None), "rasterize_gaussians_backward")
+                if failure:
+                    raise failure[0]
             else:
                 _n.check(_n.vcr_rasterize_backward(*args), "rasterize_gaussians_backward")
         else:
@@ -216,7 +231,8 @@ class _RasterizeGaussians(torch.autograd.Function):
             # inputs that were absent (zero-sized placeholders) get no gradient
             return g if ref.numel() != 0 else None
 
-        return (g_means3D, g_means2D, g_means2D_densify, match(g_sh, sh), match(g_colors, colors_precomp),
+        need = ctx.needs_input_grad      # means2D / means2D_densify may have been passed as None
+        return (g_means3D, g_means2D if need[1] else None, g_means2D_densify if need[2] else None, match(g_sh, sh), match(g_colors, colors_precomp),
                 match(g_normals, normals_precomp), match(g_objects, semantics_precomp), g_opacity, match(g_scales, scales),
                 match(g_rot, rotations), match(g_cov3D, cov3Ds_precomp), None, None, None)
 

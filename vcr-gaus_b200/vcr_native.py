@@ -53,6 +53,18 @@ vcr_rasterize_backward = _sig(
      c_float, c_float, P_, P_, P_, P_, P_,
      P_, P_, P_, P_, P_, P_, P_, P_, P_, P_, P_, P_, P_, c_int, c_void_p])
 
+CHUNK_FN = ctypes.CFUNCTYPE(None, c_void_p, c_int, c_int, c_int)   # (user, chunk, first_gaussian, n_gaussians)
+vcr_rasterize_backward_chunked = _sig(
+    "vcr_rasterize_backward_chunked", c_int,
+    [c_int, c_int, c_int, c_int, P_, c_int, c_int, P_, P_, P_, P_, P_, P_, P_, P_, c_float, P_, P_, P_, P_, P_, P_,
+     c_float, c_float, P_, P_, P_, P_, P_,
+     P_, P_, P_, P_, P_, P_, P_, P_, P_, P_, P_, P_, P_, c_int, c_void_p, c_int, CHUNK_FN, c_void_p])
+
+vcr_multimem_allreduce_sum = _sig("vcr_multimem_allreduce_sum", c_int,
+                                  [c_void_p, c_int, POINTER(ctypes.c_longlong), POINTER(ctypes.c_longlong), c_int, c_int, c_int, c_void_p])
+
+vcr_densify_stats_accumulate = _sig("vcr_densify_stats_accumulate", c_int, [c_int, P_, P_, P_, P_, P_, c_void_p])
+
 vcr_mark_visible = _sig("vcr_mark_visible", c_int, [c_int, P_, P_, P_, P_, c_void_p])
 
 vcr_rasterize_count = _sig(
@@ -126,6 +138,7 @@ DECLARED_SYMBOLS = [
     "vcr_knn_scratch_bytes", "vcr_dist2_knn3", "vcr_geom_layout", "vcr_binning_layout", "vcr_image_layout",
     "vcr_knn_noalloc_max_points", "vcr_dist2_knn3_noalloc", "vcr_view_loss_forward", "vcr_view_loss_backward",
     "vcr_profile_enable", "vcr_profile_kernel_count", "vcr_profile_kernel_name", "vcr_profile_read",
+    "vcr_rasterize_backward_chunked", "vcr_densify_stats_accumulate", "vcr_multimem_allreduce_sum",
 ]
 
 

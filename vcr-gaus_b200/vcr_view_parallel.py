@@ -13,6 +13,7 @@ rank renders a different view; the only exchange is
 
 Backends: "nccl" on GPUs (NVLink 5 / NVSwitch), "gloo" on CPU for the tests.  No collective is issued at world size 1.
 """
+import ctypes
 import os
 from typing import Dict, Optional
 
@@ -45,10 +46,12 @@ class GaussianBucket:
     `params[name]` are views into `flat`; their `.grad` are views into `grad_flat`, so autograd accumulates straight
     into the bucket and the gradient exchange is a single collective with no packing copy."""
 
-    def __init__(self, tensors: Dict[str, torch.Tensor], device=None, direct: bool = False):
+    def __init__(self, tensors: Dict[str, torch.Tensor], device=None, direct: bool = False, grad_storage=None):
         """direct=True: the rasterizer's backward writes each parameter gradient straight into `grad_flat` (through the
         `_vcr_grad_out` hook of diff_gaussian_rasterization) and autograd adopts views of it as `.grad` — no per-step
-        memset of the bucket and no accumulate pass.  The price: exactly one backward per `zero_grad()`."""
+        memset of the bucket and no accumulate pass.  The price: exactly one backward per `zero_grad()`.
+        grad_storage: a flat float32 tensor to use as `grad_flat` (ViewParallel.symmetric_gradient_storage() for the
+        NVSwitch-multicast exchange); default is an ordinary allocation."""
         self.direct = direct
         P = tensors["means3D"].shape[0]
         self.P = P
@@ -62,7 +65,12 @@ class GaussianBucket:
         self.numel = off
         device = device if device is not None else tensors["means3D"].device
         self.flat = torch.empty(off, dtype=torch.float32, device=device)
-        self.grad_flat = torch.zeros(off, dtype=torch.float32, device=device)
+        if grad_storage is None:
+            self.grad_flat = torch.zeros(off, dtype=torch.float32, device=device)
+        else:
+            if grad_storage.dtype != torch.float32 or grad_storage.numel() < off or not grad_storage.is_contiguous():
+                raise ValueError("grad_storage must be a contiguous float32 tensor of at least numel_for(tensors) elements")
+            self.grad_flat = grad_storage.view(-1)[:off].zero_()
         self.params = {}
         for name, o, n, shape in self.layout:
             self.flat[o:o + n].copy_(tensors[name].reshape(-1))
@@ -72,6 +80,10 @@ class GaussianBucket:
             else:
                 p.grad = self.grad_flat[o:o + n].view(shape)
             self.params[name] = p
+
+    @staticmethod
+    def numel_for(tensors: Dict[str, torch.Tensor]) -> int:
+        return sum(tensors[name].numel() for name, _ in PARAM_LAYOUT)
 
     def zero_grad(self):
         if self.direct:
@@ -100,9 +112,26 @@ class ViewParallel:
         perm = torch.randperm(n_views, generator=g)
         return int(perm[(k * self.world + self.rank) % n_views])
 
+    def cost_ordered_shard(self, local_costs, seed: int = 0):
+        """Order in which this rank should visit ITS shard of the views so that the `world` views of one step cost about
+        the same: position k of the returned list is the rank's j-th cheapest view, where j = sigma(k) is a permutation
+        shared by all ranks (seeded, so the visiting order still changes from epoch to epoch with `seed`).  Every step
+        ends with the gradient exchange, i.e. with a wait for the slowest rank; pairing views of equal cost removes that
+        wait.  `local_costs`: one number per local view (e.g. the rasterizer's instance count R from the previous epoch).
+        No communication."""
+        n = len(local_costs)
+        by_cost = sorted(range(n), key=lambda v: (local_costs[v], v))
+        sigma = torch.randperm(n, generator=torch.Generator().manual_seed(seed * 7_919 + 17)).tolist()
+        return [by_cost[j] for j in sigma]
+
     def allreduce_gradients(self, bucket: GaussianBucket, average: bool = True, async_op: bool = False):
         """SUM (or mean) of the flat gradient bucket over ranks.  Returns the work handle when async_op."""
         if self.world == 1:
+            return None
+        if getattr(self, "transport", "nccl") == "multimem" and self._in_symmetric_storage(bucket):
+            self.multimem_allreduce(bucket)
+            if average:
+                bucket.grad_flat.div_(self.world)
             return None
         work = dist.all_reduce(bucket.grad_flat, op=dist.ReduceOp.SUM, group=self.group, async_op=async_op)
         if average:
@@ -112,11 +141,175 @@ class ViewParallel:
             bucket.grad_flat.div_(self.world)
         return work
 
+    def symmetric_gradient_storage(self, numel: int, device):
+        """Allocate a float32 gradient bucket in symmetric memory (same offset on every rank) and map the NVLink multicast
+        object that spans the ranks' copies.  Collective: every rank calls it with the same numel.  Returns None when the
+        GPUs have no multicast support (then use the NCCL transport).  torch's symmetric-memory runtime is used for the
+        allocation, the rendezvous and the inter-GPU barrier only; the data movement is this library's kernel."""
+        if self.world == 1:
+            return None
+        try:
+            import torch.distributed._symmetric_memory as symm_mem
+            group = self.group if self.group is not None else dist.group.WORLD
+            t = symm_mem.empty(int(numel), dtype=torch.float32, device=torch.device(device))
+            hdl = symm_mem.rendezvous(t, group)
+            ok = torch.tensor([1 if getattr(hdl, "multicast_ptr", 0) else 0], device=t.device)
+        except Exception:
+            t, hdl = None, None
+            ok = torch.tensor([0], device=torch.device(device))
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.group)     # every rank takes the same decision
+        if int(ok) == 0:
+            return None
+        self._symm = (t, hdl)
+        return t
+
+    def _in_symmetric_storage(self, bucket: GaussianBucket) -> bool:
+        t, _ = getattr(self, "_symm", (None, None))
+        return t is not None and bucket.grad_flat.data_ptr() == t.data_ptr()
+
+    def multimem_allreduce(self, bucket: GaussianBucket):
+        """SUM of the whole bucket over ranks on the current stream with this library's NVSwitch-multicast kernel
+        (vcr_multimem_allreduce_sum): barrier (every rank's gradients are written) -> one launch -> barrier (every rank's
+        stores have landed).  The bucket must live in symmetric_gradient_storage()."""
+        import vcr_native as _n
+        if not self._in_symmetric_storage(bucket):
+            raise ValueError("multimem_allreduce needs GaussianBucket(grad_storage=symmetric_gradient_storage(...))")
+        _, hdl = self._symm
+        one = ctypes.c_longlong * 1
+        hdl.barrier(channel=0, timeout_ms=30000)
+        _n.check(_n.vcr_multimem_allreduce_sum(ctypes.c_void_p(int(hdl.multicast_ptr)), 1, one(0), one(bucket.numel), self.rank,
+                                               self.world, int(os.environ.get("VCR_MM_BLOCKS", "0")),
+                                               ctypes.c_void_p(torch.cuda.current_stream(bucket.grad_flat.device).cuda_stream)),
+                 "multimem_allreduce_sum")
+        hdl.barrier(channel=0, timeout_ms=30000)
+
+    def pick_transport(self, bucket: GaussianBucket, iters: int = 10):
+        """Time the exchange of this bucket both ways (NCCL all_reduce; the multicast kernel when the bucket is in symmetric
+        storage), keep the faster as `self.transport` and return the measured milliseconds.  Which one wins depends on the
+        number of ranks: through the switch every element also loops back to its own GPU, which costs 1/world of the
+        traffic — 50 % extra at 2 ranks, 14 % at 8 — while the in-switch reduction saves NCCL's per-peer work.
+        Collective; the bucket's gradient contents are clobbered."""
+        self.transport = "nccl"
+        if self.world == 1:
+            return {}
+        dev = bucket.grad_flat.device
+        ways = {"nccl": lambda: dist.all_reduce(bucket.grad_flat, op=dist.ReduceOp.SUM, group=self.group)}
+        if self._in_symmetric_storage(bucket):
+            ways["multimem"] = lambda: self.multimem_allreduce(bucket)
+        ms = {}
+        for name, fn in ways.items():
+            bucket.grad_flat.zero_()
+            for _ in range(3):
+                fn()
+            torch.cuda.synchronize(dev)
+            dist.barrier(group=self.group)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(iters):
+                fn()
+            e1.record()
+            torch.cuda.synchronize(dev)
+            t = torch.tensor([e0.elapsed_time(e1) / iters], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)     # same number, hence same choice, on every rank
+            ms[name] = float(t)
+        self.transport = min(ms, key=ms.get)
+        bucket.grad_flat.zero_()
+        return ms
+
+    def overlap_gradients(self, bucket: GaussianBucket, n_chunks: int = 4, transport: str = "nccl"):
+        """Pipeline the gradient exchange with the tail of the backward: the rasterizer's per-Gaussian backward stage is
+        issued as `n_chunks` launches over consecutive Gaussian ranges (vcr_rasterize_backward_chunked) and the all-reduce
+        of each range's rows of the bucket is queued as soon as that launch is enqueued, so the exchange of range c runs on
+        the communication stream while range c+1 is being computed.  The five row slices of a range (one per parameter
+        group) go out as ONE coalesced collective.  Needs a `direct=True` bucket (gradients land in the bucket while the
+        backward is still running) and exactly one rasterizer backward per step; call finish_gradients() afterwards in
+        place of allreduce_gradients().  A no-op at world size 1."""
+        if not bucket.direct:
+            raise ValueError("overlap_gradients needs GaussianBucket(direct=True)")
+        self._pending = []
+        if self.world == 1:
+            return
+        rows = [(off, n // bucket.P) for _, off, n, _ in bucket.layout]
+        self._transport = transport
+        if transport == "multimem":
+            # transport="multimem": the bucket lives in symmetric_gradient_storage(); each range is exchanged by ONE launch
+            # of this library's two-shot kernel (multimem.ld_reduce / multimem.st through the NVSwitch,
+            # csrc/view_parallel.cu) on a side stream, bracketed by the symmetric-memory barrier
+            import vcr_native as _n
+            t, hdl = getattr(self, "_symm", (None, None))
+            if t is None or bucket.grad_flat.data_ptr() != t.data_ptr():
+                raise ValueError("transport='multimem' needs GaussianBucket(grad_storage=symmetric_gradient_storage(...))")
+            dev = bucket.grad_flat.device
+            self._comm = torch.cuda.Stream(device=dev)
+            mc = ctypes.c_void_p(int(hdl.multicast_ptr))
+            nr = len(rows)
+            blocks = int(os.environ.get("VCR_MM_BLOCKS", "0"))
+            arr = ctypes.c_longlong * nr
+
+            def on_chunk(_chunk, first, count):
+                ev = torch.cuda.Event()
+                ev.record()                                    # this range's gradient rows are final after this point
+                with torch.cuda.stream(self._comm):
+                    self._comm.wait_event(ev)
+                    hdl.barrier(channel=0, timeout_ms=30000)   # ... on every rank
+                    _n.check(_n.vcr_multimem_allreduce_sum(mc, nr, arr(*[off + first * per for off, per in rows]),
+                                                           arr(*[count * per for _, per in rows]), self.rank, self.world,
+                                                           blocks, ctypes.c_void_p(self._comm.cuda_stream)),
+                             "multimem_allreduce_sum")
+                self._pending.append(None)
+
+            def finish():
+                with torch.cuda.stream(self._comm):
+                    hdl.barrier(channel=0, timeout_ms=30000)   # every rank's stores have landed everywhere
+                    done = torch.cuda.Event()
+                    done.record()
+                torch.cuda.current_stream().wait_event(done)
+            self._mm_finish = finish
+        elif transport == "nccl":
+            def on_chunk(_chunk, first, count):
+                with dist._coalescing_manager(group=self.group, async_ops=True) as cm:
+                    for off, per in rows:
+                        dist.all_reduce(bucket.grad_flat[off + first * per: off + (first + count) * per],
+                                        op=dist.ReduceOp.SUM, group=self.group)
+                self._pending.append(cm)
+        else:
+            raise ValueError("transport must be 'nccl' or 'multimem'")
+
+        bucket.params["means3D"]._vcr_chunk_hook = (max(int(n_chunks), 1), on_chunk)
+
+    def finish_gradients(self, bucket: GaussianBucket, average: bool = False):
+        """Order the current stream after every chunk exchange queued by the overlap_gradients() hook during the last
+        backward.  Returns the number of chunk collectives that were pending."""
+        pending, self._pending = getattr(self, "_pending", []), []
+        if getattr(self, "_transport", "nccl") == "multimem":
+            if pending:
+                self._mm_finish()
+        else:
+            for cm in pending:
+                cm.wait()
+        if average and self.world > 1:
+            bucket.grad_flat.div_(self.world)
+        return len(pending)
+
     def accumulate_densification_stats(self, xyz_gradient_accum, denom, max_radii2D, grad_means2D_densify, radii):
         """Per view, LOCAL: add_densification_stats (scene/gaussian_model.py:669-671) + the max_radii2D update
         (trainer.py:345).  No communication: sums and maxima commute, and the statistics are only read when the model
         densifies (every 100 iterations, trainer.py:357-370), so the ranks are combined there, once, by
         sync_densification_stats().  Tensors are updated in place; shapes [P,1], [P,1], [P]."""
+        if radii.is_cuda:
+            # one fused pass (csrc/view_parallel.cu) instead of ~10 small PyTorch launches
+            import vcr_native as _n
+            g, r = grad_means2D_densify.contiguous(), radii.contiguous()
+            ok = (g.dtype == torch.float32 and r.dtype == torch.int32 and all(
+                t.dtype == torch.float32 and t.is_contiguous() and t.is_cuda for t in (xyz_gradient_accum, denom, max_radii2D)))
+            if not ok:
+                raise TypeError("densification statistics: expected contiguous float32 accumulators, float32 grads, int32 radii")
+            _n.check(_n.vcr_densify_stats_accumulate(int(r.numel()), g.data_ptr(), r.data_ptr(), xyz_gradient_accum.data_ptr(),
+                                                     denom.data_ptr(), max_radii2D.data_ptr(),
+                                                     ctypes.c_void_p(torch.cuda.current_stream(r.device).cuda_stream)),
+                     "densify_stats_accumulate")
+            return
+        # CPU tensors (the gloo tests): the same three updates in PyTorch
         visible = radii > 0
         xyz_gradient_accum.add_((torch.norm(grad_means2D_densify[:, :2], dim=-1) * visible).unsqueeze(1))
         denom.add_(visible.unsqueeze(1).to(denom.dtype))
