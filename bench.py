@@ -22,6 +22,7 @@ Arms
                  as `cpu_baseline` inside the default arm at N = 1.
 """
 import argparse
+import gc
 import json
 import math
 import os
@@ -115,22 +116,56 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------------------------
-def build_workload(args, rank, world):
-    """Scene (identical on every rank) + this rank's views, all on the CPU."""
+def build_scene(args):
     import vcr_synth as S
     scene = S.make_scene(args.gaussians, seed=0)
     scene.scales.mul_(args.footprint)
+    return scene
+
+
+def build_views(args, scene, world, view_ids, light=False):
+    """Views `view_ids` of the ring of args.views * world cameras, on the CPU.  light=True: camera and rasterizer inputs only
+    (enough to measure a view's cost), no ground-truth images."""
+    import vcr_synth as S
     views = []
     n_total = args.views * world
-    for v in range(args.views):
-        cam = S.make_camera(args.width, args.height, idx=v * world + rank, n_views=n_total)
-        g = torch.Generator().manual_seed(10_000 + v * world + rank)
-        H, W = args.height, args.width
-        gt_image = torch.rand((3, H, W), generator=g)
-        gt_normal = F.normalize(torch.randn((H, W, 3), generator=g) * 0.4 + torch.tensor([0.0, 0.0, -1.0]), dim=-1)
-        views.append(dict(cam=cam, inp=S.raster_inputs(scene, cam, use_dirs=True, use_sem=False, seed=v),
-                          gt_image=gt_image.contiguous(), gt_normal=gt_normal.contiguous()))
-    return scene, views
+    for gid in view_ids:
+        cam = S.make_camera(args.width, args.height, idx=gid, n_views=n_total)
+        view = dict(id=gid, cam=cam, inp=S.raster_inputs(scene, cam, use_dirs=True, use_sem=False, seed=gid // world))
+        if not light:
+            g = torch.Generator().manual_seed(10_000 + gid)
+            H, W = args.height, args.width
+            gt_image = torch.rand((3, H, W), generator=g)
+            gt_normal = F.normalize(torch.randn((H, W, 3), generator=g) * 0.4 + torch.tensor([0.0, 0.0, -1.0]), dim=-1)
+            view.update(gt_image=gt_image.contiguous(), gt_normal=gt_normal.contiguous())
+        views.append(view)
+    return views
+
+
+def build_workload(args, rank, world):
+    """Scene (identical on every rank) + this rank's default shard of the views (every world-th camera of the ring)."""
+    scene = build_scene(args)
+    return scene, build_views(args, scene, world, [v * world + rank for v in range(args.views)])
+
+
+def measure_view_costs(args, bucket, views, dev):
+    """R (number of (tile, Gaussian) instances) of each view: one forward without autograd — what a trainer knows about a
+    view from the previous epoch."""
+    from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+    p = bucket.params
+    costs = []
+    for v in views:
+        i = v["inp"]
+        rs = GaussianRasterizationSettings(image_height=args.height, image_width=args.width, tanfovx=i["tanfovx"], tanfovy=i["tanfovy"],
+                                           bg=i["bg"].to(dev), scale_modifier=1.0, viewmatrix=i["viewmatrix"].to(dev),
+                                           projmatrix=i["projmatrix"].to(dev), sh_degree=3, campos=i["campos"].to(dev),
+                                           prefiltered=False, debug=False, f_count=0)
+        with torch.no_grad():
+            GaussianRasterizer(rs)(means3D=p["means3D"].detach(), means2D=None, opacities=p["opacities"].detach(), shs=p["shs"].detach(),
+                                   normals_precomp=i["normals"].to(dev), scales=p["scales"].detach(), rotations=p["rotations"].detach(),
+                                   dirs=i["dirs"].to(dev))
+        costs.append(float(last_num_rendered()))
+    return costs
 
 
 def ref_dnormal_chain(depth, K, gt_normal, render_normal, exp_t):
@@ -227,20 +262,17 @@ class Stepper:
         self.copy_stream = torch.cuda.Stream(device=dev)
         self._prefetched = None
         self.diag_events = None
-        self.view_cost = [0.0] * len(views)      # R of each local view, measured during the first warm-up pass
-        self.order = list(range(len(views)))
         self.skip = os.environ.get("VCR_BENCH_SKIP", "")   # diagnosis only: "grads", "stats" or "grads,stats"
         # N > 1: pipeline the gradient all-reduce with the per-Gaussian backward stage in this many ranges (0 = one
         # all-reduce after the backward)
-        # (measured: no gain from the pipelining at 2 or 8 GPUs — the exchange slows the overlapped launches down by as much
-        # as it hides — so the default is one exchange after the backward)
-        self.chunks = int(os.environ.get("VCR_BENCH_CHUNKS", "0")) if (impl == "ours" and vp.world > 1) else 0
-        self.exchange_ms = {}
+        self.chunks, self.exchange_ms = 0, {}
         if impl == "ours" and vp.world > 1:
             self.exchange_ms = vp.pick_transport(bucket)          # NCCL or the multicast kernel, whichever is faster here
             forced = os.environ.get("VCR_BENCH_TRANSPORT")
             if forced in ("nccl", "multimem") and (forced == "nccl" or bucket.transport == "multimem"):
                 vp.transport = forced
+            # pipelining pays with the multicast kernel (a quarter of the SMs, 8 GPUs: -0.04 ms/step), not with NCCL
+            self.chunks = int(os.environ.get("VCR_BENCH_CHUNKS", "4" if vp.transport == "multimem" else "0"))
         if self.chunks > 0 and "grads" not in self.skip:
             vp.overlap_gradients(bucket, n_chunks=self.chunks, transport=vp.transport)
         if impl == "reference":
@@ -254,17 +286,8 @@ class Stepper:
         # normals_precomp depends on the view (flip towards the camera + w2c rotation): precomputed per view on device
         self.normals = [v["inp"]["normals"].to(dev).requires_grad_(True) for v in views]
 
-    def note_view_cost(self, i):
-        """Warm-up bookkeeping: remember the number of (tile, Gaussian) instances R of local view i (what a trainer knows
-        from the previous epoch).  After the last view, N > 1: order the local shard by cost so that step k takes every
-        rank's k-th cheapest view — the ranks of one step then finish together instead of waiting for the slowest view
-        (ViewParallel.cost_ordered_shard)."""
-        self.view_cost[i] = float(last_num_rendered())
-        if i == len(self.views) - 1 and self.vp.world > 1 and self.impl == "ours" and os.environ.get("VCR_BENCH_BALANCE", "1") == "1":
-            self.order = self.vp.cost_ordered_shard(self.view_cost, seed=0)
-
     def _issue_prefetch(self, i):
-        k = self.order[i % len(self.views)]
+        k = i % len(self.views)
         with torch.cuda.stream(self.copy_stream):
             d = {name: t.to(self.dev, non_blocking=True) for name, t in self.host[k].items()}
             ev = torch.cuda.Event()
@@ -275,7 +298,7 @@ class Stepper:
         self._prefetched = (i, d, ev)
 
     def step(self, i, e2e):
-        k = self.order[i % len(self.views)]
+        k = i % len(self.views)
         p = self.bucket.params
         if e2e:
             # per-view inputs come from pinned host memory every step; like a data loader with prefetch depth 1 the
@@ -436,7 +459,7 @@ def main():
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
     vp = VP.ViewParallel()
-    scene, views = build_workload(args, rank, world)
+    scene = build_scene(args)
     impl = args.impl
     if impl == "reference":
         import ref_ab
@@ -445,6 +468,21 @@ def main():
                 emit(({"impl": "reference", "unavailable": "oracle/_ref/_C.so (reference CUDA build) not present on this box"}))
             return
     bucket = clone_params(scene, dev, direct=(impl == "ours"), vp=vp)
+    view_ids = [v * world + rank for v in range(args.views)]          # default shard: every world-th camera of the ring
+    balanced = world > 1 and impl == "ours" and os.environ.get("VCR_BENCH_BALANCE", "1") == "1"
+    if balanced:
+        # Cost-balanced sharding: every step ends with the gradient exchange, i.e. with a wait for the slowest rank, so the
+        # `world` views of one step should cost the same.  Each rank measures R of its default shard, the costs are
+        # gathered, and ViewParallel.balanced_view_table deals views of equal cost to the ranks of one step.
+        mine = torch.tensor(measure_view_costs(args, bucket, build_views(args, scene, world, view_ids, light=True), dev), device=dev)
+        allc = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(allc, mine)
+        costs = [0.0] * (args.views * world)
+        for r in range(world):
+            for v in range(args.views):
+                costs[v * world + r] = float(allc[r][v])
+        view_ids = [row[rank] for row in vp.balanced_view_table(costs, seed=0)]
+    views = build_views(args, scene, world, view_ids)
     stepper = Stepper(args, impl, bucket, views, dev, vp)
 
     import vcr_native as N
@@ -456,11 +494,13 @@ def main():
     # per-view buffer size (the binning buffer depends on R) and no cudaMalloc lands in the timed region
     # ... and long enough (a fixed count, identical on every rank) for clocks and power state to settle under load
     sampler = ClockSampler(dev.index or 0)
+    # no cyclic garbage collection inside the measured regions: a generation-2 pass on ONE rank stalls that rank's launches
+    # for milliseconds and, through the per-step exchange, every other rank with it (the step creates no reference cycles)
+    gc.collect()
+    gc.disable()
     n_warm = max(args.warmup, 3 * len(views), 200 if impl == "ours" else 60)
     for i in range(n_warm):
         stepper.step(i, False)
-        if i < len(views):
-            stepper.note_view_cost(i)
     if impl == "ours":
         N.profile_read(reset=True)
     ms, clocks = timed_region(stepper, args.steps, 0, False, dev, world, sampler=sampler)
@@ -495,7 +535,7 @@ def main():
                    "l2": "working set per step (parameters + gradients + per-view state > 600 MB) exceeds the 126 MB L2; views rotate every step",
                    "not_in_step": "SSIM, Adam (outside the hot path, SURVEY.md 8f)"},
         "clocks": clocks,
-        "exchange": ({"chosen": vp.transport, "ms_per_236MB_bucket": stepper.exchange_ms, "view_order": "cost-ordered shard" if stepper.order != list(range(len(views))) else "as listed"}
+        "exchange": ({"chosen": vp.transport, "ms_per_236MB_bucket": stepper.exchange_ms, "view_sharding": "cost-balanced (balanced_view_table)" if balanced else "every world-th camera"}
                      if world > 1 and impl == "ours" else None),
         "e2e": {"value": e2e_vps, "unit": "views/s", "h2d_bytes_per_step": stepper.h2d_bytes, "d2h_bytes_per_step": stepper.d2h_bytes,
                 "ms_per_step": ms_e2e / args.steps},

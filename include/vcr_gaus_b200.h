@@ -200,7 +200,7 @@ int vcr_densify_stats_accumulate(int P, const float* grad_means2D_densify, const
  * ranges [first_float_host[i], +n_floats_host[i]) this rank reduces its 1/world share with multimem.ld_reduce (the sum is
  * formed inside the switch) and writes it to every rank with multimem.st: a two-shot all-reduce(SUM) in ONE launch, S
  * bytes in and S bytes out per GPU.  The range arrays are HOST arrays, consumed before the call returns.  `blocks` <= 0
- * picks 74.  The launch waits for nobody: the caller must order it after every rank has written the ranges and
+ * picks 37.  The launch waits for nobody: the caller must order it after every rank has written the ranges and
  * order consumers after every rank's launch has completed (symmetric-memory barrier on `stream`, see
  * vcr_view_parallel.py).  All ranks must pass identical ranges. */
 int vcr_multimem_allreduce_sum(void* multicast_base, int n_ranges, const long long* first_float_host,

@@ -13,7 +13,7 @@ import pytest
 import torch
 
 from oracle import oracle as O
-from util import CudaRun, make_case, np_inputs, rel_l2
+from util import CudaRun, make_case, np_inputs, rel_l2, settings_from
 
 pytestmark = pytest.mark.gpu
 
@@ -187,3 +187,35 @@ def test_mark_visible_and_aux_modes():
     o3 = O.rasterize_forward(npi, mode=3)
     assert ((cnt3.cpu().numpy() > 0) != (o3["gaussians_count"] > 0)).mean() < 1e-3
     assert abs(int(cnt3.sum()) - int(o3["gaussians_count"].sum())) <= 4
+
+
+def test_no_reference_cycles_per_view():
+    """A forward+backward must release its per-view buffers by reference counting alone: with the cyclic garbage collector
+    switched off (as training loops do to avoid its pauses) device memory must not grow from view to view."""
+    import gc
+    from diff_gaussian_rasterization import GaussianRasterizer
+    inp, _, _ = make_case(20000, 400, 300, seed=2)
+    dev = torch.device("cuda")
+    params = {k: inp[k].to(dev).requires_grad_(True) for k in ("means3D", "shs", "opacities", "scales", "rotations")}
+    normals, dirs = inp["normals"].to(dev), inp["dirs"].to(dev)
+
+    def one_view():
+        out, radii = GaussianRasterizer(settings_from(inp, dev))(
+            means3D=params["means3D"], means2D=torch.zeros_like(params["means3D"], requires_grad=True), shs=params["shs"],
+            normals_precomp=normals, opacities=params["opacities"], scales=params["scales"], rotations=params["rotations"], dirs=dirs)
+        out.sum().backward()
+        for p in params.values():
+            p.grad = None
+
+    gc.collect()
+    gc.disable()
+    try:
+        one_view()
+        torch.cuda.synchronize()
+        base = torch.cuda.memory_allocated()
+        for _ in range(5):
+            one_view()
+        torch.cuda.synchronize()
+        assert torch.cuda.memory_allocated() == base, "per-view buffers are kept alive by a reference cycle"
+    finally:
+        gc.enable()

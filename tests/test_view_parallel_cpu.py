@@ -122,3 +122,26 @@ def test_single_process_is_a_no_op():
     assert vp.allreduce_gradients(b) is None
     views = [vp.view_for_step(s, 6, seed=0) for s in range(6)]
     assert sorted(views) == list(range(6))
+
+
+def test_balanced_view_table():
+    """Views of one step cost about the same, nobody gets a view twice, and the ranks' totals are level."""
+    sys.path.insert(0, PKG)
+    import vcr_view_parallel as VP
+    vp = VP.ViewParallel()
+    vp.world, vp.rank = 4, 1
+    g = torch.Generator().manual_seed(3)
+    costs = (1.0 + torch.rand(38, generator=g)).tolist()            # 38 views, 4 ranks -> 9 steps, 2 views left out
+    table = vp.balanced_view_table(costs, seed=5)
+    assert len(table) == 9 and all(len(row) == 4 for row in table)
+    flat = [v for row in table for v in row]
+    assert len(set(flat)) == 36
+    left_out = set(range(38)) - set(flat)
+    assert all(costs[v] >= max(costs[u] for u in flat) for v in left_out)   # the two most expensive ones
+    srt = sorted(costs)
+    worst_gap = max(srt[i + 3] - srt[i] for i in range(len(srt) - 3))
+    assert all(max(costs[v] for v in row) - min(costs[v] for v in row) <= worst_gap + 1e-12 for row in table)
+    totals = [sum(costs[row[r]] for row in table) for r in range(4)]
+    assert max(totals) - min(totals) < 0.02 * sum(totals) / 4
+    assert table != vp.balanced_view_table(costs, seed=6), "the visiting order must change with the seed"
+    assert sorted(map(sorted, table)) == sorted(map(sorted, vp.balanced_view_table(costs, seed=6))), "... but not the groups"

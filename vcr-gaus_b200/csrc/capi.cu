@@ -297,7 +297,7 @@ int vcr_multimem_allreduce_sum(void* multicast_base, int n_ranges, const long lo
     if (!first_float_host || !n_floats_host) { vcr_set_error("NULL range arrays"); return 1; }
     for (int i = 0; i < n_ranges; i++)
         if (first_float_host[i] < 0 || n_floats_host[i] < 0) { vcr_set_error("negative range"); return 1; }
-    if (blocks <= 0) blocks = 74;   // 2.4 MB in flight already saturates the links; half the SMs stay free (tools/mm_bench.py)
+    if (blocks <= 0) blocks = 37;   // 1.2 MB in flight already saturates the links (tools/mm_bench.py); 3/4 of the SMs stay free
     return vcr_launch_multimem_allreduce(static_cast<float*>(multicast_base), n_ranges, first_float_host, n_floats_host, rank, world,
                                          blocks, reinterpret_cast<cudaStream_t>(stream));
 }

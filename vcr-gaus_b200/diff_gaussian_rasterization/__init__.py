@@ -32,17 +32,18 @@ class _Buffers:
 
     def __init__(self, device):
         self.device = device
-        self.t = {}
-        self.cb = {}
-        for name in ("geom", "binning", "img"):
-            self.cb[name] = _n.ALLOC_FN(self._make(name))
+        held = self.t = {}
 
-    def _make(self, name):
-        def alloc(_user, nbytes):
-            t = torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
-            self.t[name] = t
-            return t.data_ptr()
-        return alloc
+        # the callbacks close over the dict, not over `self`: no reference cycle, so the buffers are released by reference
+        # counting as soon as the autograd node drops them (a cycle would keep ~600 MB per view alive until the next pass
+        # of the cyclic garbage collector)
+        def make(name):
+            def alloc(_user, nbytes):
+                t = torch.empty(int(nbytes), dtype=torch.uint8, device=device)
+                held[name] = t
+                return t.data_ptr()
+            return alloc
+        self.cb = {name: _n.ALLOC_FN(make(name)) for name in ("geom", "binning", "img")}
 
     def get(self, name):
         return self.t.get(name, torch.empty(0, dtype=torch.uint8, device=self.device))

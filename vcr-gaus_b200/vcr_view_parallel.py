@@ -112,17 +112,21 @@ class ViewParallel:
         perm = torch.randperm(n_views, generator=g)
         return int(perm[(k * self.world + self.rank) % n_views])
 
-    def cost_ordered_shard(self, local_costs, seed: int = 0):
-        """Order in which this rank should visit ITS shard of the views so that the `world` views of one step cost about
-        the same: position k of the returned list is the rank's j-th cheapest view, where j = sigma(k) is a permutation
-        shared by all ranks (seeded, so the visiting order still changes from epoch to epoch with `seed`).  Every step
-        ends with the gradient exchange, i.e. with a wait for the slowest rank; pairing views of equal cost removes that
-        wait.  `local_costs`: one number per local view (e.g. the rasterizer's instance count R from the previous epoch).
+    def balanced_view_table(self, costs, seed: int = 0):
+        """Cost-balanced replacement for view_for_step: a table of steps, each a list of `world` view ids (entry r is rank
+        r's view), such that the views of one step cost about the same and every rank's column has about the same total.
+        Every step ends with the gradient exchange, i.e. with a wait for the slowest rank; dealing views of equal cost to
+        the ranks of a step removes that wait.  `costs[v]`: a number per view, identical on every rank (e.g. the
+        rasterizer's instance count R from the previous epoch, all-gathered).  Views are sorted by cost, cut into groups
+        of `world`, each group is rotated by its index (so no rank always gets a group's cheapest view) and the groups
+        are visited in a seeded random order shared by all ranks.  len(costs) % world views are left out of the epoch.
         No communication."""
-        n = len(local_costs)
-        by_cost = sorted(range(n), key=lambda v: (local_costs[v], v))
-        sigma = torch.randperm(n, generator=torch.Generator().manual_seed(seed * 7_919 + 17)).tolist()
-        return [by_cost[j] for j in sigma]
+        n, w = len(costs), self.world
+        by_cost = sorted(range(n), key=lambda v: (costs[v], v))
+        groups = [by_cost[k * w:(k + 1) * w] for k in range(n // w)]
+        groups = [g[k % w:] + g[:k % w] for k, g in enumerate(groups)]
+        sigma = torch.randperm(len(groups), generator=torch.Generator().manual_seed(seed * 7_919 + 17)).tolist()
+        return [groups[j] for j in sigma]
 
     def allreduce_gradients(self, bucket: GaussianBucket, average: bool = True, async_op: bool = False):
         """SUM (or mean) of the flat gradient bucket over ranks.  Returns the work handle when async_op."""
