@@ -149,8 +149,8 @@ def build_workload(args, rank, world):
 
 
 def measure_view_costs(args, bucket, views, dev):
-    """R (number of (tile, Gaussian) instances) of each view: one forward without autograd — what a trainer knows about a
-    view from the previous epoch."""
+    """Milliseconds of one rasterizer forward+backward of each view (CUDA events, best of two after one untimed pass) — what
+    a trainer knows about a view from the previous epoch.  The instance count R alone predicts it to ~5 % only."""
     from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
     p = bucket.params
     costs = []
@@ -160,11 +160,22 @@ def measure_view_costs(args, bucket, views, dev):
                                            bg=i["bg"].to(dev), scale_modifier=1.0, viewmatrix=i["viewmatrix"].to(dev),
                                            projmatrix=i["projmatrix"].to(dev), sh_degree=3, campos=i["campos"].to(dev),
                                            prefiltered=False, debug=False, f_count=0)
-        with torch.no_grad():
-            GaussianRasterizer(rs)(means3D=p["means3D"].detach(), means2D=None, opacities=p["opacities"].detach(), shs=p["shs"].detach(),
-                                   normals_precomp=i["normals"].to(dev), scales=p["scales"].detach(), rotations=p["rotations"].detach(),
-                                   dirs=i["dirs"].to(dev))
-        costs.append(float(last_num_rendered()))
+        normals, dirs = i["normals"].to(dev), i["dirs"].to(dev)
+        g = torch.ones((10, args.height, args.width), device=dev)
+        best = float("inf")
+        for rep in range(3):
+            bucket.zero_grad()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            out, _ = GaussianRasterizer(rs)(means3D=p["means3D"], means2D=None, opacities=p["opacities"], shs=p["shs"],
+                                            normals_precomp=normals, scales=p["scales"], rotations=p["rotations"], dirs=dirs)
+            out.backward(g)
+            e1.record()
+            torch.cuda.synchronize(dev)
+            if rep > 0:
+                best = min(best, e0.elapsed_time(e1))
+        costs.append(best)
+    bucket.zero_grad()
     return costs
 
 
@@ -472,7 +483,7 @@ def main():
     balanced = world > 1 and impl == "ours" and os.environ.get("VCR_BENCH_BALANCE", "1") == "1"
     if balanced:
         # Cost-balanced sharding: every step ends with the gradient exchange, i.e. with a wait for the slowest rank, so the
-        # `world` views of one step should cost the same.  Each rank measures R of its default shard, the costs are
+        # `world` views of one step should cost the same.  Each rank times its default shard once, the costs are
         # gathered, and ViewParallel.balanced_view_table deals views of equal cost to the ranks of one step.
         mine = torch.tensor(measure_view_costs(args, bucket, build_views(args, scene, world, view_ids, light=True), dev), device=dev)
         allc = [torch.zeros_like(mine) for _ in range(world)]
