@@ -173,16 +173,16 @@ __global__ void __launch_bounds__(256) radix_scan_hist_kernel(uint32_t* __restri
 //   - pairs are first scattered into shared memory in block-sorted order so the global stores are
 //     runs of consecutive addresses per digit
 // ------------------------------------------------------------------------------------------------
-#define RADIX_THREADS 512
+#define RADIX_THREADS VCR_RADIX_THREADS
 #define RADIX_WARPS (RADIX_THREADS / 32)
-#define RADIX_ITEMS 8
+#define RADIX_ITEMS VCR_RADIX_ITEMS
 #define RADIX_TILE (RADIX_THREADS * RADIX_ITEMS)
 #define FLAG_LOCAL 0x40000000u
 #define FLAG_GLOBAL 0x80000000u
 #define FLAG_MASK 0xC0000000u
 #define RADIX_SMEM_BYTES (RADIX_TILE * 8 + RADIX_TILE * 4 + RADIX_WARPS * 256 * 4 + 256 * 4 + 256 * 4 + 128)
 
-__global__ void __launch_bounds__(RADIX_THREADS, 2) radix_pass_kernel(const uint64_t* __restrict__ keys_in,
+__global__ void __launch_bounds__(RADIX_THREADS, VCR_RADIX_MINBLOCKS) radix_pass_kernel(const uint64_t* __restrict__ keys_in,
                                                                       const uint32_t* __restrict__ vals_in,
                                                                       uint64_t* __restrict__ keys_out,
                                                                       uint32_t* __restrict__ vals_out, uint32_t R, int shift,
@@ -223,7 +223,18 @@ __global__ void __launch_bounds__(RADIX_THREADS, 2) radix_pass_kernel(const uint
         const bool valid = li < n;
         const uint32_t d = (uint32_t)(key[i] >> shift) & mask;
         const uint32_t vmask = __ballot_sync(0xffffffffu, valid);
+#ifdef VCR_RADIX_BALLOT
+        // peer mask from one ballot per digit bit: constant cost, whereas match.any costs one round per distinct digit
+        uint32_t peers = vmask;
+#pragma unroll
+        for (int b = 0; b < 8; b++) {
+            const uint32_t bit = (d >> b) & 1u;
+            const uint32_t m = __ballot_sync(0xffffffffu, bit != 0u);
+            peers &= bit ? m : ~m;
+        }
+#else
         const uint32_t peers = __match_any_sync(0xffffffffu, d) & vmask;
+#endif
         uint32_t prev = 0;
         if (valid) prev = my_hist[d];
         rank[i] = prev + __popc(peers & ((1u << lane) - 1u));

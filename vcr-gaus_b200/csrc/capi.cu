@@ -88,7 +88,7 @@ size_t ImageState::bytes(int W, int H) {
     const size_t tiles = (size_t)((W + VCR_TILE_X - 1) / VCR_TILE_X) * ((H + VCR_TILE_Y - 1) / VCR_TILE_Y);
     return reinterpret_cast<size_t>(s.tile_order + tiles) + 256;
 }
-static inline size_t radix_blocks(size_t R) { return (R + 4095) / 4096; }
+static inline size_t radix_blocks(size_t R) { return (R + VCR_RADIX_TILE - 1) / VCR_RADIX_TILE; }
 BinningState BinningState::carve(char* chunk, int R) {
     BinningState b;
     const size_t n = (size_t)R;
