@@ -194,6 +194,28 @@ int vcr_rasterize_backward_chunked(
 int vcr_densify_stats_accumulate(int P, const float* grad_means2D_densify, const int* radii, float* xyz_gradient_accum,
                                  float* denom, float* max_radii2D, void* stream);
 
+/* Everything render() computes per Gaussian before it calls the rasterizer, fused:
+ *   opacities = sigmoid(opacity_raw), scales = exp(scaling_raw), rotations = normalize(rotation_raw),
+ *   shs = cat(features_dc, features_rest)                              (scene/gaussian_model.py:125-162)
+ *   normals = column argmin(scales) of build_rotation(rotations)       (scene/gaussian_model.py:168-192,
+ *             flipped to point away from the camera and rotated         tools/general_utils.py:98-119,
+ *             into camera space by R_w2c                                 gaussian_renderer/__init__.py:95-101)
+ * n_rest = SH coefficients beyond DC (15 at degree 3); features_dc f32[P,1,3], features_rest f32[P,n_rest,3],
+ * shs f32[P,1+n_rest,3].  valid (u8[P], may be NULL = all) is the inside mask of get_normal(is_all=False): Gaussians
+ * outside get a zero normal and no normal gradient.  cam_center f32[3] and R_w2c f32[3,3] (row-major, the reference's
+ * torch.tensor(camera.R.T)) are DEVICE arrays.  aux u8[P] carries the argmin axis / flip sign to the backward.
+ * The backward takes the gradients of the five outputs and returns those of the raw parameters (xyz only enters
+ * the non-differentiable flip test). */
+int vcr_prologue_forward(int P, int n_rest, const float* xyz, const float* features_dc, const float* features_rest,
+                         const float* opacity_raw, const float* scaling_raw, const float* rotation_raw,
+                         const uint8_t* valid, const float* cam_center, const float* R_w2c, float* opacities,
+                         float* scales, float* rotations, float* shs, float* normals, uint8_t* aux, void* stream);
+int vcr_prologue_backward(int P, int n_rest, const float* rotation_raw, const float* opacities, const float* scales,
+                          const float* rotations, const uint8_t* aux, const float* R_w2c, const float* dL_dopacities,
+                          const float* dL_dscales, const float* dL_drotations, const float* dL_dshs,
+                          const float* dL_dnormals, float* dL_dfeatures_dc, float* dL_dfeatures_rest,
+                          float* dL_dopacity_raw, float* dL_dscaling_raw, float* dL_drotation_raw, void* stream);
+
 /* Gradient exchange of the view-parallel layer through the NVSwitch (the reference is single-GPU and
  * has no counterpart).  `multicast_base` is the multicast mapping (NVLink SHARP, e.g. torch symmetric memory's
  * multicast_ptr) of a float buffer that every rank holds at the same offset.  For each of the n_ranges (<= 8) float

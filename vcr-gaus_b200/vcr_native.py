@@ -63,6 +63,9 @@ vcr_rasterize_backward_chunked = _sig(
 vcr_multimem_allreduce_sum = _sig("vcr_multimem_allreduce_sum", c_int,
                                   [c_void_p, c_int, POINTER(ctypes.c_longlong), POINTER(ctypes.c_longlong), c_int, c_int, c_int, c_void_p])
 
+vcr_prologue_forward = _sig("vcr_prologue_forward", c_int, [c_int, c_int] + [P_] * 15 + [c_void_p])
+vcr_prologue_backward = _sig("vcr_prologue_backward", c_int, [c_int, c_int] + [P_] * 16 + [c_void_p])
+
 vcr_densify_stats_accumulate = _sig("vcr_densify_stats_accumulate", c_int, [c_int, P_, P_, P_, P_, P_, c_void_p])
 
 vcr_mark_visible = _sig("vcr_mark_visible", c_int, [c_int, P_, P_, P_, P_, c_void_p])
@@ -138,7 +141,7 @@ DECLARED_SYMBOLS = [
     "vcr_knn_scratch_bytes", "vcr_dist2_knn3", "vcr_geom_layout", "vcr_binning_layout", "vcr_image_layout",
     "vcr_knn_noalloc_max_points", "vcr_dist2_knn3_noalloc", "vcr_view_loss_forward", "vcr_view_loss_backward",
     "vcr_profile_enable", "vcr_profile_kernel_count", "vcr_profile_kernel_name", "vcr_profile_read",
-    "vcr_rasterize_backward_chunked", "vcr_densify_stats_accumulate", "vcr_multimem_allreduce_sum",
+    "vcr_rasterize_backward_chunked", "vcr_densify_stats_accumulate", "vcr_multimem_allreduce_sum", "vcr_prologue_forward", "vcr_prologue_backward",
 ]
 
 
