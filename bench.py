@@ -225,6 +225,56 @@ class RefRasterFn(torch.autograd.Function):
         return None, g3d, gsh, gnrm, gop, gsc, grot, None, None, None
 
 
+def ref_prologue_chain(xyz, fdc, frest, o_raw, s_raw, r_raw, cam_center, R_w2c):
+    """What the reference's render() does per Gaussian before the rasterizer call (scene/gaussian_model.py:125-192,
+    tools/general_utils.py:98-119, gaussian_renderer/__init__.py:95-101; is_all=True), as the same PyTorch op chain."""
+    opacity, scaling, rotation = torch.sigmoid(o_raw), torch.exp(s_raw), F.normalize(r_raw)
+    shs = torch.cat((fdc, frest), dim=1)
+    r = rotation
+    norm = torch.sqrt(r[:, 0] * r[:, 0] + r[:, 1] * r[:, 1] + r[:, 2] * r[:, 2] + r[:, 3] * r[:, 3])
+    q = r / norm[:, None]
+    R = torch.zeros((q.size(0), 3, 3), device=q.device)
+    w, x, y, z = q[:, 0], q[:, 1], q[:, 2], q[:, 3]
+    R[:, 0, 0] = 1 - 2 * (y * y + z * z); R[:, 0, 1] = 2 * (x * y - w * z); R[:, 0, 2] = 2 * (x * z + w * y)
+    R[:, 1, 0] = 2 * (x * y + w * z); R[:, 1, 1] = 1 - 2 * (x * x + z * z); R[:, 1, 2] = 2 * (y * z - w * x)
+    R[:, 2, 0] = 2 * (x * z - w * y); R[:, 2, 1] = 2 * (y * z + w * x); R[:, 2, 2] = 1 - 2 * (x * x + y * y)
+    axis = torch.argmin(scaling, dim=-1)
+    normal = R.gather(2, axis[:, None, None].expand(-1, 3, -1)).squeeze(-1)
+    view_dir = xyz - cam_center
+    normal = normal * ((((view_dir * normal).sum(dim=-1) > 0) * 1 - 0.5) * 2)[..., None]
+    return opacity, scaling, rotation, shs, normal @ R_w2c.transpose(0, 1)
+
+
+def time_prologue(args, scene, view, dev, iters=20):
+    """render()'s per-Gaussian prologue, forward + backward: this library's fused kernels vs the reference's PyTorch chain.
+    Not part of the step (both arms of the bench start from post-activation tensors); reported beside it."""
+    from vcr_prologue import gaussian_prologue
+    shs = scene.shs.to(dev)
+    leaves = [t.requires_grad_(True) for t in (shs[:, :1].clone(), shs[:, 1:].clone(),
+                                               torch.logit(scene.opacities.to(dev).clamp(1e-4, 1 - 1e-4)),
+                                               torch.log(scene.scales.to(dev)), scene.rotations.to(dev) * 1.3)]
+    xyz = scene.means3D.to(dev)
+    cc = view["inp"]["campos"].to(dev)
+    M = view["inp"]["viewmatrix"].to(dev)[:3, :3].t().contiguous()
+    out = {}
+    cot = None
+    for name, fn in (("fused_ms", gaussian_prologue), ("pytorch_chain_ms", ref_prologue_chain)):
+        for k in range(iters + 3):
+            if k == 3:
+                torch.cuda.synchronize(dev)
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+            res = fn(xyz, *leaves, cc, M)
+            if cot is None:
+                cot = [torch.randn_like(t) for t in res]
+            torch.autograd.grad(res, leaves, cot)
+        e1.record()
+        torch.cuda.synchronize(dev)
+        out[name] = e0.elapsed_time(e1) / iters
+    out["what"] = f"forward+backward of render()'s per-Gaussian prologue, P = {xyz.shape[0]}; not part of the step"
+    return out
+
+
 def clone_params(scene, dev, direct=False, vp=None):
     """Parameters + flat gradient bucket.  With a ViewParallel layer at N > 1 the bucket is placed in symmetric memory so
     that the gradient exchange can go through the NVSwitch multicast kernel (VCR_BENCH_TRANSPORT=nccl forces NCCL)."""
@@ -589,6 +639,11 @@ def main():
         out["kernels"] = per_kernel
         out["ms_per_step_with_kernel_events"] = ms_prof / args.steps if ms_prof else None
     out["scene"] = stats
+    if world == 1:
+        try:
+            out["render_prologue"] = time_prologue(args, scene, views[0], dev)
+        except Exception as ex:  # never lose the bench line over the side measurement
+            out["render_prologue"] = {"error": f"{type(ex).__name__}: {ex}"}
     if not args.no_cpu_baseline and world == 1:
         vps, dt, R = cpu_oracle_views_per_s(args, views[0])
         out["cpu_baseline"] = {"value": vps, "unit": "views/s", "cores": os.cpu_count(), "kind": "port",

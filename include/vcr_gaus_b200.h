@@ -216,6 +216,17 @@ int vcr_prologue_backward(int P, int n_rest, const float* rotation_raw, const fl
                           const float* dL_dnormals, float* dL_dfeatures_dc, float* dL_dfeatures_rest,
                           float* dL_dopacity_raw, float* dL_dscaling_raw, float* dL_drotation_raw, void* stream);
 
+/* SSIM of tools/loss_utils.py:47-92 (11x11 Gaussian window, sigma 1.5, zero padding, C1 = 0.01^2, C2 = 0.03^2) over
+ * `planes` independent height x width images (planes = batch x channels), fused.
+ * forward: *ssim_sum (device double) = sum of the SSIM map over all elements (the caller divides by planes*H*W for
+ * size_average=True); dmaps f32[3,planes,H,W] receives the map's partial derivatives for the backward.
+ * backward: dL_dimg1 = dL_dssim (device f32 scalar, gradient of the MEAN) * d mean(ssim) / d img1.  img2 is the
+ * ground truth and gets no gradient. */
+int vcr_ssim_forward(int planes, int height, int width, const float* img1, const float* img2, float* dmaps,
+                     double* ssim_sum, void* stream);
+int vcr_ssim_backward(int planes, int height, int width, const float* img1, const float* img2, const float* dmaps,
+                      const float* dL_dssim, float* dL_dimg1, void* stream);
+
 /* Gradient exchange of the view-parallel layer through the NVSwitch (the reference is single-GPU and
  * has no counterpart).  `multicast_base` is the multicast mapping (NVLink SHARP, e.g. torch symmetric memory's
  * multicast_ptr) of a float buffer that every rank holds at the same offset.  For each of the n_ranges (<= 8) float

@@ -1,0 +1,166 @@
+// ssim.cu — the photometric SSIM term (tools/loss_utils.py:47-92: 11x11 Gaussian window, sigma 1.5, zero padding, mean over
+// all elements), forward and backward as one separable-convolution kernel each.
+//
+// The reference runs five grouped conv2d over the image pair plus ~15 elementwise kernels forward, and autograd's mirror
+// image backward.  Here: forward = one pass that stages a 26x26 halo tile of both images in shared memory, convolves the
+// five moments (x, y, xx, yy, xy) horizontally then vertically, evaluates the SSIM map, adds its sum to one double, and
+// stores the three partial derivatives of the map w.r.t. (mu1, E[xx], E[xy]) per pixel; backward = one pass that convolves
+// those three maps with the same window and combines them with the pixel values.  HBM bound: 20 B/element forward,
+// 24 B/element backward.
+#include "common.cuh"
+
+#define SSIM_R 5
+#define SSIM_T 16
+#define SSIM_H (SSIM_T + 2 * SSIM_R)   // 26
+
+__constant__ float c_ssim_w[2 * SSIM_R + 1];
+
+__global__ void __launch_bounds__(256) ssim_forward_kernel(const int H, const int W, const float* __restrict__ img1,
+                                                           const float* __restrict__ img2, float* __restrict__ dmaps,
+                                                           double* __restrict__ total, const size_t plane_count) {
+    __shared__ float s_a[SSIM_H][SSIM_H + 1], s_b[SSIM_H][SSIM_H + 1];
+    __shared__ float s_h[5][SSIM_H][SSIM_T + 1];
+    __shared__ float s_red[8];
+    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+    const size_t plane = (size_t)blockIdx.z * H * W;
+    const int x0 = blockIdx.x * SSIM_T - SSIM_R, y0 = blockIdx.y * SSIM_T - SSIM_R;
+    for (int i = tid; i < SSIM_H * SSIM_H; i += 256) {
+        const int ly = i / SSIM_H, lx = i - ly * SSIM_H;
+        const int gy = y0 + ly, gx = x0 + lx;
+        const bool in = gy >= 0 && gy < H && gx >= 0 && gx < W;
+        s_a[ly][lx] = in ? __ldg(img1 + plane + (size_t)gy * W + gx) : 0.f;     // conv2d(padding=5): zeros outside
+        s_b[ly][lx] = in ? __ldg(img2 + plane + (size_t)gy * W + gx) : 0.f;
+    }
+    __syncthreads();
+    for (int i = tid; i < SSIM_H * SSIM_T; i += 256) {
+        const int ly = i / SSIM_T, x = i - ly * SSIM_T;
+        float m1 = 0.f, m2 = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
+#pragma unroll
+        for (int k = 0; k <= 2 * SSIM_R; k++) {
+            const float w = c_ssim_w[k], a = s_a[ly][x + k], b = s_b[ly][x + k];
+            const float wa = w * a, wb = w * b;
+            m1 += wa; m2 += wb; e11 = fmaf(wa, a, e11); e22 = fmaf(wb, b, e22); e12 = fmaf(wa, b, e12);
+        }
+        s_h[0][ly][x] = m1; s_h[1][ly][x] = m2; s_h[2][ly][x] = e11; s_h[3][ly][x] = e22; s_h[4][ly][x] = e12;
+    }
+    __syncthreads();
+    float m1 = 0.f, m2 = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
+#pragma unroll
+    for (int k = 0; k <= 2 * SSIM_R; k++) {
+        const float w = c_ssim_w[k];
+        m1 = fmaf(w, s_h[0][ty + k][tx], m1); m2 = fmaf(w, s_h[1][ty + k][tx], m2); e11 = fmaf(w, s_h[2][ty + k][tx], e11);
+        e22 = fmaf(w, s_h[3][ty + k][tx], e22); e12 = fmaf(w, s_h[4][ty + k][tx], e12);
+    }
+    const int gx = blockIdx.x * SSIM_T + tx, gy = blockIdx.y * SSIM_T + ty;
+    float val = 0.f;
+    if (gx < W && gy < H) {
+        const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;
+        const float s1 = e11 - m1 * m1, s2 = e22 - m2 * m2, s12 = e12 - m1 * m2;
+        const float N1 = 2.f * m1 * m2 + C1, N2 = 2.f * s12 + C2, D1 = m1 * m1 + m2 * m2 + C1, D2 = s1 + s2 + C2;
+        const float inv = 1.f / (D1 * D2);
+        val = N1 * N2 * inv;
+        // partial derivatives of the map w.r.t. mu1 (E[xx], E[xy] held fixed), E[xx] and E[xy]
+        const float d_e12 = 2.f * N1 * inv;
+        const float d_e11 = -val / D2;
+        const float d_m1 = 2.f * m2 * (N2 - N1) * inv - val * 2.f * m1 * (D2 - D1) * inv;
+        const size_t o = plane + (size_t)gy * W + gx;
+        dmaps[o] = d_m1; dmaps[plane_count + o] = d_e11; dmaps[2 * plane_count + o] = d_e12;
+    }
+    val = vcr_warp_sum(val);
+    if ((tid & 31) == 0) s_red[tid >> 5] = val;
+    __syncthreads();
+    if (tid == 0) {
+        float t = 0.f;
+#pragma unroll
+        for (int k = 0; k < 8; k++) t += s_red[k];
+        atomicAdd(total, (double)t);
+    }
+}
+
+__global__ void __launch_bounds__(256) ssim_backward_kernel(const int H, const int W, const float* __restrict__ img1,
+                                                            const float* __restrict__ img2, const float* __restrict__ dmaps,
+                                                            const float* __restrict__ dL_dssim, const float scale,
+                                                            float* __restrict__ dL_dimg1, const size_t plane_count) {
+    __shared__ float s_m[3][SSIM_H][SSIM_H + 1];
+    __shared__ float s_h[3][SSIM_H][SSIM_T + 1];
+    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+    const size_t plane = (size_t)blockIdx.z * H * W;
+    const int x0 = blockIdx.x * SSIM_T - SSIM_R, y0 = blockIdx.y * SSIM_T - SSIM_R;
+    for (int i = tid; i < SSIM_H * SSIM_H; i += 256) {
+        const int ly = i / SSIM_H, lx = i - ly * SSIM_H;
+        const int gy = y0 + ly, gx = x0 + lx;
+        const bool in = gy >= 0 && gy < H && gx >= 0 && gx < W;
+        const size_t o = plane + (size_t)(in ? gy : 0) * W + (in ? gx : 0);
+#pragma unroll
+        for (int q = 0; q < 3; q++) s_m[q][ly][lx] = in ? __ldg(dmaps + q * plane_count + o) : 0.f;   // no map outside the image
+    }
+    __syncthreads();
+    for (int i = tid; i < SSIM_H * SSIM_T; i += 256) {
+        const int ly = i / SSIM_T, x = i - ly * SSIM_T;
+        float a = 0.f, b = 0.f, c = 0.f;
+#pragma unroll
+        for (int k = 0; k <= 2 * SSIM_R; k++) {
+            const float w = c_ssim_w[k];
+            a = fmaf(w, s_m[0][ly][x + k], a); b = fmaf(w, s_m[1][ly][x + k], b); c = fmaf(w, s_m[2][ly][x + k], c);
+        }
+        s_h[0][ly][x] = a; s_h[1][ly][x] = b; s_h[2][ly][x] = c;
+    }
+    __syncthreads();
+    const int gx = blockIdx.x * SSIM_T + tx, gy = blockIdx.y * SSIM_T + ty;
+    if (gx >= W || gy >= H) return;
+    float a = 0.f, b = 0.f, c = 0.f;
+#pragma unroll
+    for (int k = 0; k <= 2 * SSIM_R; k++) {
+        const float w = c_ssim_w[k];
+        a = fmaf(w, s_h[0][ty + k][tx], a); b = fmaf(w, s_h[1][ty + k][tx], b); c = fmaf(w, s_h[2][ty + k][tx], c);
+    }
+    const size_t o = plane + (size_t)gy * W + gx;
+    const float x = __ldg(img1 + o), y = __ldg(img2 + o);
+    // d mean(ssim) / d img1[p] = (1/count) * sum_q [ dS_q/dmu1 + dS_q/dE11 * 2 x_p + dS_q/dE12 * y_p ] * w(q - p)
+    dL_dimg1[o] = (__ldg(dL_dssim) * scale) * (a + 2.f * x * b + y * c);
+}
+
+static int ssim_upload_window(cudaStream_t s) {
+    // tools/loss_utils.py:47-49: exp(-(x - 5)^2 / (2 * 1.5^2)) as float32, divided by its float32 sum
+    static bool done_dev[64] = {false};
+    int dev = 0;
+    VCR_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev >= 0 && dev < 64 && done_dev[dev]) return 0;
+    float g[2 * SSIM_R + 1], sum = 0.f;
+    for (int k = 0; k <= 2 * SSIM_R; k++) { g[k] = (float)exp(-(double)((k - SSIM_R) * (k - SSIM_R)) / (2.0 * 1.5 * 1.5)); sum += g[k]; }
+    for (int k = 0; k <= 2 * SSIM_R; k++) g[k] /= sum;
+    VCR_CUDA_TRY(cudaMemcpyToSymbolAsync(c_ssim_w, g, sizeof(g), 0, cudaMemcpyHostToDevice, s));
+    VCR_CUDA_TRY(cudaStreamSynchronize(s));          // g lives on this stack frame; once per device
+    if (dev >= 0 && dev < 64) done_dev[dev] = true;
+    return 0;
+}
+
+extern "C" int vcr_ssim_forward(int planes, int height, int width, const float* img1, const float* img2, float* dmaps,
+                                double* ssim_sum, void* stream) {
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    if (planes <= 0 || height <= 0 || width <= 0) { vcr_set_error("ssim_forward: empty image"); return 1; }
+    if (!img1 || !img2 || !dmaps || !ssim_sum) { vcr_set_error("ssim_forward: NULL argument"); return 1; }
+    if (planes > 65535) { vcr_set_error("ssim_forward: more than 65535 image planes"); return 1; }
+    if (ssim_upload_window(s)) return 1;
+    VCR_CUDA_TRY(cudaMemsetAsync(ssim_sum, 0, sizeof(double), s));
+    VcrProfScope prof(VCR_K_SSIM, s);
+    const dim3 grid((width + SSIM_T - 1) / SSIM_T, (height + SSIM_T - 1) / SSIM_T, planes);
+    ssim_forward_kernel<<<grid, 256, 0, s>>>(height, width, img1, img2, dmaps, ssim_sum, (size_t)planes * height * width);
+    VCR_LAUNCH_CHECK("ssim_forward_kernel");
+    return 0;
+}
+
+extern "C" int vcr_ssim_backward(int planes, int height, int width, const float* img1, const float* img2, const float* dmaps,
+                                 const float* dL_dssim, float* dL_dimg1, void* stream) {
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    if (planes <= 0 || height <= 0 || width <= 0) { vcr_set_error("ssim_backward: empty image"); return 1; }
+    if (!img1 || !img2 || !dmaps || !dL_dssim || !dL_dimg1) { vcr_set_error("ssim_backward: NULL argument"); return 1; }
+    if (planes > 65535) { vcr_set_error("ssim_backward: more than 65535 image planes"); return 1; }
+    if (ssim_upload_window(s)) return 1;
+    VcrProfScope prof(VCR_K_SSIM, s);
+    const dim3 grid((width + SSIM_T - 1) / SSIM_T, (height + SSIM_T - 1) / SSIM_T, planes);
+    const size_t count = (size_t)planes * height * width;
+    ssim_backward_kernel<<<grid, 256, 0, s>>>(height, width, img1, img2, dmaps, dL_dssim, (float)(1.0 / (double)count), dL_dimg1, count);
+    VCR_LAUNCH_CHECK("ssim_backward_kernel");
+    return 0;
+}

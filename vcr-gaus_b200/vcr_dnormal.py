@@ -139,3 +139,41 @@ def view_loss(outmap, gt_image, gt_normal, intr, mask=None, w_l1=1.0, w_mono=0.0
     Returns the scalar loss; with return_terms also the raw sums (see include/vcr_gaus_b200.h) for logging."""
     loss, sums = _ViewLoss.apply(outmap, gt_image, gt_normal, mask, _intr(intr), exp_t, mask_depth_max, w_l1, w_mono, w_dn)
     return (loss, sums) if return_terms else loss
+
+
+class _SSIM(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, img1, img2):
+        for t, name in ((img1, "img1"), (img2, "img2")):
+            if not t.is_cuda or t.dtype != torch.float32:
+                raise RuntimeError(f"ssim: {name} must be a float32 CUDA tensor; there is no CPU fallback")
+        if img1.shape != img2.shape or img1.ndim not in (3, 4):
+            raise RuntimeError("ssim: expected two [C,H,W] or [B,C,H,W] tensors of the same shape")
+        a, b = img1.contiguous(), img2.contiguous()
+        H, W = a.shape[-2], a.shape[-1]
+        planes = a.numel() // (H * W)
+        dmaps = torch.empty((3,) + tuple(a.shape), dtype=torch.float32, device=a.device)
+        total = torch.empty(1, dtype=torch.float64, device=a.device)
+        _n.check(_n.vcr_ssim_forward(planes, H, W, a.data_ptr(), b.data_ptr(), dmaps.data_ptr(), total.data_ptr(), _stream()),
+                 "ssim_forward")
+        ctx.save_for_backward(a, b, dmaps)
+        return (total / a.numel()).to(torch.float32).reshape(())
+
+    @staticmethod
+    def backward(ctx, g):
+        a, b, dmaps = ctx.saved_tensors
+        H, W = a.shape[-2], a.shape[-1]
+        grad = torch.empty_like(a)
+        gg = g.to(torch.float32).contiguous().reshape(1)
+        _n.check(_n.vcr_ssim_backward(a.numel() // (H * W), H, W, a.data_ptr(), b.data_ptr(), dmaps.data_ptr(), gg.data_ptr(),
+                                      grad.data_ptr(), _stream()), "ssim_backward")
+        return grad, None
+
+
+def ssim(img1, img2, window_size=11, size_average=True):
+    """tools/loss_utils.py:54-92 `ssim(img1, img2)` — the mean SSIM of two images with the reference's 11x11 Gaussian window —
+    as one fused kernel per direction (the reference: five grouped conv2d + ~15 elementwise launches each way).
+    Differentiable w.r.t. img1; img2 is treated as ground truth.  Only the reference's defaults are built."""
+    if window_size != 11 or not size_average:
+        raise NotImplementedError("fused ssim implements the reference's defaults (window_size=11, size_average=True)")
+    return _SSIM.apply(img1, img2)
