@@ -9,8 +9,9 @@ a seeded synthetic scene of 1,000,000 Gaussians (SH degree 3), 1920x1080 views w
 mono-normal + confidence-weighted depth-normal (D-Normal), backward into every per-Gaussian parameter.
 One "step" = one such view per GPU (fwd + loss + bwd); with N > 1 each rank renders a different view of the same
 replicated scene and the flat gradient bucket + densification statistics are all-reduced with NCCL (weak scaling).
-`value` = views/s over all ranks (so ms/view at N = 1 is `ms_per_step`).  SSIM and the Adam update are outside the
-hot path and are not part of a step in either arm.
+`value` = views/s over all ranks (so ms/view at N = 1 is `ms_per_step`).  SSIM, the per-Gaussian prologue of render() and
+the Adam update are outside the hot path and are not part of a step in either arm; the complete
+training iteration including them is timed beside it at N = 1 and reported as `full_step` (both arms).
 
 Arms
   ours           this repository (GaussianRasterizer -> ctypes -> libvcr_gaus_b200.so, fused D-Normal kernels)
@@ -273,6 +274,95 @@ def time_prologue(args, scene, view, dev, iters=20):
         out[name] = e0.elapsed_time(e1) / iters
     out["what"] = f"forward+backward of render()'s per-Gaussian prologue, P = {xyz.shape[0]}; not part of the step"
     return out
+
+
+def ref_ssim_chain(img1, img2):
+    """tools/loss_utils.py:47-92 restated (11x11 Gaussian window, grouped conv2d), for the reference arm of `full_step`."""
+    gauss = torch.Tensor([math.exp(-(x - 5) ** 2 / float(2 * 1.5 ** 2)) for x in range(11)])
+    g1 = (gauss / gauss.sum()).unsqueeze(1)
+    window = g1.mm(g1.t()).float().unsqueeze(0).unsqueeze(0).expand(3, 1, 11, 11).contiguous().to(img1.device)
+    mu1, mu2 = F.conv2d(img1, window, padding=5, groups=3), F.conv2d(img2, window, padding=5, groups=3)
+    mu1_sq, mu2_sq, mu1_mu2 = mu1.pow(2), mu2.pow(2), mu1 * mu2
+    s1 = F.conv2d(img1 * img1, window, padding=5, groups=3) - mu1_sq
+    s2 = F.conv2d(img2 * img2, window, padding=5, groups=3) - mu2_sq
+    s12 = F.conv2d(img1 * img2, window, padding=5, groups=3) - mu1_mu2
+    C1, C2 = 0.01 ** 2, 0.03 ** 2
+    return (((2 * mu1_mu2 + C1) * (2 * s12 + C2)) / ((mu1_sq + mu2_sq + C1) * (s1 + s2 + C2))).mean()
+
+
+LAMBDA_DSSIM = 0.2      # configs/reconstruct.yaml lambda_dssim
+RAW_NAMES = ("xyz", "f_dc", "f_rest", "opacity", "scaling", "rotation")
+RAW_LRS = dict(xyz=1.6e-4, f_dc=2.5e-3, f_rest=2.5e-3 / 20, opacity=0.05, scaling=5e-3, rotation=1e-3)
+
+
+def time_full_step(args, impl, scene, stepper, dev, steps):
+    """One COMPLETE training iteration per view, from the raw parameters to the updated raw parameters, the way trainer.py
+    runs it: per-Gaussian prologue -> rasterize -> loss (L1 + SSIM + mono-normal + D-Normal) -> backward -> Adam.
+    `ours`: fused prologue, fused view loss + fused SSIM, BucketAdam.  `reference`: the reference's PyTorch chains around its
+    CUDA rasterizer and torch.optim.Adam(eps=1e-15) with its six groups.  Reported beside the bench metric (whose step is
+    the rasterizer + D-Normal hot path only), single GPU."""
+    import vcr_view_parallel as VP
+    shs = scene.shs.to(dev)
+    raw = dict(xyz=scene.means3D.to(dev), f_dc=shs[:, :1].contiguous(), f_rest=shs[:, 1:].contiguous(),
+               opacity=torch.logit(scene.opacities.to(dev).clamp(1e-4, 1 - 1e-4)), scaling=torch.log(scene.scales.to(dev)),
+               rotation=scene.rotations.to(dev).clone())
+    H, W = args.height, args.width
+    if impl == "ours":
+        from vcr_dnormal import ssim, view_loss
+        from vcr_prologue import gaussian_prologue
+        bucket = VP.GaussianBucket(raw, device=dev, names=RAW_NAMES, direct=True)   # kernels write the gradients into the bucket
+        p, opt = bucket.params, VP.BucketAdam(bucket, RAW_LRS)
+    else:
+        p = {k: v.clone().requires_grad_(True) for k, v in raw.items()}
+        opt = torch.optim.Adam([{"params": [p[k]], "lr": RAW_LRS[k], "name": k} for k in RAW_NAMES], lr=0.0, eps=1e-15)
+
+    def one(i):
+        k = i % len(stepper.views)
+        d = stepper.devv[k]
+        cam = d["cam"]
+        view, proj, campos, bg = cam[0:16].view(4, 4), cam[16:32].view(4, 4), cam[32:35], cam[35:38]
+        R_w2c = view[:3, :3].t()
+        gt_n = d["gt_normal"]
+        if impl == "ours":
+            opac, scales, rots, sh, normals = gaussian_prologue(p["xyz"], p["f_dc"], p["f_rest"], p["opacity"], p["scaling"], p["rotation"],
+                                                                campos, R_w2c)
+            rs = stepper.GRS(image_height=H, image_width=W, tanfovx=stepper.tanx, tanfovy=stepper.tany, bg=bg, scale_modifier=1.0,
+                             viewmatrix=view, projmatrix=proj, sh_degree=3, campos=campos, prefiltered=False, debug=False, f_count=0)
+            means2D = torch.zeros_like(p["xyz"], requires_grad=True)
+            out, radii = stepper.GR(rs)(means3D=p["xyz"], means2D=means2D, means2D_densify=torch.zeros_like(p["xyz"], requires_grad=True),
+                                        shs=sh, normals_precomp=normals, opacities=opac, scales=scales, rotations=rots,
+                                        dirs=stepper.dirs, inside=stepper.inside)
+            loss = view_loss(out, d["gt_image"], gt_n, stepper.K4, w_l1=1.0 - LAMBDA_DSSIM, w_mono=LAMBDA_MONO, w_dn=LAMBDA_DN, exp_t=EXP_T)
+            loss = loss + LAMBDA_DSSIM * (1.0 - ssim(out[:3], d["gt_image"]))
+            bucket.zero_grad()
+            loss.backward()
+            opt.step()
+        else:
+            opac, scales, rots, sh, normals = ref_prologue_chain(p["xyz"], p["f_dc"], p["f_rest"], p["opacity"], p["scaling"], p["rotation"],
+                                                                 campos, R_w2c)
+            st = dict(bg=bg, view=view, proj=proj, campos=campos, tanx=stepper.tanx, tany=stepper.tany, H=H, W=W, deg=3)
+            out, radii = RefRasterFn.apply(stepper.C, p["xyz"], sh, normals, opac, scales, rots, stepper.dirs, stepper.inside, st)
+            image, depth, normal, _alpha, _sem = out.split([3, 1, 3, 1, 2], dim=0)
+            rn = F.normalize(normal.permute(1, 2, 0), dim=-1)
+            loss = (1.0 - LAMBDA_DSSIM) * (image - d["gt_image"]).abs().mean() + LAMBDA_DSSIM * (1.0 - ref_ssim_chain(image[None], d["gt_image"][None]))
+            loss = loss + LAMBDA_MONO * ((rn - gt_n).abs().sum(-1).mean() + (1.0 - (rn * gt_n).sum(-1)).mean())
+            loss = loss + LAMBDA_DN * ref_dnormal_chain(depth, stepper.K, gt_n, rn, EXP_T)
+            opt.zero_grad(set_to_none=True)
+            loss.backward()
+            opt.step()
+
+    for i in range(max(3 * len(stepper.views), 24)):
+        one(i)
+    torch.cuda.synchronize(dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        one(i)
+    e1.record()
+    torch.cuda.synchronize(dev)
+    ms = e0.elapsed_time(e1) / steps
+    return {"ms_per_step": ms, "views_per_s": 1e3 / ms, "steps": steps,
+            "includes": "raw parameters -> prologue -> rasterize fwd -> L1 + SSIM + mono-normal + D-Normal -> backward -> Adam (6 groups, eps 1e-15)"}
 
 
 def clone_params(scene, dev, direct=False, vp=None):
@@ -603,6 +693,11 @@ def main():
         "e2e": {"value": e2e_vps, "unit": "views/s", "h2d_bytes_per_step": stepper.h2d_bytes, "d2h_bytes_per_step": stepper.d2h_bytes,
                 "ms_per_step": ms_e2e / args.steps},
     }
+    if world == 1 and not os.environ.get("VCR_BENCH_NO_FULL_STEP"):
+        try:
+            out["full_step"] = time_full_step(args, impl, scene, stepper, dev, args.steps)
+        except Exception as ex:  # a side measurement must never cost the bench line
+            out["full_step"] = {"error": f"{type(ex).__name__}: {ex}"}
     if impl == "reference":
         out["impl"] = "reference"
         out["config"]["reference_build"] = "unmodified reference sources, nvcc 12.9, compute_90 PTX JIT-compiled for sm_100 (see DESIGN.md)"

@@ -227,6 +227,16 @@ int vcr_ssim_forward(int planes, int height, int width, const float* img1, const
 int vcr_ssim_backward(int planes, int height, int width, const float* img1, const float* img2, const float* dmaps,
                       const float* dL_dssim, float* dL_dimg1, void* stream);
 
+/* One Adam step (torch.optim.Adam semantics: no weight decay, no amsgrad) over a flat parameter tensor and its flat
+ * gradient, with a learning rate per contiguous range — the reference's six per-Gaussian parameter groups
+ * (scene/gaussian_model.py:241-258, eps = 1e-15) become six ranges of the view-parallel bucket and ONE launch
+ * (SURVEY.md 8f rank 3).  group_end_host[k] is the exclusive end (in floats) of range k, ascending, the last one equal
+ * to numel; lr_host[k] its learning rate; `step` counts from 1 (bias correction); every gradient is multiplied by
+ * grad_scale first (1/world after a SUM all-reduce).  All four device buffers must be 16-byte aligned. */
+int vcr_adam_step(long long numel, float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int n_groups,
+                  const long long* group_end_host, const float* lr_host, float beta1, float beta2, float eps, int step,
+                  float grad_scale, void* stream);
+
 /* Gradient exchange of the view-parallel layer through the NVSwitch (the reference is single-GPU and
  * has no counterpart).  `multicast_base` is the multicast mapping (NVLink SHARP, e.g. torch symmetric memory's
  * multicast_ptr) of a float buffer that every rank holds at the same offset.  For each of the n_ranges (<= 8) float

@@ -120,3 +120,42 @@ def test_prologue_feeds_the_rasterizer():
     out.square().mean().backward()
     for k, v in raw.items():
         assert v.grad is not None and torch.isfinite(v.grad).all() and float(v.grad.abs().sum()) > 0, k
+
+
+def test_prologue_writes_gradients_into_a_direct_bucket():
+    """With GaussianBucket(direct=True, names=raw groups) the prologue's and the rasterizer's backward kernels write every raw
+    gradient straight into the flat bucket; same numbers as the ordinary autograd path."""
+    import vcr_view_parallel as VP
+    from vcr_prologue import gaussian_prologue
+    from diff_gaussian_rasterization import GaussianRasterizer
+    from util import make_case, settings_from
+    inp, _, _ = make_case(2500, 128, 96, seed=8)
+    dev = torch.device("cuda")
+    shs = inp["shs"].to(dev)
+    raw = dict(xyz=inp["means3D"].to(dev), f_dc=shs[:, :1].contiguous(), f_rest=shs[:, 1:].contiguous(),
+               opacity=torch.logit(inp["opacities"].to(dev).clamp(1e-4, 1 - 1e-4)), scaling=torch.log(inp["scales"].to(dev)),
+               rotation=inp["rotations"].to(dev) * 0.6)
+    names = tuple(raw)
+    view = inp["viewmatrix"].to(dev)
+    dL = torch.randn((10, 96, 128), generator=torch.Generator().manual_seed(4)).to(dev)
+
+    def run(p):
+        opac, scales, rots, sh, normals = gaussian_prologue(p["xyz"], p["f_dc"], p["f_rest"], p["opacity"], p["scaling"], p["rotation"],
+                                                            inp["campos"].to(dev), view[:3, :3].t())
+        out, _ = GaussianRasterizer(settings_from(inp, dev))(
+            means3D=p["xyz"], means2D=None, shs=sh, normals_precomp=normals, opacities=opac, scales=scales, rotations=rots,
+            dirs=inp["dirs"].to(dev))
+        out.backward(dL)
+
+    bucket = VP.GaussianBucket(raw, device=dev, names=names, direct=True)
+    bucket.grad_flat.fill_(float("nan"))
+    run(bucket.params)
+    torch.cuda.synchronize()
+    assert torch.isfinite(bucket.grad_flat).all(), "some gradient rows were not written into the bucket"
+    for k in names:
+        assert bucket.params[k].grad.data_ptr() == bucket.grad_flat[bucket.layout[names.index(k)][1]:].data_ptr(), k
+    plain = {k: v.clone().requires_grad_(True) for k, v in raw.items()}
+    run(plain)
+    for k, off, n, shape in bucket.layout:
+        a, b = bucket.grad_flat[off:off + n].view(shape).double(), plain[k].grad.double()
+        assert float((a - b).norm() / b.norm().clamp_min(1e-30)) <= 1e-5, k

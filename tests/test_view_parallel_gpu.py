@@ -89,3 +89,36 @@ def test_densify_stats_kernel_matches_reference_updates():
     assert torch.equal(denom, e_denom) and torch.equal(max_r, e_max)
     torch.testing.assert_close(accum, e_accum, rtol=1e-6, atol=1e-7)              # sqrt(x*x+y*y): contraction may differ by 1 ulp
     assert float(denom.max()) == 2.0 and float((denom == 0).sum()) > 0
+
+
+def test_bucket_adam_matches_torch_adam():
+    """BucketAdam == torch.optim.Adam with the reference's six groups (scene/gaussian_model.py:241-258, eps=1e-15), three
+    steps with a learning-rate change in between and a gradient scale."""
+    import vcr_view_parallel as VP
+    P = 10_007
+    dev = torch.device("cuda")
+    g = torch.Generator().manual_seed(1)
+    shapes = dict(xyz=(P, 3), f_dc=(P, 1, 3), f_rest=(P, 15, 3), opacity=(P, 1), scaling=(P, 3), rotation=(P, 4))
+    names = tuple(shapes)
+    init = {k: torch.randn(s, generator=g).to(dev) for k, s in shapes.items()}
+    lrs = dict(xyz=1.6e-4, f_dc=2.5e-3, f_rest=2.5e-3 / 20, opacity=0.05, scaling=5e-3, rotation=1e-3)
+    bucket = VP.GaussianBucket(init, device=dev, names=names)
+    assert bucket.numel == 59 * P and tuple(bucket.params) == names
+    opt = VP.BucketAdam(bucket, lrs)
+    ref_p = {k: v.clone().requires_grad_(True) for k, v in init.items()}
+    ref = torch.optim.Adam([{"params": [ref_p[k]], "lr": lrs[k], "name": k} for k in names], lr=0.0, eps=1e-15)
+    for step in range(3):
+        grads = {k: torch.randn(s, generator=g).to(dev) * (10.0 ** (step - 1)) for k, s in shapes.items()}
+        scale = 0.5 if step == 1 else 1.0
+        for k in names:
+            bucket.params[k].grad.copy_(grads[k])
+            ref_p[k].grad = grads[k] * scale
+        if step == 2:
+            opt.set_lr("xyz", 8e-5)
+            ref.param_groups[0]["lr"] = 8e-5
+        opt.step(grad_scale=scale)
+        ref.step()
+        for k in names:
+            torch.testing.assert_close(bucket.params[k].detach(), ref_p[k].detach(), rtol=2e-6, atol=1e-7, msg=lambda m, k=k: f"{k} step {step}: {m}")
+    with pytest.raises(KeyError):
+        VP.BucketAdam(bucket, {"xyz": 1.0})

@@ -28,7 +28,7 @@ static long long g_launches[VCR_K_COUNT] = {0};
 static const char* kKernelNames[VCR_K_COUNT] = {
     "preprocess_kernel", "scan_block_sums_kernel", "duplicate_kernel", "radix_scan_hist_kernel", "radix_pass_kernel",
     "tile_ranges_kernel", "render_forward_kernel", "render_backward_kernel", "preprocess_backward_kernel",
-    "dnormal_forward_kernel", "dnormal_backward_kernel", "render_aux_kernel", "knn_kernels", "mark_visible_kernel", "memset", "densify_stats_kernel", "multimem_allreduce_kernel", "prologue_kernels", "ssim_kernels"};
+    "dnormal_forward_kernel", "dnormal_backward_kernel", "render_aux_kernel", "knn_kernels", "mark_visible_kernel", "memset", "densify_stats_kernel", "multimem_allreduce_kernel", "prologue_kernels", "ssim_kernels", "adam_step_kernel"};
 static cudaEvent_t prof_event() {
     if (!g_prof_pool.empty()) { cudaEvent_t e = g_prof_pool.back(); g_prof_pool.pop_back(); return e; }
     cudaEvent_t e; cudaEventCreate(&e); return e;

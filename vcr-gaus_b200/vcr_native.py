@@ -69,6 +69,10 @@ vcr_prologue_backward = _sig("vcr_prologue_backward", c_int, [c_int, c_int] + [P
 vcr_ssim_forward = _sig("vcr_ssim_forward", c_int, [c_int, c_int, c_int, P_, P_, P_, P_, c_void_p])
 vcr_ssim_backward = _sig("vcr_ssim_backward", c_int, [c_int, c_int, c_int, P_, P_, P_, P_, P_, c_void_p])
 
+vcr_adam_step = _sig("vcr_adam_step", c_int,
+                     [ctypes.c_longlong, P_, P_, P_, P_, c_int, POINTER(ctypes.c_longlong), POINTER(c_float), c_float, c_float, c_float,
+                      c_int, c_float, c_void_p])
+
 vcr_densify_stats_accumulate = _sig("vcr_densify_stats_accumulate", c_int, [c_int, P_, P_, P_, P_, P_, c_void_p])
 
 vcr_mark_visible = _sig("vcr_mark_visible", c_int, [c_int, P_, P_, P_, P_, c_void_p])
@@ -144,7 +148,7 @@ DECLARED_SYMBOLS = [
     "vcr_knn_scratch_bytes", "vcr_dist2_knn3", "vcr_geom_layout", "vcr_binning_layout", "vcr_image_layout",
     "vcr_knn_noalloc_max_points", "vcr_dist2_knn3_noalloc", "vcr_view_loss_forward", "vcr_view_loss_backward",
     "vcr_profile_enable", "vcr_profile_kernel_count", "vcr_profile_kernel_name", "vcr_profile_read",
-    "vcr_rasterize_backward_chunked", "vcr_densify_stats_accumulate", "vcr_multimem_allreduce_sum", "vcr_prologue_forward", "vcr_prologue_backward", "vcr_ssim_forward", "vcr_ssim_backward",
+    "vcr_rasterize_backward_chunked", "vcr_densify_stats_accumulate", "vcr_multimem_allreduce_sum", "vcr_prologue_forward", "vcr_prologue_backward", "vcr_ssim_forward", "vcr_ssim_backward", "vcr_adam_step",
 ]
 
 

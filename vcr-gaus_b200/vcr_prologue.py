@@ -58,6 +58,8 @@ class _Prologue(torch.autograd.Function):
                                              normals.data_ptr(), aux.data_ptr(), _stream(xyz)), "prologue_forward")
         ctx.save_for_backward(r_raw, opac, scales, rots, aux, M)
         ctx.shapes = (features_dc.shape, features_rest.shape, n_rest)
+        # optional zero-copy gradient destinations (vcr_view_parallel.GaussianBucket(direct=True)), as in the rasterizer
+        ctx.grad_out = tuple(getattr(t, "_vcr_grad_out", None) for t in (features_dc, features_rest, opacity_raw, scaling_raw, rotation_raw))
         return opac, scales, rots, shs, normals
 
     @staticmethod
@@ -71,8 +73,13 @@ class _Prologue(torch.autograd.Function):
             return torch.zeros(shape, **f) if t is None else _c(t, "gradient")
         g_opac, g_scales, g_rots = g(g_opac, (P, 1)), g(g_scales, (P, 3)), g(g_rots, (P, 4))
         g_shs, g_normals = g(g_shs, (P, 1 + n_rest, 3)), g(g_normals, (P, 3))
-        d_dc, d_rest = torch.empty(dc_shape, **f), torch.empty(rest_shape, **f)
-        d_o, d_s, d_r = torch.empty((P, 1), **f), torch.empty((P, 3), **f), torch.empty((P, 4), **f)
+        def dest(i, shape):
+            buf = ctx.grad_out[i]
+            if buf is not None and buf.is_cuda and buf.dtype == torch.float32 and buf.is_contiguous() and tuple(buf.shape) == tuple(shape):
+                return buf.view(shape)       # a fresh view of the bucket: autograd adopts it as .grad without a copy
+            return torch.empty(shape, **f)
+        d_dc, d_rest = dest(0, dc_shape), dest(1, rest_shape)
+        d_o, d_s, d_r = dest(2, (P, 1)), dest(3, (P, 3)), dest(4, (P, 4))
         if P:
             _n.check(_n.vcr_prologue_backward(P, n_rest, r_raw.data_ptr(), opac.data_ptr(), scales.data_ptr(), rots.data_ptr(),
                                               aux.data_ptr(), M.data_ptr(), g_opac.data_ptr(), g_scales.data_ptr(),

@@ -46,24 +46,29 @@ class GaussianBucket:
     `params[name]` are views into `flat`; their `.grad` are views into `grad_flat`, so autograd accumulates straight
     into the bucket and the gradient exchange is a single collective with no packing copy."""
 
-    def __init__(self, tensors: Dict[str, torch.Tensor], device=None, direct: bool = False, grad_storage=None):
+    def __init__(self, tensors: Dict[str, torch.Tensor], device=None, direct: bool = False, grad_storage=None, names=None):
         """direct=True: the rasterizer's backward writes each parameter gradient straight into `grad_flat` (through the
         `_vcr_grad_out` hook of diff_gaussian_rasterization) and autograd adopts views of it as `.grad` — no per-step
         memset of the bucket and no accumulate pass.  The price: exactly one backward per `zero_grad()`.
         grad_storage: a flat float32 tensor to use as `grad_flat` (ViewParallel.symmetric_gradient_storage() for the
-        NVSwitch-multicast exchange); default is an ordinary allocation."""
+        NVSwitch-multicast exchange); default is an ordinary allocation.
+        names: the keys of `tensors` to pack, in bucket order; default = the rasterizer's inputs (PARAM_LAYOUT).  A trainer
+        that keeps the raw parameters in the bucket passes e.g. ("xyz", "f_dc", "f_rest", "opacity", "scaling",
+        "rotation") — the reference's optimizer groups (scene/gaussian_model.py:241-248) — and steps them with BucketAdam."""
         self.direct = direct
-        P = tensors["means3D"].shape[0]
+        names = tuple(names) if names is not None else tuple(n for n, _ in PARAM_LAYOUT)
+        self.names = names
+        P = tensors[names[0]].shape[0]
         self.P = P
         self.layout = []
         off = 0
-        for name, _ in PARAM_LAYOUT:
+        for name in names:
             t = tensors[name]
             n = t.numel()
             self.layout.append((name, off, n, tuple(t.shape)))
             off += n
         self.numel = off
-        device = device if device is not None else tensors["means3D"].device
+        device = device if device is not None else tensors[names[0]].device
         self.flat = torch.empty(off, dtype=torch.float32, device=device)
         if grad_storage is None:
             self.grad_flat = torch.zeros(off, dtype=torch.float32, device=device)
@@ -82,8 +87,8 @@ class GaussianBucket:
             self.params[name] = p
 
     @staticmethod
-    def numel_for(tensors: Dict[str, torch.Tensor]) -> int:
-        return sum(tensors[name].numel() for name, _ in PARAM_LAYOUT)
+    def numel_for(tensors: Dict[str, torch.Tensor], names=None) -> int:
+        return sum(tensors[name].numel() for name in (names if names is not None else [n for n, _ in PARAM_LAYOUT]))
 
     def zero_grad(self):
         if self.direct:
@@ -95,6 +100,43 @@ class GaussianBucket:
     @property
     def floats_per_gaussian(self):
         return self.numel // max(self.P, 1)
+
+
+class BucketAdam:
+    """torch.optim.Adam(groups, lr=0.0, eps=1e-15) of the reference (scene/gaussian_model.py:241-258) over a GaussianBucket:
+    one learning rate per parameter group = per contiguous range of the flat tensors, the whole step in ONE kernel
+    (vcr_adam_step, csrc/adam.cu).  `lrs`: {group name: lr}; change one with set_lr (the xyz schedule,
+    gaussian_model.py:264-270).  step(grad_scale) multiplies the gradients by grad_scale on the fly (1/world after a SUM
+    all-reduce).  CUDA only."""
+
+    def __init__(self, bucket: GaussianBucket, lrs: Dict[str, float], betas=(0.9, 0.999), eps: float = 1e-15):
+        if not bucket.flat.is_cuda:
+            raise RuntimeError("BucketAdam needs a CUDA bucket; there is no CPU fallback")
+        missing = [n for n in bucket.names if n not in lrs]
+        if missing:
+            raise KeyError(f"no learning rate for {missing}")
+        self.bucket, self.lrs, self.betas, self.eps = bucket, dict(lrs), betas, eps
+        self.exp_avg = torch.zeros_like(bucket.flat)
+        self.exp_avg_sq = torch.zeros_like(bucket.flat)
+        self.steps = 0
+
+    def set_lr(self, name: str, lr: float):
+        if name not in self.lrs:
+            raise KeyError(name)
+        self.lrs[name] = float(lr)
+
+    @torch.no_grad()
+    def step(self, grad_scale: float = 1.0):
+        import vcr_native as _n
+        b = self.bucket
+        self.steps += 1
+        n = len(b.layout)
+        ends = (ctypes.c_longlong * n)(*[off + cnt for _, off, cnt, _ in b.layout])
+        lrs = (ctypes.c_float * n)(*[self.lrs[name] for name, _, _, _ in b.layout])
+        _n.check(_n.vcr_adam_step(b.numel, b.flat.data_ptr(), b.grad_flat.data_ptr(), self.exp_avg.data_ptr(),
+                                  self.exp_avg_sq.data_ptr(), n, ends, lrs, self.betas[0], self.betas[1], self.eps, self.steps,
+                                  float(grad_scale), ctypes.c_void_p(torch.cuda.current_stream(b.flat.device).cuda_stream)),
+                 "adam_step")
 
 
 class ViewParallel:
