@@ -29,6 +29,19 @@ def test_ab_against_reference_cuda(P, W, H, use_dirs, use_sem, deg, seed):
     if ref_ab.load() is None:
         pytest.skip("oracle/_ref reference extension not built / not loadable here")
     inp, sc, cam = make_case(P, W, H, seed=seed, use_dirs=use_dirs, use_sem=use_sem, sh_degree=deg)
+    _check_ab(inp, W, H, use_sem)
+
+
+def test_ab_at_bench_size():
+    """The same gates at the size the bench is quoted on: 1 M Gaussians, 1920x1080, R ~ 6.5 M instances."""
+    if ref_ab.load() is None:
+        pytest.skip("oracle/_ref reference extension not built / not loadable here")
+    inp, sc, cam = make_case(1_000_000, 1920, 1080, seed=0, use_dirs=True, use_sem=False, sh_degree=3)
+    inp["scales"] = inp["scales"] * 2.0                 # bench.py --footprint 2.0
+    _check_ab(inp, 1920, 1080, False)
+
+
+def _check_ab(inp, W, H, use_sem):
     ref = ref_ab.RefRun(inp)
     run = CudaRun(inp)
     rd, cd = ref.decode(), run.decode()
