@@ -610,6 +610,8 @@ def main():
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
     vp = VP.ViewParallel()
+    all_cores = os.sched_getaffinity(0)
+    numa_cores = VP.bind_to_gpu_numa_node(local) if os.environ.get("VCR_BENCH_NUMA", "1") == "1" else 0
     scene = build_scene(args)
     impl = args.impl
     if impl == "reference":
@@ -686,7 +688,8 @@ def main():
                                    + (f", pipelined with the backward in {stepper.chunks} Gaussian ranges)" if stepper.chunks else ")"))
                    if world > 1 else "single GPU",
                    "l2": "working set per step (parameters + gradients + per-view state > 600 MB) exceeds the 126 MB L2; views rotate every step",
-                   "not_in_step": "SSIM, Adam (outside the hot path, SURVEY.md 8f)"},
+                   "not_in_step": "SSIM, Adam, per-Gaussian prologue (outside the hot path, SURVEY.md 8f; see full_step)",
+                   "host": f"process bound to the {numa_cores} cores next to its GPU" if numa_cores else "no CPU binding"},
         "clocks": clocks,
         "exchange": ({"chosen": vp.transport, "ms_per_236MB_bucket": stepper.exchange_ms, "view_sharding": "cost-balanced (balanced_view_table)" if balanced else "every world-th camera"}
                      if world > 1 and impl == "ours" else None),
@@ -740,6 +743,7 @@ def main():
         except Exception as ex:  # never lose the bench line over the side measurement
             out["render_prologue"] = {"error": f"{type(ex).__name__}: {ex}"}
     if not args.no_cpu_baseline and world == 1:
+        os.sched_setaffinity(0, all_cores)        # the CPU baseline gets every host core, not just the GPU's NUMA node
         vps, dt, R = cpu_oracle_views_per_s(args, views[0])
         out["cpu_baseline"] = {"value": vps, "unit": "views/s", "cores": os.cpu_count(), "kind": "port",
                                "sample": f"one full {args.width}x{args.height} view of the same scene, rasterize fwd+bwd, CPU oracle with OpenMP ({dt:.1f} s)"}

@@ -40,6 +40,33 @@ def init_from_env(backend: Optional[str] = None):
     return rank, world, local
 
 
+def bind_to_gpu_numa_node(device_index: int):
+    """Restrict this process to the CPU cores next to its GPU (NVML's ideal CPU affinity for the device, intersected with the
+    cores the process may use) so that the pinned host buffers of its data loader are allocated on that NUMA node and the
+    per-view host->device copies do not cross the socket interconnect.  One process per GPU makes this a per-process
+    setting.  Returns the number of cores kept, or 0 if nothing was changed (no NVML, single-node host, restricted
+    cpuset)."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        try:
+            uuid = str(torch.cuda.get_device_properties(device_index).uuid)
+            h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid) if not uuid.startswith("GPU-") else uuid)
+        except Exception:
+            h = pynvml.nvmlDeviceGetHandleByIndex(device_index)
+        n_cpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (n_cpu + 63) // 64)
+        near = {64 * w + b for w, word in enumerate(words) for b in range(64) if (int(word) >> b) & 1}
+        allowed = os.sched_getaffinity(0)
+        keep = near & allowed
+        if not keep or keep == allowed:
+            return 0
+        os.sched_setaffinity(0, keep)
+        return len(keep)
+    except Exception:
+        return 0
+
+
 class GaussianBucket:
     """All per-Gaussian parameters in ONE flat tensor and all their gradients in ONE flat tensor.
 
@@ -144,6 +171,8 @@ class ViewParallel:
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.transport = "nccl"        # "multimem" after pick_transport() found the multicast kernel faster
+        self._pending = []
 
     def view_for_step(self, step: int, n_views: int, seed: int = 0) -> int:
         """Rank r takes views r, r+world, ... of a seeded permutation of the camera list, reshuffled every epoch
