@@ -723,17 +723,20 @@ def main():
     out["gpu_launches"] = launches
     if per_kernel:
         dom = max(per_kernel, key=lambda r: r["ms_per_step"])
+        issue = {}
         traffic = None      # DRAM bytes per launch of that kernel, from the committed ncu --set full capture of this workload
         try:
             tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
             same = (args.gaussians, args.width, args.height, args.footprint) == (1_000_000, 1920, 1080, 2.0)
             traffic = int(tr[dom["kernel"]]["bytes"]) if same else None
+            issue = {k: tr[dom["kernel"]][k] for k in ("issue_active_pct", "warp_instructions", "dram_pct_of_peak") if k in tr[dom["kernel"]]}
         except Exception:
             pass
         out["roofline"] = {"kernel": dom["kernel"], "bound": "hbm", "achieved": dom["achieved_gbs"], "peak": hbm_peak, "unit": "GB/s",
                            "frac": dom["achieved_gbs"] / hbm_peak, "traffic": traffic, "peak_source": peak_src,
                            "algorithmic_bytes_per_launch": dom["bytes_per_launch"],
-                           "note": "compositing kernels are FP32-issue / atomic bound, not HBM bound (DESIGN.md); the HBM fraction is reported as the contract asks"}
+                           "note": "compositing kernels are FP32-issue / atomic bound, not HBM bound (DESIGN.md); the HBM fraction is reported as the contract asks",
+                           "issue_bound": dict(issue, source=tr[dom["kernel"]]["source"]) if issue else None}
         out["kernels"] = per_kernel
         out["ms_per_step_with_kernel_events"] = ms_prof / args.steps if ms_prof else None
     out["scene"] = stats

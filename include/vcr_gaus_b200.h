@@ -194,6 +194,10 @@ int vcr_rasterize_backward_chunked(
 int vcr_densify_stats_accumulate(int P, const float* grad_means2D_densify, const int* radii, float* xyz_gradient_accum,
                                  float* denom, float* max_radii2D, void* stream);
 
+/* *loss (device f32) = w_l1*s0/(3N) + w_mono*(s1+s2)/N + w_dn*(s3+s4)/s5 (last term 0 when s5 == 0) from the sums of
+ * vcr_view_loss_forward, N = width*height: one launch instead of a dozen single-element PyTorch launches. */
+int vcr_view_loss_total(const float* sums, int width, int height, float w_l1, float w_mono, float w_dn, float* loss, void* stream);
+
 /* Everything render() computes per Gaussian before it calls the rasterizer, fused:
  *   opacities = sigmoid(opacity_raw), scales = exp(scaling_raw), rotations = normalize(rotation_raw),
  *   shs = cat(features_dc, features_rest)                              (scene/gaussian_model.py:125-162)

@@ -286,6 +286,16 @@ __global__ void __launch_bounds__(256) view_loss_backward_kernel(const DnParams 
     dL_dout[7 * HW + pix] = 0.f; dL_dout[8 * HW + pix] = 0.f; dL_dout[9 * HW + pix] = 0.f;
 }
 
+// the scalar loss from the six sums: one thread instead of a dozen single-element PyTorch launches
+__global__ void view_loss_total_kernel(const float* __restrict__ sums, const float N, const float w_l1, const float w_mono,
+                                       const float w_dn, float* __restrict__ loss) {
+    if (threadIdx.x != 0) return;
+    const float s5 = sums[5];
+    const float dn = s5 > 0.f ? (sums[3] + sums[4]) / fmaxf(s5, 1.0f) : 0.f;
+    *loss = __fadd_rn(__fadd_rn(__fdiv_rn(__fmul_rn(w_l1, sums[0]), 3.0f * N), __fdiv_rn(__fmul_rn(w_mono, sums[1] + sums[2]), N)),
+                      __fmul_rn(w_dn, dn));
+}
+
 extern "C" {
 
 int vcr_view_loss_forward(const float* outmap, const float* gt_image, const float* gt_normal, const uint8_t* mask, int width,
@@ -314,6 +324,15 @@ int vcr_view_loss_backward(const float* outmap, const float* gt_image, const flo
     VcrProfScope prof(VCR_K_DNORMAL_BWD, s);
     view_loss_backward_kernel<<<grid, 256, 0, s>>>(p, outmap, gt_image, sums, dL_dloss, w_l1, w_mono, w_dn, dL_doutmap);
     VCR_LAUNCH_CHECK("view_loss_backward_kernel");
+    return 0;
+}
+
+int vcr_view_loss_total(const float* sums, int width, int height, float w_l1, float w_mono, float w_dn, float* loss, void* stream) {
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    if (!sums || !loss || width <= 0 || height <= 0) { vcr_set_error("view_loss_total: bad argument"); return 1; }
+    VcrProfScope prof(VCR_K_DNORMAL_FWD, s);
+    view_loss_total_kernel<<<1, 32, 0, s>>>(sums, (float)((double)width * (double)height), w_l1, w_mono, w_dn, loss);
+    VCR_LAUNCH_CHECK("view_loss_total_kernel");
     return 0;
 }
 

@@ -109,9 +109,9 @@ class _ViewLoss(torch.autograd.Function):
                                           float(exp_t), float(mask_depth_max), sums.data_ptr(), _stream()), "view_loss_forward")
         ctx.save_for_backward(o, gi, gn, m if m is not None else torch.empty(0, dtype=torch.uint8, device=o.device), sums)
         ctx.meta = (W, H, fx, fy, cx, cy, float(exp_t), float(mask_depth_max), float(w_l1), float(w_mono), float(w_dn))
-        N = float(H * W)
-        dn = torch.where(sums[5] > 0, (sums[3] + sums[4]) / torch.clamp(sums[5], min=1.0), torch.zeros_like(sums[5]))
-        loss = w_l1 * sums[0] / (3.0 * N) + w_mono * (sums[1] + sums[2]) / N + w_dn * dn
+        loss = torch.empty((), dtype=torch.float32, device=o.device)
+        _n.check(_n.vcr_view_loss_total(sums.data_ptr(), W, H, float(w_l1), float(w_mono), float(w_dn), loss.data_ptr(), _stream()),
+                 "view_loss_total")
         ctx.mark_non_differentiable(sums)
         return loss, sums
 
