@@ -194,6 +194,15 @@ int vcr_rasterize_backward_chunked(
 int vcr_densify_stats_accumulate(int P, const float* grad_means2D_densify, const int* radii, float* xyz_gradient_accum,
                                  float* denom, float* max_radii2D, void* stream);
 
+/* Parity view of the binning state (tests; no caller in the reference).  The production forward sorts the Gaussians by
+ * depth first, emits their (tile, Gaussian) instances in that order and then sorts by tile id only, which yields the
+ * reference's sorted point list and tile ranges without ever materialising the reference's intermediate lists.  This
+ * call writes them, bit for bit in the reference's formats, into the binning / geometry buffers of a finished forward:
+ * the duplicated keys and values in Gaussian-index order (duplicateWithKeys, rasterizer_impl.cu:70-111), point_offsets
+ * (the inclusive scan, :283) and the sorted 64-bit keys (tile << 32 | depth bits, :309-314).  Idempotent. */
+int vcr_binning_reference_lists(int P, int R, int width, int height, const int* radii, char* geom_buffer, char* binning_buffer,
+                                void* stream);
+
 /* *loss (device f32) = w_l1*s0/(3N) + w_mono*(s1+s2)/N + w_dn*(s3+s4)/s5 (last term 0 when s5 == 0) from the sums of
  * vcr_view_loss_forward, N = width*height: one launch instead of a dozen single-element PyTorch launches. */
 int vcr_view_loss_total(const float* sums, int width, int height, float w_l1, float w_mono, float w_dn, float* loss, void* stream);

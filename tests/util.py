@@ -74,6 +74,13 @@ class CudaRun:
             nbytes = count * np.dtype(dtype).itemsize
             return buf[off:off + nbytes].cpu().numpy().view(dtype).copy()
 
+        # The production forward keeps bare tile ids as sort keys and never builds the reference's intermediate lists;
+        # this call materialises them (duplicated keys/values in index order, point_offsets, 64-bit sorted keys) so that
+        # they can be compared bit for bit.  It does not touch point_list or the tile ranges.
+        if R > 0:
+            n.check(n.vcr_binning_reference_lists(P, R, W, H, self.radii.data_ptr(), sv["geom"].data_ptr(), sv["binning"].data_ptr(),
+                                                  ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)), "binning_reference_lists")
+            torch.cuda.synchronize()
         gv = n.GeomView()
         n.vcr_geom_layout(ctypes.c_void_p(sv["geom"].data_ptr()), P, ctypes.byref(gv))
         g = sv["geom"]

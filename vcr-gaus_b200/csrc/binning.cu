@@ -145,6 +145,143 @@ __global__ void __launch_bounds__(256) duplicate_kernel(int P, int gx, int gy, c
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Production emission: instances in DEPTH order.  Sorting the P Gaussians by depth first (vcr_launch_gaussian_sort) and
+// emitting their instances in that order leaves only the tile id to sort by (2 passes for up to 65536 tiles instead of
+// 6 passes over 44-45 key bits); the result is the same list the reference's (tile | depth) sort produces.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) sorted_block_sums_kernel(int P, const uint32_t* __restrict__ sorted_ids,
+                                                                const uint32_t* __restrict__ tiles_touched,
+                                                                uint32_t* __restrict__ sums) {
+    __shared__ uint32_t warp_tot[8];
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    const uint32_t v = i < P ? tiles_touched[sorted_ids[i]] : 0u;
+    const uint32_t wsum = __reduce_add_sync(0xffffffffu, v);
+    if ((threadIdx.x & 31) == 0) warp_tot[threadIdx.x >> 5] = wsum;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t t = 0;
+#pragma unroll
+        for (int w = 0; w < 8; w++) t += warp_tot[w];
+        sums[blockIdx.x] = t;
+    }
+}
+
+__global__ void __launch_bounds__(256) duplicate_sorted_kernel(int P, int gx, int gy, const int* __restrict__ radii,
+                                                               const GeomState g, const uint32_t* __restrict__ sorted_ids,
+                                                               const uint32_t* __restrict__ sorted_sums,
+                                                               uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
+                                                               uint32_t* __restrict__ ghist, int npass, int tile_bits) {
+    __shared__ uint32_t incl[256];
+    __shared__ uint32_t s_gid[256];
+    __shared__ int s_x0[256], s_y0[256], s_w[256];
+    __shared__ uint32_t warp_tot[8];
+    __shared__ uint32_t hist[2][256];
+    const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+    const int i = blockIdx.x * 256 + t;
+    hist[0][t] = 0u; hist[1][t] = 0u;
+
+    uint32_t tiles = 0, gid = 0;
+    int x0 = 0, y0 = 0, rw = 0;
+    if (i < P) {
+        gid = sorted_ids[i];
+        tiles = g.tiles_touched[gid];
+        if (tiles > 0) {
+            int2 rmin, rmax;
+            vcr_get_rect(g.means2D[gid], radii[gid], gx, gy, rmin, rmax);
+            x0 = rmin.x; y0 = rmin.y; rw = rmax.x - rmin.x;
+        }
+    }
+    uint32_t inc = tiles;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t n = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += n;
+    }
+    if (lane == 31) warp_tot[w] = inc;
+    __syncthreads();
+    uint32_t wex = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) wex += (k < w) ? warp_tot[k] : 0u;
+    inc += wex;
+    incl[t] = inc;
+    s_gid[t] = gid; s_x0[t] = x0; s_y0[t] = y0; s_w[t] = rw;
+    const uint32_t base = sorted_sums[blockIdx.x];
+    __syncthreads();
+    const uint32_t total = incl[255];
+    for (uint32_t k = t; k < total; k += 256) {
+        int lo = 0, hi = 255;                           // smallest entry with incl > k
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            if (incl[mid] > k) hi = mid; else lo = mid + 1;
+        }
+        const uint32_t local = k - (lo ? incl[lo - 1] : 0u);
+        const int wdt = s_w[lo];
+        const int y = s_y0[lo] + (int)(local / (uint32_t)wdt);
+        const int x = s_x0[lo] + (int)(local % (uint32_t)wdt);
+        const uint32_t tile = (uint32_t)(y * gx + x);
+        keys_out[base + k] = (uint64_t)tile;
+        vals_out[base + k] = s_gid[lo];
+        for (int p = 0; p < npass; p++) {
+            const int nb = min(8, tile_bits - 8 * p);
+            atomicAdd(&hist[p][(tile >> (8 * p)) & ((1u << nb) - 1u)], 1u);
+        }
+    }
+    __syncthreads();
+    for (int p = 0; p < npass; p++) {
+        const uint32_t c = hist[p][t];
+        if (c) atomicAdd(&ghist[p * 256 + t], c);
+    }
+}
+
+int vcr_launch_duplicate_sorted(const FwdParams& p, GeomState& g, BinningState& b, int R, int tile_bits, cudaStream_t s) {
+    (void)R;
+    const int npass = (tile_bits + 7) / 8;
+    if (npass > 2) { vcr_set_error("more than 65536 tiles are not supported"); return 1; }
+    const int nb = (p.P + 255) / 256;
+    { VcrProfScope m(VCR_K_MEMSET, s); VCR_CUDA_TRY(cudaMemsetAsync(b.sort_hist, 0, VCR_MAX_PASSES * 256 * sizeof(uint32_t), s)); }
+    {
+        VcrProfScope prof(VCR_K_SCAN, s, 2);
+        sorted_block_sums_kernel<<<nb, 256, 0, s>>>(p.P, g.gs_vals[0], g.tiles_touched, g.sorted_sums);
+        VCR_LAUNCH_CHECK("sorted_block_sums_kernel");
+        scan_block_sums_kernel<<<1, 1024, 0, s>>>(g.sorted_sums, nb, g.num_rendered + 2);
+        VCR_LAUNCH_CHECK("scan_block_sums_kernel");
+    }
+    VcrProfScope prof(VCR_K_DUPLICATE, s);
+    duplicate_sorted_kernel<<<nb, 256, 0, s>>>(p.P, p.gx, p.gy, p.radii, g, g.gs_vals[0], g.sorted_sums, b.alt_keys, b.alt_vals,
+                                               b.sort_hist, npass, tile_bits);
+    VCR_LAUNCH_CHECK("duplicate_sorted_kernel");
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Parity view (tests only): materialise the lists in the REFERENCE's formats from the production state —
+//   point_list_keys_unsorted / point_list_unsorted : duplicateWithKeys' output, Gaussian-index order, (tile << 32 | depth)
+//   point_offsets                                  : the inclusive scan of tiles_touched in index order
+//   point_list_keys                                : the sorted keys as (tile << 32 | depth) (production keeps bare tiles)
+// sort_hist[VCR_MAX_PASSES*256 - 1] remembers that the sorted keys have been rewritten, so a second call is harmless.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) reference_keys_kernel(uint32_t R, uint64_t* __restrict__ keys, const uint32_t* __restrict__ point_list,
+                                                             const float* __restrict__ depths, const uint32_t* __restrict__ flag) {
+    const uint32_t i = blockIdx.x * 256u + threadIdx.x;
+    if (i >= R || *flag) return;
+    keys[i] = (keys[i] << 32) | (uint64_t)__float_as_uint(depths[point_list[i]]);
+}
+__global__ void set_flag_kernel(uint32_t* flag) { *flag = 1u; }
+
+int vcr_launch_reference_lists(int P, int R, int gx, int gy, const int* radii, GeomState& g, BinningState& b, cudaStream_t s) {
+    if (R <= 0) return 0;
+    uint32_t* flag = b.sort_hist + VCR_MAX_PASSES * 256 - 1;
+    duplicate_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, gx, gy, radii, g, b.point_list_keys_unsorted, b.point_list_unsorted,
+                                                     b.sort_hist, 0, 0);
+    VCR_LAUNCH_CHECK("duplicate_kernel");
+    reference_keys_kernel<<<((uint32_t)R + 255u) / 256u, 256, 0, s>>>((uint32_t)R, b.point_list_keys, b.point_list, g.depths, flag);
+    VCR_LAUNCH_CHECK("reference_keys_kernel");
+    set_flag_kernel<<<1, 1, 0, s>>>(flag);
+    VCR_LAUNCH_CHECK("set_flag_kernel");
+    return 0;
+}
+
 // Exclusive scan of each pass's 256-bin histogram (one block per pass).
 __global__ void __launch_bounds__(256) radix_scan_hist_kernel(uint32_t* __restrict__ ghist) {
     __shared__ uint32_t warp_tot[8];
@@ -223,8 +360,10 @@ __global__ void __launch_bounds__(RADIX_THREADS, VCR_RADIX_MINBLOCKS) radix_pass
         const bool valid = li < n;
         const uint32_t d = (uint32_t)(key[i] >> shift) & mask;
         const uint32_t vmask = __ballot_sync(0xffffffffu, valid);
-#ifdef VCR_RADIX_BALLOT
-        // peer mask from one ballot per digit bit: constant cost, whereas match.any costs one round per distinct digit
+#ifndef VCR_RADIX_MATCH_ANY
+        // peer mask from one ballot per digit bit: constant cost, whereas match.any costs one round per distinct digit in
+        // the warp — and both the depth-ordered emission (adjacent tiles of one Gaussian) and the index-ordered depth keys
+        // put ~30 distinct digits into a warp (89 us against 62 for the low tile byte)
         uint32_t peers = vmask;
 #pragma unroll
         for (int b = 0; b < 8; b++) {
@@ -275,18 +414,29 @@ __global__ void __launch_bounds__(RADIX_THREADS, VCR_RADIX_MINBLOCKS) radix_pass
         // decoupled look-back
         uint32_t excl = 0;
         if (bid > 0) {
+            // Walk back over the predecessors' words, RB_LOOK of them in flight at a time: when all blocks of a pass are
+            // resident at once (the P-sized depth sort: a few hundred blocks) block i has to look ~i/2 blocks back, and
+            // one dependent L2 round trip per block made that walk the longest thing in the kernel.
+            constexpr int RB_LOOK = 8;
             int j = (int)bid - 1;
             uint32_t spins = 0;
-            while (true) {
-                const uint32_t v = status[(size_t)j * 256 + t];
-                const uint32_t f = v & FLAG_MASK;
-                if (f == 0u) {
-                    if (++spins > (1u << 26)) { atomicExch(err_flag, 1u); break; }
-                    continue;
+            bool found = false;
+            while (!found) {
+                uint32_t v[RB_LOOK];
+#pragma unroll
+                for (int k = 0; k < RB_LOOK; k++) v[k] = (j - k >= 0) ? status[(size_t)(j - k) * 256 + t] : 0u;
+                int used = 0;
+#pragma unroll
+                for (int k = 0; k < RB_LOOK; k++) {
+                    if (found || used != k) continue;            // stop at the first word that is not published yet
+                    const uint32_t f = v[k] & FLAG_MASK;
+                    if (f == 0u) continue;
+                    excl += v[k] & ~FLAG_MASK;
+                    used = k + 1;
+                    if (f == FLAG_GLOBAL) found = true;
                 }
-                excl += v & ~FLAG_MASK;
-                if (f == FLAG_GLOBAL) break;
-                j--;
+                j -= used;
+                if (!found && used == 0 && ++spins > (1u << 26)) { atomicExch(err_flag, 1u); break; }
             }
             my_status[t] = FLAG_GLOBAL | (excl + cnt);
         }
@@ -314,18 +464,11 @@ __global__ void __launch_bounds__(RADIX_THREADS, VCR_RADIX_MINBLOCKS) radix_pass
     }
 }
 
-int vcr_launch_offsets_and_duplicate(const FwdParams& p, GeomState& g, BinningState& b, int R, int npass, int key_bits,
-                                     cudaStream_t s) {
-    (void)R;
-    { VcrProfScope m(VCR_K_MEMSET, s); VCR_CUDA_TRY(cudaMemsetAsync(b.sort_hist, 0, VCR_MAX_PASSES * 256 * sizeof(uint32_t), s)); }
-    VcrProfScope prof(VCR_K_DUPLICATE, s);
-    duplicate_kernel<<<(p.P + 255) / 256, 256, 0, s>>>(p.P, p.gx, p.gy, p.radii, g, b.point_list_keys_unsorted,
-                                                       b.point_list_unsorted, b.sort_hist, npass, key_bits);
-    VCR_LAUNCH_CHECK("duplicate_kernel");
-    return 0;
-}
-
-int vcr_launch_radix_sort(BinningState& b, int R, int key_bits, cudaStream_t s) {
+// Stable LSD sort of n (u64 key, u32 value) pairs over key bits [0, key_bits), 8 bits per pass.  `hist` holds the digit
+// histogram of every pass ([npass][256], turned into exclusive offsets here); the sorted pairs end in (kA, vA), with
+// (kB, vB) as the other ping-pong buffer.  (kA, vA) may alias the input when the number of passes is even.
+static int radix_sort_run(const uint64_t* kin, const uint32_t* vin, uint64_t* kA, uint32_t* vA, uint64_t* kB, uint32_t* vB,
+                          uint32_t n, int key_bits, uint32_t* hist, uint32_t* status, cudaStream_t s) {
     // the opt-in shared-memory size is a per-device function attribute
     static bool attr_set_dev[64] = {false};
     int dev_ = 0;
@@ -335,28 +478,47 @@ int vcr_launch_radix_sort(BinningState& b, int R, int key_bits, cudaStream_t s) 
         attr_set_dev[dev_] = true;
     }
     const int npass = (key_bits + 7) / 8;
-    const uint32_t nblocks = ((uint32_t)R + RADIX_TILE - 1) / RADIX_TILE;
-    { VcrProfScope prof(VCR_K_RADIX_HIST, s); radix_scan_hist_kernel<<<npass, 256, 0, s>>>(b.sort_hist); }
+    const uint32_t nblocks = (n + RADIX_TILE - 1) / RADIX_TILE;
+    { VcrProfScope prof(VCR_K_RADIX_HIST, s); radix_scan_hist_kernel<<<npass, 256, 0, s>>>(hist); }
     VCR_LAUNCH_CHECK("radix_scan_hist_kernel");
     // status words for all passes + one ticket per pass + error flag, zeroed in one memset
     const size_t words = (size_t)npass * nblocks * 256 + 16;
-    { VcrProfScope m(VCR_K_MEMSET, s); VCR_CUDA_TRY(cudaMemsetAsync(b.sort_status, 0, words * sizeof(uint32_t), s)); }
-    uint32_t* tickets = b.sort_status + (size_t)npass * nblocks * 256;
-    const uint64_t* kin = b.point_list_keys_unsorted;
-    const uint32_t* vin = b.point_list_unsorted;
+    { VcrProfScope m(VCR_K_MEMSET, s); VCR_CUDA_TRY(cudaMemsetAsync(status, 0, words * sizeof(uint32_t), s)); }
+    uint32_t* tickets = status + (size_t)npass * nblocks * 256;
     for (int pass = 0; pass < npass; pass++) {
         const bool to_final = ((npass - 1 - pass) % 2) == 0;
-        uint64_t* kout = to_final ? b.point_list_keys : b.alt_keys;
-        uint32_t* vout = to_final ? b.point_list : b.alt_vals;
+        uint64_t* kout = to_final ? kA : kB;
+        uint32_t* vout = to_final ? vA : vB;
         const int nbits = key_bits - 8 * pass < 8 ? key_bits - 8 * pass : 8;
         VcrProfScope prof(VCR_K_RADIX_PASS, s);
-        radix_pass_kernel<<<nblocks, RADIX_THREADS, RADIX_SMEM_BYTES, s>>>(
-            kin, vin, kout, vout, (uint32_t)R, 8 * pass, nbits, b.sort_hist + pass * 256,
-            b.sort_status + (size_t)pass * nblocks * 256, tickets + pass, tickets + 15);
+        radix_pass_kernel<<<nblocks, RADIX_THREADS, RADIX_SMEM_BYTES, s>>>(kin, vin, kout, vout, n, 8 * pass, nbits, hist + pass * 256,
+                                                                           status + (size_t)pass * nblocks * 256, tickets + pass,
+                                                                           tickets + 15);
         VCR_LAUNCH_CHECK("radix_pass_kernel");
         kin = kout; vin = vout;
     }
     return 0;
+}
+
+// Generic entry (kNN's Morton sort): input in the *_unsorted pair, result in (point_list_keys, point_list).
+int vcr_launch_radix_sort(BinningState& b, int R, int key_bits, cudaStream_t s) {
+    return radix_sort_run(b.point_list_keys_unsorted, b.point_list_unsorted, b.point_list_keys, b.point_list, b.alt_keys, b.alt_vals,
+                          (uint32_t)R, key_bits, b.sort_hist, b.sort_status, s);
+}
+
+// Sort ALL Gaussians by depth bits (stable, i.e. ties in index order): 4 passes over P pairs written by preprocess_kernel.
+// Result in g.gs_keys[0] / g.gs_vals[0]; Gaussians that are not rendered (key 0xFFFFFFFF) end up behind the others.
+int vcr_launch_gaussian_sort(int P, GeomState& g, cudaStream_t s) {
+    return radix_sort_run(g.gs_keys[0], g.gs_vals[0], g.gs_keys[0], g.gs_vals[0], g.gs_keys[1], g.gs_vals[1], (uint32_t)P, 32, g.gs_hist,
+                          g.gs_status, s);
+}
+
+// Stable sort of the R instances (emitted in depth order by duplicate_sorted_kernel) by tile id alone: ceil(tile_bits/8)
+// passes.  Within a tile the depth order of the emission survives, which is exactly the order the reference gets from
+// sorting (tile << 32 | depth) keys.  Input in (alt_keys, alt_vals), result in (point_list_keys, point_list).
+int vcr_launch_tile_sort(BinningState& b, int R, int tile_bits, cudaStream_t s) {
+    return radix_sort_run(b.alt_keys, b.alt_vals, b.point_list_keys, b.point_list, b.point_list_keys_unsorted, b.point_list_unsorted,
+                          (uint32_t)R, tile_bits, b.sort_hist, b.sort_status, s);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -365,10 +527,10 @@ int vcr_launch_radix_sort(BinningState& b, int R, int key_bits, cudaStream_t s) 
 __global__ void __launch_bounds__(256) tile_ranges_kernel(uint32_t L, const uint64_t* __restrict__ keys, uint2* __restrict__ ranges) {
     const uint32_t idx = blockIdx.x * 256u + threadIdx.x;
     if (idx >= L) return;
-    const uint32_t cur = (uint32_t)(keys[idx] >> 32);
+    const uint32_t cur = (uint32_t)keys[idx];          // the production keys are bare tile ids
     if (idx == 0) ranges[cur].x = 0;
     else {
-        const uint32_t prev = (uint32_t)(keys[idx - 1] >> 32);
+        const uint32_t prev = (uint32_t)keys[idx - 1];
         if (cur != prev) { ranges[prev].y = idx; ranges[cur].x = idx; }
     }
     if (idx == L - 1) ranges[cur].y = L;

@@ -51,6 +51,7 @@ static inline void carve_one(char*& p, T*& out, size_t count) {
     out = reinterpret_cast<T*>(p);
     p += count * sizeof(T);
 }
+static inline size_t radix_blocks(size_t R) { return (R + VCR_RADIX_TILE - 1) / VCR_RADIX_TILE; }
 GeomState GeomState::carve(char* chunk, int P) {
     GeomState g;
     const size_t n = (size_t)P;
@@ -65,12 +66,19 @@ GeomState GeomState::carve(char* chunk, int P) {
     carve_one(chunk, g.point_offsets, n);
     carve_one(chunk, g.block_sums, (n + 255) / 256 + 1);
     carve_one(chunk, g.num_rendered, (size_t)4);
+    carve_one(chunk, g.gs_keys[0], n);
+    carve_one(chunk, g.gs_keys[1], n);
+    carve_one(chunk, g.gs_vals[0], n);
+    carve_one(chunk, g.gs_vals[1], n);
+    carve_one(chunk, g.gs_hist, (size_t)4 * 256);
+    carve_one(chunk, g.gs_status, (size_t)4 * radix_blocks(n) * 256 + 16);
+    carve_one(chunk, g.sorted_sums, (n + 255) / 256 + 1);
     return g;
 }
 size_t GeomState::bytes(int P) {
     char* base = nullptr;
     GeomState g = carve(base, P);
-    return reinterpret_cast<size_t>(g.num_rendered + 4) + 256;
+    return reinterpret_cast<size_t>(g.sorted_sums + ((size_t)P + 255) / 256 + 1) + 256;
 }
 ImageState ImageState::carve(char* chunk, int W, int H) {
     ImageState s;
@@ -88,7 +96,6 @@ size_t ImageState::bytes(int W, int H) {
     const size_t tiles = (size_t)((W + VCR_TILE_X - 1) / VCR_TILE_X) * ((H + VCR_TILE_Y - 1) / VCR_TILE_Y);
     return reinterpret_cast<size_t>(s.tile_order + tiles) + 256;
 }
-static inline size_t radix_blocks(size_t R) { return (R + VCR_RADIX_TILE - 1) / VCR_RADIX_TILE; }
 BinningState BinningState::carve(char* chunk, int R) {
     BinningState b;
     const size_t n = (size_t)R;
@@ -118,13 +125,25 @@ static uint32_t higher_msb(uint32_t n) {  // rasterizer_impl.cu:35-50
     return msb;
 }
 
-// pinned word the device copy of R is read back through (one per host thread)
-static int read_back_u32x4(const uint32_t* dev, uint32_t out[4], cudaStream_t s) {
-    static thread_local uint32_t* pinned = nullptr;
-    if (!pinned) VCR_CUDA_TRY(cudaHostAlloc(reinterpret_cast<void**>(&pinned), 4 * sizeof(uint32_t), cudaHostAllocDefault));
-    VCR_CUDA_TRY(cudaMemcpyAsync(pinned, dev, 4 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
-    VCR_CUDA_TRY(cudaStreamSynchronize(s));
-    memcpy(out, pinned, 4 * sizeof(uint32_t));
+// The device copy of R is read back through a pinned word (one per host thread).  The copy is followed by an event, not
+// by a stream synchronisation: work queued behind it (the Gaussian-level depth sort) keeps the GPU busy while the host
+// waits for R, sizes the binning buffer and issues the rest of the forward.
+struct ReadBack {
+    uint32_t* pinned = nullptr;
+    cudaEvent_t ev = nullptr;
+};
+static int read_back_begin(const uint32_t* dev, ReadBack*& rb_out, cudaStream_t s) {
+    static thread_local ReadBack rb;
+    if (!rb.pinned) VCR_CUDA_TRY(cudaHostAlloc(reinterpret_cast<void**>(&rb.pinned), 4 * sizeof(uint32_t), cudaHostAllocDefault));
+    if (!rb.ev) VCR_CUDA_TRY(cudaEventCreateWithFlags(&rb.ev, cudaEventDisableTiming));
+    VCR_CUDA_TRY(cudaMemcpyAsync(rb.pinned, dev, 4 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    VCR_CUDA_TRY(cudaEventRecord(rb.ev, s));
+    rb_out = &rb;
+    return 0;
+}
+static int read_back_end(ReadBack* rb, uint32_t out[4]) {
+    VCR_CUDA_TRY(cudaEventSynchronize(rb->ev));
+    memcpy(out, rb->pinned, 4 * sizeof(uint32_t));
     return 0;
 }
 
@@ -161,7 +180,10 @@ static int forward_front(vcr_alloc_fn geometry_buffer, vcr_alloc_fn binning_buff
     if (debug_sync(debug, s, "preprocess")) return 1;
     if (vcr_launch_scan_block_sums(p.P, g, s)) return 1;
     uint32_t host[4];
-    if (read_back_u32x4(g.num_rendered, host, s)) return 1;
+    ReadBack* rb = nullptr;
+    if (read_back_begin(g.num_rendered, rb, s)) return 1;
+    if (vcr_launch_gaussian_sort(p.P, g, s)) return 1;          // runs while the host waits for R
+    if (read_back_end(rb, host)) return 1;
     if (host[1]) { vcr_set_error("Point is filtered although prefiltered is set. This shouldn't happen!"); return 1; }
     const int R = (int)host[0];
     *num_rendered_host = R;
@@ -170,13 +192,13 @@ static int forward_front(vcr_alloc_fn geometry_buffer, vcr_alloc_fn binning_buff
     if (!bchunk) { vcr_set_error("binning buffer callback returned NULL"); return 1; }
     b = BinningState::carve(bchunk, R);
     const int tiles = p.gx * p.gy;
-    const int key_bits = 32 + (int)higher_msb((uint32_t)tiles);
-    const int npass = (key_bits + 7) / 8;
+    const int tile_bits = (int)higher_msb((uint32_t)tiles);     // the reference sorts bits [0, 32 + this), rasterizer_impl.cu:305-314
     if (R > 0) {
-        if (vcr_launch_offsets_and_duplicate(p, g, b, R, npass, key_bits, s)) return 1;
+        if (debug_sync(debug, s, "depth sort")) return 1;
+        if (vcr_launch_duplicate_sorted(p, g, b, R, tile_bits, s)) return 1;
         if (debug_sync(debug, s, "duplicate")) return 1;
-        if (vcr_launch_radix_sort(b, R, key_bits, s)) return 1;
-        if (debug_sync(debug, s, "radix sort")) return 1;
+        if (vcr_launch_tile_sort(b, R, tile_bits, s)) return 1;
+        if (debug_sync(debug, s, "tile sort")) return 1;
     }
     if (vcr_launch_tile_ranges(b, img, R, tiles, s)) return 1;
     if (debug_sync(debug, s, "tile ranges")) return 1;
@@ -300,6 +322,16 @@ int vcr_multimem_allreduce_sum(void* multicast_base, int n_ranges, const long lo
     if (blocks <= 0) blocks = 37;   // 1.2 MB in flight already saturates the links (tools/mm_bench.py); 3/4 of the SMs stay free
     return vcr_launch_multimem_allreduce(static_cast<float*>(multicast_base), n_ranges, first_float_host, n_floats_host, rank, world,
                                          blocks, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int vcr_binning_reference_lists(int P, int R, int width, int height, const int* radii, char* geom_buffer, char* binning_buffer,
+                                void* stream) {
+    if (P <= 0 || R <= 0) return 0;
+    if (!radii || !geom_buffer || !binning_buffer || width <= 0 || height <= 0) { vcr_set_error("binning_reference_lists: bad argument"); return 1; }
+    GeomState g = GeomState::carve(geom_buffer, P);
+    BinningState b = BinningState::carve(binning_buffer, R);
+    return vcr_launch_reference_lists(P, R, (width + VCR_TILE_X - 1) / VCR_TILE_X, (height + VCR_TILE_Y - 1) / VCR_TILE_Y, radii, g, b,
+                                      reinterpret_cast<cudaStream_t>(stream));
 }
 
 int vcr_densify_stats_accumulate(int P, const float* grad_means2D_densify, const int* radii, float* xyz_gradient_accum,

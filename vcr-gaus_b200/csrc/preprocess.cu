@@ -169,12 +169,16 @@ __global__ void __launch_bounds__(256) preprocess_kernel(const FwdParams p, cons
     const int idx = blockIdx.x * 256 + threadIdx.x;
     __shared__ float sV[16], sP[16];
     __shared__ uint32_t warp_tiles[8];
+    __shared__ uint32_t s_dhist[4][256];          // digit histograms of the depth keys (Gaussian-level sort, binning.cu)
     if (threadIdx.x < 16) sV[threadIdx.x] = __ldg(p.viewmatrix + threadIdx.x);
     else if (threadIdx.x < 32) sP[threadIdx.x - 16] = __ldg(p.projmatrix + threadIdx.x - 16);
+#pragma unroll
+    for (int k = 0; k < 4; k++) s_dhist[k][threadIdx.x] = 0u;
     __syncthreads();
 
     uint32_t tiles = 0;
     int radius = 0;
+    uint32_t dkey = 0xFFFFFFFFu;                  // Gaussians that are not rendered sort behind every depth
     if (idx < p.P) {
         const float3 m = make_float3(__ldg(p.means3D + 3 * idx), __ldg(p.means3D + 3 * idx + 1), __ldg(p.means3D + 3 * idx + 2));
         const float vx = vcr_affine3(sV[0], sV[4], sV[8], sV[12], m.x, m.y, m.z);
@@ -231,6 +235,7 @@ __global__ void __launch_bounds__(256) preprocess_kernel(const FwdParams p, cons
                                                        __fmul_rn(cov.x, det_inv), __ldg(p.opacities + idx));
                     radius = (int)my_radius;
                     tiles = (uint32_t)area;
+                    if (tiles) dkey = __float_as_uint(vz);
                 }
             }
         } else if (p.prefiltered) {
@@ -239,6 +244,13 @@ __global__ void __launch_bounds__(256) preprocess_kernel(const FwdParams p, cons
         }
         p.radii[idx] = radius;
         g.tiles_touched[idx] = tiles;
+    }
+    // input of the Gaussian-level depth sort: (depth bits, index) + the digit histograms of its four passes
+    if (idx < p.P) {
+        g.gs_keys[0][idx] = (uint64_t)dkey;
+        g.gs_vals[0][idx] = (uint32_t)idx;
+#pragma unroll
+        for (int k = 0; k < 4; k++) atomicAdd(&s_dhist[k][(dkey >> (8 * k)) & 255u], 1u);
     }
     // phase 1 of the prefix sum: per-block total
     const uint32_t wsum = __reduce_add_sync(0xffffffffu, tiles);
@@ -249,6 +261,11 @@ __global__ void __launch_bounds__(256) preprocess_kernel(const FwdParams p, cons
 #pragma unroll
         for (int w = 0; w < 8; w++) t += warp_tiles[w];
         g.block_sums[blockIdx.x] = t;
+    }
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const uint32_t c = s_dhist[k][threadIdx.x];
+        if (c) atomicAdd(&g.gs_hist[k * 256 + threadIdx.x], c);
     }
 }
 
@@ -264,6 +281,7 @@ __global__ void __launch_bounds__(256) mark_visible_kernel(int P, const float* _
 int vcr_launch_preprocess(const FwdParams& p, GeomState& g, cudaStream_t s) {
     const int blocks = (p.P + 255) / 256;
     { VcrProfScope m(VCR_K_MEMSET, s); VCR_CUDA_TRY(cudaMemsetAsync(g.num_rendered, 0, 4 * sizeof(uint32_t), s)); }
+    { VcrProfScope m(VCR_K_MEMSET, s); VCR_CUDA_TRY(cudaMemsetAsync(g.gs_hist, 0, 4 * 256 * sizeof(uint32_t), s)); }
     VcrProfScope prof(VCR_K_PREPROCESS, s);
     preprocess_kernel<<<blocks, 256, 0, s>>>(p, g);
     VCR_LAUNCH_CHECK("preprocess_kernel");

@@ -66,6 +66,7 @@ vcr_multimem_allreduce_sum = _sig("vcr_multimem_allreduce_sum", c_int,
 vcr_prologue_forward = _sig("vcr_prologue_forward", c_int, [c_int, c_int] + [P_] * 15 + [c_void_p])
 vcr_prologue_backward = _sig("vcr_prologue_backward", c_int, [c_int, c_int] + [P_] * 16 + [c_void_p])
 
+vcr_binning_reference_lists = _sig("vcr_binning_reference_lists", c_int, [c_int, c_int, c_int, c_int, P_, P_, P_, c_void_p])
 vcr_view_loss_total = _sig("vcr_view_loss_total", c_int, [P_, c_int, c_int, c_float, c_float, c_float, P_, c_void_p])
 vcr_ssim_forward = _sig("vcr_ssim_forward", c_int, [c_int, c_int, c_int, P_, P_, P_, P_, c_void_p])
 vcr_ssim_backward = _sig("vcr_ssim_backward", c_int, [c_int, c_int, c_int, P_, P_, P_, P_, P_, c_void_p])
@@ -149,7 +150,7 @@ DECLARED_SYMBOLS = [
     "vcr_knn_scratch_bytes", "vcr_dist2_knn3", "vcr_geom_layout", "vcr_binning_layout", "vcr_image_layout",
     "vcr_knn_noalloc_max_points", "vcr_dist2_knn3_noalloc", "vcr_view_loss_forward", "vcr_view_loss_backward",
     "vcr_profile_enable", "vcr_profile_kernel_count", "vcr_profile_kernel_name", "vcr_profile_read",
-    "vcr_rasterize_backward_chunked", "vcr_densify_stats_accumulate", "vcr_multimem_allreduce_sum", "vcr_prologue_forward", "vcr_prologue_backward", "vcr_ssim_forward", "vcr_ssim_backward", "vcr_adam_step", "vcr_view_loss_total",
+    "vcr_rasterize_backward_chunked", "vcr_densify_stats_accumulate", "vcr_multimem_allreduce_sum", "vcr_prologue_forward", "vcr_prologue_backward", "vcr_ssim_forward", "vcr_ssim_backward", "vcr_adam_step", "vcr_view_loss_total", "vcr_binning_reference_lists",
 ]
 
 
