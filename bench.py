@@ -374,9 +374,12 @@ def clone_params(scene, dev, direct=False, vp=None):
     store = None
     if vp is not None and vp.world > 1 and direct and os.environ.get("VCR_BENCH_TRANSPORT", "multimem") == "multimem":
         # (symmetric storage is also fine for NCCL, so it is allocated whenever the multicast kernel may be chosen)
-        store = vp.symmetric_gradient_storage(VP.GaussianBucket.numel_for(tensors), dev)
+        store = vp.symmetric_gradient_storage(vp.exchange_floats(tensors), dev)
     b = VP.GaussianBucket(tensors, device=dev, direct=direct, grad_storage=store)
     b.transport = "multimem" if store is not None else "nccl"
+    b.compact = bool(vp is not None and vp.world > 1 and direct and os.environ.get("VCR_BENCH_COMPACT", "1") == "1")
+    if b.compact:
+        vp.compact_sh_exchange(b, sh_degree=3)     # exchange 3 instead of 48 floats per Gaussian for the SH coefficients
     return b
 
 
@@ -422,8 +425,9 @@ class Stepper:
             forced = os.environ.get("VCR_BENCH_TRANSPORT")
             if forced in ("nccl", "multimem") and (forced == "nccl" or bucket.transport == "multimem"):
                 vp.transport = forced
-            # pipelining pays with the multicast kernel (a quarter of the SMs, 8 GPUs: -0.04 ms/step), not with NCCL
-            self.chunks = int(os.environ.get("VCR_BENCH_CHUNKS", "4" if vp.transport == "multimem" else "0"))
+            # pipelining pays with the multicast kernel (a quarter of the SMs, 8 GPUs: -0.04 ms/step), not with NCCL; the
+            # compact exchange is too small to be worth pipelining
+            self.chunks = 0 if bucket.compact else int(os.environ.get("VCR_BENCH_CHUNKS", "4" if vp.transport == "multimem" else "0"))
         if self.chunks > 0 and "grads" not in self.skip:
             vp.overlap_gradients(bucket, n_chunks=self.chunks, transport=vp.transport)
         if impl == "reference":
@@ -509,7 +513,9 @@ class Stepper:
             e[1].record()
         skip = self.skip
         if self.vp.world > 1 and "grads" not in skip:
-            if self.chunks > 0:
+            if getattr(self.bucket, "compact", False):
+                self.vp.exchange_compact(self.bucket, campos)
+            elif self.chunks > 0:
                 self.vp.finish_gradients(self.bucket)
             else:
                 self.vp.allreduce_gradients(self.bucket, average=False)
@@ -685,13 +691,14 @@ def main():
                                f"ray/plane-intersection depth, loss = L1 + mono-normal + D-Normal; rasterize fwd+bwd per view",
                    "parallelism": (f"view-parallel x{world} (replicated Gaussians, all-reduce of the flat gradient bucket via "
                                    + ("own NVSwitch-multicast kernel" if vp.transport == "multimem" else "NCCL")
+                                   + (", SH gradient exchanged as 3 colour-gradient floats per Gaussian and rebuilt per rank" if getattr(bucket, "compact", False) else "")
                                    + (f", pipelined with the backward in {stepper.chunks} Gaussian ranges)" if stepper.chunks else ")"))
                    if world > 1 else "single GPU",
                    "l2": "working set per step (parameters + gradients + per-view state > 600 MB) exceeds the 126 MB L2; views rotate every step",
                    "not_in_step": "SSIM, Adam, per-Gaussian prologue (outside the hot path, SURVEY.md 8f; see full_step)",
                    "host": f"process bound to the {numa_cores} cores next to its GPU" if numa_cores else "no CPU binding"},
         "clocks": clocks,
-        "exchange": ({"chosen": vp.transport, "ms_per_236MB_bucket": stepper.exchange_ms, "view_sharding": "cost-balanced (balanced_view_table)" if balanced else "every world-th camera"}
+        "exchange": ({"chosen": vp.transport, "ms_per_exchange": stepper.exchange_ms, "compact_sh": bool(getattr(bucket, "compact", False)), "view_sharding": "cost-balanced (balanced_view_table)" if balanced else "every world-th camera"}
                      if world > 1 and impl == "ours" else None),
         "e2e": {"value": e2e_vps, "unit": "views/s", "h2d_bytes_per_step": stepper.h2d_bytes, "d2h_bytes_per_step": stepper.d2h_bytes,
                 "ms_per_step": ms_e2e / args.steps},

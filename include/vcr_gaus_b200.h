@@ -184,7 +184,8 @@ int vcr_rasterize_backward_chunked(
     void* stream,
     int n_chunks,
     vcr_chunk_fn chunk_enqueued,
-    void* chunk_user);
+    void* chunk_user,
+    float* dL_dcolor_masked);    /* optional f32[P,3], see vcr_sh_grad_from_colors; when non-NULL dL_dsh is NOT written */
 
 /* Per-view densification statistics, in place, for Gaussians with radii > 0:
  *   xyz_gradient_accum[i] += |grad_means2D_densify[i, 0:2]|;  denom[i] += 1     (scene/gaussian_model.py:669-671)
@@ -249,6 +250,24 @@ int vcr_ssim_backward(int planes, int height, int width, const float* img1, cons
 int vcr_adam_step(long long numel, float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int n_groups,
                   const long long* group_end_host, const float* lr_host, float beta1, float beta2, float eps, int step,
                   float grad_scale, void* stream);
+
+/* Compact exchange of the SH gradient (view-parallel; no reference counterpart).  For one view the gradient of the
+ * loss w.r.t. the SH coefficients of a Gaussian is the outer product of its clamp-masked colour gradient (3 floats) with
+ * the SH basis of the direction camera -> Gaussian (computeColorFromSH backward, DGR/cuda_rasterizer/backward.cu:20-139),
+ * so the ranks need not all-reduce 48 floats per Gaussian: vcr_rasterize_backward_chunked(..., dL_dcolor_masked) hands out
+ * the 3 floats, the ranks all-gather them together with their camera positions, and this call rebuilds
+ *   dL_dsh[g] = sum over ranks r of basis(normalize(means3D[g] - campos_r)) (x) dcolor_r[g]
+ * on every rank, in rank order.  `slices`: world slices of slice_stride floats, slice r = [ dcolor_r f32[P,3] | campos_r
+ * f32[3] | padding ].  dL_dsh f32[P,M,3] is fully written. */
+int vcr_sh_grad_from_colors(int P, int D, int M, int world, const float* means3D, const float* slices, long long slice_stride,
+                            float* dL_dsh, void* stream);
+
+/* vcr_multimem_allreduce_sum plus, in the same launch, this rank's contribution to an all-gather: the floats
+ * [bcast_first, +bcast_count) of the symmetric buffer (local_base = this rank's own mapping of it, bcast_first a
+ * multiple of 4) are read locally and multicast to every rank.  Same ordering contract as vcr_multimem_allreduce_sum. */
+int vcr_multimem_exchange(void* multicast_base, const float* local_base, int n_ranges, const long long* first_float_host,
+                          const long long* n_floats_host, long long bcast_first, long long bcast_count, int rank, int world,
+                          int blocks, void* stream);
 
 /* Gradient exchange of the view-parallel layer through the NVSwitch (the reference is single-GPU and
  * has no counterpart).  `multicast_base` is the multicast mapping (NVLink SHARP, e.g. torch symmetric memory's

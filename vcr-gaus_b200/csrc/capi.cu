@@ -249,12 +249,12 @@ int vcr_rasterize_backward_chunked(int P, int D, int M, int R, const float* back
                            float* dL_dmean2D_densify, float* dL_dopacity, float* dL_dcolor, float* dL_dnormal, float* dL_dobjects,
                            float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
                            const uint8_t* inside, char* scratch, int debug, void* stream, int n_chunks,
-                           vcr_chunk_fn chunk_enqueued, void* chunk_user) {
+                           vcr_chunk_fn chunk_enqueued, void* chunk_user, float* dL_dcolor_masked) {
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
     if (P <= 0) { vcr_set_error("P must be positive"); return 1; }
     if (!geom_buffer || !binning_buffer || !img_buffer || !scratch) { vcr_set_error("NULL state/scratch buffer"); return 1; }
     if (!dL_dpix || !dL_dmean2D || !dL_dmean2D_densify || !dL_dopacity || !dL_dcolor || !dL_dnormal || !dL_dobjects ||
-        !dL_dmean3D || !dL_dcov3D || !dL_dscale || !dL_drot || (M > 0 && shs && !dL_dsh)) {
+        !dL_dmean3D || !dL_dcov3D || !dL_dscale || !dL_drot || (M > 0 && shs && !dL_dsh && !dL_dcolor_masked)) {
         vcr_set_error("NULL gradient output");
         return 1;
     }
@@ -272,6 +272,7 @@ int vcr_rasterize_backward_chunked(int P, int D, int M, int R, const float* back
     p.dL_dmean2D = dL_dmean2D; p.dL_dmean2D_densify = dL_dmean2D_densify; p.dL_dopacity = dL_dopacity; p.dL_dcolor = dL_dcolor;
     p.dL_dnormal = dL_dnormal; p.dL_dobjects = dL_dobjects; p.dL_dmean3D = dL_dmean3D; p.dL_dcov3D = dL_dcov3D; p.dL_dsh = dL_dsh;
     p.dL_dscale = dL_dscale; p.dL_drot = dL_drot; p.inside = inside;
+    p.dL_dcolor_masked = shs ? dL_dcolor_masked : nullptr;
     p.acc = reinterpret_cast<float*>(vcr_align256(reinterpret_cast<size_t>(scratch)));
     GeomState g = GeomState::carve(geom_buffer, P);
     BinningState b = BinningState::carve(binning_buffer, R);
@@ -307,7 +308,30 @@ int vcr_rasterize_backward(int P, int D, int M, int R, const float* background, 
                                           alpha, depth, scales, scale_modifier, rotations, cov3D_precomp, viewmatrix, projmatrix, dirs,
                                           campos, tan_fovx, tan_fovy, radii, geom_buffer, binning_buffer, img_buffer, dL_dpix,
                                           dL_dmean2D, dL_dmean2D_densify, dL_dopacity, dL_dcolor, dL_dnormal, dL_dobjects, dL_dmean3D,
-                                          dL_dcov3D, dL_dsh, dL_dscale, dL_drot, inside, scratch, debug, stream, 1, nullptr, nullptr);
+                                          dL_dcov3D, dL_dsh, dL_dscale, dL_drot, inside, scratch, debug, stream, 1, nullptr, nullptr, nullptr);
+}
+
+int vcr_sh_grad_from_colors(int P, int D, int M, int world, const float* means3D, const float* slices, long long slice_stride,
+                            float* dL_dsh, void* stream) {
+    if (P <= 0) return 0;
+    if (!means3D || !slices || !dL_dsh || world < 1 || M < 1 || slice_stride < 3LL * P + 3) { vcr_set_error("sh_grad_from_colors: bad argument"); return 1; }
+    return vcr_launch_sh_grad_from_colors(P, D, M, world, means3D, slices, slice_stride, dL_dsh, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int vcr_multimem_exchange(void* multicast_base, const float* local_base, int n_ranges, const long long* first_float_host,
+                          const long long* n_floats_host, long long bcast_first, long long bcast_count, int rank, int world,
+                          int blocks, void* stream) {
+    if (!multicast_base) { vcr_set_error("NULL multicast address (no NVLink multicast mapping for this buffer)"); return 1; }
+    if (n_ranges < 0 || n_ranges > 8) { vcr_set_error("at most 8 ranges per launch"); return 1; }
+    if (world < 1 || rank < 0 || rank >= world) { vcr_set_error("bad rank / world"); return 1; }
+    if (n_ranges > 0 && (!first_float_host || !n_floats_host)) { vcr_set_error("NULL range arrays"); return 1; }
+    for (int i = 0; i < n_ranges; i++)
+        if (first_float_host[i] < 0 || n_floats_host[i] < 0) { vcr_set_error("negative range"); return 1; }
+    if (bcast_count < 0 || bcast_first < 0 || (bcast_count > 0 && (!local_base || (bcast_first & 3)))) { vcr_set_error("bad broadcast range (16-byte aligned start, local base required)"); return 1; }
+    if (n_ranges == 0 && bcast_count == 0) return 0;
+    if (blocks <= 0) blocks = 37;
+    return vcr_launch_multimem_exchange(static_cast<float*>(multicast_base), local_base, n_ranges, first_float_host, n_floats_host,
+                                        bcast_first, bcast_count, rank, world, blocks, reinterpret_cast<cudaStream_t>(stream));
 }
 
 int vcr_multimem_allreduce_sum(void* multicast_base, int n_ranges, const long long* first_float_host,

@@ -18,6 +18,19 @@ static __device__ __constant__ float kC3[7] = {-0.5900435899266435f, 2.890611442
 // Per-Gaussian work.  With COOP (M == 16) the SH gradient is not written here: the thread leaves its 16 basis values
 // and its 3 clamp-masked colour gradients in shared memory (both pre-zeroed by the caller) and the block writes the
 // [256][16][3] gradient tile with fully coalesced stores afterwards.
+// dRGB/dsh_k for the unit view direction (x, y, z): the SH basis of computeColorFromSH (forward.cu:22-74), shared by the
+// three channels.  Used by the backward below and by the view-parallel reconstruction of dL_dsh at the end of this file.
+__device__ __forceinline__ void vcr_sh_basis(const float x, const float y, const float z, float (&basis)[16]) {
+    const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+    basis[0] = kC0;
+    basis[1] = -kC1 * y; basis[2] = kC1 * z; basis[3] = -kC1 * x;
+    basis[4] = kC2[0] * xy; basis[5] = kC2[1] * yz; basis[6] = kC2[2] * (2.f * zz - xx - yy);
+    basis[7] = kC2[3] * xz; basis[8] = kC2[4] * (xx - yy);
+    basis[9] = kC3[0] * y * (3.f * xx - yy); basis[10] = kC3[1] * xy * z; basis[11] = kC3[2] * y * (4.f * zz - xx - yy);
+    basis[12] = kC3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy); basis[13] = kC3[4] * x * (4.f * zz - xx - yy);
+    basis[14] = kC3[5] * z * (xx - yy); basis[15] = kC3[6] * x * (xx - 3.f * yy);
+}
+
 template <bool COOP>
 __device__ __forceinline__ void preprocess_backward_body(const BwdParams& p, const GeomState& g, const int idx, const float* V,
                                                          const float* Pm, float* s_basis, float* s_gg) {
@@ -37,7 +50,8 @@ __device__ __forceinline__ void preprocess_backward_body(const BwdParams& p, con
         for (int k = 0; k < 6; k++) p.dL_dcov3D[6 * i + k] = 0.f;
 #pragma unroll
         for (int k = 0; k < 4; k++) p.dL_drot[4 * i + k] = 0.f;
-        if (!COOP && p.dL_dsh) for (int k = 0; k < 3 * M; k++) p.dL_dsh[i * 3 * M + k] = 0.f;
+        if (p.dL_dcolor_masked) { p.dL_dcolor_masked[3 * i] = 0.f; p.dL_dcolor_masked[3 * i + 1] = 0.f; p.dL_dcolor_masked[3 * i + 2] = 0.f; }
+        else if (!COOP && p.dL_dsh) for (int k = 0; k < 3 * M; k++) p.dL_dsh[i * 3 * M + k] = 0.f;
         return;
     }
 
@@ -168,17 +182,14 @@ __device__ __forceinline__ void preprocess_backward_body(const BwdParams& p, con
         for (int ch = 0; ch < 3; ch++) gg[ch] = a[ACC_COLOR_R + ch] * (g.clamped[3 * i + ch] ? 0.f : 1.f);
         float ddx = 0.f, ddy = 0.f, ddz = 0.f;
         const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
-        // basis values (dRGB/dsh_k), shared by the three channels
         float basis[16];
-        basis[0] = kC0;
-        basis[1] = -kC1 * y; basis[2] = kC1 * z; basis[3] = -kC1 * x;
-        basis[4] = kC2[0] * xy; basis[5] = kC2[1] * yz; basis[6] = kC2[2] * (2.f * zz - xx - yy);
-        basis[7] = kC2[3] * xz; basis[8] = kC2[4] * (xx - yy);
-        basis[9] = kC3[0] * y * (3.f * xx - yy); basis[10] = kC3[1] * xy * z; basis[11] = kC3[2] * y * (4.f * zz - xx - yy);
-        basis[12] = kC3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy); basis[13] = kC3[4] * x * (4.f * zz - xx - yy);
-        basis[14] = kC3[5] * z * (xx - yy); basis[15] = kC3[6] * x * (xx - 3.f * yy);
+        vcr_sh_basis(x, y, z, basis);
         const int nact = (D + 1) * (D + 1);
-        if (COOP) {
+        if (p.dL_dcolor_masked) {
+            // compact mode: hand out the masked colour gradient; dL_dsh = basis (x) this is rebuilt after the exchange
+#pragma unroll
+            for (int ch = 0; ch < 3; ch++) p.dL_dcolor_masked[3 * i + ch] = gg[ch];
+        } else if (COOP) {
 #pragma unroll
             for (int k = 0; k < 16; k++) s_basis[threadIdx.x * 17 + k] = k < nact ? basis[k] : 0.f;
 #pragma unroll
@@ -220,6 +231,8 @@ __device__ __forceinline__ void preprocess_backward_body(const BwdParams& p, con
         gm[0] += ((+sum2 - dox * dox) * ddx - doy * dox * ddy - doz * dox * ddz) * invsum32;
         gm[1] += (-dox * doy * ddx + (sum2 - doy * doy) * ddy - doz * doy * ddz) * invsum32;
         gm[2] += (-dox * doz * ddx - doy * doz * ddy + (sum2 - doz * doz) * ddz) * invsum32;
+    } else if (p.dL_dcolor_masked) {
+        p.dL_dcolor_masked[3 * i] = 0.f; p.dL_dcolor_masked[3 * i + 1] = 0.f; p.dL_dcolor_masked[3 * i + 2] = 0.f;
     } else if (!COOP && p.dL_dsh) {
         for (int k = 0; k < 3 * M; k++) p.dL_dsh[i * 3 * M + k] = 0.f;
     }
@@ -314,10 +327,63 @@ int vcr_launch_preprocess_backward(const BwdParams& p, GeomState& g, int first_g
     // Gaussians [first_gaussian, first_gaussian + n_gaussians); first_gaussian must be a multiple of 256 (one block's worth)
     if (n_gaussians <= 0) return 0;
     VcrProfScope prof(VCR_K_PREPROCESS_BWD, s);
-    const bool coop = p.shs != nullptr && p.M == 16 && p.dL_dsh != nullptr;
+    const bool coop = p.shs != nullptr && p.M == 16 && p.dL_dsh != nullptr && p.dL_dcolor_masked == nullptr;
     const int first_block = first_gaussian / 256, blocks = (n_gaussians + 255) / 256;
     if (coop) preprocess_backward_kernel<true><<<blocks, 256, 0, s>>>(p, g, first_block);
     else preprocess_backward_kernel<false><<<blocks, 256, 0, s>>>(p, g, first_block);
     VCR_LAUNCH_CHECK("preprocess_backward_kernel");
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// View-parallel reconstruction of the SH gradient.  On every rank the SH gradient of a view is the outer product of the
+// clamp-masked colour gradient (3 floats) with the SH basis of the direction camera -> Gaussian, i.e. rank one per
+// Gaussian and view.  Instead of all-reducing 48 floats per Gaussian the ranks therefore all-gather 3 (+ their camera
+// position) and each rebuilds   dL_dsh[g] = sum_r basis(normalize(mean[g] - campos_r)) (x) dcolor_r[g]   locally, in rank
+// order (so all replicas get the same bits).  `slices` holds one slice per rank: [3P colour gradients | campos xyz | pad].
+// ------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) sh_grad_from_colors_kernel(const int P, const int D, const int M, const int world,
+                                                                  const float* __restrict__ means3D, const float* __restrict__ slices,
+                                                                  const long long slice_stride, float* __restrict__ dL_dsh) {
+    const int idx = blockIdx.x * 256 + threadIdx.x;
+    if (idx >= P) return;
+    const size_t i = (size_t)idx;
+    const float3 mean = make_float3(__ldg(means3D + 3 * i), __ldg(means3D + 3 * i + 1), __ldg(means3D + 3 * i + 2));
+    float acc[48];
+#pragma unroll
+    for (int k = 0; k < 48; k++) acc[k] = 0.f;
+    const int nact = min((D + 1) * (D + 1), 16);
+    for (int r = 0; r < world; r++) {
+        const float* sl = slices + (size_t)r * slice_stride;
+        const float g0 = __ldg(sl + 3 * i), g1 = __ldg(sl + 3 * i + 1), g2 = __ldg(sl + 3 * i + 2);
+        if (g0 == 0.f && g1 == 0.f && g2 == 0.f) continue;              // not rendered / fully clamped on that rank
+        const float dox = mean.x - __ldg(sl + 3 * (size_t)P), doy = mean.y - __ldg(sl + 3 * (size_t)P + 1),
+                    doz = mean.z - __ldg(sl + 3 * (size_t)P + 2);
+        const float len = sqrtf(dox * dox + doy * doy + doz * doz);
+        float basis[16];
+        vcr_sh_basis(dox / len, doy / len, doz / len, basis);
+#pragma unroll
+        for (int k = 0; k < 16; k++) {
+            const float bk = k < nact ? basis[k] : 0.f;
+            acc[3 * k] += bk * g0; acc[3 * k + 1] += bk * g1; acc[3 * k + 2] += bk * g2;
+        }
+    }
+    float* out = dL_dsh + i * 3 * (size_t)M;
+    if (M == 16) {
+        float4* o4 = reinterpret_cast<float4*>(out);
+#pragma unroll
+        for (int q = 0; q < 12; q++) o4[q] = make_float4(acc[4 * q], acc[4 * q + 1], acc[4 * q + 2], acc[4 * q + 3]);
+    } else {
+#pragma unroll
+        for (int e = 0; e < 48; e++) if (e < 3 * M) out[e] = acc[e];
+        for (int e = 48; e < 3 * M; e++) out[e] = 0.f;
+    }
+}
+
+int vcr_launch_sh_grad_from_colors(int P, int D, int M, int world, const float* means3D, const float* slices, long long slice_stride,
+                                   float* dL_dsh, cudaStream_t s) {
+    VcrProfScope prof(VCR_K_PREPROCESS_BWD, s);
+    sh_grad_from_colors_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, D, M, world, means3D, slices, slice_stride, dL_dsh);
+    VCR_LAUNCH_CHECK("sh_grad_from_colors_kernel");
     return 0;
 }

@@ -98,6 +98,67 @@ __global__ void __launch_bounds__(512) multimem_allreduce_kernel(float* __restri
     }
 }
 
+// The same two-shot reduction of up to 8 ranges plus, in the same launch, an all-gather contribution: this rank's slice
+// [bcast_first, +bcast_count) of the symmetric buffer is read locally and multicast to every rank (multimem.st), i.e. S
+// bytes out once and (world-1) x S bytes in per GPU with the replication done by the switch.  Used by the compact SH
+// exchange: all-reduce the 11 non-SH floats per Gaussian, all-gather the 3 colour-gradient floats.
+__global__ void __launch_bounds__(512) multimem_exchange_kernel(float* __restrict__ mc, const float* __restrict__ local,
+                                                                const MmRanges rg, const long long bfirst, const long long bcount,
+                                                                const int rank, const int world) {
+    const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long nthreads = (long long)gridDim.x * blockDim.x;
+    // broadcast part first: plain local loads, stores that the switch replicates
+    {
+        const long long nv = bcount >> 2;
+        const float4* src = reinterpret_cast<const float4*>(local + bfirst);
+        float* dst = mc + bfirst;
+        long long v = tid;
+        for (; v + (MM_UNROLL - 1) * nthreads < nv; v += MM_UNROLL * nthreads) {
+            float4 x[MM_UNROLL];
+#pragma unroll
+            for (int u = 0; u < MM_UNROLL; u++) x[u] = src[v + u * nthreads];
+#pragma unroll
+            for (int u = 0; u < MM_UNROLL; u++) mm_st4(dst + 4 * (v + u * nthreads), x[u]);
+        }
+        for (; v < nv; v += nthreads) mm_st4(dst + 4 * v, src[v]);
+        if (tid == 0) for (long long i = nv << 2; i < bcount; i++) mm_st1(dst + i, local[bfirst + i]);
+    }
+    for (int r = 0; r < rg.n; r++) {
+        const long long f0 = rg.first[r], f1 = f0 + rg.count[r];
+        const long long a = (f0 + 3) & ~3LL, b = f1 & ~3LL;
+        if (b > a) {
+            const long long nv = (b - a) >> 2;
+            const long long v0 = nv * rank / world, v1 = nv * (rank + 1) / world;
+            float* base = mc + a;
+            long long v = v0 + tid;
+            for (; v + (MM_UNROLL - 1) * nthreads < v1; v += MM_UNROLL * nthreads) {
+                float4 x[MM_UNROLL];
+#pragma unroll
+                for (int u = 0; u < MM_UNROLL; u++) x[u] = mm_ld_reduce4(base + 4 * (v + u * nthreads));
+#pragma unroll
+                for (int u = 0; u < MM_UNROLL; u++) mm_st4(base + 4 * (v + u * nthreads), x[u]);
+            }
+            for (; v < v1; v += nthreads) mm_st4(base + 4 * v, mm_ld_reduce4(base + 4 * v));
+        }
+        if (rank == 0 && tid == 0) {
+            const long long he = a < f1 ? a : f1;
+            for (long long i = f0; i < he; i++) mm_st1(mc + i, mm_ld_reduce1(mc + i));
+            for (long long i = (b > he ? b : he); i < f1; i++) mm_st1(mc + i, mm_ld_reduce1(mc + i));
+        }
+    }
+}
+
+int vcr_launch_multimem_exchange(float* mc, const float* local, int n_ranges, const long long* first, const long long* count,
+                                 long long bcast_first, long long bcast_count, int rank, int world, int blocks, cudaStream_t s) {
+    MmRanges rg;
+    rg.n = n_ranges;
+    for (int i = 0; i < VCR_MM_MAX_RANGES; i++) { rg.first[i] = i < n_ranges ? first[i] : 0; rg.count[i] = i < n_ranges ? count[i] : 0; }
+    VcrProfScope prof(VCR_K_MM_ALLREDUCE, s);
+    multimem_exchange_kernel<<<blocks, 512, 0, s>>>(mc, local, rg, bcast_first, bcast_count, rank, world);
+    VCR_LAUNCH_CHECK("multimem_exchange_kernel");
+    return 0;
+}
+
 int vcr_launch_multimem_allreduce(float* mc, int n_ranges, const long long* first, const long long* count, int rank, int world,
                                   int blocks, cudaStream_t s) {
     MmRanges rg;

@@ -151,6 +151,10 @@ class _RasterizeGaussians(torch.autograd.Function):
         # Optional chunk hook (vcr_view_parallel.ViewParallel.overlap_gradients): `means3D._vcr_chunk_hook = (n_chunks, fn)`
         # makes the backward run its per-Gaussian stage in n_chunks launches and call fn(chunk, first, count) after each.
         ctx.chunk_hook = getattr(means3D, "_vcr_chunk_hook", None)
+        # Optional compact SH gradient (vcr_view_parallel.ViewParallel.compact_sh_exchange): `sh._vcr_sh_compact` is a
+        # float32 [P,3] destination for the clamp-masked colour gradient; the backward then does NOT write dL_dsh (the
+        # returned tensor is filled after the exchange by vcr_sh_grad_from_colors).
+        ctx.sh_compact = getattr(sh, "_vcr_sh_compact", None)
         depth, alpha = outmap[3:4], outmap[7:8]
         ctx.save_for_backward(colors_precomp, normals_precomp, semantics_precomp, means3D, scales, rotations, cov3Ds_precomp,
                               radii, sh, geomBuffer, binningBuffer, imgBuffer, alpha, depth, dirs, inside)
@@ -209,8 +213,12 @@ class _RasterizeGaussians(torch.autograd.Function):
                     torch.save(cpu_args, "snapshot_bw.dump")
                     print("\nAn error occured in backward. Writing snapshot_bw.dump for debugging.\n")
                     raise ex
-            elif getattr(ctx, "chunk_hook", None) is not None:
-                n_chunks, hook = ctx.chunk_hook
+            elif getattr(ctx, "chunk_hook", None) is not None or getattr(ctx, "sh_compact", None) is not None:
+                n_chunks, hook = ctx.chunk_hook if getattr(ctx, "chunk_hook", None) is not None else (1, lambda *a: None)
+                compact = getattr(ctx, "sh_compact", None)
+                if compact is not None and not (compact.is_cuda and compact.dtype == torch.float32 and compact.is_contiguous()
+                                                and compact.numel() == 3 * P):
+                    raise RuntimeError("_vcr_sh_compact must be a contiguous float32 CUDA tensor with 3 floats per Gaussian")
                 failure = []
                 def _cb(_user, chunk, first, count):
                     try:
@@ -218,7 +226,8 @@ class _RasterizeGaussians(torch.autograd.Function):
                     except BaseException as ex:      # exceptions cannot cross the C frame; re-raised below
                         failure.append(ex)
                 cb = _n.CHUNK_FN(_cb)
-                _n.check(_n.vcr_rasterize_backward_chunked(*args, int(n_chunks), cb, None), "rasterize_gaussians_backward")
+                _n.check(_n.vcr_rasterize_backward_chunked(*args, int(n_chunks), cb, None, _n.ptr(compact)),
+                         "rasterize_gaussians_backward")
                 if failure:
                     raise failure[0]
             else:

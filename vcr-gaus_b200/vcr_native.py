@@ -58,7 +58,7 @@ vcr_rasterize_backward_chunked = _sig(
     "vcr_rasterize_backward_chunked", c_int,
     [c_int, c_int, c_int, c_int, P_, c_int, c_int, P_, P_, P_, P_, P_, P_, P_, P_, c_float, P_, P_, P_, P_, P_, P_,
      c_float, c_float, P_, P_, P_, P_, P_,
-     P_, P_, P_, P_, P_, P_, P_, P_, P_, P_, P_, P_, P_, c_int, c_void_p, c_int, CHUNK_FN, c_void_p])
+     P_, P_, P_, P_, P_, P_, P_, P_, P_, P_, P_, P_, P_, c_int, c_void_p, c_int, CHUNK_FN, c_void_p, P_])
 
 vcr_multimem_allreduce_sum = _sig("vcr_multimem_allreduce_sum", c_int,
                                   [c_void_p, c_int, POINTER(ctypes.c_longlong), POINTER(ctypes.c_longlong), c_int, c_int, c_int, c_void_p])
@@ -74,6 +74,11 @@ vcr_ssim_backward = _sig("vcr_ssim_backward", c_int, [c_int, c_int, c_int, P_, P
 vcr_adam_step = _sig("vcr_adam_step", c_int,
                      [ctypes.c_longlong, P_, P_, P_, P_, c_int, POINTER(ctypes.c_longlong), POINTER(c_float), c_float, c_float, c_float,
                       c_int, c_float, c_void_p])
+
+vcr_sh_grad_from_colors = _sig("vcr_sh_grad_from_colors", c_int, [c_int, c_int, c_int, c_int, P_, P_, ctypes.c_longlong, P_, c_void_p])
+vcr_multimem_exchange = _sig("vcr_multimem_exchange", c_int,
+                             [c_void_p, P_, c_int, POINTER(ctypes.c_longlong), POINTER(ctypes.c_longlong), ctypes.c_longlong,
+                              ctypes.c_longlong, c_int, c_int, c_int, c_void_p])
 
 vcr_densify_stats_accumulate = _sig("vcr_densify_stats_accumulate", c_int, [c_int, P_, P_, P_, P_, P_, c_void_p])
 
@@ -150,7 +155,7 @@ DECLARED_SYMBOLS = [
     "vcr_knn_scratch_bytes", "vcr_dist2_knn3", "vcr_geom_layout", "vcr_binning_layout", "vcr_image_layout",
     "vcr_knn_noalloc_max_points", "vcr_dist2_knn3_noalloc", "vcr_view_loss_forward", "vcr_view_loss_backward",
     "vcr_profile_enable", "vcr_profile_kernel_count", "vcr_profile_kernel_name", "vcr_profile_read",
-    "vcr_rasterize_backward_chunked", "vcr_densify_stats_accumulate", "vcr_multimem_allreduce_sum", "vcr_prologue_forward", "vcr_prologue_backward", "vcr_ssim_forward", "vcr_ssim_backward", "vcr_adam_step", "vcr_view_loss_total", "vcr_binning_reference_lists",
+    "vcr_rasterize_backward_chunked", "vcr_densify_stats_accumulate", "vcr_multimem_allreduce_sum", "vcr_prologue_forward", "vcr_prologue_backward", "vcr_ssim_forward", "vcr_ssim_backward", "vcr_adam_step", "vcr_view_loss_total", "vcr_binning_reference_lists", "vcr_sh_grad_from_colors", "vcr_multimem_exchange",
 ]
 
 

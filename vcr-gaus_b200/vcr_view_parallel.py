@@ -238,6 +238,72 @@ class ViewParallel:
         self._symm = (t, hdl)
         return t
 
+    # ---- compact exchange of the SH gradient -------------------------------------------------------------------------
+    def exchange_floats(self, tensors: Dict[str, torch.Tensor]) -> int:
+        """Floats of symmetric storage for a bucket of `tensors` plus the all-gather slices of compact_sh_exchange()."""
+        P = tensors["means3D"].shape[0]
+        return (GaussianBucket.numel_for(tensors) + 3) // 4 * 4 + self.world * self._slice_stride(P)
+
+    @staticmethod
+    def _slice_stride(P: int) -> int:
+        return (3 * P + 3 + 3) // 4 * 4          # [3P colour gradients | campos xyz | pad], a multiple of 16 bytes
+
+    def compact_sh_exchange(self, bucket: GaussianBucket, sh_degree: int = 3):
+        """Exchange 3 instead of 48 floats per Gaussian for the SH coefficients.  For ONE view, dL/dSH of a Gaussian is the
+        outer product of its clamp-masked colour gradient with the SH basis of the direction camera -> Gaussian, so it is
+        enough to all-GATHER the colour gradients (and the ranks' camera positions) and let every rank rebuild and sum the
+        outer products itself (vcr_sh_grad_from_colors), in rank order.  The other per-Gaussian gradients (11 floats) are
+        all-reduced as before.  Per GPU and step this moves 44 B + world x 12 B per Gaussian instead of 236 B.
+        After this call the rasterizer's backward no longer writes the SH gradient into the bucket; call
+        exchange_compact(bucket, campos) after the backward in place of allreduce_gradients().  Needs direct=True."""
+        if not bucket.direct:
+            raise ValueError("compact_sh_exchange needs GaussianBucket(direct=True)")
+        P, dev = bucket.P, bucket.grad_flat.device
+        stride = self._slice_stride(P)
+        off0 = (bucket.numel + 3) // 4 * 4
+        t, _ = getattr(self, "_symm", (None, None))
+        if self._in_symmetric_storage(bucket) and t.numel() >= off0 + self.world * stride:
+            flat = t.view(-1)[off0:off0 + self.world * stride]
+            self._compact_off0 = off0
+        else:
+            flat = torch.zeros(self.world * stride, dtype=torch.float32, device=dev)
+            self._compact_off0 = None            # not reachable through the multicast mapping: NCCL only
+        self._slices = flat.view(self.world, stride)
+        self._slices.zero_()
+        self._compact = (P, stride, int(sh_degree))
+        if self.world > 1:
+            bucket.params["shs"]._vcr_sh_compact = self._slices[self.rank, :3 * P].view(P, 3)
+
+    def exchange_compact(self, bucket: GaussianBucket, campos: torch.Tensor, transport: Optional[str] = None):
+        """The gradient exchange of compact_sh_exchange(): all-gather of [colour gradients | campos], all-reduce of the
+        non-SH groups, reconstruction of the summed SH gradient into the bucket.  On the current stream."""
+        if self.world == 1:
+            return
+        import vcr_native as _n
+        P, stride, D = self._compact
+        transport = transport or self.transport
+        own = self._slices[self.rank]
+        own[3 * P:3 * P + 3].copy_(campos.reshape(-1)[:3])
+        ranges = [(off, n) for name, off, n, _ in bucket.layout if name != "shs"]
+        stream = ctypes.c_void_p(torch.cuda.current_stream(bucket.grad_flat.device).cuda_stream)
+        if transport == "multimem" and self._compact_off0 is not None:
+            t, hdl = self._symm
+            arr = ctypes.c_longlong * len(ranges)
+            hdl.barrier(channel=0, timeout_ms=30000)
+            _n.check(_n.vcr_multimem_exchange(ctypes.c_void_p(int(hdl.multicast_ptr)), t.data_ptr(), len(ranges),
+                                              arr(*[a for a, _ in ranges]), arr(*[n for _, n in ranges]),
+                                              self._compact_off0 + self.rank * stride, stride, self.rank, self.world,
+                                              int(os.environ.get("VCR_MM_BLOCKS", "0")), stream), "multimem_exchange")
+            hdl.barrier(channel=0, timeout_ms=30000)
+        else:
+            dist.all_gather_into_tensor(self._slices.view(-1), own, group=self.group)      # in place: own is slice `rank`
+            with dist._coalescing_manager(group=self.group, async_ops=False):
+                for a, n in ranges:
+                    dist.all_reduce(bucket.grad_flat[a:a + n], op=dist.ReduceOp.SUM, group=self.group)
+        name, off, n, shape = next(item for item in bucket.layout if item[0] == "shs")
+        _n.check(_n.vcr_sh_grad_from_colors(P, D, shape[1], self.world, bucket.params["means3D"].data_ptr(), self._slices.data_ptr(),
+                                            stride, bucket.grad_flat[off:off + n].data_ptr(), stream), "sh_grad_from_colors")
+
     def _in_symmetric_storage(self, bucket: GaussianBucket) -> bool:
         t, _ = getattr(self, "_symm", (None, None))
         return t is not None and bucket.grad_flat.data_ptr() == t.data_ptr()
@@ -268,9 +334,15 @@ class ViewParallel:
         if self.world == 1:
             return {}
         dev = bucket.grad_flat.device
-        ways = {"nccl": lambda: dist.all_reduce(bucket.grad_flat, op=dist.ReduceOp.SUM, group=self.group)}
-        if self._in_symmetric_storage(bucket):
-            ways["multimem"] = lambda: self.multimem_allreduce(bucket)
+        if getattr(self, "_compact", None) is not None:      # compact_sh_exchange() is set up: time THAT exchange
+            cam = torch.zeros(3, device=dev)
+            ways = {"nccl": lambda: self.exchange_compact(bucket, cam, transport="nccl")}
+            if self._compact_off0 is not None:
+                ways["multimem"] = lambda: self.exchange_compact(bucket, cam, transport="multimem")
+        else:
+            ways = {"nccl": lambda: dist.all_reduce(bucket.grad_flat, op=dist.ReduceOp.SUM, group=self.group)}
+            if self._in_symmetric_storage(bucket):
+                ways["multimem"] = lambda: self.multimem_allreduce(bucket)
         ms = {}
         for name, fn in ways.items():
             bucket.grad_flat.zero_()
