@@ -346,14 +346,14 @@ __global__ void __launch_bounds__(256) sh_grad_from_colors_kernel(const int P, c
                                                                   const float* __restrict__ means3D, const float* __restrict__ slices,
                                                                   const long long slice_stride, float* __restrict__ dL_dsh) {
     const int idx = blockIdx.x * 256 + threadIdx.x;
-    if (idx >= P) return;
-    const size_t i = (size_t)idx;
+    const bool live = idx < P;
+    const size_t i = (size_t)(live ? idx : 0);
     const float3 mean = make_float3(__ldg(means3D + 3 * i), __ldg(means3D + 3 * i + 1), __ldg(means3D + 3 * i + 2));
     float acc[48];
 #pragma unroll
     for (int k = 0; k < 48; k++) acc[k] = 0.f;
     const int nact = min((D + 1) * (D + 1), 16);
-    for (int r = 0; r < world; r++) {
+    for (int r = 0; r < (live ? world : 0); r++) {
         const float* sl = slices + (size_t)r * slice_stride;
         const float g0 = __ldg(sl + 3 * i), g1 = __ldg(sl + 3 * i + 1), g2 = __ldg(sl + 3 * i + 2);
         if (g0 == 0.f && g1 == 0.f && g2 == 0.f) continue;              // not rendered / fully clamped on that rank
@@ -368,12 +368,26 @@ __global__ void __launch_bounds__(256) sh_grad_from_colors_kernel(const int P, c
             acc[3 * k] += bk * g0; acc[3 * k + 1] += bk * g1; acc[3 * k + 2] += bk * g2;
         }
     }
-    float* out = dL_dsh + i * 3 * (size_t)M;
     if (M == 16) {
-        float4* o4 = reinterpret_cast<float4*>(out);
+        // coalesced store of the block's [256][48] tile through shared memory, in two halves of 24 floats per Gaussian
+        // (row stride 25: conflict-free per-thread rows); 96-byte runs per Gaussian and half, i.e. whole sectors
+        __shared__ float s_t[256 * 25];
+        const size_t tile0 = (size_t)blockIdx.x * 256;
+        const int n_g = min(256, P - (int)tile0);
 #pragma unroll
-        for (int q = 0; q < 12; q++) o4[q] = make_float4(acc[4 * q], acc[4 * q + 1], acc[4 * q + 2], acc[4 * q + 3]);
-    } else {
+        for (int h = 0; h < 2; h++) {
+            __syncthreads();
+#pragma unroll
+            for (int e = 0; e < 24; e++) s_t[threadIdx.x * 25 + e] = acc[24 * h + e];
+            __syncthreads();
+            for (int q = threadIdx.x; q < n_g * 6; q += 256) {
+                const int gi = q / 6, f4 = q - gi * 6;
+                const float* src = s_t + gi * 25 + 4 * f4;
+                reinterpret_cast<float4*>(dL_dsh + (tile0 + gi) * 48 + 24 * h)[f4] = make_float4(src[0], src[1], src[2], src[3]);
+            }
+        }
+    } else if (live) {
+        float* out = dL_dsh + i * 3 * (size_t)M;
 #pragma unroll
         for (int e = 0; e < 48; e++) if (e < 3 * M) out[e] = acc[e];
         for (int e = 48; e < 3 * M; e++) out[e] = 0.f;
