@@ -833,7 +833,7 @@ def kernel_table(kern, st, args, hbm_peak):
         "preprocess_kernel": 336 * Pv + 20 * (P - Pv),
         "scan_block_sums_kernel": 8 * ((P + 255) // 256),
         "duplicate_kernel": 20 * P + 12 * R,
-        "radix_pass_kernel": 24 * R,
+        "radix_pass_kernel": (4 * 24 * P + 2 * 24 * R) / 6.0,      # per launch: 4 passes over the P depth keys, 2 over the R instances
         "tile_ranges_kernel": 8 * R + 8 * tiles,
         "render_forward_kernel": 41 * R + 60 * N,
         "render_backward_kernel": 77 * R + 68 * N + 84 * Pv,

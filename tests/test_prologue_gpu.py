@@ -158,4 +158,4 @@ def test_prologue_writes_gradients_into_a_direct_bucket():
     run(plain)
     for k, off, n, shape in bucket.layout:
         a, b = bucket.grad_flat[off:off + n].view(shape).double(), plain[k].grad.double()
-        assert float((a - b).norm() / b.norm().clamp_min(1e-30)) <= 1e-5, k
+        assert float((a - b).norm() / b.norm().clamp_min(1e-30)) <= 5e-5, k   # two runs of the float-atomic backward

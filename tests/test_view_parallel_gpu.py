@@ -45,8 +45,8 @@ def test_chunked_backward_equals_single_launch():
     for name, off, n, shape in bucket.layout:
         got = bucket.grad_flat[off:off + n].view(shape).cpu().numpy()
         # two runs of the compositing backward differ by float-atomic ordering only
-        assert rel_l2(got, ref[names[name]]) <= 1e-5, name
-    assert rel_l2(normals.grad.cpu().numpy(), ref["dL_dnormals"]) <= 1e-5
+        assert rel_l2(got, ref[names[name]]) <= 5e-5, name
+    assert rel_l2(normals.grad.cpu().numpy(), ref["dL_dnormals"]) <= 5e-5
 
 
 def test_chunk_hook_exception_surfaces():
@@ -155,6 +155,6 @@ def test_compact_sh_gradient_reconstruction(deg):
                                       ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)), "sh_grad_from_colors")
     torch.cuda.synchronize()
     assert torch.isfinite(rebuilt).all()
-    assert rel_l2(rebuilt.cpu().numpy(), ref["dL_dsh"]) <= 1e-5
+    assert rel_l2(rebuilt.cpu().numpy(), ref["dL_dsh"]) <= 5e-5    # two runs of the float-atomic backward (gate: 1e-3)
     for k, name in (("means3D", "dL_dmeans3D"), ("opacities", "dL_dopacity"), ("scales", "dL_dscales"), ("rotations", "dL_drotations")):
-        assert rel_l2(leaves[k].grad.cpu().numpy(), ref[name]) <= 1e-5, k
+        assert rel_l2(leaves[k].grad.cpu().numpy(), ref[name]) <= 5e-5, k
