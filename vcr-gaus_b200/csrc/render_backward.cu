@@ -30,6 +30,7 @@ template <bool HAS_DIRS>
 struct RbStage {                     // one staging buffer (24 KB with intersection depth, 20 KB without)
     StagedGeoB geo[RB_BATCH];
     float4 box[RB_BATCH];            // conservative footprint box {xlo, xhi, ylo, yhi}
+    float2 ex[RB_BATCH];             // exact strip test: { -(tau + slack), 1 / conic.x }  (vcr_alpha_rowtest)
     float4 nrm[RB_BATCH];            // normal.xyz, semantics[0]
     float4 col[RB_BATCH];            // rgb, semantics[1]
     float4 xv[HAS_DIRS ? RB_BATCH : 1];  // view-space position (intersection mode)
@@ -157,6 +158,7 @@ __global__ void __launch_bounds__(256) render_backward_kernel(
         StagedGeoB sg;
         sg.x = xy.x; sg.y = xy.y; sg.ca = co.x; sg.cb = co.y; sg.cc = co.z; sg.op = co.w;
         st.box[tid] = vcr_alpha_bbox(xy, co);
+        st.ex[tid] = vcr_alpha_rowtest(co);
         if (HAS_DIRS) {
             const float3 xv = make_float3(__ldg(xyz_view + 3 * (size_t)id), __ldg(xyz_view + 3 * (size_t)id + 1),
                                           __ldg(xyz_view + 3 * (size_t)id + 2));
@@ -189,8 +191,12 @@ __global__ void __launch_bounds__(256) render_backward_kernel(
             if (k * 32 >= cnt) break;
             const int jj = k * 32 + lane;
             const float4 bx = st.box[jj];
-            const bool hit = jj < cnt && (uint32_t)(first_pos - jj) < warp_last && bx.x <= strip_x1 && bx.y >= strip_x0 &&
-                             bx.z <= strip_y1 && bx.w >= strip_y0;
+            bool hit = jj < cnt && (uint32_t)(first_pos - jj) < warp_last && bx.x <= strip_x1 && bx.y >= strip_x0 &&
+                       bx.z <= strip_y1 && bx.w >= strip_y0;
+            if (hit) {
+                const float4 gq = *reinterpret_cast<const float4*>(&st.geo[jj]);        // x, y, ca, cb
+                hit = vcr_strip_may_contribute(gq.x, gq.y, gq.z, gq.w, st.geo[jj].cc, st.ex[jj], strip_x0, strip_x1, strip_y0);
+            }
             uint32_t m = __ballot_sync(0xffffffffu, hit);
             while (m) {
                 const int j = k * 32 + __ffs(m) - 1;

@@ -31,6 +31,7 @@ template <int MODE>
 struct RfStage {                       // one staging buffer
     StagedGeo geo[RF_BATCH];
     float4 box[RF_BATCH];              // conservative {xlo, xhi, ylo, yhi} of the alpha >= 1/255 footprint
+    float2 ex[RF_BATCH];               // exact strip test: { -(tau + slack), 1 / conic.x }  (vcr_alpha_rowtest)
     float4 nrm[MODE == 0 ? RF_BATCH : 1];                              // normal.xyz, semantics[0]
     float4 col[MODE != VCR_MODE_VISI_ACC ? RF_BATCH : 1];              // rgb, semantics[1]
 };
@@ -77,6 +78,7 @@ __global__ void __launch_bounds__(256, 4) render_forward_kernel(
         StagedGeo sg;
         sg.x = xy.x; sg.y = xy.y; sg.ca = co.x; sg.cb = co.y; sg.cc = co.z; sg.op = co.w;
         st.box[tid] = vcr_alpha_bbox(xy, co);
+        st.ex[tid] = vcr_alpha_rowtest(co);
         uint32_t ins = 1u;
         float o0 = 0.f, o1 = 0.f;
         if (MODE == 0) {
@@ -123,7 +125,11 @@ __global__ void __launch_bounds__(256, 4) render_forward_kernel(
             if (k * 32 >= cnt) break;
             const int jj = k * 32 + lane;
             const float4 bx = st.box[jj];
-            const bool hit = jj < cnt && bx.x <= strip_x1 && bx.y >= strip_x0 && bx.z <= strip_y1 && bx.w >= strip_y0;
+            bool hit = jj < cnt && bx.x <= strip_x1 && bx.y >= strip_x0 && bx.z <= strip_y1 && bx.w >= strip_y0;
+            if (hit) {
+                const float4 gq = *reinterpret_cast<const float4*>(&st.geo[jj]);        // x, y, ca, cb
+                hit = vcr_strip_may_contribute(gq.x, gq.y, gq.z, gq.w, st.geo[jj].cc, st.ex[jj], strip_x0, strip_x1, strip_y0);
+            }
             uint32_t m = __ballot_sync(0xffffffffu, hit);
             while (m) {
                 // m is warp-uniform, so every lane passes here once per candidate: a safe place to vote
