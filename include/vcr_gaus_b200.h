@@ -121,11 +121,11 @@ int vcr_rasterize_backward(
     float* dL_dmean2D,           /* f32[P,3] */
     float* dL_dmean2D_densify,   /* f32[P,3] */
     float* dL_dopacity,          /* f32[P,1] */
-    float* dL_dcolor,            /* f32[P,3] */
+    float* dL_dcolor,            /* f32[P,3]; may be NULL when colors_precomp is NULL */
     float* dL_dnormal,           /* f32[P,3] */
-    float* dL_dobjects,          /* f32[P,2] */
+    float* dL_dobjects,          /* f32[P,2]; may be NULL when sh_objs is NULL */
     float* dL_dmean3D,           /* f32[P,3] */
-    float* dL_dcov3D,            /* f32[P,6] */
+    float* dL_dcov3D,            /* f32[P,6]; may be NULL when cov3D_precomp is NULL */
     float* dL_dsh,               /* f32[P,M,3] (may be NULL when M == 0) */
     float* dL_dscale,            /* f32[P,3] */
     float* dL_drot,              /* f32[P,4] */

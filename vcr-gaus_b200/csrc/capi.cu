@@ -253,8 +253,11 @@ int vcr_rasterize_backward_chunked(int P, int D, int M, int R, const float* back
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
     if (P <= 0) { vcr_set_error("P must be positive"); return 1; }
     if (!geom_buffer || !binning_buffer || !img_buffer || !scratch) { vcr_set_error("NULL state/scratch buffer"); return 1; }
-    if (!dL_dpix || !dL_dmean2D || !dL_dmean2D_densify || !dL_dopacity || !dL_dcolor || !dL_dnormal || !dL_dobjects ||
-        !dL_dmean3D || !dL_dcov3D || !dL_dscale || !dL_drot || (M > 0 && shs && !dL_dsh && !dL_dcolor_masked)) {
+    // dL_dcolor / dL_dobjects / dL_dcov3D may be NULL: they are the gradients of optional INPUTS (colors_precomp, sh_objs,
+    // cov3D_precomp); a caller that did not pass the input has no use for the array and saves its 44 B per Gaussian of writes
+    if (!dL_dpix || !dL_dmean2D || !dL_dmean2D_densify || !dL_dopacity || !dL_dnormal ||
+        !dL_dmean3D || !dL_dscale || !dL_drot || (colors_precomp && !dL_dcolor) || (sh_objs && !dL_dobjects) ||
+        (cov3D_precomp && !dL_dcov3D) || (M > 0 && shs && !dL_dsh && !dL_dcolor_masked)) {
         vcr_set_error("NULL gradient output");
         return 1;
     }

@@ -41,13 +41,14 @@ __device__ __forceinline__ void preprocess_backward_body(const BwdParams& p, con
     if (!(p.radii[idx] > 0)) {
 #pragma unroll
         for (int k = 0; k < 3; k++) {
-            p.dL_dmean2D[3 * i + k] = 0.f; p.dL_dmean2D_densify[3 * i + k] = 0.f; p.dL_dcolor[3 * i + k] = 0.f;
+            p.dL_dmean2D[3 * i + k] = 0.f; p.dL_dmean2D_densify[3 * i + k] = 0.f;
+            if (p.dL_dcolor) p.dL_dcolor[3 * i + k] = 0.f;
             p.dL_dnormal[3 * i + k] = 0.f; p.dL_dmean3D[3 * i + k] = 0.f; p.dL_dscale[3 * i + k] = 0.f;
         }
         p.dL_dopacity[i] = 0.f;
-        p.dL_dobjects[2 * i] = 0.f; p.dL_dobjects[2 * i + 1] = 0.f;
+        if (p.dL_dobjects) { p.dL_dobjects[2 * i] = 0.f; p.dL_dobjects[2 * i + 1] = 0.f; }
 #pragma unroll
-        for (int k = 0; k < 6; k++) p.dL_dcov3D[6 * i + k] = 0.f;
+        for (int k = 0; k < 6; k++) if (p.dL_dcov3D) p.dL_dcov3D[6 * i + k] = 0.f;
 #pragma unroll
         for (int k = 0; k < 4; k++) p.dL_drot[4 * i + k] = 0.f;
         if (p.dL_dcolor_masked) { p.dL_dcolor_masked[3 * i] = 0.f; p.dL_dcolor_masked[3 * i + 1] = 0.f; p.dL_dcolor_masked[3 * i + 2] = 0.f; }
@@ -75,8 +76,8 @@ __device__ __forceinline__ void preprocess_backward_body(const BwdParams& p, con
     p.dL_dmean2D_densify[3 * i + 2] = 0.f;
     p.dL_dopacity[i] = a[ACC_M0];
 #pragma unroll
-    for (int k = 0; k < 3; k++) { p.dL_dcolor[3 * i + k] = a[ACC_COLOR_R + k]; p.dL_dnormal[3 * i + k] = a[ACC_NORMAL_X + k]; }
-    p.dL_dobjects[2 * i] = a[ACC_OBJ_0]; p.dL_dobjects[2 * i + 1] = a[ACC_OBJ_1];
+    for (int k = 0; k < 3; k++) { if (p.dL_dcolor) p.dL_dcolor[3 * i + k] = a[ACC_COLOR_R + k]; p.dL_dnormal[3 * i + k] = a[ACC_NORMAL_X + k]; }
+    if (p.dL_dobjects) { p.dL_dobjects[2 * i] = a[ACC_OBJ_0]; p.dL_dobjects[2 * i + 1] = a[ACC_OBJ_1]; }
     const float gcx = -0.5f * co.w * a[ACC_MXX], gcy = -0.5f * co.w * a[ACC_MXY], gcz = -0.5f * co.w * a[ACC_MYY];
 
     const float3 mean = make_float3(__ldg(p.means3D + 3 * i), __ldg(p.means3D + 3 * i + 1), __ldg(p.means3D + 3 * i + 2));
@@ -131,7 +132,7 @@ __device__ __forceinline__ void preprocess_backward_body(const BwdParams& p, con
         for (int k = 0; k < 6; k++) gcov[k] = 0.f;
     }
 #pragma unroll
-    for (int k = 0; k < 6; k++) p.dL_dcov3D[6 * i + k] = gcov[k];
+    for (int k = 0; k < 6; k++) if (p.dL_dcov3D) p.dL_dcov3D[6 * i + k] = gcov[k];
     float dL_dT0[3], dL_dT1[3];
 #pragma unroll
     for (int k = 0; k < 3; k++) {

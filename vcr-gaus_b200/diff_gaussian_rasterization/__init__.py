@@ -179,12 +179,13 @@ class _RasterizeGaussians(torch.autograd.Function):
 
         g_means2D = torch.empty((P, 3), **f)
         g_means2D_densify = torch.empty((P, 3), **f)
-        g_colors = torch.empty((P, NUM_CHANNELS), **f)
+        # gradients of optional inputs are only produced when the input was given (the library skips the writes otherwise)
+        g_colors = torch.empty((P, NUM_CHANNELS), **f) if colors_precomp.numel() != 0 else None
         g_normals = torch.empty((P, 3), **f)
-        g_objects = torch.empty((P, NUM_OBJECTS), **f)
+        g_objects = torch.empty((P, NUM_OBJECTS), **f) if semantics_precomp.numel() != 0 else None
         g_opacity = dest(2, (P, 1))
         g_means3D = dest(0, (P, 3))
-        g_cov3D = torch.empty((P, 6), **f)
+        g_cov3D = torch.empty((P, 6), **f) if cov3Ds_precomp.numel() != 0 else None
         g_sh = dest(1, (P, M, 3))
         g_scales = dest(3, (P, 3))
         g_rot = dest(4, (P, 4))
@@ -199,8 +200,8 @@ class _RasterizeGaussians(torch.autograd.Function):
                     _n.ptr(_f32c(rotations)), _n.ptr(_f32c(cov3Ds_precomp)), _n.ptr(view), _n.ptr(proj), _n.ptr(_f32c(dirs)),
                     _n.ptr(campos), float(rs.tanfovx), float(rs.tanfovy), radii.data_ptr(), geomBuffer.data_ptr(),
                     binningBuffer.data_ptr(), imgBuffer.data_ptr(), grad_c.data_ptr(), g_means2D.data_ptr(),
-                    g_means2D_densify.data_ptr(), g_opacity.data_ptr(), g_colors.data_ptr(), g_normals.data_ptr(),
-                    g_objects.data_ptr(), g_means3D.data_ptr(), g_cov3D.data_ptr(), _n.ptr(g_sh), g_scales.data_ptr(),
+                    g_means2D_densify.data_ptr(), g_opacity.data_ptr(), _n.ptr(g_colors), g_normals.data_ptr(),
+                    _n.ptr(g_objects), g_means3D.data_ptr(), _n.ptr(g_cov3D), _n.ptr(g_sh), g_scales.data_ptr(),
                     g_rot.data_ptr(), inside.contiguous().data_ptr(), scratch.data_ptr(), int(bool(rs.debug)), _stream())
             if rs.debug:
                 cpu_args = cpu_deep_copy_tuple((rs.bg, means3D, radii, colors_precomp, normals_precomp, semantics_precomp, scales,
@@ -235,11 +236,12 @@ class _RasterizeGaussians(torch.autograd.Function):
         else:
             for t in (g_means2D, g_means2D_densify, g_colors, g_normals, g_objects, g_opacity, g_means3D, g_cov3D, g_sh,
                       g_scales, g_rot):
-                t.zero_()
+                if t is not None:
+                    t.zero_()
 
         def match(g, ref):
             # inputs that were absent (zero-sized placeholders) get no gradient
-            return g if ref.numel() != 0 else None
+            return g if (g is not None and ref.numel() != 0) else None
 
         need = ctx.needs_input_grad      # means2D / means2D_densify may have been passed as None
         return (g_means3D, g_means2D if need[1] else None, g_means2D_densify if need[2] else None, match(g_sh, sh), match(g_colors, colors_precomp),
