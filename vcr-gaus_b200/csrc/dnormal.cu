@@ -125,43 +125,66 @@ __device__ __forceinline__ float3 dn_grad_c(const DnParams& p, int u, int v, flo
     return make_float3(dn.x * inv, dn.y * inv, dn.z * inv);
 }
 
+// Tile of VL_TW x VL_TH pixels per 256-thread block (two rows per thread).  The backward is a 5-point gather: the depth
+// gradient of a pixel collects cross(dy, gc) from its left/right neighbours and cross(gc, dx) from its upper/lower ones,
+// where gc = dL/d(cross product) of THAT neighbour.  gc costs four depth loads, the ground-truth and rendered normals, a
+// square root, a division and an exp, so it is evaluated once per pixel of the tile + a one-pixel halo into shared memory
+// (1.2 evaluations per output) instead of once per (pixel, neighbour) pair (4-5 per output).
+#define VL_TW 32
+#define VL_TH 16
 __global__ void __launch_bounds__(256) dnormal_backward_kernel(const DnParams p, const float* __restrict__ sums,
                                                                const float* __restrict__ dL_dloss,
                                                                const float* __restrict__ dL_dest, float* __restrict__ dL_ddepth) {
-    const int u = blockIdx.x * 32 + (threadIdx.x & 31);
-    const int v = blockIdx.y * 8 + (threadIdx.x >> 5);
-    if (u >= p.W || v >= p.H) return;
+    constexpr int HWD = VL_TW + 2, HHT = VL_TH + 2;
+    __shared__ float s_tx[3][HHT][HWD];      // dL/ddx(q) = dy(q) x gc(q) at the halo tile
+    __shared__ float s_ty[3][HHT][HWD];      // dL/ddy(q) = gc(q) x dx(q)
     const float cnt = __ldg(sums + 2);
     const float scale = cnt > 0.f ? __ldg(dL_dloss) / cnt : 0.f;
-    float3 gX = make_float3(0.f, 0.f, 0.f);
-    // contributions through dx(q): q = (u-1,v) [+s], q = (u+1,v) [-s], q = (u,v) at a border [-1 / +1]
-    // dL/ddx(q) = dy(q) x gc(q);  dL/ddy(q) = gc(q) x dx(q)
-    auto via_dx = [&](int qu, float coef) {
-        float3 dx, dy;
-        const float3 gc = dn_grad_c(p, qu, v, scale, dL_dest, dx, dy);
-        const float3 t = cross3(dy, gc);
-        gX.x += coef * t.x; gX.y += coef * t.y; gX.z += coef * t.z;
-    };
-    auto via_dy = [&](int qv, float coef) {
-        float3 dx, dy;
-        const float3 gc = dn_grad_c(p, u, qv, scale, dL_dest, dx, dy);
-        const float3 t = cross3(gc, dx);
-        gX.x += coef * t.x; gX.y += coef * t.y; gX.z += coef * t.z;
-    };
-    if (p.W > 1) {
-        if (u > 0) { const int q = u - 1; via_dx(q, (q > 0) ? 0.5f : 1.0f); }               // X(p) is the upper sample of q
-        if (u < p.W - 1) { const int q = u + 1; via_dx(q, (q < p.W - 1) ? -0.5f : -1.0f); } // X(p) is the lower sample of q
-        if (u == 0) via_dx(0, -1.0f);
-        if (u == p.W - 1) via_dx(u, 1.0f);
+    const int u_base = blockIdx.x * VL_TW, v_base = blockIdx.y * VL_TH;
+    for (int idx = threadIdx.x; idx < HWD * HHT; idx += 256) {
+        const int ly = idx / HWD, lx = idx - ly * HWD;
+        const int qu = u_base + lx - 1, qv = v_base + ly - 1;
+        float3 tx = make_float3(0.f, 0.f, 0.f), ty = tx;
+        if (qu >= 0 && qu < p.W && qv >= 0 && qv < p.H) {
+            float3 dx, dy;
+            const float3 gc = dn_grad_c(p, qu, qv, scale, dL_dest, dx, dy);
+            tx = cross3(dy, gc);
+            ty = cross3(gc, dx);
+        }
+        s_tx[0][ly][lx] = tx.x; s_tx[1][ly][lx] = tx.y; s_tx[2][ly][lx] = tx.z;
+        s_ty[0][ly][lx] = ty.x; s_ty[1][ly][lx] = ty.y; s_ty[2][ly][lx] = ty.z;
     }
-    if (p.H > 1) {
-        if (v > 0) { const int q = v - 1; via_dy(q, (q > 0) ? 0.5f : 1.0f); }
-        if (v < p.H - 1) { const int q = v + 1; via_dy(q, (q < p.H - 1) ? -0.5f : -1.0f); }
-        if (v == 0) via_dy(0, -1.0f);
-        if (v == p.H - 1) via_dy(v, 1.0f);
+    __syncthreads();
+#pragma unroll
+    for (int half = 0; half < 2; half++) {
+        const int lx = threadIdx.x & 31, ly = (threadIdx.x >> 5) + 8 * half;
+        const int u = u_base + lx, v = v_base + ly;
+        if (u >= p.W || v >= p.H) continue;
+        float3 gX = make_float3(0.f, 0.f, 0.f);
+        // contributions through dx(q): q = (u-1,v) [+s], q = (u+1,v) [-s], q = (u,v) at a border [-1 / +1]
+        auto via_dx = [&](int qu, float coef) {
+            const int hx = qu - u_base + 1, hy = ly + 1;
+            gX.x += coef * s_tx[0][hy][hx]; gX.y += coef * s_tx[1][hy][hx]; gX.z += coef * s_tx[2][hy][hx];
+        };
+        auto via_dy = [&](int qv, float coef) {
+            const int hx = lx + 1, hy = qv - v_base + 1;
+            gX.x += coef * s_ty[0][hy][hx]; gX.y += coef * s_ty[1][hy][hx]; gX.z += coef * s_ty[2][hy][hx];
+        };
+        if (p.W > 1) {
+            if (u > 0) { const int q = u - 1; via_dx(q, (q > 0) ? 0.5f : 1.0f); }               // X(p) is the upper sample of q
+            if (u < p.W - 1) { const int q = u + 1; via_dx(q, (q < p.W - 1) ? -0.5f : -1.0f); } // X(p) is the lower sample of q
+            if (u == 0) via_dx(0, -1.0f);
+            if (u == p.W - 1) via_dx(u, 1.0f);
+        }
+        if (p.H > 1) {
+            if (v > 0) { const int q = v - 1; via_dy(q, (q > 0) ? 0.5f : 1.0f); }
+            if (v < p.H - 1) { const int q = v + 1; via_dy(q, (q < p.H - 1) ? -0.5f : -1.0f); }
+            if (v == 0) via_dy(0, -1.0f);
+            if (v == p.H - 1) via_dy(v, 1.0f);
+        }
+        const float ax = ((u + 0.5f) - p.cx) * p.inv_fx, ay = ((v + 0.5f) - p.cy) * p.inv_fy;
+        dL_ddepth[(size_t)v * p.W + u] = gX.x * ax + gX.y * ay + gX.z;
     }
-    const float ax = ((u + 0.5f) - p.cx) * p.inv_fx, ay = ((v + 0.5f) - p.cy) * p.inv_fy;
-    dL_ddepth[(size_t)v * p.W + u] = gX.x * ax + gX.y * ay + gX.z;
 }
 
 // ------------------------------------------------------------------------------------------------------------------
@@ -216,13 +239,7 @@ __global__ void __launch_bounds__(256) view_loss_forward_kernel(const DnParams p
     }
 }
 
-// Tile of VL_TW x VL_TH pixels per 256-thread block (two rows per thread).  The D-Normal part is a 5-point gather: the depth
-// gradient of a pixel collects cross(dy, gc) from its left/right neighbours and cross(gc, dx) from its upper/lower ones,
-// where gc = dL/d(cross product) of THAT neighbour.  gc costs four depth loads, the ground-truth and rendered normals, a
-// square root, a division and an exp, so it is evaluated once per pixel of the tile + a one-pixel halo into shared memory
-// (1.2 evaluations per output) instead of once per (pixel, neighbour) pair (4-5 per output).
-#define VL_TW 32
-#define VL_TH 16
+// Same halo-tile scheme as dnormal_backward_kernel (VL_TW x VL_TH pixels per block) for the D-Normal part.
 __global__ void __launch_bounds__(256) view_loss_backward_kernel(const DnParams p, const float* __restrict__ out,
                                                                  const float* __restrict__ gt_image, const float* __restrict__ sums,
                                                                  const float* __restrict__ dL_dloss, float w_l1, float w_mono,
@@ -382,7 +399,7 @@ int vcr_dnormal_backward(const float* depth, const float* gt_normal, const float
     if (!depth || !gt_normal || !sums || !dL_dloss || !dL_ddepth || width <= 0 || height <= 0) { vcr_set_error("dnormal_backward: bad argument"); return 1; }
     if (exp_t > 0.f && !render_normal) { vcr_set_error("dnormal_backward: render_normal is required when exp_t > 0"); return 1; }
     DnParams p{depth, gt_normal, render_normal, mask, width, height, 1.0f / fx, 1.0f / fy, cx, cy, exp_t, mask_depth_max, 3, 1};
-    const dim3 grid((width + 31) / 32, (height + 7) / 8);
+    const dim3 grid((width + VL_TW - 1) / VL_TW, (height + VL_TH - 1) / VL_TH);
     VcrProfScope prof(VCR_K_DNORMAL_BWD, s);
     dnormal_backward_kernel<<<grid, 256, 0, s>>>(p, sums, dL_dloss, dL_dest_normal, dL_ddepth);
     VCR_LAUNCH_CHECK("dnormal_backward_kernel");
