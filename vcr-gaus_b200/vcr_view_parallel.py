@@ -258,6 +258,9 @@ class ViewParallel:
         exchange_compact(bucket, campos) after the backward in place of allreduce_gradients().  Needs direct=True."""
         if not bucket.direct:
             raise ValueError("compact_sh_exchange needs GaussianBucket(direct=True)")
+        if "shs" not in bucket.params or "means3D" not in bucket.params:
+            raise ValueError("compact_sh_exchange needs a bucket of the rasterizer's inputs (means3D, shs, ...): the rank-one "
+                             "structure belongs to the gradient of the `shs` tensor the rasterizer is called with")
         P, dev = bucket.P, bucket.grad_flat.device
         stride = self._slice_stride(P)
         off0 = (bucket.numel + 3) // 4 * 4
