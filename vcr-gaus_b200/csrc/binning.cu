@@ -21,39 +21,37 @@
 __global__ void __launch_bounds__(1024) scan_block_sums_kernel(uint32_t* __restrict__ block_sums, int nb,
                                                                uint32_t* __restrict__ num_rendered) {
     __shared__ uint32_t warp_tot[32];
-    __shared__ uint32_t carry_s;
     const int t = threadIdx.x, lane = t & 31, w = t >> 5;
-    if (t == 0) carry_s = 0;
+    // every thread owns `ipt` consecutive entries: one block-wide scan of the per-thread totals instead of one per 1024 entries
+    const int ipt = (nb + 1023) / 1024;
+    const int first = t * ipt, last = min(first + ipt, nb);
+    uint32_t v = 0;
+    for (int i = first; i < last; i++) v += block_sums[i];
+    uint32_t inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t n = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += n;
+    }
+    if (lane == 31) warp_tot[w] = inc;
     __syncthreads();
-    for (int base = 0; base < nb; base += 1024) {
-        const int i = base + t;
-        const uint32_t v = i < nb ? block_sums[i] : 0u;
-        uint32_t inc = v;
+    if (w == 0) {
+        uint32_t x = warp_tot[lane];
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
-            const uint32_t n = __shfl_up_sync(0xffffffffu, inc, o);
-            if (lane >= o) inc += n;
+            const uint32_t n = __shfl_up_sync(0xffffffffu, x, o);
+            if (lane >= o) x += n;
         }
-        if (lane == 31) warp_tot[w] = inc;
-        __syncthreads();
-        if (w == 0) {
-            uint32_t x = warp_tot[lane];
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const uint32_t n = __shfl_up_sync(0xffffffffu, x, o);
-                if (lane >= o) x += n;
-            }
-            warp_tot[lane] = x;  // inclusive over warps
-        }
-        __syncthreads();
-        const uint32_t carry = carry_s;
-        const uint32_t warp_excl = w ? warp_tot[w - 1] : 0u;
-        if (i < nb) block_sums[i] = carry + warp_excl + inc - v;
-        __syncthreads();
-        if (t == 1023) carry_s = carry + warp_excl + inc;
-        __syncthreads();
+        warp_tot[lane] = x;  // inclusive over warps
     }
-    if (t == 0) num_rendered[0] = carry_s;
+    __syncthreads();
+    uint32_t run = (w ? warp_tot[w - 1] : 0u) + inc - v;     // exclusive prefix of this thread's first entry
+    for (int i = first; i < last; i++) {
+        const uint32_t c = block_sums[i];
+        block_sums[i] = run;
+        run += c;
+    }
+    if (t == 1023) num_rendered[0] = warp_tot[31];
 }
 
 int vcr_launch_scan_block_sums(int P, GeomState& g, cudaStream_t s) {
