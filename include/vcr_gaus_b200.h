@@ -61,8 +61,9 @@ size_t vcr_binning_bytes(int num_rendered);
 
 /* Full forward pass of one view.  On success *num_rendered_host receives R (the number of
  * (Gaussian, tile) instances).  out_color is f32[10,H,W] and radii is i32[P]; both are fully
- * written (no pre-zeroing needed).  One host synchronisation on `stream` happens inside (to learn
- * R before sizing the binning buffer), as in the reference (rasterizer_impl.cu:287). */
+ * written (no pre-zeroing needed).  The host waits once inside (to learn R before sizing the binning
+ * buffer, as in the reference, rasterizer_impl.cu:287) — on an event recorded after the copy of R, while
+ * work already queued behind it on `stream` keeps running. */
 int vcr_rasterize_forward(
     vcr_alloc_fn geometry_buffer, vcr_alloc_fn binning_buffer, vcr_alloc_fn image_buffer, void* alloc_user,
     int P, int D, int M,

@@ -1,17 +1,21 @@
-// binning.cu — Gaussian -> tile instance lists: prefix sum, key duplication, stable LSD radix sort on
-// (tile | depth) keys, per-tile ranges.  All hand-written (no CUB/thrust).
+// binning.cu — Gaussian -> tile instance lists: prefix sums, depth sort of the Gaussians, instance emission in depth order,
+// stable LSD radix sort by tile id, per-tile ranges, tile schedule.  All hand-written (no CUB/thrust).
 //
 // Replaces, in the reference (DGR/cuda_rasterizer/rasterizer_impl.cu):
-//   cub::DeviceScan::InclusiveSum            :283      -> preprocess block sums + scan_block_sums_kernel
-//                                                         + the in-block scan inside duplicate_kernel
-//   duplicateWithKeys                        :70-111   -> duplicate_kernel (block-cooperative, coalesced)
-//   cub::DeviceRadixSort::SortPairs          :309-314  -> radix_pass_kernel (one launch per 8-bit digit,
-//                                                         decoupled look-back, warp-match ranking)
-//   cudaMemset + identifyTileRanges          :316-323  -> tile_ranges_kernel
+//   cub::DeviceScan::InclusiveSum            :283      -> preprocess block sums + scan_block_sums_kernel (-> R), then
+//                                                         sorted_block_sums_kernel + scan for the depth-ordered emission
+//   duplicateWithKeys                        :70-111   -> duplicate_sorted_kernel (block-cooperative, coalesced; emits in
+//                                                         depth order).  duplicate_kernel = the reference's index order,
+//                                                         used by the parity view only
+//   cub::DeviceRadixSort::SortPairs          :309-314  -> radix_pass_kernel: 4 passes over the P (depth, index) pairs +
+//                                                         ceil(tile_bits / 8) passes over the R (tile, index) pairs
+//   cudaMemset + identifyTileRanges          :316-323  -> tile_ranges_kernel (+ tile_order_kernel, the block schedule)
 //
-// Results are bit-identical to the reference by construction: the unsorted arrays have the same
-// element order (Gaussian index ascending, row-major inside the rectangle), and the sort is stable
-// over bits [0, 32+bit), like CUB's.
+// The sorted point list and the tile ranges are bit-identical to the reference's by construction: a stable sort by tile of
+// an emission that is already in (depth, index) order yields, inside every tile, the order (depth, index) — which is what
+// CUB's stable sort of (tile << 32 | depth) keys over the reference's index-ordered emission yields.  The reference's
+// intermediate lists (index-ordered duplicated keys, point_offsets, 64-bit sorted keys) are produced on demand by
+// vcr_launch_reference_lists for the parity tests.
 #include "common.cuh"
 
 // ------------------------------------------------------------------------------------------------

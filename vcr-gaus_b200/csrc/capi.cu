@@ -154,7 +154,8 @@ static int debug_sync(int debug, cudaStream_t s, const char* what) {  // CHECK_C
     return 0;
 }
 
-// Shared front half of every forward variant: preprocess -> scan -> R -> duplicate -> sort -> ranges.
+// Shared front half of every forward variant: preprocess -> scan -> R read-back (event) || depth sort of the Gaussians ->
+// emission in depth order -> sort by tile -> ranges + tile schedule.
 static int forward_front(vcr_alloc_fn geometry_buffer, vcr_alloc_fn binning_buffer, vcr_alloc_fn image_buffer, void* user,
                          FwdParams& p, GeomState& g, BinningState& b, ImageState& img, int debug, int* num_rendered_host,
                          cudaStream_t s) {
