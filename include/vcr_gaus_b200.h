@@ -14,6 +14,14 @@
  *   vcr_dist2_knn3               <- SimpleKNN::knn                            submodules/simple-knn/simple_knn.h:17
  *   vcr_dnormal_forward/backward <- tools/normal_utils.py:30-41 + tools/loss_utils.py:122-142 + trainer.py:266-280
  *                                   (a PyTorch op chain in the reference; one fused kernel each way here)
+ *   vcr_view_loss_forward/backward/total <- the image-space losses of trainer.py:236-280 (L1 + mono-normal + D-Normal)
+ *   vcr_ssim_forward/backward    <- tools/loss_utils.py:47-92
+ *   vcr_prologue_forward/backward <- the per-Gaussian prologue of render(), gaussian_renderer/__init__.py:60-101
+ *   vcr_adam_step                <- torch.optim.Adam over the six groups of scene/gaussian_model.py:241-258
+ *   vcr_densify_stats_accumulate <- trainer.py:345 + scene/gaussian_model.py:669-671
+ * and, with no counterpart in the (single-GPU) reference, the view-parallel pieces: vcr_rasterize_backward_chunked,
+ * vcr_multimem_allreduce_sum, vcr_multimem_exchange, vcr_sh_grad_from_colors; plus the test-only parity view
+ * vcr_binning_reference_lists and vcr_dist2_knn3_noalloc.
  *
  * Conventions
  *   - All pointers are DEVICE pointers unless the name ends in _host.  The caller owns all memory;
