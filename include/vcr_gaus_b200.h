@@ -278,6 +278,16 @@ int vcr_multimem_exchange(void* multicast_base, const float* local_base, int n_r
                           const long long* n_floats_host, long long bcast_first, long long bcast_count, int rank, int world,
                           int blocks, void* stream);
 
+/* Prune as stream compaction (replaces the ~18 boolean-mask indexing operations of _prune_optimizer,
+ * scene/gaussian_model.py:442-460): rows i with keep[i] != 0 of every array a (f32[P, width[a]]) are copied, in order, to
+ * dst[a] (row j = the j-th kept row).  src / dst / width are HOST arrays of n_arrays entries (device pointers inside);
+ * src and dst must not overlap.  scratch: vcr_compact_scratch_bytes(P) device bytes.  The number of kept rows is written
+ * to *n_kept_device (device u32, may be NULL); a caller that needs it on the host before sizing dst counts the mask
+ * itself.  One prefix sum + one gather launch per 8 arrays. */
+size_t vcr_compact_scratch_bytes(int P);
+int vcr_compact_rows(int P, const uint8_t* keep, int n_arrays, const float* const* src_host, float* const* dst_host,
+                     const int* width_host, char* scratch, uint32_t* n_kept_device, void* stream);
+
 /* Gradient exchange of the view-parallel layer through the NVSwitch (the reference is single-GPU and
  * has no counterpart).  `multicast_base` is the multicast mapping (NVLink SHARP, e.g. torch symmetric memory's
  * multicast_ptr) of a float buffer that every rank holds at the same offset.  For each of the n_ranges (<= 8) float

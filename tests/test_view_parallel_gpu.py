@@ -158,3 +158,39 @@ def test_compact_sh_gradient_reconstruction(deg):
     assert rel_l2(rebuilt.cpu().numpy(), ref["dL_dsh"]) <= 5e-5    # two runs of the float-atomic backward (gate: 1e-3)
     for k, name in (("means3D", "dL_dmeans3D"), ("opacities", "dL_dopacity"), ("scales", "dL_dscales"), ("rotations", "dL_drotations")):
         assert rel_l2(leaves[k].grad.cpu().numpy(), ref[name]) <= 5e-5, k
+
+
+def test_prune_and_grow_matches_boolean_indexing():
+    """prune_and_grow == the reference's prune_points + densification_postfix on parameters and both Adam moments
+    (scene/gaussian_model.py:442-531): kept rows in order, new rows appended with zero moments."""
+    import vcr_view_parallel as VP
+    P, n_new = 70_001, 1234
+    dev = torch.device("cuda")
+    g = torch.Generator().manual_seed(8)
+    shapes = dict(xyz=(P, 3), f_dc=(P, 1, 3), f_rest=(P, 15, 3), opacity=(P, 1), scaling=(P, 3), rotation=(P, 4))
+    names = tuple(shapes)
+    init = {k: torch.randn(s, generator=g).to(dev) for k, s in shapes.items()}
+    bucket = VP.GaussianBucket(init, device=dev, names=names)
+    opt = VP.BucketAdam(bucket, {k: 1e-3 for k in names})
+    opt.exp_avg.normal_(generator=None); opt.exp_avg_sq.uniform_()
+    opt.steps = 7
+    keep = (torch.rand(P, generator=g) > 0.37).to(dev)
+    keep[:300] = False; keep[-5:] = True                                # a fully pruned block and a kept tail
+    old_m = {k: opt.exp_avg[o:o + n].view(s).clone() for k, o, n, s in bucket.layout}
+    old_v = {k: opt.exp_avg_sq[o:o + n].view(s).clone() for k, o, n, s in bucket.layout}
+    new, opt2, n_kept = VP.prune_and_grow(bucket, keep, n_new=n_new, optimizer=opt)
+    torch.cuda.synchronize()
+    assert n_kept == int(keep.sum()) and new.P == n_kept + n_new and new.numel == 59 * new.P and opt2.steps == 7
+    for k, o, n, s in new.layout:
+        assert s[0] == new.P and tuple(s[1:]) == tuple(shapes[k][1:])
+        assert torch.equal(new.params[k].detach()[:n_kept], init[k][keep]), k          # param[mask]
+        m2, v2 = opt2.exp_avg[o:o + n].view(s), opt2.exp_avg_sq[o:o + n].view(s)
+        assert torch.equal(m2[:n_kept], old_m[k][keep]) and torch.equal(v2[:n_kept], old_v[k][keep]), k
+        assert float(m2[n_kept:].abs().max()) == 0.0 and float(v2[n_kept:].abs().max()) == 0.0   # cat(zeros)
+        assert new.params[k].grad.data_ptr() == new.grad_flat[o:].data_ptr()
+    # nothing kept / everything kept
+    none, _, z = VP.prune_and_grow(bucket, torch.zeros(P, dtype=torch.bool, device=dev), n_new=3)
+    assert z == 0 and none.P == 3
+    full, _, a = VP.prune_and_grow(bucket, torch.ones(P, dtype=torch.bool, device=dev))
+    torch.cuda.synchronize()
+    assert a == P and torch.equal(full.flat, bucket.flat)

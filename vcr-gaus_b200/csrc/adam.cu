@@ -68,3 +68,127 @@ extern "C" int vcr_adam_step(long long numel, float* params, const float* grads,
     VCR_LAUNCH_CHECK("adam_step_kernel");
     return 0;
 }
+
+// ------------------------------------------------------------------------------------------------------------------
+// Densify / prune as stream compaction.  The reference prunes with ~18 boolean-mask indexing
+// operations (every parameter group and both Adam moments: _prune_optimizer, scene/gaussian_model.py:442-460) and grows
+// with as many torch.cat (cat_tensors_to_optimizer, :480-502).  Here: one exclusive prefix sum of the keep mask, then ONE
+// gather launch that moves the kept rows of up to 8 arrays (of different row widths) into their new places.
+// ------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) keep_block_sums_kernel(int P, const uint8_t* __restrict__ keep, uint32_t* __restrict__ sums) {
+    __shared__ uint32_t warp_tot[8];
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    const uint32_t v = (i < P && keep[i]) ? 1u : 0u;
+    const uint32_t wsum = __reduce_add_sync(0xffffffffu, v);
+    if ((threadIdx.x & 31) == 0) warp_tot[threadIdx.x >> 5] = wsum;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t t = 0;
+#pragma unroll
+        for (int w = 0; w < 8; w++) t += warp_tot[w];
+        sums[blockIdx.x] = t;
+    }
+}
+
+// one block: exclusive scan of the block sums in place, total -> sums[nb]
+__global__ void __launch_bounds__(1024) keep_scan_kernel(uint32_t* __restrict__ sums, int nb) {
+    __shared__ uint32_t warp_tot[32];
+    const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+    const int ipt = (nb + 1023) / 1024;
+    const int first = t * ipt, last = min(first + ipt, nb);
+    uint32_t v = 0;
+    for (int i = first; i < last; i++) v += sums[i];
+    uint32_t inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t n = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += n;
+    }
+    if (lane == 31) warp_tot[w] = inc;
+    __syncthreads();
+    if (w == 0) {
+        uint32_t x = warp_tot[lane];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t n = __shfl_up_sync(0xffffffffu, x, o);
+            if (lane >= o) x += n;
+        }
+        warp_tot[lane] = x;
+    }
+    __syncthreads();
+    uint32_t run = (w ? warp_tot[w - 1] : 0u) + inc - v;
+    for (int i = first; i < last; i++) {
+        const uint32_t c = sums[i];
+        sums[i] = run;
+        run += c;
+    }
+    if (t == 1023) sums[nb] = warp_tot[31];
+}
+
+#define VCR_COMPACT_MAX_ARRAYS 8
+struct CompactArrays {
+    const float* src[VCR_COMPACT_MAX_ARRAYS];
+    float* dst[VCR_COMPACT_MAX_ARRAYS];
+    int width[VCR_COMPACT_MAX_ARRAYS];      // floats per row
+    int n;
+};
+
+// block b handles rows [256 b, 256 b + 256): in-block rank of every kept row, then for each array the block's kept rows
+// are copied float by float with consecutive threads on consecutive output floats (the kept rows of a block are contiguous
+// in the output)
+__global__ void __launch_bounds__(256) compact_rows_kernel(int P, const uint8_t* __restrict__ keep, const uint32_t* __restrict__ sums,
+                                                           const CompactArrays arr) {
+    __shared__ uint32_t s_src[256];          // source row of the block's j-th kept row
+    __shared__ uint32_t warp_tot[8];
+    const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+    const int i = blockIdx.x * 256 + t;
+    const bool k = i < P && keep[i];
+    const uint32_t ball = __ballot_sync(0xffffffffu, k);
+    if (lane == 0) warp_tot[w] = __popc(ball);
+    __syncthreads();
+    uint32_t wex = 0, total = 0;
+#pragma unroll
+    for (int q = 0; q < 8; q++) { wex += (q < w) ? warp_tot[q] : 0u; total += warp_tot[q]; }
+    if (k) s_src[wex + __popc(ball & ((1u << lane) - 1u))] = (uint32_t)i;
+    __syncthreads();
+    const size_t base = sums[blockIdx.x];
+    for (int a = 0; a < arr.n; a++) {
+        const int wd = arr.width[a];
+        const float* __restrict__ src = arr.src[a];
+        float* __restrict__ dst = arr.dst[a] + base * wd;
+        const uint32_t n = total * (uint32_t)wd;
+        for (uint32_t e = t; e < n; e += 256) {
+            const uint32_t j = e / (uint32_t)wd, c = e - j * (uint32_t)wd;
+            dst[e] = __ldg(src + (size_t)s_src[j] * wd + c);
+        }
+    }
+}
+
+extern "C" size_t vcr_compact_scratch_bytes(int P) { return ((size_t)(P + 255) / 256 + 2) * sizeof(uint32_t) + 256; }
+
+extern "C" int vcr_compact_rows(int P, const uint8_t* keep, int n_arrays, const float* const* src_host, float* const* dst_host,
+                                const int* width_host, char* scratch, uint32_t* n_kept_device, void* stream) {
+    if (P <= 0) return 0;
+    if (!keep || !scratch || n_arrays < 0 || (n_arrays > 0 && (!src_host || !dst_host || !width_host))) { vcr_set_error("compact_rows: NULL argument"); return 1; }
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    uint32_t* sums = reinterpret_cast<uint32_t*>(vcr_align256(reinterpret_cast<size_t>(scratch)));
+    const int nb = (P + 255) / 256;
+    VcrProfScope prof(VCR_K_ADAM, s, 2 + (n_arrays + VCR_COMPACT_MAX_ARRAYS - 1) / VCR_COMPACT_MAX_ARRAYS);
+    keep_block_sums_kernel<<<nb, 256, 0, s>>>(P, keep, sums);
+    VCR_LAUNCH_CHECK("keep_block_sums_kernel");
+    keep_scan_kernel<<<1, 1024, 0, s>>>(sums, nb);
+    VCR_LAUNCH_CHECK("keep_scan_kernel");
+    if (n_kept_device) VCR_CUDA_TRY(cudaMemcpyAsync(n_kept_device, sums + nb, sizeof(uint32_t), cudaMemcpyDeviceToDevice, s));
+    for (int a0 = 0; a0 < n_arrays; a0 += VCR_COMPACT_MAX_ARRAYS) {
+        CompactArrays arr;
+        memset(&arr, 0, sizeof(arr));
+        arr.n = n_arrays - a0 < VCR_COMPACT_MAX_ARRAYS ? n_arrays - a0 : VCR_COMPACT_MAX_ARRAYS;
+        for (int a = 0; a < arr.n; a++) {
+            if (!src_host[a0 + a] || !dst_host[a0 + a] || width_host[a0 + a] <= 0) { vcr_set_error("compact_rows: bad array %d", a0 + a); return 1; }
+            arr.src[a] = src_host[a0 + a]; arr.dst[a] = dst_host[a0 + a]; arr.width[a] = width_host[a0 + a];
+        }
+        compact_rows_kernel<<<nb, 256, 0, s>>>(P, keep, sums, arr);
+        VCR_LAUNCH_CHECK("compact_rows_kernel");
+    }
+    return 0;
+}

@@ -80,6 +80,9 @@ vcr_multimem_exchange = _sig("vcr_multimem_exchange", c_int,
                              [c_void_p, P_, c_int, POINTER(ctypes.c_longlong), POINTER(ctypes.c_longlong), ctypes.c_longlong,
                               ctypes.c_longlong, c_int, c_int, c_int, c_void_p])
 
+vcr_compact_scratch_bytes = _sig("vcr_compact_scratch_bytes", c_size_t, [c_int])
+vcr_compact_rows = _sig("vcr_compact_rows", c_int, [c_int, P_, c_int, POINTER(c_void_p), POINTER(c_void_p), POINTER(c_int), P_, P_, c_void_p])
+
 vcr_densify_stats_accumulate = _sig("vcr_densify_stats_accumulate", c_int, [c_int, P_, P_, P_, P_, P_, c_void_p])
 
 vcr_mark_visible = _sig("vcr_mark_visible", c_int, [c_int, P_, P_, P_, P_, c_void_p])
@@ -155,7 +158,7 @@ DECLARED_SYMBOLS = [
     "vcr_knn_scratch_bytes", "vcr_dist2_knn3", "vcr_geom_layout", "vcr_binning_layout", "vcr_image_layout",
     "vcr_knn_noalloc_max_points", "vcr_dist2_knn3_noalloc", "vcr_view_loss_forward", "vcr_view_loss_backward",
     "vcr_profile_enable", "vcr_profile_kernel_count", "vcr_profile_kernel_name", "vcr_profile_read",
-    "vcr_rasterize_backward_chunked", "vcr_densify_stats_accumulate", "vcr_multimem_allreduce_sum", "vcr_prologue_forward", "vcr_prologue_backward", "vcr_ssim_forward", "vcr_ssim_backward", "vcr_adam_step", "vcr_view_loss_total", "vcr_binning_reference_lists", "vcr_sh_grad_from_colors", "vcr_multimem_exchange",
+    "vcr_rasterize_backward_chunked", "vcr_densify_stats_accumulate", "vcr_multimem_allreduce_sum", "vcr_prologue_forward", "vcr_prologue_backward", "vcr_ssim_forward", "vcr_ssim_backward", "vcr_adam_step", "vcr_view_loss_total", "vcr_binning_reference_lists", "vcr_compact_scratch_bytes", "vcr_compact_rows", "vcr_sh_grad_from_colors", "vcr_multimem_exchange",
 ]
 
 

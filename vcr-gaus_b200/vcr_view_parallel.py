@@ -166,6 +166,66 @@ class BucketAdam:
                  "adam_step")
 
 
+def prune_and_grow(bucket: GaussianBucket, keep: torch.Tensor, n_new: int = 0, optimizer: Optional[BucketAdam] = None):
+    """Densify / prune on the flat bucket: a new GaussianBucket whose first rows are the rows of `bucket` with keep != 0, in
+    order, followed by `n_new` rows for the caller to fill (clones / splits), and — when `optimizer` is given — a new
+    BucketAdam whose moments are compacted the same way (zeros for the new rows, as cat_tensors_to_optimizer does).
+    Replaces prune_points + densification_postfix of the reference (scene/gaussian_model.py:442-531: ~18 boolean-mask
+    indexing operations and as many torch.cat) by one prefix sum and one gather launch per 8 arrays (vcr_compact_rows).
+    `keep`: bool / uint8 CUDA tensor [P].  One host read of the kept count (the new bucket has to be sized).  Returns
+    (new_bucket, new_optimizer or None, n_kept)."""
+    import vcr_native as _n
+    if not bucket.flat.is_cuda or not keep.is_cuda:
+        raise RuntimeError("prune_and_grow needs CUDA tensors; there is no CPU fallback")
+    P, dev = bucket.P, bucket.flat.device
+    k8 = (keep.to(torch.uint8) if keep.dtype == torch.bool else keep).contiguous()
+    if k8.numel() != P or k8.dtype != torch.uint8:
+        raise ValueError("keep must have one bool / uint8 entry per Gaussian")
+    n_kept = int(k8.sum())
+    P2 = n_kept + int(n_new)
+    shapes = {name: (P2,) + tuple(shape[1:]) for name, _, _, shape in bucket.layout}
+    # group-major layout of the new bucket: every group is compacted into its own slice
+    new = GaussianBucket.__new__(GaussianBucket)
+    new.direct, new.names, new.P, new.layout = bucket.direct, bucket.names, P2, []
+    off = 0
+    for name, _, n, shape in bucket.layout:
+        per = n // max(P, 1)
+        new.layout.append((name, off, per * P2, shapes[name]))
+        off += per * P2
+    new.numel = off
+    new.flat = torch.empty(off, dtype=torch.float32, device=dev)
+    new.grad_flat = torch.zeros(off, dtype=torch.float32, device=dev)
+    srcs, dsts, widths = [], [], []
+    moments = []
+    if optimizer is not None:
+        opt2 = BucketAdam.__new__(BucketAdam)
+        opt2.bucket, opt2.lrs, opt2.betas, opt2.eps, opt2.steps = new, dict(optimizer.lrs), optimizer.betas, optimizer.eps, optimizer.steps
+        opt2.exp_avg = torch.zeros(off, dtype=torch.float32, device=dev)          # zeros for the new rows
+        opt2.exp_avg_sq = torch.zeros(off, dtype=torch.float32, device=dev)
+        moments = [(optimizer.exp_avg, opt2.exp_avg), (optimizer.exp_avg_sq, opt2.exp_avg_sq)]
+    else:
+        opt2 = None
+    for (name, o1, n1, _), (_, o2, _, _) in zip(bucket.layout, new.layout):
+        per = n1 // max(P, 1)
+        for src, dst in [(bucket.flat, new.flat)] + moments:
+            srcs.append(src.data_ptr() + 4 * o1); dsts.append(dst.data_ptr() + 4 * o2); widths.append(per)
+    scratch = torch.empty(int(_n.vcr_compact_scratch_bytes(P)), dtype=torch.uint8, device=dev)
+    n = len(srcs) if n_kept > 0 else 0             # nothing to move when every row is pruned
+    if n:
+        _n.check(_n.vcr_compact_rows(P, k8.data_ptr(), n, (ctypes.c_void_p * n)(*srcs), (ctypes.c_void_p * n)(*dsts),
+                                     (ctypes.c_int * n)(*widths), scratch.data_ptr(), None,
+                                     ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)), "compact_rows")
+    new.params = {}
+    for name, o, cnt, shape in new.layout:
+        p = new.flat[o:o + cnt].view(shape).requires_grad_(True)
+        if new.direct:
+            p._vcr_grad_out = new.grad_flat[o:o + cnt].view(shape)
+        else:
+            p.grad = new.grad_flat[o:o + cnt].view(shape)
+        new.params[name] = p
+    return new, opt2, n_kept
+
+
 class ViewParallel:
     def __init__(self, group=None):
         self.group = group
