@@ -145,3 +145,36 @@ def test_balanced_view_table():
     assert max(totals) - min(totals) < 0.02 * sum(totals) / 4
     assert table != vp.balanced_view_table(costs, seed=6), "the visiting order must change with the seed"
     assert sorted(map(sorted, table)) == sorted(map(sorted, vp.balanced_view_table(costs, seed=6))), "... but not the groups"
+
+
+def test_bucket_layouts_and_cuda_only_pieces():
+    """Host-side bookkeeping of the bucket (custom group names, exchange sizing) and the loud failure of the CUDA-only
+    pieces on CPU tensors (there is no CPU fallback for kernels)."""
+    import pytest
+    sys.path.insert(0, PKG)
+    import vcr_view_parallel as VP
+    P = 10
+    raw = dict(xyz=torch.randn(P, 3), f_dc=torch.randn(P, 1, 3), f_rest=torch.randn(P, 15, 3), opacity=torch.randn(P, 1),
+               scaling=torch.randn(P, 3), rotation=torch.randn(P, 4))
+    names = tuple(raw)
+    b = VP.GaussianBucket(raw, names=names)
+    assert b.numel == 59 * P and b.floats_per_gaussian == 59 and tuple(b.params) == names
+    assert [n for n, _, _, _ in b.layout] == list(names)
+    assert torch.equal(b.params["f_rest"].detach(), raw["f_rest"]) and b.params["f_rest"].grad.shape == (P, 15, 3)
+    assert VP.GaussianBucket.numel_for(raw, names) == 59 * P
+    vp = VP.ViewParallel()
+    std = dict(means3D=raw["xyz"], shs=torch.randn(P, 16, 3), opacities=raw["opacity"], scales=raw["scaling"], rotations=raw["rotation"])
+    stride = VP.ViewParallel._slice_stride(P)
+    assert stride % 4 == 0 and stride >= 3 * P + 3
+    assert vp.exchange_floats(std) == (59 * P + 3) // 4 * 4 + vp.world * stride
+    with pytest.raises(RuntimeError):
+        VP.BucketAdam(b, {k: 1e-3 for k in names})
+    with pytest.raises(RuntimeError):
+        VP.prune_and_grow(b, torch.ones(P, dtype=torch.bool))
+    with pytest.raises(ValueError):
+        vp.compact_sh_exchange(VP.GaussianBucket(std))                       # needs direct=True
+    with pytest.raises(ValueError):
+        vp.compact_sh_exchange(VP.GaussianBucket(raw, names=names, direct=True))   # needs the rasterizer's inputs
+    with pytest.raises(ValueError):
+        vp.overlap_gradients(VP.GaussianBucket(std))
+    assert VP.bind_to_gpu_numa_node(0) >= 0
