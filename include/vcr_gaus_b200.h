@@ -34,6 +34,12 @@
  *     grow callbacks, exactly like the reference's std::function<char*(size_t)> resize lambdas
  *     (DGR/rasterize_points.cu:28-34, rasterizer.h:32-34).  The byte layout is private to this
  *     library (documented in DESIGN.md); forward and backward agree on it.
+ *   - Alignment: `rotations` (f32[P,4]), `shs` and `dL_dsh` when M == 16 (f32[P,16,3]), `dL_drot`, and the
+ *     prologue's rotation_raw / rotations / dL_drotations / dL_drotation_raw are accessed as float4 and must be
+ *     16-byte aligned; the buffers of vcr_adam_step likewise.  A tensor that starts a torch allocation always is;
+ *     a slice of a flat parameter bucket is only if its float offset is a multiple of 4
+ *     (vcr_view_parallel.GaussianBucket pads its groups accordingly).  Misaligned pointers are rejected with an
+ *     error before anything is launched.  All other arrays only need their natural 4-byte alignment.
  *   - Return value: 0 = success, non-zero = error; vcr_last_error() returns a thread-local message.
  *     Negative num_rendered is never returned.
  */

@@ -24,6 +24,13 @@ def _fake_view_grads(P, view):
     return grads, radii.to(torch.int32), g2d
 
 
+def _groups(bucket):
+    """The gradient bucket without the alignment padding between the groups: the groups' rows, concatenated in bucket order."""
+    for _, off, _, _ in bucket.layout:
+        assert off % 4 == 0, "every group must start on a 16-byte boundary"
+    return torch.cat([bucket.grad_flat[off:off + n] for _, off, n, _ in bucket.layout]).clone()
+
+
 def _worker(rank, world, port, P, out_dir):
     sys.path.insert(0, PKG)
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank))
@@ -49,7 +56,7 @@ def _worker(rank, world, port, P, out_dir):
         vp.allreduce_gradients(bucket, average=False)
         vp.reduce_densification_stats(accum, denom, max_r, g2d, radii)
         vp.accumulate_densification_stats(lazy[0], lazy[1], lazy[2], g2d, radii)
-        torch.save({"view": view, "grad": bucket.grad_flat.clone(), "accum": accum.clone(), "denom": denom.clone(),
+        torch.save({"view": view, "grad": _groups(bucket), "accum": accum.clone(), "denom": denom.clone(),
                     "max_r": max_r.clone(), "flat": bucket.flat.clone()}, os.path.join(out_dir, f"r{rank}_s{step}.pt"))
     vp.sync_densification_stats(*lazy)
     # chunk-pipelined exchange: the rasterizer's backward calls the hook once per Gaussian range; here the hook is driven
@@ -66,7 +73,7 @@ def _worker(rank, world, port, P, out_dir):
             dbucket.grad_flat[off + a * per: off + b * per] = grads[name].reshape(-1)[a * per: b * per]
         hook(c, a, b - a)
     assert vp.finish_gradients(dbucket) == n_chunks
-    torch.save({"grad": dbucket.grad_flat.clone()}, os.path.join(out_dir, f"r{rank}_chunked.pt"))
+    torch.save({"grad": _groups(dbucket)}, os.path.join(out_dir, f"r{rank}_chunked.pt"))
     torch.save({"accum": lazy[0], "denom": lazy[1], "max_r": lazy[2]}, os.path.join(out_dir, f"r{rank}_lazy.pt"))
     dist.destroy_process_group()
 
@@ -118,7 +125,10 @@ def test_single_process_is_a_no_op():
          "scales": torch.rand((5, 3)), "rotations": torch.randn((5, 4))}
     b = VP.GaussianBucket(t)
     (b.params["means3D"].sum() * 2 + b.params["shs"].sum()).backward()
-    assert torch.equal(b.grad_flat[:15], torch.full((15,), 2.0)) and torch.equal(b.grad_flat[15:15 + 240], torch.ones(240))
+    off_sh = b.layout[1][1]
+    assert off_sh == 16 and off_sh % 4 == 0                                   # 15 floats of means3D + 1 pad float
+    assert torch.equal(b.grad_flat[:15], torch.full((15,), 2.0)) and torch.equal(b.grad_flat[off_sh:off_sh + 240], torch.ones(240))
+    assert float(b.grad_flat[15]) == 0.0 and float(b.flat[15]) == 0.0         # the pad stays zero
     assert vp.allreduce_gradients(b) is None
     views = [vp.view_for_step(s, 6, seed=0) for s in range(6)]
     assert sorted(views) == list(range(6))
@@ -158,15 +168,20 @@ def test_bucket_layouts_and_cuda_only_pieces():
                scaling=torch.randn(P, 3), rotation=torch.randn(P, 4))
     names = tuple(raw)
     b = VP.GaussianBucket(raw, names=names)
-    assert b.numel == 59 * P and b.floats_per_gaussian == 59 and tuple(b.params) == names
+    pad4 = lambda n: (n + 3) // 4 * 4  # noqa: E731
+    padded = sum(pad4(t.numel()) for t in raw.values())
+    assert b.numel == padded and b.floats_per_gaussian == 59 and tuple(b.params) == names
+    assert all(off % 4 == 0 for _, off, _, _ in b.layout), "groups must start 16-byte aligned for every P"
     assert [n for n, _, _, _ in b.layout] == list(names)
     assert torch.equal(b.params["f_rest"].detach(), raw["f_rest"]) and b.params["f_rest"].grad.shape == (P, 15, 3)
-    assert VP.GaussianBucket.numel_for(raw, names) == 59 * P
+    assert VP.GaussianBucket.numel_for(raw, names) == padded
     vp = VP.ViewParallel()
     std = dict(means3D=raw["xyz"], shs=torch.randn(P, 16, 3), opacities=raw["opacity"], scales=raw["scaling"], rotations=raw["rotation"])
     stride = VP.ViewParallel._slice_stride(P)
     assert stride % 4 == 0 and stride >= 3 * P + 3
-    assert vp.exchange_floats(std) == (59 * P + 3) // 4 * 4 + vp.world * stride
+    assert vp.exchange_floats(std) == sum(pad4(t.numel()) for t in std.values()) + vp.world * stride
+    grown = vp.exchange_floats(std, capacity=3 * P + 1)
+    assert grown >= VP.GaussianBucket.numel_for({k: torch.zeros((3 * P + 1,) + t.shape[1:]) for k, t in std.items()}) + vp.world * VP.ViewParallel._slice_stride(3 * P + 1)
     with pytest.raises(RuntimeError):
         VP.BucketAdam(b, {k: 1e-3 for k in names})
     with pytest.raises(RuntimeError):

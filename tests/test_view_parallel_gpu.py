@@ -9,12 +9,14 @@ from util import CudaRun, make_case, rel_l2, settings_from
 pytestmark = pytest.mark.gpu
 
 
-def test_chunked_backward_equals_single_launch():
+@pytest.mark.parametrize("P", [3000, 3001, 10_007])
+def test_chunked_backward_equals_single_launch(P):
     """The per-Gaussian backward stage in 5 launches writes the same gradients as in one, straight into the flat bucket,
-    and reports consecutive ranges starting at multiples of 256 that cover every Gaussian."""
+    and reports consecutive ranges starting at multiples of 256 that cover every Gaussian.  P = 3001 / 10007: the bucket's
+    groups would start at float offsets 3P, 51P, ... — 16-byte aligned only through the bucket's padding."""
     import vcr_view_parallel as VP
     from diff_gaussian_rasterization import GaussianRasterizer
-    P, W, H = 3000, 320, 200                      # 12 blocks of 256 -> ragged split into 5 ranges, last block partial
+    W, H = 320, 200                               # 12+ blocks of 256 -> ragged split into 5 ranges, last block partial
     inp, _, _ = make_case(P, W, H, seed=3, use_dirs=True, use_sem=False)
     dev = torch.device("cuda")
     g = torch.Generator().manual_seed(5)
@@ -25,7 +27,9 @@ def test_chunked_backward_equals_single_launch():
 
     tensors = {k: inp[k].to(dev) for k in ("means3D", "shs", "opacities", "scales", "rotations")}
     bucket = VP.GaussianBucket(tensors, device=dev, direct=True)
-    bucket.grad_flat.fill_(float("nan"))          # every element must be overwritten
+    assert all(off % 4 == 0 and bucket.params[name].data_ptr() % 16 == 0 for name, off, _, _ in bucket.layout)
+    for _, off, n, _ in bucket.layout:
+        bucket.grad_flat[off:off + n].fill_(float("nan"))      # every element of every group must be overwritten
     calls = []
     bucket.params["means3D"]._vcr_chunk_hook = (5, lambda c, first, count: calls.append((c, first, count)))
     p = bucket.params
@@ -103,7 +107,7 @@ def test_bucket_adam_matches_torch_adam():
     init = {k: torch.randn(s, generator=g).to(dev) for k, s in shapes.items()}
     lrs = dict(xyz=1.6e-4, f_dc=2.5e-3, f_rest=2.5e-3 / 20, opacity=0.05, scaling=5e-3, rotation=1e-3)
     bucket = VP.GaussianBucket(init, device=dev, names=names)
-    assert bucket.numel == 59 * P and tuple(bucket.params) == names
+    assert bucket.floats_per_gaussian == 59 and tuple(bucket.params) == names
     opt = VP.BucketAdam(bucket, lrs)
     ref_p = {k: v.clone().requires_grad_(True) for k, v in init.items()}
     ref = torch.optim.Adam([{"params": [ref_p[k]], "lr": lrs[k], "name": k} for k in names], lr=0.0, eps=1e-15)
@@ -124,14 +128,14 @@ def test_bucket_adam_matches_torch_adam():
         VP.BucketAdam(bucket, {"xyz": 1.0})
 
 
-@pytest.mark.parametrize("deg", [3, 1, 0])
-def test_compact_sh_gradient_reconstruction(deg):
+@pytest.mark.parametrize("deg,P", [(3, 4000), (1, 4000), (0, 4000), (3, 3001), (3, 10_007)])
+def test_compact_sh_gradient_reconstruction(deg, P):
     """dL_dsh rebuilt from the clamp-masked colour gradient + camera position (vcr_sh_grad_from_colors) equals the SH gradient
     the backward writes itself; every other gradient is unchanged by the compact mode."""
     import ctypes
     import vcr_native as N
     from diff_gaussian_rasterization import GaussianRasterizer
-    P, W, H = 4000, 200, 160
+    W, H = 200, 160
     inp, _, _ = make_case(P, W, H, seed=6, sh_degree=deg)
     dev = torch.device("cuda")
     dL = torch.randn((10, H, W), generator=torch.Generator().manual_seed(2)).to(dev)
@@ -180,7 +184,8 @@ def test_prune_and_grow_matches_boolean_indexing():
     old_v = {k: opt.exp_avg_sq[o:o + n].view(s).clone() for k, o, n, s in bucket.layout}
     new, opt2, n_kept = VP.prune_and_grow(bucket, keep, n_new=n_new, optimizer=opt)
     torch.cuda.synchronize()
-    assert n_kept == int(keep.sum()) and new.P == n_kept + n_new and new.numel == 59 * new.P and opt2.steps == 7
+    assert n_kept == int(keep.sum()) and new.P == n_kept + n_new and new.floats_per_gaussian == 59 and opt2.steps == 7
+    assert all(o % 4 == 0 for _, o, _, _ in new.layout)
     for k, o, n, s in new.layout:
         assert s[0] == new.P and tuple(s[1:]) == tuple(shapes[k][1:])
         assert torch.equal(new.params[k].detach()[:n_kept], init[k][keep]), k          # param[mask]
@@ -194,3 +199,85 @@ def test_prune_and_grow_matches_boolean_indexing():
     full, _, a = VP.prune_and_grow(bucket, torch.ones(P, dtype=torch.bool, device=dev))
     torch.cuda.synchronize()
     assert a == P and torch.equal(full.flat, bucket.flat)
+
+
+def test_rasterize_through_bucket_after_prune_and_grow():
+    """A densification leaves a Gaussian count that is not a multiple of 4.  The rasterizer's float4 accesses (shs, rotations,
+    dL_dsh, dL_drot) must still find 16-byte aligned groups in the new bucket, and forward + backward through it must give
+    what plain leaf tensors of the same values give."""
+    import vcr_view_parallel as VP
+    from diff_gaussian_rasterization import GaussianRasterizer
+    P, W, H = 5000, 240, 176
+    inp, _, _ = make_case(P, W, H, seed=4, use_dirs=True, use_sem=False)
+    dev = torch.device("cuda")
+    tensors = {k: inp[k].to(dev) for k in ("means3D", "shs", "opacities", "scales", "rotations")}
+    bucket = VP.GaussianBucket(tensors, device=dev, direct=True)
+    keep = torch.ones(P, dtype=torch.bool, device=dev)
+    keep[torch.arange(0, P, 7, device=dev)] = False                  # 4285 kept
+    n_new = 2
+    new, _, n_kept = VP.prune_and_grow(bucket, keep, n_new=n_new)
+    P2 = n_kept + n_new
+    assert P2 % 4 != 0 and new.P == P2
+    with torch.no_grad():                                            # the new rows: clones of the first two kept Gaussians
+        for name in new.names:
+            new.params[name][n_kept:] = new.params[name][:n_new]
+    assert all(new.params[name].data_ptr() % 16 == 0 for name in new.names)
+    sel = torch.cat([keep.nonzero(as_tuple=True)[0], keep.nonzero(as_tuple=True)[0][:n_new]]).cpu()
+    inp2 = dict(inp)
+    for k in ("means3D", "shs", "opacities", "scales", "rotations", "normals"):
+        inp2[k] = inp[k][sel].contiguous()
+    for name in new.names:
+        assert torch.equal(new.params[name].detach().cpu(), inp2[name])
+    dL = torch.randn((10, H, W), generator=torch.Generator().manual_seed(9))
+    plain = CudaRun(inp2)
+    ref = plain.backward(dL)
+    p = new.params
+    out, radii = GaussianRasterizer(settings_from(inp2, dev))(
+        means3D=p["means3D"], means2D=None, shs=p["shs"], normals_precomp=inp2["normals"].to(dev), opacities=p["opacities"],
+        scales=p["scales"], rotations=p["rotations"], dirs=inp2["dirs"].to(dev))
+    assert torch.equal(out, plain.out) and torch.equal(radii, plain.radii)
+    out.backward(dL.to(dev))
+    torch.cuda.synchronize()
+    assert p["shs"].grad.data_ptr() == new.grad_flat[new.layout[1][1]:].data_ptr(), "gradient was not written in place"
+    names = dict(means3D="dL_dmeans3D", shs="dL_dsh", opacities="dL_dopacity", scales="dL_dscales", rotations="dL_drotations")
+    for name, off, n, shape in new.layout:
+        assert rel_l2(new.grad_flat[off:off + n].view(shape).cpu().numpy(), ref[names[name]]) <= 5e-5, name
+
+
+def test_misaligned_float4_arrays():
+    """Through the Python API a rotations / shs view that does not start on a 16-byte boundary is copied and works; through the
+    C ABI the same pointer is refused with a message instead of faulting inside a kernel."""
+    import ctypes
+    import vcr_native as N
+    from diff_gaussian_rasterization import GaussianRasterizer, _Buffers
+    P, W, H = 1001, 96, 64
+    inp, _, _ = make_case(P, W, H, seed=2)
+    dev = torch.device("cuda")
+    plain = CudaRun(inp)
+    # views at float offset 1 of a larger allocation: contiguous, 4-byte aligned, not 16-byte aligned
+    rot_store = torch.zeros(4 * P + 1, device=dev); rot_store[1:] = inp["rotations"].to(dev).reshape(-1)
+    sh_store = torch.zeros(48 * P + 1, device=dev); sh_store[1:] = inp["shs"].to(dev).reshape(-1)
+    rot, sh = rot_store[1:].view(P, 4).requires_grad_(True), sh_store[1:].view(P, 16, 3).requires_grad_(True)
+    assert rot.data_ptr() % 16 != 0 and sh.data_ptr() % 16 != 0
+    means = inp["means3D"].to(dev).requires_grad_(True)
+    out, radii = GaussianRasterizer(settings_from(inp, dev))(
+        means3D=means, means2D=None, shs=sh, normals_precomp=inp["normals"].to(dev), opacities=inp["opacities"].to(dev),
+        scales=inp["scales"].to(dev), rotations=rot, dirs=inp["dirs"].to(dev))
+    assert torch.equal(out, plain.out) and torch.equal(radii, plain.radii)
+    out.sum().backward()
+    torch.cuda.synchronize()
+    assert torch.isfinite(rot.grad).all() and torch.isfinite(sh.grad).all()
+    # C ABI: refused before any launch
+    bufs = _Buffers(dev)
+    o = torch.empty((10, H, W), device=dev); r = torch.empty(P, dtype=torch.int32, device=dev)
+    ins = torch.ones(P, dtype=torch.bool, device=dev)
+    t = {k: inp[k].to(dev).contiguous() for k in ("bg", "means3D", "normals", "opacities", "scales", "viewmatrix", "projmatrix", "dirs", "campos", "shs")}
+    n_host = ctypes.c_int(0)
+    st = N.vcr_rasterize_forward(bufs.cb["geom"], bufs.cb["binning"], bufs.cb["img"], None, P, 3, 16, t["bg"].data_ptr(), W, H,
+                                 t["means3D"].data_ptr(), t["shs"].data_ptr(), None, t["normals"].data_ptr(), None, t["opacities"].data_ptr(),
+                                 t["scales"].data_ptr(), 1.0, rot.data_ptr(), None, t["viewmatrix"].data_ptr(), t["projmatrix"].data_ptr(),
+                                 t["dirs"].data_ptr(), t["campos"].data_ptr(), float(inp["tanfovx"]), float(inp["tanfovy"]), 0,
+                                 o.data_ptr(), r.data_ptr(), ins.data_ptr(), 0, ctypes.byref(n_host),
+                                 ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+    assert st != 0 and b"16-byte aligned" in N.vcr_last_error()
+    torch.cuda.synchronize()

@@ -166,6 +166,9 @@ static int forward_front(vcr_alloc_fn geometry_buffer, vcr_alloc_fn binning_buff
     if (!p.colors_precomp && !p.shs) { vcr_set_error("either shs or colors_precomp is required"); return 1; }
     if (!p.cov3D_precomp && (!p.scales || !p.rotations)) { vcr_set_error("either cov3D_precomp or scales+rotations is required"); return 1; }
     if (!p.colors_precomp && !p.cam_pos) { vcr_set_error("cam_pos is required for SH colours"); return 1; }
+    // float4 accesses (include/vcr_gaus_b200.h "Alignment"): a misaligned pointer would fault inside the kernel
+    if (!p.cov3D_precomp && (reinterpret_cast<size_t>(p.rotations) & 15)) { vcr_set_error("rotations must be 16-byte aligned (read as float4)"); return 1; }
+    if (!p.colors_precomp && p.M == 16 && (reinterpret_cast<size_t>(p.shs) & 15)) { vcr_set_error("shs must be 16-byte aligned when M == 16 (read as float4)"); return 1; }
     p.gx = (p.W + VCR_TILE_X - 1) / VCR_TILE_X;
     p.gy = (p.H + VCR_TILE_Y - 1) / VCR_TILE_Y;
     p.focal_y = p.H / (2.0f * p.tan_fovy);  // rasterizer_impl.cu:227-228
@@ -263,6 +266,14 @@ int vcr_rasterize_backward_chunked(int P, int D, int M, int R, const float* back
         return 1;
     }
     if (!normals_precomp || !inside || !radii || !alpha || !depth) { vcr_set_error("NULL required input"); return 1; }
+    if (scales && ((reinterpret_cast<size_t>(rotations) | reinterpret_cast<size_t>(dL_drot)) & 15)) {
+        vcr_set_error("rotations and dL_drot must be 16-byte aligned (float4 accesses)");
+        return 1;
+    }
+    if (shs && M == 16 && dL_dsh && !dL_dcolor_masked && (reinterpret_cast<size_t>(dL_dsh) & 15)) {
+        vcr_set_error("dL_dsh must be 16-byte aligned when M == 16 (written as float4)");
+        return 1;
+    }
     BwdParams p;
     memset(&p, 0, sizeof(p));
     p.P = P; p.D = D; p.M = M; p.R = R; p.W = width; p.H = height;
@@ -319,6 +330,7 @@ int vcr_sh_grad_from_colors(int P, int D, int M, int world, const float* means3D
                             float* dL_dsh, void* stream) {
     if (P <= 0) return 0;
     if (!means3D || !slices || !dL_dsh || world < 1 || M < 1 || slice_stride < 3LL * P + 3) { vcr_set_error("sh_grad_from_colors: bad argument"); return 1; }
+    if (M == 16 && (reinterpret_cast<size_t>(dL_dsh) & 15)) { vcr_set_error("sh_grad_from_colors: dL_dsh must be 16-byte aligned when M == 16 (written as float4)"); return 1; }
     return vcr_launch_sh_grad_from_colors(P, D, M, world, means3D, slices, slice_stride, dL_dsh, reinterpret_cast<cudaStream_t>(stream));
 }
 

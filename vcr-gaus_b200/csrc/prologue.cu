@@ -158,6 +158,10 @@ extern "C" int vcr_prologue_forward(int P, int n_rest, const float* xyz, const f
         vcr_set_error("prologue_forward: NULL argument");
         return 1;
     }
+    if ((reinterpret_cast<size_t>(rotation_raw) | reinterpret_cast<size_t>(rotations)) & 15) {
+        vcr_set_error("prologue_forward: rotation_raw and rotations must be 16-byte aligned (read / written as float4)");
+        return 1;
+    }
     PrologueParams p;
     memset(&p, 0, sizeof(p));
     p.P = P; p.n_rest = n_rest; p.xyz = xyz; p.features_dc = features_dc; p.features_rest = features_rest;
@@ -177,6 +181,11 @@ extern "C" int vcr_prologue_backward(int P, int n_rest, const float* rotation_ra
         !dL_drotations || !dL_dshs || !dL_dnormals || !dL_dfeatures_dc || (n_rest > 0 && !dL_dfeatures_rest) || !dL_dopacity_raw ||
         !dL_dscaling_raw || !dL_drotation_raw) {
         vcr_set_error("prologue_backward: NULL argument");
+        return 1;
+    }
+    if ((reinterpret_cast<size_t>(rotation_raw) | reinterpret_cast<size_t>(rotations) | reinterpret_cast<size_t>(dL_drotations) |
+         reinterpret_cast<size_t>(dL_drotation_raw)) & 15) {
+        vcr_set_error("prologue_backward: rotation_raw, rotations, dL_drotations and dL_drotation_raw must be 16-byte aligned (float4 accesses)");
         return 1;
     }
     PrologueParams p;

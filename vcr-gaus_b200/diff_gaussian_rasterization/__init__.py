@@ -49,8 +49,10 @@ class _Buffers:
         return self.t.get(name, torch.empty(0, dtype=torch.uint8, device=self.device))
 
 
-def _f32c(t):
-    """contiguous float32 view of an input, the way rasterize_points.cu calls .contiguous() on everything (:119-146)."""
+def _f32c(t, align16=False):
+    """contiguous float32 view of an input, the way rasterize_points.cu calls .contiguous() on everything (:119-146).
+    align16: the kernels read this array as float4 (rotations, shs); a contiguous view that does not start on a 16-byte
+    boundary (a slice of a larger tensor) is copied into a fresh allocation instead of being rejected by the library."""
     if t is None:
         return None
     if t.numel() == 0:
@@ -59,7 +61,10 @@ def _f32c(t):
         raise RuntimeError("diff_gaussian_rasterization (B200 build) needs CUDA tensors; there is no CPU fallback")
     if t.dtype != torch.float32:
         raise RuntimeError(f"expected float32, got {t.dtype}")
-    return t.contiguous()
+    t = t.contiguous()
+    if align16 and t.data_ptr() % 16:
+        t = t.clone()
+    return t
 
 
 def _stream():
@@ -110,9 +115,9 @@ class _RasterizeGaussians(torch.autograd.Function):
         if P == 0:  # rasterize_points.cu:106
             outmap.zero_()
         else:
-            means3D_c, sh_c, colors_c = _f32c(means3D), _f32c(sh), _f32c(colors_precomp)
+            means3D_c, sh_c, colors_c = _f32c(means3D), _f32c(sh, True), _f32c(colors_precomp)
             normals_c, sem_c, opac_c = _f32c(normals_precomp), _f32c(semantics_precomp), _f32c(opacities)
-            scales_c, rot_c, cov_c, dirs_c = _f32c(scales), _f32c(rotations), _f32c(cov3Ds_precomp), _f32c(dirs)
+            scales_c, rot_c, cov_c, dirs_c = _f32c(scales), _f32c(rotations, True), _f32c(cov3Ds_precomp), _f32c(dirs)
             inside_c = inside.contiguous()
             if inside_c.dtype != torch.bool:
                 raise RuntimeError("inside must be a bool tensor")
@@ -173,7 +178,8 @@ class _RasterizeGaussians(torch.autograd.Function):
         f = dict(dtype=torch.float32, device=device)
         def dest(i, shape):
             buf = ctx.grad_out[i] if hasattr(ctx, "grad_out") else None
-            if buf is not None and buf.is_cuda and buf.dtype == torch.float32 and buf.is_contiguous() and tuple(buf.shape) == tuple(shape):
+            if (buf is not None and buf.is_cuda and buf.dtype == torch.float32 and buf.is_contiguous()
+                    and tuple(buf.shape) == tuple(shape) and buf.data_ptr() % 16 == 0):
                 return buf.view(shape)   # a fresh view: autograd can adopt it without a copy
             return torch.empty(shape, **f)
 
@@ -194,10 +200,11 @@ class _RasterizeGaussians(torch.autograd.Function):
             bg, view, proj, campos = _settings_tensors(rs, device)
             grad_c = _f32c(grad_color)
             alpha_c, depth_c = alpha.contiguous(), depth.contiguous()
-            args = (P, int(rs.sh_degree), M, int(ctx.num_rendered), _n.ptr(bg), W, H, _n.ptr(_f32c(means3D)), _n.ptr(_f32c(sh)),
+            sh_c, rot_c = _f32c(sh, True), _f32c(rotations, True)    # (held until the launch has been enqueued)
+            args = (P, int(rs.sh_degree), M, int(ctx.num_rendered), _n.ptr(bg), W, H, _n.ptr(_f32c(means3D)), _n.ptr(sh_c),
                     _n.ptr(_f32c(colors_precomp)), _n.ptr(_f32c(normals_precomp)), _n.ptr(_f32c(semantics_precomp)),
                     alpha_c.data_ptr(), depth_c.data_ptr(), _n.ptr(_f32c(scales)), float(rs.scale_modifier),
-                    _n.ptr(_f32c(rotations)), _n.ptr(_f32c(cov3Ds_precomp)), _n.ptr(view), _n.ptr(proj), _n.ptr(_f32c(dirs)),
+                    _n.ptr(rot_c), _n.ptr(_f32c(cov3Ds_precomp)), _n.ptr(view), _n.ptr(proj), _n.ptr(_f32c(dirs)),
                     _n.ptr(campos), float(rs.tanfovx), float(rs.tanfovy), radii.data_ptr(), geomBuffer.data_ptr(),
                     binningBuffer.data_ptr(), imgBuffer.data_ptr(), grad_c.data_ptr(), g_means2D.data_ptr(),
                     g_means2D_densify.data_ptr(), g_opacity.data_ptr(), _n.ptr(g_colors), g_normals.data_ptr(),
@@ -263,11 +270,12 @@ class _RasterizeGaussians(torch.autograd.Function):
             return count, score, color, radii
         bufs = _Buffers(device)
         bg, view, proj, campos = _settings_tensors(rs, device)
-        sh_c = _f32c(sh)
+        sh_c = _f32c(sh, True)
         M = sh_c.shape[1] if sh_c is not None and sh_c.numel() != 0 else 0
         n_host = ctypes.c_int(0)
+        rot_c = _f32c(rotations, True)
         common = (_n.ptr(_f32c(means3D)), _n.ptr(sh_c), _n.ptr(_f32c(colors_precomp)), _n.ptr(_f32c(opacities)),
-                  _n.ptr(_f32c(scales)), float(rs.scale_modifier), _n.ptr(_f32c(rotations)), _n.ptr(_f32c(cov3Ds_precomp)),
+                  _n.ptr(_f32c(scales)), float(rs.scale_modifier), _n.ptr(rot_c), _n.ptr(_f32c(cov3Ds_precomp)),
                   _n.ptr(view), _n.ptr(proj), _n.ptr(campos), float(rs.tanfovx), float(rs.tanfovy), int(bool(rs.prefiltered)))
         if mode == 1:
             _n.check(_n.vcr_rasterize_count(bufs.cb["geom"], bufs.cb["binning"], bufs.cb["img"], None, P, int(rs.sh_degree), M,

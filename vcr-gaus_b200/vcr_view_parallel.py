@@ -22,6 +22,14 @@ import torch.distributed as dist
 
 # per-Gaussian parameter groups, in bucket order (name, trailing shape)
 PARAM_LAYOUT = (("means3D", (3,)), ("shs", (16, 3)), ("opacities", (1,)), ("scales", (3,)), ("rotations", (4,)))
+# Every group starts on a 16-byte boundary inside the flat tensors: the kernels read `shs` / `rotations` and write
+# `dL_dsh` / `dL_drot` with float4 accesses (include/vcr_gaus_b200.h, "Alignment").  Without the padding the group
+# offsets 3P, 51P, ... would be 16-byte aligned only when P is a multiple of 4 — which it never is after a densification.
+GROUP_ALIGN_FLOATS = 4
+
+
+def _pad4(n: int) -> int:
+    return (int(n) + GROUP_ALIGN_FLOATS - 1) // GROUP_ALIGN_FLOATS * GROUP_ALIGN_FLOATS
 
 
 def init_from_env(backend: Optional[str] = None):
@@ -93,21 +101,30 @@ class GaussianBucket:
             t = tensors[name]
             n = t.numel()
             self.layout.append((name, off, n, tuple(t.shape)))
-            off += n
-        self.numel = off
+            off += _pad4(n)          # the next group starts 16-byte aligned; the (at most 3) pad floats stay zero
         device = device if device is not None else tensors[names[0]].device
-        self.flat = torch.empty(off, dtype=torch.float32, device=device)
-        if grad_storage is None:
-            self.grad_flat = torch.zeros(off, dtype=torch.float32, device=device)
-        else:
-            if grad_storage.dtype != torch.float32 or grad_storage.numel() < off or not grad_storage.is_contiguous():
-                raise ValueError("grad_storage must be a contiguous float32 tensor of at least numel_for(tensors) elements")
-            self.grad_flat = grad_storage.view(-1)[:off].zero_()
-        self.params = {}
+        self._allocate(off, device, grad_storage)
         for name, o, n, shape in self.layout:
             self.flat[o:o + n].copy_(tensors[name].reshape(-1))
+        self._make_views()
+
+    def _allocate(self, numel, device, grad_storage):
+        self.numel = numel
+        self.flat = torch.zeros(numel, dtype=torch.float32, device=device)
+        if grad_storage is None:
+            self.grad_flat = torch.zeros(numel, dtype=torch.float32, device=device)
+        else:
+            if grad_storage.dtype != torch.float32 or grad_storage.numel() < numel or not grad_storage.is_contiguous():
+                raise ValueError("grad_storage must be a contiguous float32 tensor of at least numel_for(tensors) elements")
+            if grad_storage.data_ptr() % 16:
+                raise ValueError("grad_storage must be 16-byte aligned")
+            self.grad_flat = grad_storage.view(-1)[:numel].zero_()
+
+    def _make_views(self):
+        self.params = {}
+        for name, o, n, shape in self.layout:
             p = self.flat[o:o + n].view(shape).requires_grad_(True)
-            if direct:
+            if self.direct:
                 p._vcr_grad_out = self.grad_flat[o:o + n].view(shape)
             else:
                 p.grad = self.grad_flat[o:o + n].view(shape)
@@ -115,7 +132,8 @@ class GaussianBucket:
 
     @staticmethod
     def numel_for(tensors: Dict[str, torch.Tensor], names=None) -> int:
-        return sum(tensors[name].numel() for name in (names if names is not None else [n for n, _ in PARAM_LAYOUT]))
+        """Floats of flat storage a bucket of `tensors` needs (every group padded to a multiple of 4 floats)."""
+        return sum(_pad4(tensors[name].numel()) for name in (names if names is not None else [n for n, _ in PARAM_LAYOUT]))
 
     def zero_grad(self):
         if self.direct:
@@ -126,7 +144,7 @@ class GaussianBucket:
 
     @property
     def floats_per_gaussian(self):
-        return self.numel // max(self.P, 1)
+        return sum(n for _, _, n, _ in self.layout) // max(self.P, 1)
 
 
 class BucketAdam:
@@ -166,14 +184,21 @@ class BucketAdam:
                  "adam_step")
 
 
-def prune_and_grow(bucket: GaussianBucket, keep: torch.Tensor, n_new: int = 0, optimizer: Optional[BucketAdam] = None):
+def prune_and_grow(bucket: GaussianBucket, keep: torch.Tensor, n_new: int = 0, optimizer: Optional[BucketAdam] = None,
+                   grad_storage: Optional[torch.Tensor] = None):
     """Densify / prune on the flat bucket: a new GaussianBucket whose first rows are the rows of `bucket` with keep != 0, in
-    order, followed by `n_new` rows for the caller to fill (clones / splits), and — when `optimizer` is given — a new
-    BucketAdam whose moments are compacted the same way (zeros for the new rows, as cat_tensors_to_optimizer does).
-    Replaces prune_points + densification_postfix of the reference (scene/gaussian_model.py:442-531: ~18 boolean-mask
-    indexing operations and as many torch.cat) by one prefix sum and one gather launch per 8 arrays (vcr_compact_rows).
-    `keep`: bool / uint8 CUDA tensor [P].  One host read of the kept count (the new bucket has to be sized).  Returns
-    (new_bucket, new_optimizer or None, n_kept)."""
+    order, followed by `n_new` rows for the caller to fill (clones / splits; zero until then), and — when `optimizer` is
+    given — a new BucketAdam whose moments are compacted the same way (zeros for the new rows, as
+    cat_tensors_to_optimizer does).  Replaces prune_points + densification_postfix of the reference
+    (scene/gaussian_model.py:442-531: ~18 boolean-mask indexing operations and as many torch.cat) by one prefix sum and
+    one gather launch per 8 arrays (vcr_compact_rows).
+    `keep`: bool / uint8 CUDA tensor [P].  One host read of the kept count (the new bucket has to be sized).
+    `grad_storage`: flat float32 storage for the new gradient bucket (the symmetric allocation of
+    ViewParallel.symmetric_gradient_storage(), which must have been sized for the grown model); default: an ordinary
+    allocation.  The new bucket has NONE of the exchange state of the old one: after this call the view-parallel set-up
+    (ViewParallel.compact_sh_exchange / overlap_gradients / pick_transport) has to be repeated on the new bucket —
+    ViewParallel.exchange_compact() refuses a bucket it was not set up for.
+    Returns (new_bucket, new_optimizer or None, n_kept)."""
     import vcr_native as _n
     if not bucket.flat.is_cuda or not keep.is_cuda:
         raise RuntimeError("prune_and_grow needs CUDA tensors; there is no CPU fallback")
@@ -183,18 +208,15 @@ def prune_and_grow(bucket: GaussianBucket, keep: torch.Tensor, n_new: int = 0, o
         raise ValueError("keep must have one bool / uint8 entry per Gaussian")
     n_kept = int(k8.sum())
     P2 = n_kept + int(n_new)
-    shapes = {name: (P2,) + tuple(shape[1:]) for name, _, _, shape in bucket.layout}
-    # group-major layout of the new bucket: every group is compacted into its own slice
+    # group-major layout of the new bucket: every group is compacted into its own 16-byte aligned slice
     new = GaussianBucket.__new__(GaussianBucket)
     new.direct, new.names, new.P, new.layout = bucket.direct, bucket.names, P2, []
     off = 0
     for name, _, n, shape in bucket.layout:
         per = n // max(P, 1)
-        new.layout.append((name, off, per * P2, shapes[name]))
-        off += per * P2
-    new.numel = off
-    new.flat = torch.empty(off, dtype=torch.float32, device=dev)
-    new.grad_flat = torch.zeros(off, dtype=torch.float32, device=dev)
+        new.layout.append((name, off, per * P2, (P2,) + tuple(shape[1:])))
+        off += _pad4(per * P2)
+    new._allocate(off, dev, grad_storage)
     srcs, dsts, widths = [], [], []
     moments = []
     if optimizer is not None:
@@ -215,14 +237,7 @@ def prune_and_grow(bucket: GaussianBucket, keep: torch.Tensor, n_new: int = 0, o
         _n.check(_n.vcr_compact_rows(P, k8.data_ptr(), n, (ctypes.c_void_p * n)(*srcs), (ctypes.c_void_p * n)(*dsts),
                                      (ctypes.c_int * n)(*widths), scratch.data_ptr(), None,
                                      ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)), "compact_rows")
-    new.params = {}
-    for name, o, cnt, shape in new.layout:
-        p = new.flat[o:o + cnt].view(shape).requires_grad_(True)
-        if new.direct:
-            p._vcr_grad_out = new.grad_flat[o:o + cnt].view(shape)
-        else:
-            p.grad = new.grad_flat[o:o + cnt].view(shape)
-        new.params[name] = p
+    new._make_views()
     return new, opt2, n_kept
 
 
@@ -299,10 +314,13 @@ class ViewParallel:
         return t
 
     # ---- compact exchange of the SH gradient -------------------------------------------------------------------------
-    def exchange_floats(self, tensors: Dict[str, torch.Tensor]) -> int:
-        """Floats of symmetric storage for a bucket of `tensors` plus the all-gather slices of compact_sh_exchange()."""
-        P = tensors["means3D"].shape[0]
-        return (GaussianBucket.numel_for(tensors) + 3) // 4 * 4 + self.world * self._slice_stride(P)
+    def exchange_floats(self, tensors: Dict[str, torch.Tensor], capacity: Optional[int] = None) -> int:
+        """Floats of symmetric storage for a bucket of `tensors` plus the all-gather slices of compact_sh_exchange().
+        capacity: the largest number of Gaussians the model may grow to (densification); default = the current count.  The
+        symmetric allocation cannot be resized, so a trainer that densifies sizes it for the grown model once."""
+        P0 = tensors["means3D"].shape[0]
+        P = max(int(capacity or 0), P0)
+        return sum(_pad4(tensors[n].numel() // max(P0, 1) * P) for n, _ in PARAM_LAYOUT) + self.world * self._slice_stride(P)
 
     @staticmethod
     def _slice_stride(P: int) -> int:
@@ -316,6 +334,7 @@ class ViewParallel:
         all-reduced as before.  Per GPU and step this moves 44 B + world x 12 B per Gaussian instead of 236 B.
         After this call the rasterizer's backward no longer writes the SH gradient into the bucket; call
         exchange_compact(bucket, campos) after the backward in place of allreduce_gradients().  Needs direct=True."""
+        self._compact = None
         if not bucket.direct:
             raise ValueError("compact_sh_exchange needs GaussianBucket(direct=True)")
         if "shs" not in bucket.params or "means3D" not in bucket.params:
@@ -323,7 +342,7 @@ class ViewParallel:
                              "structure belongs to the gradient of the `shs` tensor the rasterizer is called with")
         P, dev = bucket.P, bucket.grad_flat.device
         stride = self._slice_stride(P)
-        off0 = (bucket.numel + 3) // 4 * 4
+        off0 = _pad4(bucket.numel)
         t, _ = getattr(self, "_symm", (None, None))
         if self._in_symmetric_storage(bucket) and t.numel() >= off0 + self.world * stride:
             flat = t.view(-1)[off0:off0 + self.world * stride]
@@ -333,7 +352,7 @@ class ViewParallel:
             self._compact_off0 = None            # not reachable through the multicast mapping: NCCL only
         self._slices = flat.view(self.world, stride)
         self._slices.zero_()
-        self._compact = (P, stride, int(sh_degree))
+        self._compact = (P, stride, int(sh_degree), bucket.grad_flat.data_ptr())
         if self.world > 1:
             bucket.params["shs"]._vcr_sh_compact = self._slices[self.rank, :3 * P].view(P, 3)
 
@@ -343,7 +362,14 @@ class ViewParallel:
         if self.world == 1:
             return
         import vcr_native as _n
-        P, stride, D = self._compact
+        if getattr(self, "_compact", None) is None:
+            raise RuntimeError("exchange_compact: call compact_sh_exchange(bucket) first")
+        P, stride, D, grad_ptr = self._compact
+        if bucket.P != P or bucket.grad_flat.data_ptr() != grad_ptr or getattr(bucket.params["shs"], "_vcr_sh_compact", None) is None:
+            # e.g. the bucket returned by prune_and_grow(): its gradients are not the ones this exchange was laid out for,
+            # and its SH gradient is not being produced in compact form — exchanging would silently diverge the replicas
+            raise RuntimeError("exchange_compact: this bucket is not the one compact_sh_exchange() was set up for "
+                               "(after prune_and_grow, call compact_sh_exchange / pick_transport again on the new bucket)")
         transport = transport or self.transport
         own = self._slices[self.rank]
         own[3 * P:3 * P + 3].copy_(campos.reshape(-1)[:3])
