@@ -1,154 +1,51 @@
 #!/usr/bin/env python
 """bench.py — the hot path of VCR-GauS on B200: forward + backward rasterization + D-Normal loss, per view.
 
-    python bench.py --gpus N --steps K --warmup W [--impl ours|reference|reference-cpu]
+    python bench.py --gpus N --steps K --warmup W [--impl ours|reference|reference-cpu] [--config metric|A|B|C|D|E]
 
-Workload (BASELINE.json `metric`: "fwd+bwd rasterize ms/view (1M Gauss, 1080p); train views/s at 1/2/4/8 GPU"):
+Default workload (BASELINE.json `metric`: "fwd+bwd rasterize ms/view (1M Gauss, 1080p); train views/s at 1/2/4/8 GPU"):
 a seeded synthetic scene of 1,000,000 Gaussians (SH degree 3), 1920x1080 views with ray/plane-intersection depth
 (`dirs`, the configured default of every reconstruction config, configs/reconstruct.yaml:10), loss = L1(RGB) +
-mono-normal + confidence-weighted depth-normal (D-Normal), backward into every per-Gaussian parameter.
-One "step" = one such view per GPU (fwd + loss + bwd); with N > 1 each rank renders a different view of the same
-replicated scene and the flat gradient bucket + densification statistics are all-reduced with NCCL (weak scaling).
-`value` = views/s over all ranks (so ms/view at N = 1 is `ms_per_step`).  SSIM, the per-Gaussian prologue of render() and
-the Adam update are outside the hot path and are not part of a step in either arm; the complete
-training iteration including them is timed beside it at N = 1 and reported as `full_step` (both arms).
+mono-normal + confidence-weighted depth-normal (D-Normal), backward into every per-Gaussian parameter, densification
+statistics updated every view.  One "step" = one such view per GPU (fwd + loss + bwd); with N > 1 each rank renders a
+different view of the same replicated scene and the per-Gaussian gradients are summed over the ranks (weak scaling).
+`value` = views/s over all ranks (so ms/view at N = 1 is `ms_per_step`).  `--config` selects the other BASELINE.json
+configurations (bench_common.CONFIGS): A (10k / 256x256), B (300k / 800x600 / 49 views / complete training iteration),
+C (1.5M / 1080p / training with densification), D (5M / 1256x828), E (one point of the rasterizer sweep, fwd+bwd only).
 
-Arms
-  ours           this repository (GaussianRasterizer -> ctypes -> libvcr_gaus_b200.so, fused D-Normal kernels)
-  reference      the UNMODIFIED reference CUDA extension (oracle/_ref, built from /root/reference by oracle/build_ref.sh)
-                 driven through its `_C` module, with the reference's PyTorch D-Normal op chain — same scene, same
-                 views, same loss, same GPU.  (The reference has no CPU implementation of this path, SURVEY.md §8c;
-                 the arm the north star asks to beat is its CUDA rasterizer "on the same B200".)
+Arms (bench_common.py holds what they share; each arm's process imports only its own implementation)
+  ours           this repository (GaussianRasterizer -> ctypes -> libvcr_gaus_b200.so, fused loss / prologue / Adam kernels)
+  reference      bench_ref.py: the reference's own CUDA extension, Python wrapper, GaussianModel, render() and loss
+                 utilities from oracle/_ref — same scene, same views, same loss, same GPU.  (The reference has no CPU
+                 implementation of this path; the arm the north star asks to beat is its CUDA rasterizer
+                 "on the same B200".)
   reference-cpu  the CPU oracle (oracle/vcr_oracle.c, a port) on all host cores; also timed, on a bounded sample,
                  as `cpu_baseline` inside the default arm at N = 1.
 """
-import argparse
 import gc
 import json
 import math
 import os
 import sys
-import threading
 import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
-for _p in (ROOT, os.path.join(ROOT, "vcr-gaus_b200"), os.path.join(ROOT, "tests")):
-    if _p not in sys.path:
-        sys.path.insert(0, _p)
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
 
 import torch  # noqa: E402
 import torch.distributed as dist  # noqa: E402
-import torch.nn.functional as F  # noqa: E402
 
-LAMBDA_DN = 0.015   # loss_weight.depth_normal, configs/tnt/base.yaml:12
-LAMBDA_MONO = 0.01  # loss_weight.mono_normal order of magnitude (configs/reconstruct.yaml)
-EXP_T = 0.5
-METRIC = "train views/s (fwd+bwd rasterize + D-Normal loss; 1M Gaussians, 1920x1080)"
+import bench_common as BC  # noqa: E402
 
 
-def parse():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=30)
-    ap.add_argument("--warmup", type=int, default=10)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "reference-cpu"])
-    ap.add_argument("--gaussians", type=int, default=1_000_000)
-    ap.add_argument("--width", type=int, default=1920)
-    ap.add_argument("--height", type=int, default=1080)
-    ap.add_argument("--views", type=int, default=8, help="distinct camera poses per rank, cycled")
-    ap.add_argument("--footprint", type=float, default=2.0, help="scale multiplier (R/P in [6,10] at the default size)")
-    ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-profile", action="store_true", help="do not bracket kernels with CUDA events")
-    return ap.parse_args()
+def _product_paths():
+    for p in (os.path.join(ROOT, "vcr-gaus_b200"),):
+        if p not in sys.path:
+            sys.path.insert(0, p)
 
 
 # ------------------------------------------------------------------------------------------------------------------
-class ClockSampler:
-    """SM clock and throttle reasons DURING the timed region, through NVML from the benchmarking thread itself.
-
-    Polling from a side thread or from an `nvidia-smi -lms` process was tried first and dropped: NVML queries contend
-    with this process's CUDA launches for the driver lock and inflated a 90 ms timed region by tens of milliseconds
-    (up to 10x with 50 ms polling); even from this thread an uncached query costs 3-10 ms of host time (tools/nvml_probe.py).
-    So one sample is taken per timed region: right after the last launch and the closing event have been enqueued, while
-    the GPU is still executing the last timed step."""
-
-    def __init__(self, index):
-        self.samples, self.reasons, self.max_mhz, self.ok = [], set(), None, False
-        try:
-            import pynvml
-            pynvml.nvmlInit()
-            self.nv = pynvml
-            try:
-                uuid = str(torch.cuda.get_device_properties(index).uuid)
-                self.h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid) if not uuid.startswith("GPU-") else uuid)
-            except Exception:
-                self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
-            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
-            self.names = {
-                getattr(pynvml, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
-                getattr(pynvml, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
-                getattr(pynvml, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
-                getattr(pynvml, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
-            }
-            self.ok = True
-        except Exception:  # pragma: no cover
-            self.ok = False
-
-    def sample(self):
-        if not self.ok:
-            return
-        nv = self.nv
-        try:
-            self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
-            try:
-                r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
-            except Exception:
-                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
-            for bit, name in self.names.items():
-                if r & bit:
-                    self.reasons.add(name)
-        except Exception:
-            pass
-
-    def result(self):
-        s = sorted(self.samples)
-        return {"sm_mhz": (s[len(s) // 2] if s else None), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
-                "samples": len(s)}
-
-
-# ------------------------------------------------------------------------------------------------------------------
-def build_scene(args):
-    import vcr_synth as S
-    scene = S.make_scene(args.gaussians, seed=0)
-    scene.scales.mul_(args.footprint)
-    return scene
-
-
-def build_views(args, scene, world, view_ids, light=False):
-    """Views `view_ids` of the ring of args.views * world cameras, on the CPU.  light=True: camera and rasterizer inputs only
-    (enough to measure a view's cost), no ground-truth images."""
-    import vcr_synth as S
-    views = []
-    n_total = args.views * world
-    for gid in view_ids:
-        cam = S.make_camera(args.width, args.height, idx=gid, n_views=n_total)
-        view = dict(id=gid, cam=cam, inp=S.raster_inputs(scene, cam, use_dirs=True, use_sem=False, seed=gid // world))
-        if not light:
-            g = torch.Generator().manual_seed(10_000 + gid)
-            H, W = args.height, args.width
-            gt_image = torch.rand((3, H, W), generator=g)
-            gt_normal = F.normalize(torch.randn((H, W, 3), generator=g) * 0.4 + torch.tensor([0.0, 0.0, -1.0]), dim=-1)
-            view.update(gt_image=gt_image.contiguous(), gt_normal=gt_normal.contiguous())
-        views.append(view)
-    return views
-
-
-def build_workload(args, rank, world):
-    """Scene (identical on every rank) + this rank's default shard of the views (every world-th camera of the ring)."""
-    scene = build_scene(args)
-    return scene, build_views(args, scene, world, [v * world + rank for v in range(args.views)])
-
-
 def measure_view_costs(args, bucket, views, dev):
     """Milliseconds of one rasterizer forward+backward of each view (CUDA events, best of two after one untimed pass) — what
     a trainer knows about a view from the previous epoch.  The instance count R alone predicts it to ~5 % only."""
@@ -180,247 +77,55 @@ def measure_view_costs(args, bucket, views, dev):
     return costs
 
 
-def ref_dnormal_chain(depth, K, gt_normal, render_normal, exp_t):
-    """The reference's D-Normal chain (tools/normal_utils.py:24-41, tools/graphics_utils.py:111-131,
-    tools/loss_utils.py:122-142, trainer.py:266-280), no mask (mask = all ones)."""
-    _, H, W = depth.shape
-    dev = depth.device
-    vx = torch.arange(W, dtype=torch.float32, device=dev).add_(0.5) / (W - 1)
-    vy = torch.arange(H, dtype=torch.float32, device=dev).add_(0.5) / (H - 1)
-    vy, vx = torch.meshgrid(vy, vx, indexing="ij")
-    ndc = torch.stack([vx, vy, depth[0]], dim=-1)
-    inv_scale = torch.tensor([[W - 1, H - 1]], device=dev)
-    cam_z = ndc[..., 2:3]
-    cam = torch.cat([ndc[..., :2] * inv_scale * cam_z, cam_z], dim=-1) @ torch.inverse(K.t())
-    dy = torch.gradient(cam, dim=0)[0]
-    dx = torch.gradient(cam, dim=1)[0]
-    est = F.normalize(torch.cross(dx, dy, dim=-1), p=2, dim=-1)
-    rn = render_normal.detach()
-    w = torch.exp((torch.sum(rn * gt_normal, dim=-1) - 1) / exp_t).detach()
-    mask = torch.ones((H, W), dtype=torch.bool, device=dev)
-    e, g, ww = est[mask], gt_normal[mask], w[mask]
-    return (ww * torch.abs(e - g).sum(dim=-1)).mean() + (ww * (1.0 - torch.sum(e * g, dim=-1))).mean()
-
-
-class RefRasterFn(torch.autograd.Function):
-    """Autograd shim over the reference `_C` module, argument tuples as in DGR/diff_gaussian_rasterization/__init__.py:186-231,
-    393-458 (the reference's Python wrapper is not copied; this builds the same calls)."""
-
-    @staticmethod
-    def forward(ctx, C, means3D, shs, normals, opac, scales, rots, dirs, inside, st):
-        e = torch.Tensor([])
-        R, out, radii, geom, binning, img = C.rasterize_gaussians(
-            st["bg"], means3D, e, normals, e, opac, scales, rots, 1.0, e, st["view"], st["proj"], dirs, st["tanx"], st["tany"],
-            st["H"], st["W"], shs, st["deg"], st["campos"], False, inside, False)
-        ctx.C, ctx.st, ctx.R = C, st, R
-        ctx.save_for_backward(means3D, shs, normals, scales, rots, dirs, inside, radii, geom, binning, img, out)
-        return out, radii
-
-    @staticmethod
-    def backward(ctx, g, _):
-        means3D, shs, normals, scales, rots, dirs, inside, radii, geom, binning, img, out = ctx.saved_tensors
-        st, e = ctx.st, torch.Tensor([])
-        (g2d, g2dd, gcol, gnrm, gobj, gop, g3d, gcov, gsh, gsc, grot) = ctx.C.rasterize_gaussians_backward(
-            st["bg"], means3D, radii, e, normals, e, scales, rots, 1.0, e, st["view"], st["proj"], dirs, st["tanx"], st["tany"],
-            g.contiguous(), shs, st["deg"], st["campos"], geom, ctx.R, binning, img, out[7:8], out[3:4], inside, False)
-        return None, g3d, gsh, gnrm, gop, gsc, grot, None, None, None
-
-
-def ref_prologue_chain(xyz, fdc, frest, o_raw, s_raw, r_raw, cam_center, R_w2c):
-    """What the reference's render() does per Gaussian before the rasterizer call (scene/gaussian_model.py:125-192,
-    tools/general_utils.py:98-119, gaussian_renderer/__init__.py:95-101; is_all=True), as the same PyTorch op chain."""
-    opacity, scaling, rotation = torch.sigmoid(o_raw), torch.exp(s_raw), F.normalize(r_raw)
-    shs = torch.cat((fdc, frest), dim=1)
-    r = rotation
-    norm = torch.sqrt(r[:, 0] * r[:, 0] + r[:, 1] * r[:, 1] + r[:, 2] * r[:, 2] + r[:, 3] * r[:, 3])
-    q = r / norm[:, None]
-    R = torch.zeros((q.size(0), 3, 3), device=q.device)
-    w, x, y, z = q[:, 0], q[:, 1], q[:, 2], q[:, 3]
-    R[:, 0, 0] = 1 - 2 * (y * y + z * z); R[:, 0, 1] = 2 * (x * y - w * z); R[:, 0, 2] = 2 * (x * z + w * y)
-    R[:, 1, 0] = 2 * (x * y + w * z); R[:, 1, 1] = 1 - 2 * (x * x + z * z); R[:, 1, 2] = 2 * (y * z - w * x)
-    R[:, 2, 0] = 2 * (x * z - w * y); R[:, 2, 1] = 2 * (y * z + w * x); R[:, 2, 2] = 1 - 2 * (x * x + y * y)
-    axis = torch.argmin(scaling, dim=-1)
-    normal = R.gather(2, axis[:, None, None].expand(-1, 3, -1)).squeeze(-1)
-    view_dir = xyz - cam_center
-    normal = normal * ((((view_dir * normal).sum(dim=-1) > 0) * 1 - 0.5) * 2)[..., None]
-    return opacity, scaling, rotation, shs, normal @ R_w2c.transpose(0, 1)
-
-
-def time_prologue(args, scene, view, dev, iters=20):
-    """render()'s per-Gaussian prologue, forward + backward: this library's fused kernels vs the reference's PyTorch chain.
-    Not part of the step (both arms of the bench start from post-activation tensors); reported beside it."""
-    from vcr_prologue import gaussian_prologue
-    shs = scene.shs.to(dev)
-    leaves = [t.requires_grad_(True) for t in (shs[:, :1].clone(), shs[:, 1:].clone(),
-                                               torch.logit(scene.opacities.to(dev).clamp(1e-4, 1 - 1e-4)),
-                                               torch.log(scene.scales.to(dev)), scene.rotations.to(dev) * 1.3)]
-    xyz = scene.means3D.to(dev)
-    cc = view["inp"]["campos"].to(dev)
-    M = view["inp"]["viewmatrix"].to(dev)[:3, :3].t().contiguous()
-    out = {}
-    cot = None
-    for name, fn in (("fused_ms", gaussian_prologue), ("pytorch_chain_ms", ref_prologue_chain)):
-        for k in range(iters + 3):
-            if k == 3:
-                torch.cuda.synchronize(dev)
-                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                e0.record()
-            res = fn(xyz, *leaves, cc, M)
-            if cot is None:
-                cot = [torch.randn_like(t) for t in res]
-            torch.autograd.grad(res, leaves, cot)
-        e1.record()
-        torch.cuda.synchronize(dev)
-        out[name] = e0.elapsed_time(e1) / iters
-    out["what"] = f"forward+backward of render()'s per-Gaussian prologue, P = {xyz.shape[0]}; not part of the step"
-    return out
-
-
-def ref_ssim_chain(img1, img2):
-    """tools/loss_utils.py:47-92 restated (11x11 Gaussian window, grouped conv2d), for the reference arm of `full_step`."""
-    gauss = torch.Tensor([math.exp(-(x - 5) ** 2 / float(2 * 1.5 ** 2)) for x in range(11)])
-    g1 = (gauss / gauss.sum()).unsqueeze(1)
-    window = g1.mm(g1.t()).float().unsqueeze(0).unsqueeze(0).expand(3, 1, 11, 11).contiguous().to(img1.device)
-    mu1, mu2 = F.conv2d(img1, window, padding=5, groups=3), F.conv2d(img2, window, padding=5, groups=3)
-    mu1_sq, mu2_sq, mu1_mu2 = mu1.pow(2), mu2.pow(2), mu1 * mu2
-    s1 = F.conv2d(img1 * img1, window, padding=5, groups=3) - mu1_sq
-    s2 = F.conv2d(img2 * img2, window, padding=5, groups=3) - mu2_sq
-    s12 = F.conv2d(img1 * img2, window, padding=5, groups=3) - mu1_mu2
-    C1, C2 = 0.01 ** 2, 0.03 ** 2
-    return (((2 * mu1_mu2 + C1) * (2 * s12 + C2)) / ((mu1_sq + mu2_sq + C1) * (s1 + s2 + C2))).mean()
-
-
-LAMBDA_DSSIM = 0.2      # configs/reconstruct.yaml lambda_dssim
-RAW_NAMES = ("xyz", "f_dc", "f_rest", "opacity", "scaling", "rotation")
-RAW_LRS = dict(xyz=1.6e-4, f_dc=2.5e-3, f_rest=2.5e-3 / 20, opacity=0.05, scaling=5e-3, rotation=1e-3)
-
-
-def time_full_step(args, impl, scene, stepper, dev, steps):
-    """One COMPLETE training iteration per view, from the raw parameters to the updated raw parameters, the way trainer.py
-    runs it: per-Gaussian prologue -> rasterize -> loss (L1 + SSIM + mono-normal + D-Normal) -> backward -> Adam.
-    `ours`: fused prologue, fused view loss + fused SSIM, BucketAdam.  `reference`: the reference's PyTorch chains around its
-    CUDA rasterizer and torch.optim.Adam(eps=1e-15) with its six groups.  Reported beside the bench metric (whose step is
-    the rasterizer + D-Normal hot path only), single GPU."""
-    import vcr_view_parallel as VP
-    shs = scene.shs.to(dev)
-    raw = dict(xyz=scene.means3D.to(dev), f_dc=shs[:, :1].contiguous(), f_rest=shs[:, 1:].contiguous(),
-               opacity=torch.logit(scene.opacities.to(dev).clamp(1e-4, 1 - 1e-4)), scaling=torch.log(scene.scales.to(dev)),
-               rotation=scene.rotations.to(dev).clone())
-    H, W = args.height, args.width
-    if impl == "ours":
-        from vcr_dnormal import ssim, view_loss
-        from vcr_prologue import gaussian_prologue
-        bucket = VP.GaussianBucket(raw, device=dev, names=RAW_NAMES, direct=True)   # kernels write the gradients into the bucket
-        p, opt = bucket.params, VP.BucketAdam(bucket, RAW_LRS)
-    else:
-        p = {k: v.clone().requires_grad_(True) for k, v in raw.items()}
-        opt = torch.optim.Adam([{"params": [p[k]], "lr": RAW_LRS[k], "name": k} for k in RAW_NAMES], lr=0.0, eps=1e-15)
-
-    def one(i):
-        k = i % len(stepper.views)
-        d = stepper.devv[k]
-        cam = d["cam"]
-        view, proj, campos, bg = cam[0:16].view(4, 4), cam[16:32].view(4, 4), cam[32:35], cam[35:38]
-        R_w2c = view[:3, :3].t()
-        gt_n = d["gt_normal"]
-        if impl == "ours":
-            opac, scales, rots, sh, normals = gaussian_prologue(p["xyz"], p["f_dc"], p["f_rest"], p["opacity"], p["scaling"], p["rotation"],
-                                                                campos, R_w2c)
-            rs = stepper.GRS(image_height=H, image_width=W, tanfovx=stepper.tanx, tanfovy=stepper.tany, bg=bg, scale_modifier=1.0,
-                             viewmatrix=view, projmatrix=proj, sh_degree=3, campos=campos, prefiltered=False, debug=False, f_count=0)
-            means2D = torch.zeros_like(p["xyz"], requires_grad=True)
-            out, radii = stepper.GR(rs)(means3D=p["xyz"], means2D=means2D, means2D_densify=torch.zeros_like(p["xyz"], requires_grad=True),
-                                        shs=sh, normals_precomp=normals, opacities=opac, scales=scales, rotations=rots,
-                                        dirs=stepper.dirs, inside=stepper.inside)
-            loss = view_loss(out, d["gt_image"], gt_n, stepper.K4, w_l1=1.0 - LAMBDA_DSSIM, w_mono=LAMBDA_MONO, w_dn=LAMBDA_DN, exp_t=EXP_T)
-            loss = loss + LAMBDA_DSSIM * (1.0 - ssim(out[:3], d["gt_image"]))
-            bucket.zero_grad()
-            loss.backward()
-            opt.step()
-        else:
-            opac, scales, rots, sh, normals = ref_prologue_chain(p["xyz"], p["f_dc"], p["f_rest"], p["opacity"], p["scaling"], p["rotation"],
-                                                                 campos, R_w2c)
-            st = dict(bg=bg, view=view, proj=proj, campos=campos, tanx=stepper.tanx, tany=stepper.tany, H=H, W=W, deg=3)
-            out, radii = RefRasterFn.apply(stepper.C, p["xyz"], sh, normals, opac, scales, rots, stepper.dirs, stepper.inside, st)
-            image, depth, normal, _alpha, _sem = out.split([3, 1, 3, 1, 2], dim=0)
-            rn = F.normalize(normal.permute(1, 2, 0), dim=-1)
-            loss = (1.0 - LAMBDA_DSSIM) * (image - d["gt_image"]).abs().mean() + LAMBDA_DSSIM * (1.0 - ref_ssim_chain(image[None], d["gt_image"][None]))
-            loss = loss + LAMBDA_MONO * ((rn - gt_n).abs().sum(-1).mean() + (1.0 - (rn * gt_n).sum(-1)).mean())
-            loss = loss + LAMBDA_DN * ref_dnormal_chain(depth, stepper.K, gt_n, rn, EXP_T)
-            opt.zero_grad(set_to_none=True)
-            loss.backward()
-            opt.step()
-
-    for i in range(max(3 * len(stepper.views), 24)):
-        one(i)
-    torch.cuda.synchronize(dev)
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for i in range(steps):
-        one(i)
-    e1.record()
-    torch.cuda.synchronize(dev)
-    ms = e0.elapsed_time(e1) / steps
-    return {"ms_per_step": ms, "views_per_s": 1e3 / ms, "steps": steps,
-            "includes": "raw parameters -> prologue -> rasterize fwd -> L1 + SSIM + mono-normal + D-Normal -> backward -> Adam (6 groups, eps 1e-15)"}
-
-
-def clone_params(scene, dev, direct=False, vp=None):
-    """Parameters + flat gradient bucket.  With a ViewParallel layer at N > 1 the bucket is placed in symmetric memory so
-    that the gradient exchange can go through the NVSwitch multicast kernel (VCR_BENCH_TRANSPORT=nccl forces NCCL)."""
+def clone_params(scene, dev, vp):
+    """Rasterizer-input parameters + flat gradient bucket.  With a ViewParallel layer at N > 1 the bucket is placed in
+    symmetric memory so that the gradient exchange can go through the NVSwitch multicast kernel (VCR_BENCH_TRANSPORT=nccl
+    forces NCCL)."""
     import vcr_view_parallel as VP
     tensors = dict(means3D=scene.means3D.to(dev), shs=scene.shs.to(dev), opacities=scene.opacities.to(dev),
                    scales=scene.scales.to(dev), rotations=scene.rotations.to(dev))
     store = None
-    if vp is not None and vp.world > 1 and direct and os.environ.get("VCR_BENCH_TRANSPORT", "multimem") == "multimem":
+    if vp.world > 1 and os.environ.get("VCR_BENCH_TRANSPORT", "multimem") == "multimem":
         # (symmetric storage is also fine for NCCL, so it is allocated whenever the multicast kernel may be chosen)
         store = vp.symmetric_gradient_storage(vp.exchange_floats(tensors), dev)
-    b = VP.GaussianBucket(tensors, device=dev, direct=direct, grad_storage=store)
+    b = VP.GaussianBucket(tensors, device=dev, direct=True, grad_storage=store)
     b.transport = "multimem" if store is not None else "nccl"
-    b.compact = bool(vp is not None and vp.world > 1 and direct and os.environ.get("VCR_BENCH_COMPACT", "1") == "1")
+    b.compact = bool(vp.world > 1 and os.environ.get("VCR_BENCH_COMPACT", "1") == "1")
     if b.compact:
         vp.compact_sh_exchange(b, sh_degree=3)     # exchange 3 instead of 48 floats per Gaussian for the SH coefficients
     return b
 
 
-class Stepper:
-    """One view: (optional H2D of the per-view inputs) -> forward -> loss -> backward -> (N>1: all-reduce) -> loss readback."""
+class HotPathStepper:
+    """One view: (optional H2D of the per-view inputs) -> forward -> loss -> backward -> (N>1: gradient exchange) ->
+    densification statistics -> loss readback."""
 
-    def __init__(self, args, impl, bucket, views, dev, vp):
-        self.args, self.impl, self.bucket, self.dev, self.vp = args, impl, bucket, dev, vp
+    def __init__(self, args, scene, views, dev, vp):
+        from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+        self.GRS, self.GR = GaussianRasterizationSettings, GaussianRasterizer
+        self.args, self.dev, self.vp = args, dev, vp
+        self.bucket = bucket = clone_params(scene, dev, vp)
         self.views = views
+        self.feed = BC.ViewFeeder(views, dev, extra=("dL_dout",) if args.step_kind == "raster" else ())
         P = bucket.P
         self.inside = torch.ones(P, dtype=torch.bool, device=dev)
         self.xyz_gradient_accum = torch.zeros((P, 1), device=dev)
         self.denom = torch.zeros((P, 1), device=dev)
         self.max_radii2D = torch.zeros((P,), device=dev)
-        # per-view host (pinned) and device copies of everything that changes with the view
-        self.host, self.devv = [], []
-        for v in views:
-            inp = v["inp"]
-            h = dict(gt_image=v["gt_image"].pin_memory(), gt_normal=v["gt_normal"].pin_memory(),
-                     cam=torch.cat([inp["viewmatrix"].reshape(-1), inp["projmatrix"].reshape(-1), inp["campos"].reshape(-1),
-                                    inp["bg"].reshape(-1)]).pin_memory())
-            self.host.append(h)
-            self.devv.append({k: t.to(dev) for k, t in h.items()})
         inp0 = views[0]["inp"]
         # all views share intrinsics and size, so `dirs` is per scene, like scene.dirs (scene/__init__.py:99-102)
         self.dirs = inp0["dirs"].to(dev)
-        self.K = views[0]["cam"].intr.to(dev)
-        self.K_host = views[0]["cam"].intr
-        self.K4 = (float(self.K_host[0, 0]), float(self.K_host[1, 1]), float(self.K_host[0, 2]), float(self.K_host[1, 2]))
+        K = views[0]["cam"].intr
+        self.K4 = (float(K[0, 0]), float(K[1, 1]), float(K[0, 2]), float(K[1, 2]))
         self.tanx, self.tany = inp0["tanfovx"], inp0["tanfovy"]
-        self.h2d_bytes = sum(t.numel() * t.element_size() for t in self.host[0].values())
         self.d2h_bytes = 4
         self.loss_host = torch.zeros(1).pin_memory()
-        self.copy_stream = torch.cuda.Stream(device=dev)
-        self._prefetched = None
         self.diag_events = None
         self.skip = os.environ.get("VCR_BENCH_SKIP", "")   # diagnosis only: "grads", "stats" or "grads,stats"
         # N > 1: pipeline the gradient all-reduce with the per-Gaussian backward stage in this many ranges (0 = one
-        # all-reduce after the backward)
+        # exchange after the backward)
         self.chunks, self.exchange_ms = 0, {}
-        if impl == "ours" and vp.world > 1:
+        if vp.world > 1:
             self.exchange_ms = vp.pick_transport(bucket)          # NCCL or the multicast kernel, whichever is faster here
             forced = os.environ.get("VCR_BENCH_TRANSPORT")
             if forced in ("nccl", "multimem") and (forced == "nccl" or bucket.transport == "multimem"):
@@ -430,74 +135,24 @@ class Stepper:
             self.chunks = 0 if bucket.compact else int(os.environ.get("VCR_BENCH_CHUNKS", "4" if vp.transport == "multimem" else "0"))
         if self.chunks > 0 and "grads" not in self.skip:
             vp.overlap_gradients(bucket, n_chunks=self.chunks, transport=vp.transport)
-        if impl == "reference":
-            import ref_ab
-            self.C = ref_ab.load()
-            if self.C is None:
-                raise RuntimeError("oracle/_ref reference extension is not available")
-        else:
-            from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
-            self.GRS, self.GR = GaussianRasterizationSettings, GaussianRasterizer
         # normals_precomp depends on the view (flip towards the camera + w2c rotation): precomputed per view on device
         self.normals = [v["inp"]["normals"].to(dev).requires_grad_(True) for v in views]
 
-    def _issue_prefetch(self, i):
-        k = i % len(self.views)
-        with torch.cuda.stream(self.copy_stream):
-            d = {name: t.to(self.dev, non_blocking=True) for name, t in self.host[k].items()}
-            ev = torch.cuda.Event()
-            ev.record(self.copy_stream)
-        # keep the tensors alive on the compute stream's timeline
-        for t in d.values():
-            t.record_stream(torch.cuda.current_stream())
-        self._prefetched = (i, d, ev)
-
-    def step(self, i, e2e):
-        k = i % len(self.views)
+    def step(self, i, e2e=False):
+        from vcr_dnormal import view_loss
+        a, vp = self.args, self.vp
+        k = i % self.feed.n
         p = self.bucket.params
-        if e2e:
-            # per-view inputs come from pinned host memory every step; like a data loader with prefetch depth 1 the
-            # copy of view i+1 is issued on a side stream while view i is being rendered (the copies stay inside the
-            # timed region, they are just overlapped)
-            if self._prefetched is None or self._prefetched[0] != i:
-                self._issue_prefetch(i)
-            _, d, ev = self._prefetched
-            torch.cuda.current_stream().wait_event(ev)
-            self._issue_prefetch(i + 1)
-        else:
-            d = self.devv[k]
-        cam = d["cam"]
-        view, proj, campos, bg = cam[0:16].view(4, 4), cam[16:32].view(4, 4), cam[32:35], cam[35:38]
-        H, W = self.args.height, self.args.width
+        d = self.feed.get(i, e2e)
+        view, proj, campos, bg = BC.ViewFeeder.camera(d)
         normals = self.normals[k]
-        if self.impl == "reference":
-            st = dict(bg=bg, view=view, proj=proj, campos=campos, tanx=self.tanx, tany=self.tany, H=H, W=W, deg=3)
-            out, radii = RefRasterFn.apply(self.C, p["means3D"], p["shs"], normals, p["opacities"], p["scales"], p["rotations"],
-                                           self.dirs, self.inside, st)
-            means2D_densify = None
-        else:
-            rs = self.GRS(image_height=H, image_width=W, tanfovx=self.tanx, tanfovy=self.tany, bg=bg, scale_modifier=1.0,
-                          viewmatrix=view, projmatrix=proj, sh_degree=3, campos=campos, prefiltered=False, debug=False, f_count=0)
-            means2D = torch.zeros_like(p["means3D"], requires_grad=True)
-            means2D_densify = torch.zeros_like(p["means3D"], requires_grad=True)
-            out, radii = self.GR(rs)(means3D=p["means3D"], means2D=means2D, means2D_densify=means2D_densify, shs=p["shs"],
-                                     normals_precomp=normals, opacities=p["opacities"], scales=p["scales"],
-                                     rotations=p["rotations"], dirs=self.dirs, inside=self.inside)
-        gt_n = d["gt_normal"]
-        if self.impl == "reference":
-            # channel split exactly like render() (gaussian_renderer/__init__.py:122-123, 133-134), losses as in trainer.py
-            image, depth, normal, _alpha, _sem = out.split([3, 1, 3, 1, 2], dim=0)
-            rn = F.normalize(normal.permute(1, 2, 0), dim=-1)
-            loss = (image - d["gt_image"]).abs().mean()
-            loss = loss + LAMBDA_MONO * ((rn - gt_n).abs().sum(-1).mean() + (1.0 - (rn * gt_n).sum(-1)).mean())
-            loss = loss + LAMBDA_DN * ref_dnormal_chain(depth, self.K, gt_n, rn, EXP_T)
-        else:
-            # the same three terms through this repository's public loss API (one fused kernel per direction).  Mean over
-            # ranks = SUM all-reduce of the gradients of loss / world: the 1/world goes into the loss weights, so there is
-            # neither a division pass over the bucket nor an extra scaling kernel
-            from vcr_dnormal import view_loss
-            sc = 1.0 / self.vp.world
-            loss = view_loss(out, d["gt_image"], gt_n, self.K4, w_l1=sc, w_mono=LAMBDA_MONO * sc, w_dn=LAMBDA_DN * sc, exp_t=EXP_T)
+        rs = self.GRS(image_height=a.height, image_width=a.width, tanfovx=self.tanx, tanfovy=self.tany, bg=bg, scale_modifier=1.0,
+                      viewmatrix=view, projmatrix=proj, sh_degree=3, campos=campos, prefiltered=False, debug=False, f_count=0)
+        means2D = torch.zeros_like(p["means3D"], requires_grad=True)
+        means2D_densify = torch.zeros_like(p["means3D"], requires_grad=True)
+        out, radii = self.GR(rs)(means3D=p["means3D"], means2D=means2D, means2D_densify=means2D_densify, shs=p["shs"],
+                                 normals_precomp=normals, opacities=p["opacities"], scales=p["scales"],
+                                 rotations=p["rotations"], dirs=self.dirs, inside=self.inside)
         self.bucket.zero_grad()
         normals.grad = None
         ev = self.diag_events
@@ -505,70 +160,150 @@ class Stepper:
             e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
             ev.append(e)
             e[0].record()
-        if self.impl == "reference" and self.vp.world > 1:
-            (loss / self.vp.world).backward()
+        if a.step_kind == "raster":
+            out.backward(d["dL_dout"])
+            loss = out[0, 0, 0].detach()
         else:
-            loss.backward()     # ours, N > 1: the chunk hook queues the gradient exchange range by range during this call
+            # the three terms through this repository's public loss API (one fused kernel per direction).  Mean over ranks =
+            # SUM all-reduce of the gradients of loss / world: the 1/world goes into the loss weights, so there is neither a
+            # division pass over the bucket nor an extra scaling kernel
+            sc = 1.0 / vp.world
+            loss = view_loss(out, d["gt_image"], d["gt_normal"], self.K4, w_l1=sc, w_mono=BC.W_MONO * sc, w_dn=BC.W_DN * sc, exp_t=BC.EXP_T)
+            loss.backward()     # N > 1 with chunks: the chunk hook queues the gradient exchange range by range during this call
         if ev is not None:
             e[1].record()
         skip = self.skip
-        if self.vp.world > 1 and "grads" not in skip:
+        if vp.world > 1 and "grads" not in skip:
             if getattr(self.bucket, "compact", False):
-                self.vp.exchange_compact(self.bucket, campos)
+                vp.exchange_compact(self.bucket, campos)
             elif self.chunks > 0:
-                self.vp.finish_gradients(self.bucket)
+                vp.finish_gradients(self.bucket)
             else:
-                self.vp.allreduce_gradients(self.bucket, average=False)
+                vp.allreduce_gradients(self.bucket, average=False)
         if ev is not None:
             e[2].record()
-        if means2D_densify is not None and "stats" not in skip:
+        if a.step_kind != "raster" and "stats" not in skip:
             # densification statistics (trainer.py:345-347), every view at every N: one fused local pass; the ranks are
             # combined every 100 steps (the reference densifies every 100 iterations, trainer.py:357-370)
-            self.vp.accumulate_densification_stats(self.xyz_gradient_accum, self.denom, self.max_radii2D,
-                                                   means2D_densify.grad, radii)
+            vp.accumulate_densification_stats(self.xyz_gradient_accum, self.denom, self.max_radii2D, means2D_densify.grad, radii)
             if (i + 1) % 100 == 0:
-                self.vp.sync_densification_stats(self.xyz_gradient_accum, self.denom, self.max_radii2D)
+                vp.sync_densification_stats(self.xyz_gradient_accum, self.denom, self.max_radii2D)
                 self.xyz_gradient_accum.zero_(); self.denom.zero_(); self.max_radii2D.zero_()
         if e2e:
             self.loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
         return loss
 
+    def local_gradient_checksums(self, i):
+        """For the exchange self-check: this rank's OWN gradients of view i (no exchange), as float64 sums per group."""
+        skip, self.skip = self.skip, "grads,stats"
+        try:
+            self.step(i, False)
+        finally:
+            self.skip = skip
+        return torch.stack([self.bucket.grad_flat[o:o + n].double().sum() for _, o, n, _ in self.bucket.layout])
 
-def timed_region(stepper, steps, warmup, e2e, dev, world, sampler=None):
-    """`sampler`: a ClockSampler built BEFORE the warm-up (NVML initialisation takes tens of milliseconds of host time; done
-    between the warm-up and the first timed step it lets the GPU fall idle and the first timed steps run at ramping clocks)."""
-    for i in range(warmup):
-        stepper.step(i, e2e)
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    torch.cuda.synchronize(dev)
-    if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize(dev)
-    ev0.record()
-    for i in range(steps):
-        stepper.step(warmup + i, e2e)
-    ev1.record()
-    if sampler:
-        sampler.sample()          # the GPU is still executing the last timed step(s); ev1 is already enqueued, so the
-                                  # 3-10 ms an (uncached) NVML query can take on the host does not enter the measurement
-    torch.cuda.synchronize(dev)
-    if world > 1:
-        dist.barrier()
-    ms = ev0.elapsed_time(ev1)
-    clocks = sampler.result() if sampler else None
-    if world > 1:
-        t = torch.tensor([ms], device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t)
-    return ms, clocks
+
+class TrainStepper:
+    """One COMPLETE training iteration per view, from the raw parameters to the updated raw parameters, the way trainer.py
+    runs it (trainer.py:323-392): per-Gaussian prologue -> rasterize -> loss (0.8 L1 + 0.2 (1 - SSIM) + mono-normal +
+    D-Normal) -> backward -> (N > 1: SUM of the raw gradient bucket) -> densification statistics -> (densify + prune every
+    100 iterations) -> Adam.  Fused prologue, fused view loss + fused SSIM, BucketAdam, device-side densification; the
+    prologue's and the rasterizer's backward kernels write the raw gradients straight into the flat bucket."""
+
+    def __init__(self, args, scene, views, dev, vp):
+        import vcr_view_parallel as VP
+        from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+        self.GRS, self.GR, self.VP = GaussianRasterizationSettings, GaussianRasterizer, VP
+        self.args, self.dev, self.vp = args, dev, vp
+        self.feed = BC.ViewFeeder(views, dev)
+        self.views = views
+        raw = {k: v.to(dev) for k, v in BC.raw_parameters(scene).items()}
+        store = None
+        self.capacity = int(args.gaussians * (1.6 if args.densify else 1.0))
+        if vp.world > 1 and os.environ.get("VCR_BENCH_TRANSPORT", "multimem") == "multimem":
+            per = sum(v.numel() // args.gaussians for v in raw.values())
+            store = vp.symmetric_gradient_storage((per * self.capacity + 64) // 4 * 4, dev)
+        self.store = store
+        self.bucket = VP.GaussianBucket(raw, device=dev, names=BC.RAW_NAMES, direct=True, grad_storage=store)
+        self.opt = VP.BucketAdam(self.bucket, BC.LRS)
+        self.exchange_ms = {}
+        if vp.world > 1:
+            self.exchange_ms = vp.pick_transport(self.bucket)
+            forced = os.environ.get("VCR_BENCH_TRANSPORT")
+            if forced == "nccl":
+                vp.transport = "nccl"
+        self._alloc_stats()
+        inp0 = views[0]["inp"]
+        self.dirs = inp0["dirs"].to(dev)
+        K = views[0]["cam"].intr
+        self.K4 = (float(K[0, 0]), float(K[1, 1]), float(K[0, 2]), float(K[1, 2]))
+        self.tanx, self.tany = inp0["tanfovx"], inp0["tanfovy"]
+        self.extent = scene.extent
+        self.d2h_bytes = 4
+        self.loss_host = torch.zeros(1).pin_memory()
+        self.iteration = 0
+        self.P_history = [self.bucket.P]
+
+    def _alloc_stats(self):
+        P, dev = self.bucket.P, self.dev
+        self.inside = torch.ones(P, dtype=torch.bool, device=dev)
+        self.xyz_gradient_accum = torch.zeros((P, 1), device=dev)
+        self.denom = torch.zeros((P, 1), device=dev)
+        self.max_radii2D = torch.zeros((P,), device=dev)
+
+    def step(self, i, e2e=False):
+        from vcr_dnormal import ssim, view_loss
+        from vcr_prologue import gaussian_prologue
+        a, vp, p = self.args, self.vp, self.bucket.params
+        self.iteration += 1
+        d = self.feed.get(i, e2e)
+        view, proj, campos, bg = BC.ViewFeeder.camera(d)
+        R_w2c = view[:3, :3].t()
+        opac, scales, rots, sh, normals = gaussian_prologue(p["xyz"], p["f_dc"], p["f_rest"], p["opacity"], p["scaling"], p["rotation"],
+                                                            campos, R_w2c)
+        rs = self.GRS(image_height=a.height, image_width=a.width, tanfovx=self.tanx, tanfovy=self.tany, bg=bg, scale_modifier=1.0,
+                      viewmatrix=view, projmatrix=proj, sh_degree=3, campos=campos, prefiltered=False, debug=False, f_count=0)
+        means2D = torch.zeros_like(p["xyz"], requires_grad=True)
+        means2D_densify = torch.zeros_like(p["xyz"], requires_grad=True)
+        out, radii = self.GR(rs)(means3D=p["xyz"], means2D=means2D, means2D_densify=means2D_densify, shs=sh, normals_precomp=normals,
+                                 opacities=opac, scales=scales, rotations=rots, dirs=self.dirs, inside=self.inside)
+        sc = 1.0 / vp.world
+        loss = view_loss(out, d["gt_image"], d["gt_normal"], self.K4, w_l1=BC.W_L1 * sc, w_mono=BC.W_MONO * sc, w_dn=BC.W_DN * sc, exp_t=BC.EXP_T)
+        loss = loss + (BC.W_SSIM * sc) * (1.0 - ssim(out[:3], d["gt_image"]))
+        self.bucket.zero_grad()
+        loss.backward()
+        if vp.world > 1:
+            vp.allreduce_gradients(self.bucket, average=False)
+        vp.accumulate_densification_stats(self.xyz_gradient_accum, self.denom, self.max_radii2D, means2D_densify.grad, radii)
+        if a.densify and self.iteration % BC.DENSIFY_INTERVAL == 0:
+            self.densify()
+        self.opt.step()
+        if e2e:
+            self.loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
+        return loss
+
+    def densify(self):
+        """densify_and_prune of the reference (scene/gaussian_model.py:645-659) on the synchronised statistics; identical
+        decisions, hence identical replicas, on every rank."""
+        from vcr_densify import densify_and_prune
+        vp = self.vp
+        vp.sync_densification_stats(self.xyz_gradient_accum, self.denom, self.max_radii2D)
+        thr = BC.densify_threshold(self.xyz_gradient_accum, self.denom)
+        self.bucket, self.opt, info = densify_and_prune(self.bucket, self.opt, self.xyz_gradient_accum, self.denom, self.max_radii2D,
+                                                        max_grad=thr, min_opacity=BC.MIN_OPACITY, extent=self.extent,
+                                                        max_screen_size=None, percent_dense=BC.PERCENT_DENSE, grad_storage=self.store)
+        self._alloc_stats()
+        self.P_history.append(self.bucket.P)
 
 
 def cpu_oracle_views_per_s(args, view, repeat=1):
     """The CPU oracle (a port; the reference has no CPU path) on one full view of the same workload, all host cores."""
+    for p in (os.path.join(ROOT, "tests"),):
+        if p not in sys.path:
+            sys.path.insert(0, p)
     from oracle import oracle as O
-    from util import np_inputs
     import numpy as np
-    inp = np_inputs(view["inp"])
+    inp = {k: (v.detach().cpu().numpy() if isinstance(v, torch.Tensor) else v) for k, v in view["inp"].items()}
     g = np.random.default_rng(0).standard_normal((10, args.height, args.width)).astype(np.float32)
     t0 = time.time()
     for _ in range(repeat):
@@ -578,62 +313,48 @@ def cpu_oracle_views_per_s(args, view, repeat=1):
     return 1.0 / dt, dt, f["binned"]["R"]
 
 
-_JSON_FD = None
-
-
-def emit(obj):
-    """The ONE JSON line goes to the process's real stdout; everything else written to fd 1 during the run (NCCL prints its
-    version banner there) has been redirected to stderr."""
-    line = (json.dumps(obj) + "\n").encode()
-    if _JSON_FD is None:
-        sys.stdout.write(line.decode()); sys.stdout.flush()
-    else:
-        os.write(_JSON_FD, line)
-
-
 def main():
-    global _JSON_FD
-    args = parse()
-    sys.stdout.flush()
-    _JSON_FD = os.dup(1)
-    os.dup2(2, 1)
+    args = BC.parse()
+    BC.claim_stdout()
+    if args.impl == "reference":
+        import bench_ref
+        bench_ref.main(args)
+        return
+    if args.impl == "reference-cpu":
+        if int(os.environ.get("RANK", "0")) == 0:
+            scene = BC.build_scene(args)
+            views = BC.build_views(args, scene, 1, [0], light=True)
+            vps, dt, R = cpu_oracle_views_per_s(args, views[0])
+            cores = BC.host_cores()
+            BC.emit({"impl": "reference", "metric": BC.METRIC, "value": vps, "unit": "views/s", "n_gpus": 0, "steps": 1, "warmup": 0,
+                     "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+                     "data": "synthetic", "config": BC.config_dict(args, 1),
+                     "cpu_baseline": {"value": vps, "unit": "views/s", "cores": cores, "kind": "port",
+                                      "sample": "one full view, rasterize fwd+bwd (no D-Normal), CPU oracle with OpenMP over all host cores"},
+                     "e2e": {"value": vps, "unit": "views/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
+        return
+    _product_paths()
+    import vcr_native as N
     import vcr_view_parallel as VP
     rank, world, local = VP.init_from_env()
-    if args.impl == "reference-cpu":
-        if rank == 0:
-            scene, views = build_workload(args, 0, 1)
-            vps, dt, R = cpu_oracle_views_per_s(args, views[0])
-            cores = os.cpu_count()
-            emit(({
-                "impl": "reference", "metric": METRIC, "value": vps, "unit": "views/s", "n_gpus": 0, "steps": 1, "warmup": 0,
-                "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-                "data": "synthetic", "config": {"workload": f"{args.gaussians} Gaussians, {args.width}x{args.height}, SH3, dirs; CPU oracle port"},
-                "cpu_baseline": {"value": vps, "unit": "views/s", "cores": cores, "kind": "port",
-                                 "sample": "one full view, rasterize fwd+bwd (no D-Normal), OpenMP over all host cores"},
-                "e2e": {"value": vps, "unit": "views/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
-        return
     assert torch.cuda.is_available(), "bench.py needs a GPU (there is no CPU fallback in the product path)"
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
     vp = VP.ViewParallel()
     all_cores = os.sched_getaffinity(0)
     numa_cores = VP.bind_to_gpu_numa_node(local) if os.environ.get("VCR_BENCH_NUMA", "1") == "1" else 0
-    scene = build_scene(args)
-    impl = args.impl
-    if impl == "reference":
-        import ref_ab
-        if ref_ab.load() is None:
-            if rank == 0:
-                emit(({"impl": "reference", "unavailable": "oracle/_ref/_C.so (reference CUDA build) not present on this box"}))
-            return
-    bucket = clone_params(scene, dev, direct=(impl == "ours"), vp=vp)
+    scene = BC.build_scene(args)
     view_ids = [v * world + rank for v in range(args.views)]          # default shard: every world-th camera of the ring
-    balanced = world > 1 and impl == "ours" and os.environ.get("VCR_BENCH_BALANCE", "1") == "1"
+    train = args.step_kind == "train"
+    balanced = world > 1 and not train and os.environ.get("VCR_BENCH_BALANCE", "1") == "1"
     if balanced:
         # Cost-balanced sharding: every step ends with the gradient exchange, i.e. with a wait for the slowest rank, so the
         # `world` views of one step should cost the same.  Each rank times its default shard once, the costs are
         # gathered, and ViewParallel.balanced_view_table deals views of equal cost to the ranks of one step.
-        mine = torch.tensor(measure_view_costs(args, bucket, build_views(args, scene, world, view_ids, light=True), dev), device=dev)
+        tmp = VP.GaussianBucket(dict(means3D=scene.means3D.to(dev), shs=scene.shs.to(dev), opacities=scene.opacities.to(dev),
+                                     scales=scene.scales.to(dev), rotations=scene.rotations.to(dev)), device=dev, direct=True)
+        mine = torch.tensor(measure_view_costs(args, tmp, BC.build_views(args, scene, world, view_ids, light=True), dev), device=dev)
+        del tmp
         allc = [torch.zeros_like(mine) for _ in range(world)]
         dist.all_gather(allc, mine)
         costs = [0.0] * (args.views * world)
@@ -641,83 +362,71 @@ def main():
             for v in range(args.views):
                 costs[v * world + r] = float(allc[r][v])
         view_ids = [row[rank] for row in vp.balanced_view_table(costs, seed=0)]
-    views = build_views(args, scene, world, view_ids)
-    stepper = Stepper(args, impl, bucket, views, dev, vp)
+    views = BC.build_views(args, scene, world, view_ids)
+    stepper = (TrainStepper if train else HotPathStepper)(args, scene, views, dev, vp)
 
-    import vcr_native as N
-    prof = (impl == "ours") and not args.no_profile
+    prof = not args.no_profile and not args.densify
     # ---- device-resident timing (`value`): K steps, launch counters on, per-kernel event brackets OFF ----
-    if impl == "ours":
-        N.vcr_profile_enable(0)
+    N.vcr_profile_enable(0)
     # warm-up: W steps, but at least three passes over the view set, so that the caching allocator has seen every
     # per-view buffer size (the binning buffer depends on R) and no cudaMalloc lands in the timed region
-    # ... and long enough (a fixed count, identical on every rank) for clocks and power state to settle under load
-    sampler = ClockSampler(dev.index or 0)
+    # ... and long enough (a fixed count, identical on every rank and in both arms) for clocks and power state to settle
+    sampler = BC.ClockSampler(dev.index or 0)
     # no cyclic garbage collection inside the measured regions: a generation-2 pass on ONE rank stalls that rank's launches
     # for milliseconds and, through the per-step exchange, every other rank with it (the step creates no reference cycles)
     gc.collect()
     gc.disable()
     # (VCR_BENCH_WARMUP_FLOOR: profiling runs under ncu lower the floor; bench numbers are always taken with the default)
-    floor = int(os.environ.get("VCR_BENCH_WARMUP_FLOOR", "200" if impl == "ours" else "60"))
+    floor = int(os.environ.get("VCR_BENCH_WARMUP_FLOOR", "200"))
     n_warm = max(args.warmup, 3 * len(views), floor)
+    if args.densify:
+        n_warm = max(args.warmup, 3 * len(views))        # a densifying run is timed from a fixed iteration count in both arms
     for i in range(n_warm):
         stepper.step(i, False)
-    if impl == "ours":
-        N.profile_read(reset=True)
-    ms, clocks = timed_region(stepper, args.steps, 0, False, dev, world, sampler=sampler)
-    counts = N.profile_read(reset=True) if impl == "ours" else {}
+    N.profile_read(reset=True)
+    ms, clocks = BC.timed_region(lambda i: stepper.step(i, False), args.steps, 0, dev, world, sampler=sampler, first=n_warm)
+    counts = N.profile_read(reset=True)
+    nxt = n_warm + args.steps
     # ---- the same K steps once more with every kernel of the library bracketed by CUDA events on its stream ----
-    # (the brackets cost ~5-10 % of a step, so they are kept out of `value`; `ms_per_step_with_kernel_events` reports it)
+    # (the brackets cost ~4 % of a step, so they are kept out of `value`; `ms_per_step_with_kernel_events` reports it)
     kern, ms_prof = {}, None
     if prof:
         N.vcr_profile_enable(1)
-        ms_prof, _ = timed_region(stepper, args.steps, 1, False, dev, world)
+        ms_prof, _ = BC.timed_region(lambda i: stepper.step(i, False), args.steps, 1, dev, world, first=nxt)
         kern = N.profile_read(reset=True)
         N.vcr_profile_enable(0)
+        nxt += args.steps + 1
     # ---- end-to-end timing (`e2e`): per-view inputs from pinned host memory, loss read back ----
     # (its own warm-up: three passes over the views in e2e mode, so that the caching allocator has seen the prefetch buffers —
     # they are freed late because of record_stream — and no cudaMalloc lands in the timed region)
-    ms_e2e, _ = timed_region(stepper, args.steps, max(args.warmup, 3 * len(views)), True, dev, world)
-    if os.environ.get("VCR_BENCH_DIAG"):
+    w_e2e = max(args.warmup, 3 * len(views))
+    ms_e2e, _ = BC.timed_region(lambda i: stepper.step(i, True), args.steps, w_e2e, dev, world, first=nxt)
+    nxt += args.steps + w_e2e
+    exchange_check = verify_exchange(stepper, vp, nxt, dev) if (world > 1 and not train) else None
+    if os.environ.get("VCR_BENCH_DIAG") and not train:
         diagnose(stepper, args, dev, rank, world)
     views_per_s = world * args.steps / (ms / 1e3)
     e2e_vps = world * args.steps / (ms_e2e / 1e3)
 
     if rank != 0:
         return
+    bucket = stepper.bucket
+    cfg = BC.config_dict(args, world)
     out = {
-        "metric": METRIC, "value": views_per_s, "unit": "views/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "metric": BC.METRIC, "value": views_per_s, "unit": "views/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-        "data": "synthetic",
-        "config": {"workload": f"{args.gaussians} Gaussians (SH degree 3), {args.width}x{args.height}, {args.views} views/rank cycled, "
-                               f"ray/plane-intersection depth, loss = L1 + mono-normal + D-Normal; rasterize fwd+bwd per view",
-                   "parallelism": (f"view-parallel x{world} (replicated Gaussians, all-reduce of the flat gradient bucket via "
-                                   + ("own NVSwitch-multicast kernel" if vp.transport == "multimem" else "NCCL")
-                                   + (", SH gradient exchanged as 3 colour-gradient floats per Gaussian and rebuilt per rank" if getattr(bucket, "compact", False) else "")
-                                   + (f", pipelined with the backward in {stepper.chunks} Gaussian ranges)" if stepper.chunks else ")"))
-                   if world > 1 else "single GPU",
-                   "l2": "working set per step (parameters + gradients + per-view state > 600 MB) exceeds the 126 MB L2; views rotate every step",
-                   "not_in_step": "SSIM, Adam, per-Gaussian prologue (outside the hot path, SURVEY.md 8f; see full_step)",
-                   "host": f"process bound to the {numa_cores} cores next to its GPU" if numa_cores else "no CPU binding"},
+        "data": "synthetic", "config": cfg,
         "clocks": clocks,
-        "exchange": ({"chosen": vp.transport, "ms_per_exchange": stepper.exchange_ms, "compact_sh": bool(getattr(bucket, "compact", False)), "view_sharding": "cost-balanced (balanced_view_table)" if balanced else "every world-th camera"}
-                     if world > 1 and impl == "ours" else None),
-        "e2e": {"value": e2e_vps, "unit": "views/s", "h2d_bytes_per_step": stepper.h2d_bytes, "d2h_bytes_per_step": stepper.d2h_bytes,
+        "host": f"process bound to the {numa_cores} cores next to its GPU" if numa_cores else "no CPU binding",
+        "exchange": ({"chosen": vp.transport, "ms_per_exchange": stepper.exchange_ms, "compact_sh": bool(getattr(bucket, "compact", False)),
+                      "pipelined_ranges": getattr(stepper, "chunks", 0),
+                      "view_sharding": "cost-balanced (balanced_view_table)" if balanced else "every world-th camera",
+                      "verified": exchange_check} if world > 1 else None),
+        "e2e": {"value": e2e_vps, "unit": "views/s", "h2d_bytes_per_step": stepper.feed.h2d_bytes, "d2h_bytes_per_step": stepper.d2h_bytes,
                 "ms_per_step": ms_e2e / args.steps},
     }
-    if world == 1 and not os.environ.get("VCR_BENCH_NO_FULL_STEP"):
-        try:
-            out["full_step"] = time_full_step(args, impl, scene, stepper, dev, args.steps)
-        except Exception as ex:  # a side measurement must never cost the bench line
-            out["full_step"] = {"error": f"{type(ex).__name__}: {ex}"}
-    if impl == "reference":
-        out["impl"] = "reference"
-        out["config"]["reference_build"] = "unmodified reference sources, nvcc 12.9, compute_90 PTX JIT-compiled for sm_100 (see DESIGN.md)"
-        out["cpu_baseline"] = {"value": None, "unit": "views/s", "cores": 0, "kind": "reference",
-                               "sample": "not a CPU run: the reference's implementation of this path is CUDA-only; this arm is its CUDA rasterizer on this GPU"}
-        out["gpu_launches"] = 0
-        emit(out)
-        return
+    if hasattr(stepper, "P_history"):
+        out["gaussians_after_each_densification"] = stepper.P_history
     # ---- roofline of the dominant kernel + per-kernel table ----
     peaks = {}
     try:
@@ -726,40 +435,100 @@ def main():
         pass
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
-    stats = scene_stats(stepper, args)
-    per_kernel = kernel_table(kern, stats, args, hbm_peak)
     launches = sum(v[2] for k, v in counts.items() if k != "memset")
     out["gpu_launches"] = launches
-    if per_kernel:
-        dom = max(per_kernel, key=lambda r: r["ms_per_step"])
-        issue = {}
-        traffic = None      # DRAM bytes per launch of that kernel, from the committed ncu --set full capture of this workload
-        try:
-            tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
-            same = (args.gaussians, args.width, args.height, args.footprint) == (1_000_000, 1920, 1080, 2.0)
-            traffic = int(tr[dom["kernel"]]["bytes"]) if same else None
-            issue = {k: tr[dom["kernel"]][k] for k in ("issue_active_pct", "warp_instructions", "dram_pct_of_peak") if k in tr[dom["kernel"]]}
-        except Exception:
-            pass
-        out["roofline"] = {"kernel": dom["kernel"], "bound": "hbm", "achieved": dom["achieved_gbs"], "peak": hbm_peak, "unit": "GB/s",
-                           "frac": dom["achieved_gbs"] / hbm_peak, "traffic": traffic, "peak_source": peak_src,
-                           "algorithmic_bytes_per_launch": dom["bytes_per_launch"],
-                           "note": "compositing kernels are FP32-issue / atomic bound, not HBM bound (DESIGN.md); the HBM fraction is reported as the contract asks",
-                           "issue_bound": dict(issue, source=tr[dom["kernel"]]["source"]) if issue else None}
-        out["kernels"] = per_kernel
+    if not train:
+        stats = scene_stats(stepper, args, clocks)
+        per_kernel = kernel_table(kern, stats, args, hbm_peak)
+        out["scene"] = stats
+        if per_kernel:
+            dom = max(per_kernel, key=lambda r: r["ms_per_step"])
+            out["roofline"] = roofline_entry(dom, stats, args, hbm_peak, peak_src, clocks)
+            out["kernels"] = per_kernel
+            out["ms_per_step_with_kernel_events"] = ms_prof / args.steps if ms_prof else None
+    else:
+        out["kernels_ms_per_step"] = {k: v[0] / max(args.steps, 1) for k, v in kern.items() if v[1]}
         out["ms_per_step_with_kernel_events"] = ms_prof / args.steps if ms_prof else None
-    out["scene"] = stats
-    if world == 1:
+    if world == 1 and args.config == "metric" and not args.no_full_step and not os.environ.get("VCR_BENCH_NO_FULL_STEP"):
         try:
-            out["render_prologue"] = time_prologue(args, scene, views[0], dev)
-        except Exception as ex:  # never lose the bench line over the side measurement
-            out["render_prologue"] = {"error": f"{type(ex).__name__}: {ex}"}
+            out["full_step"] = time_full_step(args, scene, views, dev, vp, args.steps)
+        except Exception as ex:  # a side measurement must never cost the bench line
+            out["full_step"] = {"error": f"{type(ex).__name__}: {ex}"}
     if not args.no_cpu_baseline and world == 1:
         os.sched_setaffinity(0, all_cores)        # the CPU baseline gets every host core, not just the GPU's NUMA node
+        out["cpu_baseline"] = cpu_baseline(args, scene, views)
+    BC.emit(out)
+
+
+def cpu_baseline(args, scene, views):
+    """The CPU oracle (kind "port": the reference has no CPU implementation of the path) on a bounded sample of the
+    workload: one full view of THIS config when that takes well under a minute (<= 1.1 M Gaussians), otherwise one view of
+    the metric's 1 M / 1080p scene; plus config A (10k Gaussians, one 256x256 view — the configuration the CPU baseline is
+    specified on), median of 5."""
+    cores = BC.host_cores()
+    big = args.gaussians > 1_100_000 or args.width * args.height > 2_100_000
+    if big:
+        import copy
+        a1 = copy.copy(args)
+        a1.gaussians, a1.width, a1.height, a1.views = 1_000_000, 1920, 1080, 1
+        sc1 = BC.build_scene(a1)
+        v1 = BC.build_views(a1, sc1, 1, [0], light=True)[0]
+        vps, dt, R = cpu_oracle_views_per_s(a1, v1)
+        sample = f"one full 1920x1080 view of the metric's 1M-Gaussian scene (this config is too large for a bounded CPU run), rasterize fwd+bwd ({dt:.1f} s)"
+    else:
         vps, dt, R = cpu_oracle_views_per_s(args, views[0])
-        out["cpu_baseline"] = {"value": vps, "unit": "views/s", "cores": os.cpu_count(), "kind": "port",
-                               "sample": f"one full {args.width}x{args.height} view of the same scene, rasterize fwd+bwd, CPU oracle with OpenMP ({dt:.1f} s)"}
-    emit(out)
+        sample = f"one full {args.width}x{args.height} view of the same scene, rasterize fwd+bwd, CPU oracle with OpenMP ({dt:.1f} s)"
+    res = {"value": vps, "unit": "views/s", "cores": cores, "kind": "port", "sample": sample}
+    try:
+        import copy
+        aA = copy.copy(args)
+        aA.gaussians, aA.width, aA.height, aA.views = 10_000, 256, 256, 1
+        scA = BC.build_scene(aA)
+        vA = BC.build_views(aA, scA, 1, [0], light=True)[0]
+        ts = sorted(cpu_oracle_views_per_s(aA, vA)[1] for _ in range(5))
+        res["config_A"] = {"ms_per_view": ts[2] * 1e3, "what": "10k Gaussians, one 256x256 view, rasterize fwd+bwd, median of 5"}
+    except Exception as ex:
+        res["config_A"] = {"error": f"{type(ex).__name__}: {ex}"}
+    return res
+
+
+def time_full_step(args, scene, views, dev, vp, steps):
+    """Side measurement at the metric's size: the complete training iteration (TrainStepper) — reported beside the bench
+    metric, whose step is the rasterizer + D-Normal hot path only.  `--config B` / `--config C` make it the step."""
+    import copy
+    a2 = copy.copy(args)
+    a2.step_kind, a2.densify = "train", False
+    st = TrainStepper(a2, scene, views, dev, vp)
+    ms, _ = BC.timed_region(lambda i: st.step(i, False), steps, max(3 * len(views), 24), dev, 1)
+    return {"ms_per_step": ms / steps, "views_per_s": 1e3 * steps / ms, "steps": steps,
+            "includes": "raw parameters -> prologue -> rasterize fwd -> 0.8 L1 + 0.2 (1-SSIM) + mono-normal + D-Normal -> backward -> Adam (6 groups, eps 1e-15)",
+            "reference": "python bench.py --impl reference --config metric reports the hot-path step; --config B the complete iteration on both arms"}
+
+
+def verify_exchange(stepper, vp, i, dev):
+    """After the timed regions, once: is the exchanged gradient of step i the SUM of the ranks' own gradients of their views?
+    Every rank first computes its local gradient of view i with the exchange skipped (float64 sums per parameter group,
+    all-gathered with NCCL), then the real step; the exchanged bucket's per-group sums must equal the sum over ranks of the
+    local ones (1e-4 relative to the group's L1 mass: float-atomic order differs between the two backward runs), and all
+    replicas must hold bit-identical buckets."""
+    local = stepper.local_gradient_checksums(i)
+    l1_local = torch.stack([stepper.bucket.grad_flat[o:o + n].double().abs().sum() for _, o, n, _ in stepper.bucket.layout])
+    both = torch.stack([local, l1_local])
+    allb = [torch.zeros_like(both) for _ in range(vp.world)]
+    dist.all_gather(allb, both)
+    want = sum(b[0] for b in allb)
+    mass = sum(b[1] for b in allb)
+    stepper.step(i, False)
+    got = torch.stack([stepper.bucket.grad_flat[o:o + n].double().sum() for _, o, n, _ in stepper.bucket.layout])
+    err = float(((got - want).abs() / mass.clamp(min=1e-30)).max())
+    # bit-identical replicas: compare a position-weighted integer checksum of the raw bits
+    bits = stepper.bucket.grad_flat.view(torch.int32).to(torch.int64)
+    chk = torch.stack([bits.sum(), (bits * (torch.arange(bits.numel(), device=dev) % 65521)).sum()])
+    allc = [torch.zeros_like(chk) for _ in range(vp.world)]
+    dist.all_gather(allc, chk)
+    same = all(bool(torch.equal(c, allc[0])) for c in allc)
+    return {"sum_of_local_gradients_rel_err": err, "ok": bool(err < 1e-4), "replicas_bit_identical": same,
+            "groups": [n for n, _, _, _ in stepper.bucket.layout]}
 
 
 def diagnose(stepper, args, dev, rank, world):
@@ -773,7 +542,7 @@ def diagnose(stepper, args, dev, rank, world):
         dist.barrier()
     for i in range(n):
         marks[i].record()
-        stepper.step(1000 + i, False)
+        stepper.step(10_000 + i, False)
     marks[n].record()
     torch.cuda.synchronize(dev)
     ev, stepper.diag_events = stepper.diag_events, None
@@ -796,33 +565,72 @@ def diagnose(stepper, args, dev, rank, world):
         print("DIAG " + json.dumps(rep), file=sys.stderr, flush=True)
 
 
-def scene_stats(stepper, args):
-    """P, visible P, R for view 0 (needed to turn kernel times into algorithmic GB/s)."""
+def scene_stats(stepper, args, clocks):
+    """P, visible P, R, sum n_contrib and the pair counts K_e / K_c of view 0 (what turns kernel times into algorithmic GB/s
+    and FLOP/s): K_e = (pixel, Gaussian) pairs whose exponent is evaluated by the forward, K_c = pairs that
+    contribute (pass every test).  Counted by the library's instrumented forward (vcr_pair_counters), outside the timed
+    regions."""
+    import vcr_native as N
+    from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+    import diff_gaussian_rasterization as D
     p = stepper.bucket.params
     v = stepper.views[0]["inp"]
-    from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
     dev = stepper.dev
     rs = GaussianRasterizationSettings(image_height=args.height, image_width=args.width, tanfovx=v["tanfovx"], tanfovy=v["tanfovy"],
                                        bg=v["bg"].to(dev), scale_modifier=1.0, viewmatrix=v["viewmatrix"].to(dev),
                                        projmatrix=v["projmatrix"].to(dev), sh_degree=3, campos=v["campos"].to(dev),
                                        prefiltered=False, debug=False, f_count=0)
-    with torch.no_grad():
-        out, radii = GaussianRasterizer(rs)(means3D=p["means3D"].detach(), means2D=None, opacities=p["opacities"].detach(),
-                                            shs=p["shs"].detach(), normals_precomp=stepper.normals[0].detach(),
-                                            scales=p["scales"].detach(), rotations=p["rotations"].detach(), dirs=stepper.dirs)
-    import vcr_native as N
+    counters = torch.zeros(8, dtype=torch.int64, device=dev)
+    N.check(N.vcr_pair_counters(counters.data_ptr()), "pair_counters")
+    try:
+        with torch.no_grad():
+            out, radii = GaussianRasterizer(rs)(means3D=p["means3D"].detach(), means2D=None, opacities=p["opacities"].detach(),
+                                                shs=p["shs"].detach(), normals_precomp=stepper.normals[0].detach(),
+                                                scales=p["scales"].detach(), rotations=p["rotations"].detach(), dirs=stepper.dirs)
+        torch.cuda.synchronize(dev)
+    finally:
+        N.check(N.vcr_pair_counters(None), "pair_counters")
     N.profile_read(reset=True)
+    c = counters.cpu().tolist()
     P = int(radii.numel())
     Pv = int((radii > 0).sum())
-    # R: re-derive from radii/rects is not needed — the autograd node is not kept under no_grad; use the tile formula
-    R = int(last_num_rendered())
+    R = int(getattr(D, "_LAST_NUM_RENDERED", 0))
     return {"P": P, "P_visible": Pv, "R": R, "R_per_P": R / max(P, 1), "pixels": args.width * args.height,
-            "tiles": ((args.width + 15) // 16) * ((args.height + 15) // 16)}
+            "tiles": ((args.width + 15) // 16) * ((args.height + 15) // 16),
+            "sum_n_contrib": c[2], "K_e": c[0], "K_c": c[1], "warp_candidates": c[3],
+            "mean_contributors_per_pixel": c[1] / max(args.width * args.height, 1)}
 
 
-def last_num_rendered():
-    import diff_gaussian_rasterization as D
-    return getattr(D, "_LAST_NUM_RENDERED", 0)
+def roofline_entry(dom, stats, args, hbm_peak, peak_src, clocks):
+    """`roofline` of the dominant kernel.  The compositing kernels are bound by FP32 instruction issue, not by HBM (their DRAM
+    traffic is below the algorithmic bytes: the per-instance re-reads hit the L2), so for them `bound` is "fp32_issue" and the
+    HBM figures the contract asks for are kept beside the FP32 fraction: achieved = (14 K_e + 160 K_c) FLOP (45 K_c
+    for the forward) per launch / launch time, peak = 2 x 128 lanes x #SM x SM clock."""
+    traffic, issue = None, {}
+    try:
+        tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        ent = tr.get(args.config, {}).get(dom["kernel"]) if isinstance(tr.get(args.config), dict) else None
+        same = (args.gaussians, args.width, args.height, args.footprint) == (BC.CONFIGS[args.config]["gaussians"], BC.CONFIGS[args.config]["width"], BC.CONFIGS[args.config]["height"], 2.0)
+        if ent and same:
+            traffic = int(ent["bytes"])
+            issue = {k: ent[k] for k in ("issue_active_pct", "warp_instructions", "dram_pct_of_peak", "source") if k in ent}
+    except Exception:
+        pass
+    compositing = dom["kernel"] in ("render_forward_kernel", "render_backward_kernel")
+    entry = {"kernel": dom["kernel"], "bound": "fp32_issue" if compositing else "hbm", "achieved": dom["achieved_gbs"], "peak": hbm_peak,
+             "unit": "GB/s", "frac": dom["achieved_gbs"] / hbm_peak, "traffic": traffic, "peak_source": peak_src,
+             "algorithmic_bytes_per_launch": dom["bytes_per_launch"], "ncu": issue or None}
+    if compositing:
+        sms = torch.cuda.get_device_properties(0).multi_processor_count
+        mhz = (clocks or {}).get("sm_mhz") or (clocks or {}).get("sm_max_mhz") or 1965
+        fp32_peak = 2.0 * 128 * sms * mhz * 1e6 / 1e12
+        flop = 14.0 * stats["K_e"] + (160.0 if dom["kernel"] == "render_backward_kernel" else 45.0) * stats["K_c"]
+        ach = flop / (dom["avg_launch_ms"] * 1e-3) / 1e12
+        entry["fp32"] = {"achieved_tflops": ach, "peak_tflops": fp32_peak, "frac": ach / fp32_peak,
+                         "flop_per_launch": flop, "formula": "14*K_e + (160 bwd | 45 fwd)*K_c (SURVEY 8d)", "sm_mhz": mhz, "sms": sms}
+        entry["note"] = ("compositing is FP32-issue bound; `achieved/peak/frac` are the HBM figures the contract asks for, `fp32` the "
+                         "fraction of the CUDA-core peak the algorithmic flops reach (the flop model counts useful arithmetic only)")
+    return entry
 
 
 def kernel_table(kern, st, args, hbm_peak):
@@ -830,12 +638,12 @@ def kernel_table(kern, st, args, hbm_peak):
     if not kern:
         return []
     P, Pv, R, N, tiles = st["P"], st["P_visible"], st["R"], st["pixels"], st["tiles"]
-    bits = 32 + max(1, math.ceil(math.log2(tiles + 1)))
+    npass_tile = (max(1, math.ceil(math.log2(max(tiles, 2)))) + 7) // 8
     alg = {
         "preprocess_kernel": 336 * Pv + 20 * (P - Pv),
         "scan_block_sums_kernel": 8 * ((P + 255) // 256),
         "duplicate_kernel": 20 * P + 12 * R,
-        "radix_pass_kernel": (4 * 24 * P + 2 * 24 * R) / 6.0,      # per launch: 4 passes over the P depth keys, 2 over the R instances
+        "radix_pass_kernel": (4 * 24 * P + npass_tile * 16 * R) / (4.0 + npass_tile),   # per launch: 4 passes over the P (u64, u32) depth pairs, the tile passes over R (u32, u32) pairs
         "tile_ranges_kernel": 8 * R + 8 * tiles,
         "render_forward_kernel": 41 * R + 60 * N,
         "render_backward_kernel": 77 * R + 68 * N + 84 * Pv,

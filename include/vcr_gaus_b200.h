@@ -19,6 +19,8 @@
  *   vcr_prologue_forward/backward <- the per-Gaussian prologue of render(), gaussian_renderer/__init__.py:60-101
  *   vcr_adam_step                <- torch.optim.Adam over the six groups of scene/gaussian_model.py:241-258
  *   vcr_densify_stats_accumulate <- trainer.py:345 + scene/gaussian_model.py:669-671
+ *   vcr_densify_decide / _fill   <- GaussianModel.densify_and_prune, scene/gaussian_model.py:579-659
+ *   vcr_compact_rows             <- prune_points / _prune_optimizer, scene/gaussian_model.py:442-478
  * and, with no counterpart in the (single-GPU) reference, the view-parallel pieces: vcr_rasterize_backward_chunked,
  * vcr_multimem_allreduce_sum, vcr_multimem_exchange, vcr_sh_grad_from_colors; plus the test-only parity view
  * vcr_binning_reference_lists and vcr_dist2_knn3_noalloc.
@@ -294,6 +296,26 @@ size_t vcr_compact_scratch_bytes(int P);
 int vcr_compact_rows(int P, const uint8_t* keep, int n_arrays, const float* const* src_host, float* const* dst_host,
                      const int* width_host, char* scratch, uint32_t* n_kept_device, void* stream);
 
+/* One densification round on the raw parameters (replaces GaussianModel.densify_and_prune, scene/gaussian_model.py:645-659:
+ * densify_and_clone :628-643, densify_and_split_along_maxscaling :579-626 and the final prune :651-657).
+ * vcr_densify_decide writes one flag byte per Gaussian — bit 0: the Gaussian itself survives (not split, not pruned),
+ * bit 1: a clone is appended, bit 2: two children split along the longest axis are appended — from the accumulated
+ * statistic grads = xyz_gradient_accum / denom (NaN -> 0) compared with max_grad, max(exp(scaling_raw)) compared with
+ * dense_limit (= percent_dense * scene_extent), sigmoid(opacity_raw) < min_opacity, and max scaling > world_limit
+ * (= 0.1 * scene_extent when the reference is called with a max_screen_size, +inf otherwise; the reference's screen-size
+ * test itself never fires because max_radii2D has been reset by then).  totals_device u32[3] receives the number of
+ * surviving originals, clones and split parents.  vcr_densify_fill then writes the n_clone + 2 n_split new rows of the six
+ * groups (xyz[3], f_dc[3], f_rest[*], opacity[1], scaling[3], rotation[4]; HOST arrays of device pointers) behind the
+ * n_kept rows that vcr_compact_rows(keep = flags & 1) has moved: clones verbatim; children at mean +- dir * 2 smax / 3 with the
+ * longest axis shrunk to smax / 1.6, everything else copied.  Row order as in the reference (kept | clones | first
+ * children | second children).  scratch: vcr_densify_scratch_bytes(P), shared by the two calls. */
+size_t vcr_densify_scratch_bytes(int P);
+int vcr_densify_decide(int P, const float* scaling_raw, const float* opacity_raw, const float* xyz_gradient_accum, const float* denom,
+                       float max_grad, float min_opacity, float dense_limit, float world_limit, uint8_t* flags, char* scratch,
+                       uint32_t* totals_device, void* stream);
+int vcr_densify_fill(int P, const uint8_t* flags, const char* scratch, int n_kept, int n_clone, int n_split,
+                     const float* const* src_host, float* const* dst_host, const int* width_host, void* stream);
+
 /* Gradient exchange of the view-parallel layer through the NVSwitch (the reference is single-GPU and
  * has no counterpart).  `multicast_base` is the multicast mapping (NVLink SHARP, e.g. torch symmetric memory's
  * multicast_ptr) of a float buffer that every rank holds at the same offset.  For each of the n_ranges (<= 8) float
@@ -400,6 +422,12 @@ int vcr_profile_enable(int enable);
 int vcr_profile_kernel_count(void);
 const char* vcr_profile_kernel_name(int id);
 int vcr_profile_read(float* ms, long long* timed, long long* launches, int reset);
+/* Pair counters (SURVEY.md §8d asks for K_e, K_c and sum n_contrib with every result; no counterpart in the reference).
+ * While a device array of at least 4 u64 is registered, vcr_rasterize_forward runs an instrumented instantiation of its
+ * compositing kernel that ADDS to it: [0] K_e = (pixel, Gaussian) pairs whose exponent was evaluated, [1] K_c = pairs that
+ * contributed, [2] sum over pixels of n_contrib, [3] (warp, Gaussian) candidates after culling.  NULL switches it off.
+ * Process-wide, not thread-safe; meant for bench.py outside its timed regions. */
+int vcr_pair_counters(unsigned long long* counters_device);
 
 /* ---- test/parity accessors: decode the opaque buffers (used by tests/, never by the product path) ---- */
 typedef struct vcr_geom_view {

@@ -2,18 +2,23 @@
 # Compile the UNMODIFIED reference CUDA extensions from the sources where they lie
 # under /root/reference into oracle/_ref/ (git-ignored, travels to the GPU box).
 #
-#   oracle/_ref/diff_gaussian_rasterization/{__init__.py -> generated loader, _C.so}
-#   oracle/_ref/simple_knn/_C.so
+#   oracle/_ref/diff_gaussian_rasterization/{_C.so, __init__.py = the reference's own Python wrapper}
+#   oracle/_ref/simple_knn/{_C.so, __init__.py (empty package marker)}
+#   oracle/_ref/pyref/{tools/*.py, scene/gaussian_model.py, scene/appearance_network.py, gaussian_renderer/__init__.py}
+#                      = the reference's own Python modules of the hot path (render(), GaussianModel, the loss and
+#                        normal utilities), staged byte for byte so that they travel to the GPU box, where
+#                        /root/reference does not exist.  scene/__init__.py is an EMPTY generated package marker (the
+#                        reference's own pulls in the dataset readers), and pyref/_stubs/ holds generated placeholder
+#                        modules for two third-party imports this image lacks (plyfile, pytorch3d.ops) — neither is
+#                        touched by the functions on the hot path.
 #
-# No reference source file is copied or patched: the one compile problem with gcc 13
-# (rasterizer_impl.h uses std::uintptr_t without <cstdint>) is solved with the
-# compiler flag `-include cstdint`.  The Python half of the reference binding
-# (diff_gaussian_rasterization/__init__.py) is NOT copied either: at test time the
-# A/B harness (tests/ref_ab.py) drives `_C` directly with the argument tuples the
-# reference wrapper builds (DGR/diff_gaussian_rasterization/__init__.py:186-220, 401-427).
+# Everything under oracle/_ref/ is git-ignored: no reference source enters the repository's history.  No reference
+# rasterizer source is patched: the one compile problem with gcc 13 (rasterizer_impl.h uses std::uintptr_t without
+# <cstdint>) is solved with the compiler flag `-include cstdint`; the GLM qualifier shim is described below.
 #
-# This is test infrastructure (the parity oracle + the `--impl reference` bench arm),
-# never the product path.
+# This is test infrastructure (the parity oracle + the `--impl reference` bench arm), never the product path.
+# Variant build: NUM_DIST=1 NUM_DEPTH2=2 bash oracle/build_ref.sh builds the distortion variant of the rasterizer
+# (DGR/cuda_rasterizer/config.h:17-18) into oracle/_ref/diff_gaussian_rasterization_dist/.
 set -euo pipefail
 REF=${REF:-/root/reference}
 HERE="$(cd "$(dirname "$0")" && pwd)"
@@ -43,6 +48,53 @@ COMMON="-O3 -std=c++17 --expt-relaxed-constexpr -Xcompiler -fPIC -include cstdin
  -DTORCH_API_INCLUDE_EXTENSION_H -D_GLIBCXX_USE_CXX11_ABI=1 -w $TORCH_INC"
 mkdir -p "$OUT/diff_gaussian_rasterization" "$OUT/simple_knn" "$OUT/obj"
 
+stage_python () {
+  # the reference's own Python half of the path, copied verbatim (git-ignored destination)
+  cp "$DGR/diff_gaussian_rasterization/__init__.py" "$OUT/diff_gaussian_rasterization/__init__.py"
+  : > "$OUT/simple_knn/__init__.py"
+  local PYREF="$OUT/pyref"
+  rm -rf "$PYREF" && mkdir -p "$PYREF/tools" "$PYREF/scene" "$PYREF/gaussian_renderer" "$PYREF/_stubs/pytorch3d"
+  cp "$REF"/tools/*.py "$PYREF/tools/"
+  cp "$REF/scene/gaussian_model.py" "$REF/scene/appearance_network.py" "$REF/scene/cameras.py" "$PYREF/scene/"
+  : > "$PYREF/scene/__init__.py"
+  cp "$REF/gaussian_renderer/__init__.py" "$PYREF/gaussian_renderer/__init__.py"
+  cat > "$PYREF/_stubs/plyfile.py" <<'STUB'
+"""Generated placeholder (oracle/build_ref.sh): `plyfile` is not installed in this image.  scene/gaussian_model.py imports
+PlyData / PlyElement for save_ply / load_ply only; nothing on the rasterizer hot path calls them."""
+
+
+class _Missing:
+    def __init__(self, *a, **k):
+        raise ImportError("plyfile is not available in this image")
+
+    @classmethod
+    def read(cls, *a, **k):
+        raise ImportError("plyfile is not available in this image")
+
+    @classmethod
+    def describe(cls, *a, **k):
+        raise ImportError("plyfile is not available in this image")
+
+
+PlyData = PlyElement = _Missing
+STUB
+  : > "$PYREF/_stubs/pytorch3d/__init__.py"
+  cat > "$PYREF/_stubs/pytorch3d/ops.py" <<'STUB'
+"""Generated placeholder (oracle/build_ref.sh): `pytorch3d` is not installed in this image.  tools/denoise_pcd.py imports
+ball_query / knn_points for point-cloud outlier removal only; nothing on the rasterizer hot path calls them."""
+
+
+def ball_query(*a, **k):
+    raise ImportError("pytorch3d is not available in this image")
+
+
+def knn_points(*a, **k):
+    raise ImportError("pytorch3d is not available in this image")
+STUB
+}
+stage_python
+if [ "${STAGE_ONLY:-0}" = "1" ]; then echo "staged: $OUT/pyref"; rm -rf "$OUT/obj"; exit 0; fi
+
 build_one () { # name srcdir arch extra sources...
   local name=$1 dir=$2 ARCH=$3 extra=$4; shift 4
   local objs=()
@@ -62,6 +114,20 @@ GLMFIX="$OUT/obj/glm_qualified"
 rm -rf "$GLMFIX" && cp -r "$DGR/third_party/glm" "$GLMFIX"
 sed -i 's/^\(\s*\)T operator()(const T& a, const T& b) { return \(min\|max\)(a, b); }/\1GLM_FUNC_QUALIFIER T operator()(const T\& a, const T\& b) { return \2(a, b); }/' "$GLMFIX/glm/detail/func_common.inl"
 grep -c "GLM_FUNC_QUALIFIER T operator()" "$GLMFIX/glm/detail/func_common.inl" | grep -q 2 || { echo "GLM qualifier shim did not apply" >&2; exit 1; }
+if [ -n "${NUM_DIST:-}" ] || [ -n "${NUM_DEPTH2:-}" ]; then
+  # distortion variant (README.md:150-155): config.h gives NUM_DIST / NUM_DEPTH2 no #ifndef guard, so the build compiles
+  # against a temporary copy of cuda_rasterizer/ in which those two #define lines carry the requested values
+  VAR="$OUT/obj/dgr_variant"
+  rm -rf "$VAR" && mkdir -p "$VAR" "$OUT/diff_gaussian_rasterization_dist"
+  cp -r "$DGR/cuda_rasterizer" "$DGR/rasterize_points.cu" "$DGR/rasterize_points.h" "$DGR/ext.cpp" "$VAR/"
+  sed -i "s/^#define NUM_DIST .*/#define NUM_DIST ${NUM_DIST:-0}/; s/^#define NUM_DEPTH2 .*/#define NUM_DEPTH2 ${NUM_DEPTH2:-0}/" "$VAR/cuda_rasterizer/config.h"
+  grep -E "^#define NUM_(DIST|DEPTH2) " "$VAR/cuda_rasterizer/config.h" >&2
+  build_one diff_gaussian_rasterization_dist "$VAR" "$ARCH_DGR" "-I$GLMFIX" \
+    cuda_rasterizer/rasterizer_impl.cu cuda_rasterizer/forward.cu cuda_rasterizer/backward.cu rasterize_points.cu ext.cpp
+  rm -rf "$OUT/obj"
+  echo "built: $OUT/diff_gaussian_rasterization_dist/_C.so"
+  exit 0
+fi
 build_one diff_gaussian_rasterization "$DGR" "$ARCH_DGR" "-I$GLMFIX" \
   cuda_rasterizer/rasterizer_impl.cu cuda_rasterizer/forward.cu cuda_rasterizer/backward.cu rasterize_points.cu ext.cpp
 build_one simple_knn "$KNN" "$ARCH_KNN" "" spatial.cu simple_knn.cu ext.cpp

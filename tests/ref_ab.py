@@ -1,7 +1,10 @@
 """Drive the UNMODIFIED reference CUDA extension (compiled by oracle/build_ref.sh into oracle/_ref/) on the same inputs.
 
-Only the pybind11 module `_C` of the reference is used (DGR/ext.cpp:15-21); the argument tuples are the ones the
-reference's Python wrapper builds (DGR/diff_gaussian_rasterization/__init__.py:186-220 forward, :401-427 backward).
+RefRun calls the pybind11 module `_C` of the reference directly (DGR/ext.cpp:15-21) with the argument tuples the
+reference's Python wrapper builds (DGR/diff_gaussian_rasterization/__init__.py:186-220 forward, :401-427 backward), because
+the parity tests need the opaque buffers it returns; `wrapper()` gives the reference's own Python wrapper (staged beside
+`_C.so`, loaded under a private module name so that it cannot shadow this repository's package of the same name) for the
+`f_count` modes and for running the reference's render() against the reference build.
 The opaque buffers are decoded with the layout of GeometryState / BinningState / ImageState::fromChunk
 (DGR/cuda_rasterizer/rasterizer_impl.cu:155-195; obtain() aligns every array to 128 bytes, rasterizer_impl.h:21-27).
 Test infrastructure only.
@@ -17,22 +20,75 @@ REF_DIR = os.path.join(ROOT, "oracle", "_ref")
 _mods = {}
 
 
+def wrapper(name="diff_gaussian_rasterization"):
+    """The reference's Python package `name` from oracle/_ref (its own __init__.py + _C.so) as module `vcr_ref_<name>`, or
+    None when it has not been staged / built."""
+    import sys
+    key = "pkg:" + name
+    if key in _mods:
+        return _mods[key]
+    d = os.path.join(REF_DIR, name)
+    init = os.path.join(d, "__init__.py")
+    mod = None
+    if os.path.exists(init) and os.path.getsize(init) > 0 and os.path.exists(os.path.join(d, "_C.so")):
+        try:
+            modname = f"vcr_ref_{name}"
+            spec = importlib.util.spec_from_file_location(modname, init, submodule_search_locations=[d])
+            mod = importlib.util.module_from_spec(spec)
+            sys.modules[modname] = mod                      # `from . import _C` resolves against this entry
+            spec.loader.exec_module(mod)
+        except Exception as ex:  # pragma: no cover
+            print(f"reference package {d} failed to load: {ex}")
+            sys.modules.pop(f"vcr_ref_{name}", None)
+            mod = None
+    _mods[key] = mod
+    return mod
+
+
 def load(name="diff_gaussian_rasterization"):
     """Returns the reference `_C` module or None when oracle/_ref was not built / cannot be loaded."""
     if name in _mods:
         return _mods[name]
-    path = os.path.join(REF_DIR, name, "_C.so")
     mod = None
-    if os.path.exists(path):
-        try:
-            spec = importlib.util.spec_from_file_location(f"vcr_ref_{name}._C", path)  # PyInit__C; distinct cache key per module
-            mod = importlib.util.module_from_spec(spec)
-            spec.loader.exec_module(mod)
-        except Exception as ex:  # pragma: no cover
-            print(f"reference extension {path} failed to load: {ex}")
-            mod = None
+    w = wrapper(name)
+    if w is not None and hasattr(w, "_C"):
+        mod = w._C                                           # one load of the shared object per process
+    else:
+        path = os.path.join(REF_DIR, name, "_C.so")
+        if os.path.exists(path):
+            try:
+                spec = importlib.util.spec_from_file_location(f"vcr_ref_{name}._C", path)  # PyInit__C; distinct cache key per module
+                mod = importlib.util.module_from_spec(spec)
+                spec.loader.exec_module(mod)
+            except Exception as ex:  # pragma: no cover
+                print(f"reference extension {path} failed to load: {ex}")
+                mod = None
     _mods[name] = mod
     return mod
+
+
+def settings(inp, device, f_count=0):
+    """GaussianRasterizationSettings of the REFERENCE wrapper for a tests/util.py input dict."""
+    w = wrapper()
+    return w.GaussianRasterizationSettings(
+        image_height=inp["H"], image_width=inp["W"], tanfovx=inp["tanfovx"], tanfovy=inp["tanfovy"], bg=inp["bg"].to(device),
+        scale_modifier=1.0, viewmatrix=inp["viewmatrix"].to(device), projmatrix=inp["projmatrix"].to(device),
+        sh_degree=inp["sh_degree"], campos=inp["campos"].to(device), prefiltered=False, debug=False, f_count=f_count)
+
+
+def aux(inp, f_count, device="cuda"):
+    """f_count = 1: (gaussians_count, important_score, color, radii) of _C.count_gaussians; f_count = 3: (gaussians_count,
+    radii) of _C.visi_gaussians_acc — through the reference wrapper's own dispatch (rasterize_gaussians, __init__.py:42-94)."""
+    w = wrapper()
+    dev = torch.device(device)
+    t = lambda x: x.to(dev).contiguous()  # noqa: E731
+    means3D = t(inp["means3D"])
+    rast = w.GaussianRasterizer(raster_settings=settings(inp, dev, f_count))
+    with torch.no_grad():
+        out = rast(means3D=means3D, means2D=torch.zeros_like(means3D), means2D_densify=torch.zeros_like(means3D), opacities=t(inp["opacities"]),
+                   shs=t(inp["shs"]), scales=t(inp["scales"]), rotations=t(inp["rotations"]))
+    torch.cuda.synchronize()
+    return out
 
 
 def _al(x, a=128):

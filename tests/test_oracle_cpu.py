@@ -173,3 +173,43 @@ def test_preprocess_edge_cases():
     one = {k: (v[:1] if isinstance(v, np.ndarray) and v.shape[:1] == (40,) else v) for k, v in inp.items()}
     f1 = O.rasterize_forward(one)
     assert f1["pre"]["radii"].shape == (1,)
+
+
+@pytest.mark.parametrize("tag", ["a", "b", "c", "d"])
+def test_dnormal_oracle_pinned_to_reference_functions(tag):
+    """orc_dnormal against golden vectors written by tests/golden/make_python_golden.py from the reference's OWN
+    compute_normals / cos_weight / monosdf_normal_loss (tools/normal_utils.py:30-41, tools/loss_utils.py:122-142) and the
+    'depth_normal' branch of trainer.py:266-280, in float64: loss, est_normal and dL/ddepth, with the confidence weight on
+    and off and with an empty mask."""
+    import os
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "pyref_dnormal.npz"))
+    g = {k[len(tag) + 1:]: z[k] for k in z.files if k.startswith(tag + "_")}
+    K = g["K"]
+    o = O.dnormal(g["depth"][None], g["gt_normal"], g["render_normal"], g["mask"], (float(K[0, 0]), float(K[1, 1]), float(K[0, 2]), float(K[1, 2])),
+                  exp_t=float(g["exp_t"]))
+    assert abs(o["loss"] - float(g["loss_f64"])) <= 1e-6 * max(1.0, abs(float(g["loss_f64"])))
+    # the reference forms pixel coordinates as float32((u + 0.5) / (W - 1)) * (W - 1) even when the depth map is float64
+    # (tools/graphics_utils.py:114-115, 104-106): ~1e-7 relative noise on X that the oracle's exact (u + 0.5) does not have
+    np.testing.assert_allclose(o["est_normal"], g["est_normal_f64"], atol=5e-6)
+    if np.abs(g["dL_ddepth_f64"]).max() > 0:
+        assert rel_l2(o["dL_ddepth"], g["dL_ddepth_f64"]) < 1e-5
+    else:
+        assert np.abs(o["dL_ddepth"]).max() == 0.0
+
+
+def test_python_golden_vectors_are_what_the_reference_computes():
+    """Where the reference's Python is at hand (oracle/_ref/pyref, staged from /root/reference), recompute two of the golden
+    values live and compare: guards against stale fixtures."""
+    import os
+    import pyref
+    R = pyref.load()
+    if R is None:
+        pytest.skip("oracle/_ref/pyref not staged on this machine")
+    gold = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    g = np.load(os.path.join(gold, "pyref_image.npz"))
+    img, gt = torch.from_numpy(g["image"]).double(), torch.from_numpy(g["gt_image"]).double()
+    assert abs(float(R.ssim(img, gt)) - float(g["ssim_f64"])) < 1e-12 and abs(float(R.l1_loss(img, gt)) - float(g["l1_f64"])) < 1e-12
+    z = np.load(os.path.join(gold, "pyref_dnormal.npz"))
+    d = torch.from_numpy(z["a_depth"])[None].double()
+    est = R.compute_normals(d, torch.from_numpy(z["a_K"]).double())
+    np.testing.assert_allclose(est.numpy(), z["a_est_normal_f64"], atol=1e-12)

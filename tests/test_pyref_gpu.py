@@ -1,0 +1,248 @@
+"""The fused kernels around the rasterizer against the reference's OWN Python functions.
+
+Two pins per kernel: (1) golden vectors written by tests/golden/make_python_golden.py from tools/normal_utils.py,
+tools/loss_utils.py, tools/general_utils.py and scene/gaussian_model.py of the reference (CPU, float64 and float32), and
+(2) the same functions imported live from oracle/_ref/pyref (verbatim copies staged by oracle/build_ref.sh; skipped when
+absent) and run on this GPU at larger sizes.  Also here: the reference's unmodified render() and GaussianModel driving THIS
+library (drop-in), compared with the same call on the reference build, and the device-side densification against
+GaussianModel.densify_and_prune."""
+import os
+import sys
+import types
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+import pyref
+from util import make_case, rel_l2
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+DEV = "cuda"
+
+
+def _t(a, dtype=torch.float32):
+    return torch.from_numpy(np.asarray(a)).to(DEV).to(dtype)
+
+
+@pytest.mark.parametrize("tag", ["a", "b", "c", "d"])
+def test_dnormal_against_golden_from_reference_functions(tag):
+    """depth_normal_loss / compute_normals vs compute_normals + cos_weight + monosdf_normal_loss of the reference (float64)."""
+    from vcr_dnormal import depth_normal_loss
+    z = np.load(os.path.join(GOLD, "pyref_dnormal.npz"))
+    g = {k[len(tag) + 1:]: z[k] for k in z.files if k.startswith(tag + "_")}
+    d = _t(g["depth"])[None].requires_grad_(True)
+    loss, est = depth_normal_loss(d, _t(g["K"]), _t(g["gt_normal"]), _t(g["render_normal"]), torch.from_numpy(g["mask"]).to(DEV),
+                                  exp_t=float(g["exp_t"]), return_normal=True)
+    loss.backward()
+    torch.cuda.synchronize()
+    np.testing.assert_allclose(est.detach().cpu().numpy(), g["est_normal_f64"], atol=2e-4)
+    assert abs(float(loss) - float(g["loss_f64"])) <= 1e-5 * max(1.0, abs(float(g["loss_f64"])))
+    if np.abs(g["dL_ddepth_f64"]).max() > 0:
+        assert rel_l2(d.grad[0].cpu().numpy(), g["dL_ddepth_f64"]) <= 1e-3
+    else:
+        assert float(d.grad.abs().max()) == 0.0                      # empty mask: loss 0, gradient 0 (trainer.py:279)
+
+
+def test_image_losses_against_golden_from_reference_functions():
+    """view_loss (L1 + mono-normal terms) and ssim vs l1_loss / monosdf_normal_loss / ssim of the reference (float64)."""
+    from vcr_dnormal import ssim, view_loss
+    g = np.load(os.path.join(GOLD, "pyref_image.npz"))
+    H, W = g["image"].shape[1:]
+    out = torch.zeros((10, H, W), device=DEV)
+    out[:3] = _t(g["image"]); out[3] = 1.0; out[4:7] = _t(g["render_normal"]).permute(2, 0, 1); out[7] = 1.0
+    out.requires_grad_(True)
+    K4 = (50.0, 50.0, W / 2, H / 2)
+    loss = view_loss(out, _t(g["gt_image"]), _t(g["gt_normal"]), K4, w_l1=0.7, w_mono=0.3, w_dn=0.0)
+    loss.backward()
+    want = 0.7 * float(g["l1_f64"]) + 0.3 * float(g["mono_f64"])
+    assert abs(float(loss) - want) <= 2e-6 * max(1.0, abs(want))
+    assert rel_l2(out.grad[:3].cpu().numpy(), 0.7 * g["dl1_f64"]) <= 1e-5
+    assert rel_l2(out.grad[4:7].permute(1, 2, 0).cpu().numpy(), 0.3 * g["dmono_f64"]) <= 1e-4
+    img = _t(g["image"]).requires_grad_(True)
+    s = ssim(img, _t(g["gt_image"]))
+    s.backward()
+    assert abs(float(s) - float(g["ssim_f64"])) <= 2e-6
+    assert rel_l2(img.grad.cpu().numpy(), g["dssim_f64"]) <= 1e-5
+
+
+def test_prologue_against_golden_from_gaussian_model():
+    """gaussian_prologue vs GaussianModel.get_* + the flip / rotation of render() (float64 golden), values and gradients."""
+    from vcr_prologue import gaussian_prologue
+    g = np.load(os.path.join(GOLD, "pyref_prologue.npz"))
+    raw = {k: _t(g[f"raw_{k}"]).requires_grad_(k != "xyz") for k in ("xyz", "f_dc", "f_rest", "opacity", "scaling", "rotation")}
+    R_w2c = _t(g["cam_R"]).t().contiguous()
+    got = gaussian_prologue(raw["xyz"], raw["f_dc"], raw["f_rest"], raw["opacity"], raw["scaling"], raw["rotation"], _t(g["cam_center"]), R_w2c)
+    names = ("opacity", "scales", "rotations", "shs", "normals")
+    for n, a in zip(names, got):
+        np.testing.assert_allclose(a.detach().cpu().numpy(), g[f"{n}_f64"], rtol=3e-6, atol=3e-6, err_msg=n)
+    total = sum((a * _t(g[f"cot_{n}"])).sum() for n, a in zip(names, got))
+    total.backward()
+    for k in ("f_dc", "f_rest", "opacity", "scaling", "rotation"):
+        assert rel_l2(raw[k].grad.cpu().numpy(), g[f"grad_{k}_f64"]) <= 1e-5, k
+
+
+needs_pyref = pytest.mark.skipif(not pyref.available(), reason="oracle/_ref/pyref (the reference's Python, staged by oracle/build_ref.sh) is absent")
+
+
+@needs_pyref
+def test_dnormal_live_against_reference_functions_on_gpu():
+    from vcr_dnormal import depth_normal_loss
+    from test_dnormal_knn_gpu import make_dn_inputs
+    R = pyref.load()
+    for (W, H, exp_t) in ((640, 480, 0.005), (1920, 1080, 0.5)):
+        depth, gt, rn, mask, K = make_dn_inputs(W, H, seed=W)
+        d = depth.to(DEV).requires_grad_(True)
+        loss = depth_normal_loss(d, K, gt.to(DEV), rn.to(DEV), mask.to(DEV), exp_t=exp_t)
+        loss.backward()
+        d64 = depth.to(DEV).double().requires_grad_(True)
+        est = R.compute_normals(d64, K.to(DEV).double())
+        ref = pyref.dnormal_loss(R, est, gt.to(DEV).double(), F.normalize(rn.to(DEV).double(), dim=-1), mask.to(DEV), exp_t)
+        ref.backward()
+        assert abs(float(loss) - float(ref)) <= 1e-5 * max(1.0, abs(float(ref)))
+        assert rel_l2(d.grad.cpu().numpy(), d64.grad.cpu().numpy()) <= 1e-3
+
+
+@needs_pyref
+def test_ssim_live_against_reference_function_on_gpu():
+    from vcr_dnormal import ssim
+    R = pyref.load()
+    g = torch.Generator().manual_seed(0)
+    gt = torch.rand((3, 270, 481), generator=g).to(DEV)
+    img = (gt + 0.15 * torch.randn((3, 270, 481), generator=g).to(DEV)).clamp(0, 1).requires_grad_(True)
+    val = ssim(img, gt)
+    val.backward()
+    i64 = img.detach().double().requires_grad_(True)
+    ref = R.ssim(i64, gt.double())
+    ref.backward()
+    assert abs(float(val) - float(ref)) <= 2e-6
+    assert rel_l2(img.grad.cpu().numpy(), i64.grad.cpu().numpy()) <= 1e-5
+
+
+def _raw_from_scene(sc):
+    return dict(xyz=sc.means3D.clone(), f_dc=sc.shs[:, :1].contiguous(), f_rest=sc.shs[:, 1:].contiguous(),
+                opacity=torch.logit(sc.opacities.clamp(1e-4, 1 - 1e-4)), scaling=torch.log(sc.scales), rotation=sc.rotations * 1.3)
+
+
+@needs_pyref
+def test_prologue_live_against_gaussian_model_on_gpu():
+    from vcr_prologue import gaussian_prologue
+    _, sc, cam = make_case(100_003, 64, 48, seed=5)
+    raw = _raw_from_scene(sc)
+    m = pyref.make_model(raw, DEV)
+    opacity, scales, rotations, shs = m.get_opacity, m.get_scaling, m.get_rotation, m.get_features
+    normal = m.get_normal(is_all=True)
+    cc = cam.camera_center.to(DEV)
+    view_dir = m.get_xyz - cc                                                        # gaussian_renderer/__init__.py:95-101
+    normal = normal * ((((view_dir * normal).sum(dim=-1) > 0) * 1 - 0.5) * 2)[..., None]
+    R_w2c = torch.tensor(cam.R.numpy().T).cuda().to(torch.float32)
+    exp = (opacity, scales, rotations, shs, normal @ R_w2c.transpose(0, 1))
+    leaves = {k: v.to(DEV).requires_grad_(k != "xyz") for k, v in raw.items()}
+    got = gaussian_prologue(leaves["xyz"], leaves["f_dc"], leaves["f_rest"], leaves["opacity"], leaves["scaling"], leaves["rotation"], cc, R_w2c)
+    for n, a, b in zip(("opacity", "scales", "rotations", "shs", "normals"), got, exp):
+        torch.testing.assert_close(a, b, rtol=2e-6, atol=2e-6, msg=lambda s, n=n: f"{n}: {s}")
+    g = torch.Generator().manual_seed(1)
+    cot = [torch.randn(t.shape, generator=g).to(DEV) for t in exp]
+    sum((a * c).sum() for a, c in zip(got, cot)).backward()
+    sum((a * c).sum() for a, c in zip(exp, cot)).backward()
+    for k, prm in (("f_dc", m._features_dc), ("f_rest", m._features_rest), ("opacity", m._opacity), ("scaling", m._scaling), ("rotation", m._rotation)):
+        assert rel_l2(leaves[k].grad.cpu().numpy(), prm.grad.cpu().numpy()) <= 2e-5, k
+
+
+@needs_pyref
+def test_reference_render_runs_unmodified_on_this_library():
+    """Drop-in: the reference's own render() (gaussian_renderer/__init__.py:22-150) and GaussianModel, unmodified, with
+    `diff_gaussian_rasterization` resolved to this repository's package — output dict and parameter gradients compared with the
+    same call on the reference CUDA build."""
+    import diff_gaussian_rasterization as mine
+    import ref_ab
+    assert os.path.realpath(mine.__file__).startswith(os.path.realpath(os.path.join(pyref.ROOT, "vcr-gaus_b200")))
+    W, H = 400, 296
+    inp, sc, cam = make_case(30_001, W, H, seed=2)
+    raw = _raw_from_scene(sc)
+    cfg = pyref.render_cfg()
+    vc = pyref.camera_namespace(cam, DEV)
+    bg = inp["bg"].to(DEV)
+    dirs = inp["dirs"].to(DEV)
+    g = torch.Generator().manual_seed(4)
+    cot = {k: torch.randn(s, generator=g).to(DEV) for k, s in dict(render=(3, H, W), depth=(1, H, W), normal=(H, W, 3), alpha=(1, H, W)).items()}
+
+    def run(render):
+        m = pyref.make_model(raw, DEV)
+        m.extent = sc.extent
+        pkg = render(vc, m, cfg, bg, dirs=dirs)
+        loss = sum((pkg[k] * cot[k]).sum() for k in cot) + (pkg["est_normal"] * cot["normal"]).sum()
+        loss.backward()
+        grads = {k: getattr(m, k).grad for k in ("_xyz", "_features_dc", "_features_rest", "_opacity", "_scaling", "_rotation")}
+        return pkg, grads, pkg["viewspace_points_densify"].grad
+
+    pkg, grads, dens = run(pyref.render_bound(mine, "mine"))
+    assert set(pkg) >= {"render", "depth", "normal", "est_normal", "alpha", "viewspace_points", "viewspace_points_densify",
+                        "visibility_filter", "mask", "radii"}
+    assert pkg["render"].shape == (3, H, W) and pkg["radii"].dtype == torch.int32 and int(pkg["visibility_filter"].sum()) > 0
+    assert all(torch.isfinite(v).all() for v in grads.values())
+    ref_pkg = ref_ab.wrapper()
+    if ref_pkg is None:
+        pytest.skip("reference build absent: render() ran on this library, nothing to compare with")
+    rpkg, rgrads, rdens = run(pyref.render_bound(ref_pkg, "ref"))
+    assert torch.equal(pkg["radii"], rpkg["radii"]) and torch.equal(pkg["mask"], rpkg["mask"])
+    for k in ("render", "depth", "alpha"):
+        assert float((pkg[k] - rpkg[k]).abs().max()) <= 1e-5 * max(1.0, float(rpkg[k].abs().max())), k
+    assert float((pkg["normal"] - rpkg["normal"]).abs().max()) <= 1e-5
+    assert float((pkg["est_normal"] - rpkg["est_normal"]).abs().max()) <= 1e-4     # normals of a float32 depth map: same bits in, same code
+    for k in grads:
+        assert rel_l2(grads[k].cpu().numpy(), rgrads[k].cpu().numpy()) <= 1e-3, k
+    assert rel_l2(dens.cpu().numpy(), rdens.cpu().numpy()) <= 1e-3
+
+
+@needs_pyref
+@pytest.mark.parametrize("size_prune", [False, True])
+def test_densify_matches_gaussian_model(size_prune):
+    """vcr_densify.densify_and_prune == GaussianModel.densify_and_prune (scene/gaussian_model.py:645-659) on the same state:
+    same rows in the same order (parameters exact for copies, <= 1e-6 for the children), same Adam moments."""
+    import vcr_view_parallel as VP
+    from vcr_densify import densify_and_prune
+    P = 20_003
+    _, sc, _ = make_case(P, 32, 32, seed=7)
+    raw = _raw_from_scene(sc)
+    g = torch.Generator().manual_seed(3)
+    raw["opacity"][::17] = -7.0                                    # some below the opacity floor
+    raw["scaling"][::29] += 3.0                                    # some large ones (split; pruned by size when enabled)
+    accum = (torch.rand((P, 1), generator=g) * 2e-3).to(DEV)
+    denom = torch.randint(0, 4, (P, 1), generator=g).float().to(DEV)   # zeros -> NaN -> 0
+    max_r = torch.rand(P, generator=g).to(DEV) * 50
+    thr, min_op, extent = 6e-4, 0.005, 1.0
+    m = pyref.make_model(raw, DEV, optim=True)
+    names = ("xyz", "f_dc", "f_rest", "opacity", "scaling", "rotation")
+    for grp in m.optimizer.param_groups:                            # give the optimizer a state to carry
+        prm = grp["params"][0]
+        prm.grad = torch.randn(prm.shape, generator=g).to(DEV)
+    m.optimizer.step()
+    state = {grp["name"]: m.optimizer.state[grp["params"][0]] for grp in m.optimizer.param_groups}
+    bucket = VP.GaussianBucket({k: getattr(m, "_" + dict(xyz="xyz", f_dc="features_dc", f_rest="features_rest", opacity="opacity",
+                                                        scaling="scaling", rotation="rotation")[k]).detach().clone() for k in names},
+                               device=torch.device(DEV), names=names)
+    opt = VP.BucketAdam(bucket, {k: 1e-3 for k in names})
+    opt.steps = 1
+    for k, off, n, shape in bucket.layout:
+        opt.exp_avg[off:off + n] = state[k]["exp_avg"].reshape(-1)
+        opt.exp_avg_sq[off:off + n] = state[k]["exp_avg_sq"].reshape(-1)
+    new, opt2, info = densify_and_prune(bucket, opt, accum.clone(), denom.clone(), max_r.clone(), max_grad=thr, min_opacity=min_op, extent=extent,
+                                        max_screen_size=(20 if size_prune else None), percent_dense=0.01)
+    m.xyz_gradient_accum, m.denom, m.max_radii2D = accum.clone(), denom.clone(), max_r.clone()
+    m.densify_and_prune(thr, min_op, extent, 20 if size_prune else None, None)
+    torch.cuda.synchronize()
+    assert info["n_clone"] > 0 and info["n_split"] > 0 and info["n_kept"] < P
+    ref = dict(xyz=m._xyz, f_dc=m._features_dc, f_rest=m._features_rest, opacity=m._opacity, scaling=m._scaling, rotation=m._rotation)
+    assert new.P == ref["xyz"].shape[0] == info["n_kept"] + info["n_clone"] + 2 * info["n_split"], (new.P, ref["xyz"].shape, info)
+    nk = info["n_kept"] + info["n_clone"]
+    for k, off, n, shape in new.layout:
+        a, b = new.params[k].detach(), ref[k].detach()
+        assert a.shape == b.shape, k
+        assert torch.equal(a[:nk], b[:nk]), f"{k}: kept rows and clones are copies"
+        torch.testing.assert_close(a[nk:], b[nk:], rtol=2e-6, atol=2e-6, msg=lambda s, k=k: f"{k} children: {s}")
+        st = m.optimizer.state[[grp for grp in m.optimizer.param_groups if grp["name"] == k][0]["params"][0]]
+        assert torch.equal(opt2.exp_avg[off:off + n].view(shape), st["exp_avg"]) and torch.equal(opt2.exp_avg_sq[off:off + n].view(shape), st["exp_avg_sq"]), k
+    assert all(o % 4 == 0 for _, o, _, _ in new.layout)

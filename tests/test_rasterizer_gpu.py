@@ -145,13 +145,14 @@ def test_everything_culled_and_empty():
     inp = dict(inp)
     inp["means3D"] = inp["means3D"] + torch.tensor([1000.0, 0.0, 0.0])   # far outside the frustum / behind
     run = CudaRun(inp)
-    assert run.saved()["R"] == 0 or (run.radii == 0).all() or True
     out = run.out.detach().cpu().numpy()
     orc = O.rasterize_forward(np_inputs(inp))
-    assert run.saved()["R"] == orc["binned"]["R"]
+    assert orc["binned"]["R"] == 0, "the case is built so that nothing is rendered"
+    assert run.saved()["R"] == 0 and bool((run.radii == 0).all())
     np.testing.assert_allclose(out, orc["out_color"], atol=1e-6)
     cb = run.backward(torch.ones_like(run.out))
-    assert np.all(cb["dL_dmeans3D"] == 0) or orc["binned"]["R"] > 0
+    for k in ("dL_dmeans3D", "dL_dsh", "dL_dopacity", "dL_dscales", "dL_drotations", "dL_dnormals"):
+        assert np.all(cb[k] == 0), k
     # P == 0 short-circuit (rasterize_points.cu:106)
     dev = torch.device("cuda")
     rs = settings_from(inp, dev)
@@ -178,14 +179,18 @@ def test_mark_visible_and_aux_modes():
     cnt, score, color, radii = GaussianRasterizer(settings_from(inp, dev, f_count=1))(**kw)
     oc = O.rasterize_forward(npi, mode=1)
     assert np.array_equal(radii.cpu().numpy(), oc["pre"]["radii"])
-    assert (cnt.cpu().numpy() != oc["gaussians_count"]).mean() < 1e-3
+    # The CPU oracle cannot reproduce MUFU.EX2: a pair whose alpha lies within an ulp of 1/255 (or whose T lies within an
+    # ulp of 1e-4) is counted by one side and not by the other — the FLIP_FRAC allowance of the pixels below, times 5 because
+    # there are ~3.4 pixels per Gaussian here and a flipped pair changes one Gaussian's count (and, through T, possibly the
+    # next one's).  The exact gate for these modes is the A/B against the reference build (test_reference_ab_gpu.py).
+    assert (cnt.cpu().numpy() != oc["gaussians_count"]).mean() <= 5 * FLIP_FRAC
     np.testing.assert_allclose(score.cpu().numpy(), oc["important_score"], rtol=1e-3, atol=1.0)
     d = np.abs(color.cpu().numpy() - oc["out_color"][:3])
     assert (d > ABS_TOL).mean() <= FLIP_FRAC
     # f_count = 3
     cnt3, radii3 = GaussianRasterizer(settings_from(inp, dev, f_count=3))(**kw)
     o3 = O.rasterize_forward(npi, mode=3)
-    assert ((cnt3.cpu().numpy() > 0) != (o3["gaussians_count"] > 0)).mean() < 1e-3
+    assert ((cnt3.cpu().numpy() > 0) != (o3["gaussians_count"] > 0)).mean() <= 5 * FLIP_FRAC
     assert abs(int(cnt3.sum()) - int(o3["gaussians_count"].sum())) <= 4
 
 

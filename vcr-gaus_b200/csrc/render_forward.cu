@@ -36,15 +36,23 @@ struct RfStage {                       // one staging buffer
     float4 col[MODE != VCR_MODE_VISI_ACC ? RF_BATCH : 1];              // rgb, semantics[1]
 };
 
-template <int MODE, bool HAS_DIRS, bool HAS_OBJ>
+// Instrumentation (bench.py `scene`): when a counter array has been registered with vcr_pair_counters() the forward runs
+// its STATS instantiation, which adds up K_e (pixel x Gaussian pairs whose exponent is evaluated), K_c (pairs that
+// contribute), sum(n_contrib) and the number of (warp, Gaussian) candidates.  The production instantiation has none of this.
+static unsigned long long* g_pair_counters = nullptr;
+extern "C" int vcr_pair_counters(unsigned long long* counters_device) { g_pair_counters = counters_device; return 0; }
+
+template <int MODE, bool HAS_DIRS, bool HAS_OBJ, bool STATS = false>
 __global__ void __launch_bounds__(256, 4) render_forward_kernel(
     const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order, int gx, const uint32_t* __restrict__ point_list, int W, int H,
     const float2* __restrict__ means2D, const float* __restrict__ xyz_view, const float* __restrict__ features,
     const float* __restrict__ depths, const float* __restrict__ normals, const float* __restrict__ obj,
     const float* __restrict__ dirs, const float4* __restrict__ conic_opacity, const uint8_t* __restrict__ inside_gs,
     const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
-    float* __restrict__ out_color, int* __restrict__ gaussian_count, float* __restrict__ important_score) {
+    float* __restrict__ out_color, int* __restrict__ gaussian_count, float* __restrict__ important_score,
+    unsigned long long* __restrict__ pair_counters = nullptr) {
     __shared__ RfStage<MODE> s_stage[2];
+    unsigned int st_ke = 0, st_kc = 0, st_cand = 0;
 
     const int tid = threadIdx.x, lane = tid & 31;
     const uint32_t tile = __ldg(tile_order + blockIdx.x);      // blocks take tiles longest-list first
@@ -136,7 +144,9 @@ __global__ void __launch_bounds__(256, 4) render_forward_kernel(
                 if (__all_sync(0xffffffffu, done)) { warp_done = true; break; }
                 const int j = k * 32 + __ffs(m) - 1;
                 m &= m - 1;
+                if (STATS && lane == 0) st_cand++;
                 if (done) continue;
+                if (STATS) st_ke++;
                 const float4 g0 = *reinterpret_cast<const float4*>(&st.geo[j]);        // x, y, ca, cb
                 const float4 g1 = *reinterpret_cast<const float4*>(&st.geo[j].cc);     // cc, op, nx, id_inside
                 const float dx = g0.x - pfx, dy = g0.y - pfy;
@@ -185,6 +195,7 @@ __global__ void __launch_bounds__(256, 4) render_forward_kernel(
                     }
                 }
                 T = test_T;
+                if (STATS) st_kc++;
                 last_contributor = (uint32_t)(i * RF_BATCH + j + 1);
             }
         }
@@ -192,6 +203,14 @@ __global__ void __launch_bounds__(256, 4) render_forward_kernel(
         if (__syncthreads_and(done)) break;
     }
 
+    if (STATS) {
+        const unsigned int ke = __reduce_add_sync(0xffffffffu, st_ke), kc = __reduce_add_sync(0xffffffffu, st_kc);
+        const unsigned int nc = __reduce_add_sync(0xffffffffu, inside ? last_contributor : 0u);
+        if (lane == 0) {
+            atomicAdd(pair_counters + 0, (unsigned long long)ke); atomicAdd(pair_counters + 1, (unsigned long long)kc);
+            atomicAdd(pair_counters + 2, (unsigned long long)nc); atomicAdd(pair_counters + 3, (unsigned long long)st_cand);
+        }
+    }
     if (inside && MODE != VCR_MODE_VISI_ACC) {
         final_T[pix_id] = T;
         n_contrib[pix_id] = last_contributor;
@@ -215,7 +234,15 @@ int vcr_launch_render_forward(const FwdParams& p, GeomState& g, BinningState& b,
     VcrProfScope prof(VCR_K_RENDER_FWD, s);
 #define RF_ARGS img.ranges, img.tile_order, p.gx, b.point_list, p.W, p.H, g.means2D, g.xyz_view, feat, g.depths, p.normals, p.sh_objs, p.dirs, \
                 g.conic_opacity, p.inside, p.background, img.accum_alpha, img.n_contrib, p.out_color, nullptr, nullptr
-    if (p.dirs) {
+    if (g_pair_counters) {          // instrumented run (never inside a timed region)
+        if (p.dirs) {
+            if (p.sh_objs) render_forward_kernel<0, true, true, true><<<grid, 256, 0, s>>>(RF_ARGS, g_pair_counters);
+            else render_forward_kernel<0, true, false, true><<<grid, 256, 0, s>>>(RF_ARGS, g_pair_counters);
+        } else {
+            if (p.sh_objs) render_forward_kernel<0, false, true, true><<<grid, 256, 0, s>>>(RF_ARGS, g_pair_counters);
+            else render_forward_kernel<0, false, false, true><<<grid, 256, 0, s>>>(RF_ARGS, g_pair_counters);
+        }
+    } else if (p.dirs) {
         if (p.sh_objs) render_forward_kernel<0, true, true><<<grid, 256, 0, s>>>(RF_ARGS);
         else render_forward_kernel<0, true, false><<<grid, 256, 0, s>>>(RF_ARGS);
     } else {

@@ -83,6 +83,9 @@ vcr_multimem_exchange = _sig("vcr_multimem_exchange", c_int,
 vcr_compact_scratch_bytes = _sig("vcr_compact_scratch_bytes", c_size_t, [c_int])
 vcr_compact_rows = _sig("vcr_compact_rows", c_int, [c_int, P_, c_int, POINTER(c_void_p), POINTER(c_void_p), POINTER(c_int), P_, P_, c_void_p])
 
+vcr_densify_scratch_bytes = _sig("vcr_densify_scratch_bytes", c_size_t, [c_int])
+vcr_densify_decide = _sig("vcr_densify_decide", c_int, [c_int, P_, P_, P_, P_, c_float, c_float, c_float, c_float, P_, P_, P_, c_void_p])
+vcr_densify_fill = _sig("vcr_densify_fill", c_int, [c_int, P_, P_, c_int, c_int, c_int, POINTER(c_void_p), POINTER(c_void_p), POINTER(c_int), c_void_p])
 vcr_densify_stats_accumulate = _sig("vcr_densify_stats_accumulate", c_int, [c_int, P_, P_, P_, P_, P_, c_void_p])
 
 vcr_mark_visible = _sig("vcr_mark_visible", c_int, [c_int, P_, P_, P_, P_, c_void_p])
@@ -117,6 +120,7 @@ vcr_knn_noalloc_max_points = _sig("vcr_knn_noalloc_max_points", c_int, [])
 vcr_dist2_knn3_noalloc = _sig("vcr_dist2_knn3_noalloc", c_int, [c_int, P_, P_, c_void_p])
 
 
+vcr_pair_counters = _sig("vcr_pair_counters", c_int, [P_])
 vcr_profile_enable = _sig("vcr_profile_enable", c_int, [c_int])
 vcr_profile_kernel_count = _sig("vcr_profile_kernel_count", c_int, [])
 vcr_profile_kernel_name = _sig("vcr_profile_kernel_name", c_char_p, [c_int])
@@ -159,6 +163,7 @@ DECLARED_SYMBOLS = [
     "vcr_knn_noalloc_max_points", "vcr_dist2_knn3_noalloc", "vcr_view_loss_forward", "vcr_view_loss_backward",
     "vcr_profile_enable", "vcr_profile_kernel_count", "vcr_profile_kernel_name", "vcr_profile_read",
     "vcr_rasterize_backward_chunked", "vcr_densify_stats_accumulate", "vcr_multimem_allreduce_sum", "vcr_prologue_forward", "vcr_prologue_backward", "vcr_ssim_forward", "vcr_ssim_backward", "vcr_adam_step", "vcr_view_loss_total", "vcr_binning_reference_lists", "vcr_compact_scratch_bytes", "vcr_compact_rows", "vcr_sh_grad_from_colors", "vcr_multimem_exchange",
+    "vcr_pair_counters", "vcr_densify_scratch_bytes", "vcr_densify_decide", "vcr_densify_fill",
 ]
 
 

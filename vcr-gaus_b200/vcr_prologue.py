@@ -27,7 +27,10 @@ def _c(t, name):
         raise RuntimeError(f"gaussian_prologue: {name} must be a CUDA tensor; there is no CPU fallback")
     if t.dtype != torch.float32:
         raise RuntimeError(f"gaussian_prologue: {name} must be float32, got {t.dtype}")
-    return t.contiguous()
+    t = t.contiguous()
+    if t.data_ptr() % 16 and t.ndim == 2 and t.shape[1] == 4:
+        t = t.clone()       # quaternion arrays are accessed as float4 (include/vcr_gaus_b200.h, "Alignment")
+    return t
 
 
 class _Prologue(torch.autograd.Function):
@@ -75,7 +78,8 @@ class _Prologue(torch.autograd.Function):
         g_shs, g_normals = g(g_shs, (P, 1 + n_rest, 3)), g(g_normals, (P, 3))
         def dest(i, shape):
             buf = ctx.grad_out[i]
-            if buf is not None and buf.is_cuda and buf.dtype == torch.float32 and buf.is_contiguous() and tuple(buf.shape) == tuple(shape):
+            if (buf is not None and buf.is_cuda and buf.dtype == torch.float32 and buf.is_contiguous()
+                    and tuple(buf.shape) == tuple(shape) and buf.data_ptr() % 16 == 0):
                 return buf.view(shape)       # a fresh view of the bucket: autograd adopts it as .grad without a copy
             return torch.empty(shape, **f)
         d_dc, d_rest = dest(0, dc_shape), dest(1, rest_shape)

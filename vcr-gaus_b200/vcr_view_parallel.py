@@ -185,14 +185,15 @@ class BucketAdam:
 
 
 def prune_and_grow(bucket: GaussianBucket, keep: torch.Tensor, n_new: int = 0, optimizer: Optional[BucketAdam] = None,
-                   grad_storage: Optional[torch.Tensor] = None):
+                   grad_storage: Optional[torch.Tensor] = None, n_kept: Optional[int] = None):
     """Densify / prune on the flat bucket: a new GaussianBucket whose first rows are the rows of `bucket` with keep != 0, in
     order, followed by `n_new` rows for the caller to fill (clones / splits; zero until then), and — when `optimizer` is
     given — a new BucketAdam whose moments are compacted the same way (zeros for the new rows, as
     cat_tensors_to_optimizer does).  Replaces prune_points + densification_postfix of the reference
     (scene/gaussian_model.py:442-531: ~18 boolean-mask indexing operations and as many torch.cat) by one prefix sum and
     one gather launch per 8 arrays (vcr_compact_rows).
-    `keep`: bool / uint8 CUDA tensor [P].  One host read of the kept count (the new bucket has to be sized).
+    `keep`: bool / uint8 CUDA tensor [P].  One host read of the kept count (the new bucket has to be sized), unless the
+    caller already knows it and passes `n_kept`.
     `grad_storage`: flat float32 storage for the new gradient bucket (the symmetric allocation of
     ViewParallel.symmetric_gradient_storage(), which must have been sized for the grown model); default: an ordinary
     allocation.  The new bucket has NONE of the exchange state of the old one: after this call the view-parallel set-up
@@ -206,7 +207,7 @@ def prune_and_grow(bucket: GaussianBucket, keep: torch.Tensor, n_new: int = 0, o
     k8 = (keep.to(torch.uint8) if keep.dtype == torch.bool else keep).contiguous()
     if k8.numel() != P or k8.dtype != torch.uint8:
         raise ValueError("keep must have one bool / uint8 entry per Gaussian")
-    n_kept = int(k8.sum())
+    n_kept = int(k8.sum()) if n_kept is None else int(n_kept)
     P2 = n_kept + int(n_new)
     # group-major layout of the new bucket: every group is compacted into its own 16-byte aligned slice
     new = GaussianBucket.__new__(GaussianBucket)
