@@ -428,6 +428,11 @@ int vcr_profile_read(float* ms, long long* timed, long long* launches, int reset
  * contributed, [2] sum over pixels of n_contrib, [3] (warp, Gaussian) candidates after culling.  NULL switches it off.
  * Process-wide, not thread-safe; meant for bench.py outside its timed regions. */
 int vcr_pair_counters(unsigned long long* counters_device);
+/* Test hook for the sort's failure path (no counterpart in the reference, whose CUB sort cannot time out): with on != 0 every
+ * multi-block radix pass is made to time out in its look-back (block 0 publishes nothing, 2000 polls).  The affected call
+ * produces invalid instance lists; the NEXT vcr_rasterize_forward / _count / _visi_acc on the device (or the same call when
+ * debug != 0) returns an error that says so.  Process-wide; for tests only. */
+int vcr_debug_radix_fault(int on);
 
 /* ---- test/parity accessors: decode the opaque buffers (used by tests/, never by the product path) ---- */
 typedef struct vcr_geom_view {

@@ -224,3 +224,39 @@ def test_no_reference_cycles_per_view():
         assert torch.cuda.memory_allocated() == base, "per-view buffers are kept alive by a reference cycle"
     finally:
         gc.enable()
+
+
+def test_radix_timeout_is_reported_not_swallowed():
+    """The sort's bounded look-back: when it gives up, the call that contains it cannot know yet (nothing is read back after
+    the sort), but it must not fault, and the next forward on the device — or the same one in debug mode — must fail loudly."""
+    import vcr_native as N
+    from diff_gaussian_rasterization import GaussianRasterizer
+    from util import settings_from
+    inp, sc, cam = make_case(20_000, 320, 240, seed=3)           # 5 radix blocks over P, > 2 over R: every pass has a look-back
+    dev = torch.device("cuda")
+    kw = dict(means3D=inp["means3D"].to(dev), means2D=None, opacities=inp["opacities"].to(dev), shs=inp["shs"].to(dev),
+              normals_precomp=inp["normals"].to(dev), scales=inp["scales"].to(dev), rotations=inp["rotations"].to(dev), dirs=inp["dirs"].to(dev))
+    good, _ = GaussianRasterizer(settings_from(inp, dev))(**kw)
+    torch.cuda.synchronize()
+    def forward(debug=False):
+        out, _ = GaussianRasterizer(settings_from(inp, dev, debug=debug))(**kw)
+        torch.cuda.synchronize()
+        return out
+
+    N.vcr_debug_radix_fault(1)
+    try:
+        forward()                                                # poisoned: returns, its outputs are unwritten, no fault
+        with pytest.raises(RuntimeError, match="look-back timed out in an earlier call"):
+            forward()                                            # the next forward reads the flag back together with R
+    finally:
+        N.vcr_debug_radix_fault(0)
+    with pytest.raises(RuntimeError, match="look-back timed out in an earlier call"):
+        forward()                     # (the failed call above had already queued its own, sabotaged, depth sort: drained here)
+    assert torch.equal(forward(), good)                          # the flag has been consumed and the library works again
+    N.vcr_debug_radix_fault(1)
+    try:
+        with pytest.raises(RuntimeError, match="instance lists of this call are invalid"):
+            forward(debug=True)                                  # debug mode: reported by the failing call itself
+    finally:
+        N.vcr_debug_radix_fault(0)
+    assert torch.equal(forward(), good)

@@ -8,7 +8,9 @@
 //                                                         depth order).  duplicate_kernel = the reference's index order,
 //                                                         used by the parity view only
 //   cub::DeviceRadixSort::SortPairs          :309-314  -> radix_pass_kernel: 4 passes over the P (depth, index) pairs +
-//                                                         ceil(tile_bits / 8) passes over the R (tile, index) pairs
+//                                                         ceil(tile_bits / 8) passes over the R (tile, index) pairs; both
+//                                                         as (u32 key, u32 value), 8 bytes per pair (the reference moves
+//                                                         12-byte (u64, u32) pairs through 6 passes)
 //   cudaMemset + identifyTileRanges          :316-323  -> tile_ranges_kernel (+ tile_order_kernel, the block schedule)
 //
 // The sorted point list and the tile ranges are bit-identical to the reference's by construction: a stable sort by tile of
@@ -17,13 +19,39 @@
 // intermediate lists (index-ordered duplicated keys, point_offsets, 64-bit sorted keys) are produced on demand by
 // vcr_launch_reference_lists for the parity tests.
 #include "common.cuh"
+#include <atomic>
+
+// A look-back that never finds its predecessor (a block that died, a corrupted status array) must not hang the GPU: the
+// spin is bounded, and a block that gives up raises this per-device flag and carries on with a wrong offset.  The flag
+// is collected by scan_block_sums_kernel into the 16 bytes the NEXT forward reads back together with R, where it becomes
+// an error (vcr_rasterize_forward: "radix sort look-back timed out"); a debug forward checks it before returning.
+// While the flag is up the kernels that consume the (now invalid) lists — duplicate_sorted_kernel, tile_ranges_kernel and the
+// compositing kernels of render_forward.cu / render_backward.cu, which get the flag's address as an argument — return at
+// once instead of indexing with garbage; the outputs of that call are then simply unwritten.
+static __device__ unsigned int g_radix_timeout = 0u;
+
+#include <mutex>
+const unsigned int* vcr_radix_abort_flag() {        // device address of the flag on the current device (cached per device)
+    static const unsigned int* cache[64] = {nullptr};
+    static std::mutex mtx;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    std::lock_guard<std::mutex> lock(mtx);
+    if (!cache[dev]) {
+        void* p = nullptr;
+        if (cudaGetSymbolAddress(&p, g_radix_timeout) != cudaSuccess) return nullptr;
+        cache[dev] = static_cast<const unsigned int*>(p);
+    }
+    return cache[dev];
+}
 
 // ------------------------------------------------------------------------------------------------
 // Prefix sum over the per-block totals written by preprocess_kernel (one block, 1024 threads).
-// block_sums[b] becomes the exclusive prefix; num_rendered[0] the grand total.
+// block_sums[b] becomes the exclusive prefix; num_rendered[0] the grand total.  With take_error the kernel also moves
+// the radix timeout flag into num_rendered[3] (the words the host reads back together with R).
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(1024) scan_block_sums_kernel(uint32_t* __restrict__ block_sums, int nb,
-                                                               uint32_t* __restrict__ num_rendered) {
+                                                               uint32_t* __restrict__ num_rendered, int take_error) {
     __shared__ uint32_t warp_tot[32];
     const int t = threadIdx.x, lane = t & 31, w = t >> 5;
     // every thread owns `ipt` consecutive entries: one block-wide scan of the per-thread totals instead of one per 1024 entries
@@ -55,13 +83,16 @@ __global__ void __launch_bounds__(1024) scan_block_sums_kernel(uint32_t* __restr
         block_sums[i] = run;
         run += c;
     }
-    if (t == 1023) num_rendered[0] = warp_tot[31];
+    if (t == 1023) {
+        num_rendered[0] = warp_tot[31];
+        if (take_error) num_rendered[3] = atomicExch(&g_radix_timeout, 0u);
+    }
 }
 
 int vcr_launch_scan_block_sums(int P, GeomState& g, cudaStream_t s) {
     const int nb = (P + 255) / 256;
     VcrProfScope prof(VCR_K_SCAN, s);
-    scan_block_sums_kernel<<<1, 1024, 0, s>>>(g.block_sums, nb, g.num_rendered);
+    scan_block_sums_kernel<<<1, 1024, 0, s>>>(g.block_sums, nb, g.num_rendered, 1);
     VCR_LAUNCH_CHECK("scan_block_sums_kernel");
     return 0;
 }
@@ -157,6 +188,7 @@ __global__ void __launch_bounds__(256) sorted_block_sums_kernel(int P, const uin
                                                                 uint32_t* __restrict__ sums) {
     __shared__ uint32_t warp_tot[8];
     const int i = blockIdx.x * 256 + threadIdx.x;
+    if (g_radix_timeout) return;                    // failed depth sort: sorted_ids is garbage
     const uint32_t v = i < P ? tiles_touched[sorted_ids[i]] : 0u;
     const uint32_t wsum = __reduce_add_sync(0xffffffffu, v);
     if ((threadIdx.x & 31) == 0) warp_tot[threadIdx.x >> 5] = wsum;
@@ -172,16 +204,17 @@ __global__ void __launch_bounds__(256) sorted_block_sums_kernel(int P, const uin
 __global__ void __launch_bounds__(256) duplicate_sorted_kernel(int P, int gx, int gy, const int* __restrict__ radii,
                                                                const GeomState g, const uint32_t* __restrict__ sorted_ids,
                                                                const uint32_t* __restrict__ sorted_sums,
-                                                               uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
+                                                               uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
                                                                uint32_t* __restrict__ ghist, int npass, int tile_bits) {
     __shared__ uint32_t incl[256];
     __shared__ uint32_t s_gid[256];
     __shared__ int s_x0[256], s_y0[256], s_w[256];
     __shared__ uint32_t warp_tot[8];
-    __shared__ uint32_t hist[2][256];
+    __shared__ uint32_t hist[4][256];
     const int t = threadIdx.x, lane = t & 31, w = t >> 5;
     const int i = blockIdx.x * 256 + t;
-    hist[0][t] = 0u; hist[1][t] = 0u;
+    if (g_radix_timeout) return;                    // the depth sort before this launch failed: sorted_ids is garbage
+    for (int p = 0; p < npass; p++) hist[p][t] = 0u;
 
     uint32_t tiles = 0, gid = 0;
     int x0 = 0, y0 = 0, rw = 0;
@@ -222,7 +255,7 @@ __global__ void __launch_bounds__(256) duplicate_sorted_kernel(int P, int gx, in
         const int y = s_y0[lo] + (int)(local / (uint32_t)wdt);
         const int x = s_x0[lo] + (int)(local % (uint32_t)wdt);
         const uint32_t tile = (uint32_t)(y * gx + x);
-        keys_out[base + k] = (uint64_t)tile;
+        keys_out[base + k] = tile;
         vals_out[base + k] = s_gid[lo];
         for (int p = 0; p < npass; p++) {
             const int nb = min(8, tile_bits - 8 * p);
@@ -238,20 +271,21 @@ __global__ void __launch_bounds__(256) duplicate_sorted_kernel(int P, int gx, in
 
 int vcr_launch_duplicate_sorted(const FwdParams& p, GeomState& g, BinningState& b, int R, int tile_bits, cudaStream_t s) {
     (void)R;
-    const int npass = (tile_bits + 7) / 8;
-    if (npass > 2) { vcr_set_error("more than 65536 tiles are not supported"); return 1; }
+    const int npass = (tile_bits + 7) / 8;          // <= 4: tile ids are 32-bit
     const int nb = (p.P + 255) / 256;
     { VcrProfScope m(VCR_K_MEMSET, s); VCR_CUDA_TRY(cudaMemsetAsync(b.sort_hist, 0, VCR_MAX_PASSES * 256 * sizeof(uint32_t), s)); }
     {
         VcrProfScope prof(VCR_K_SCAN, s, 2);
         sorted_block_sums_kernel<<<nb, 256, 0, s>>>(p.P, g.gs_vals[0], g.tiles_touched, g.sorted_sums);
         VCR_LAUNCH_CHECK("sorted_block_sums_kernel");
-        scan_block_sums_kernel<<<1, 1024, 0, s>>>(g.sorted_sums, nb, g.num_rendered + 2);
+        scan_block_sums_kernel<<<1, 1024, 0, s>>>(g.sorted_sums, nb, g.num_rendered + 2, 0);
         VCR_LAUNCH_CHECK("scan_block_sums_kernel");
     }
     VcrProfScope prof(VCR_K_DUPLICATE, s);
-    duplicate_sorted_kernel<<<nb, 256, 0, s>>>(p.P, p.gx, p.gy, p.radii, g, g.gs_vals[0], g.sorted_sums, b.alt_keys, b.alt_vals,
-                                               b.sort_hist, npass, tile_bits);
+    // the sort ends in buffer A (tile_keys, point_list): an even number of passes may start there, an odd number starts in B
+    uint32_t* ek = (npass & 1) ? b.alt_keys : b.tile_keys;
+    uint32_t* ev = (npass & 1) ? b.alt_vals : b.point_list;
+    duplicate_sorted_kernel<<<nb, 256, 0, s>>>(p.P, p.gx, p.gy, p.radii, g, g.gs_vals[0], g.sorted_sums, ek, ev, b.sort_hist, npass, tile_bits);
     VCR_LAUNCH_CHECK("duplicate_sorted_kernel");
     return 0;
 }
@@ -260,27 +294,23 @@ int vcr_launch_duplicate_sorted(const FwdParams& p, GeomState& g, BinningState& 
 // Parity view (tests only): materialise the lists in the REFERENCE's formats from the production state —
 //   point_list_keys_unsorted / point_list_unsorted : duplicateWithKeys' output, Gaussian-index order, (tile << 32 | depth)
 //   point_offsets                                  : the inclusive scan of tiles_touched in index order
-//   point_list_keys                                : the sorted keys as (tile << 32 | depth) (production keeps bare tiles)
-// sort_hist[VCR_MAX_PASSES*256 - 1] remembers that the sorted keys have been rewritten, so a second call is harmless.
+//   point_list_keys                                : the sorted keys as (tile << 32 | depth) (production keeps bare u32 tiles)
+// The three arrays are separate from everything the production path reads, so the call can be repeated.
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) reference_keys_kernel(uint32_t R, uint64_t* __restrict__ keys, const uint32_t* __restrict__ point_list,
-                                                             const float* __restrict__ depths, const uint32_t* __restrict__ flag) {
+__global__ void __launch_bounds__(256) reference_keys_kernel(uint32_t R, uint64_t* __restrict__ keys, const uint32_t* __restrict__ tiles,
+                                                             const uint32_t* __restrict__ point_list, const float* __restrict__ depths) {
     const uint32_t i = blockIdx.x * 256u + threadIdx.x;
-    if (i >= R || *flag) return;
-    keys[i] = (keys[i] << 32) | (uint64_t)__float_as_uint(depths[point_list[i]]);
+    if (i >= R) return;
+    keys[i] = ((uint64_t)tiles[i] << 32) | (uint64_t)__float_as_uint(depths[point_list[i]]);
 }
-__global__ void set_flag_kernel(uint32_t* flag) { *flag = 1u; }
 
 int vcr_launch_reference_lists(int P, int R, int gx, int gy, const int* radii, GeomState& g, BinningState& b, cudaStream_t s) {
     if (R <= 0) return 0;
-    uint32_t* flag = b.sort_hist + VCR_MAX_PASSES * 256 - 1;
     duplicate_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, gx, gy, radii, g, b.point_list_keys_unsorted, b.point_list_unsorted,
                                                      b.sort_hist, 0, 0);
     VCR_LAUNCH_CHECK("duplicate_kernel");
-    reference_keys_kernel<<<((uint32_t)R + 255u) / 256u, 256, 0, s>>>((uint32_t)R, b.point_list_keys, b.point_list, g.depths, flag);
+    reference_keys_kernel<<<((uint32_t)R + 255u) / 256u, 256, 0, s>>>((uint32_t)R, b.point_list_keys, b.tile_keys, b.point_list, g.depths);
     VCR_LAUNCH_CHECK("reference_keys_kernel");
-    set_flag_kernel<<<1, 1, 0, s>>>(flag);
-    VCR_LAUNCH_CHECK("set_flag_kernel");
     return 0;
 }
 
@@ -305,7 +335,7 @@ __global__ void __launch_bounds__(256) radix_scan_hist_kernel(uint32_t* __restri
 }
 
 // ------------------------------------------------------------------------------------------------
-// One stable radix pass (<= 8 bits) over R (u64 key, u32 value) pairs.
+// One stable radix pass (<= 8 bits) over R (u32 key, u32 value) pairs.
 //   - tiles of 4096 pairs per 256-thread block, taken in ticket order (forward progress for look-back)
 //   - in-block stable ranks: per-warp running digit counters + __match_any_sync peer masks
 //   - cross-block digit offsets: decoupled look-back on (flag | count) words, one thread per digit
@@ -319,18 +349,21 @@ __global__ void __launch_bounds__(256) radix_scan_hist_kernel(uint32_t* __restri
 #define FLAG_LOCAL 0x40000000u
 #define FLAG_GLOBAL 0x80000000u
 #define FLAG_MASK 0xC0000000u
-#define RADIX_SMEM_BYTES (RADIX_TILE * 8 + RADIX_TILE * 4 + RADIX_WARPS * 256 * 4 + 256 * 4 + 256 * 4 + 128)
+#define RADIX_SMEM_BYTES (RADIX_TILE * 4 + RADIX_TILE * 4 + RADIX_WARPS * 256 * 4 + 256 * 4 + 256 * 4 + 128)
 
-__global__ void __launch_bounds__(RADIX_THREADS, VCR_RADIX_MINBLOCKS) radix_pass_kernel(const uint64_t* __restrict__ keys_in,
+static uint32_t g_radix_spin_limit = 1u << 26;      // vcr_debug_radix_fault() lowers it and silences block 0
+static int g_radix_fault = 0;
+
+__global__ void __launch_bounds__(RADIX_THREADS, VCR_RADIX_MINBLOCKS) radix_pass_kernel(const uint32_t* __restrict__ keys_in,
                                                                       const uint32_t* __restrict__ vals_in,
-                                                                      uint64_t* __restrict__ keys_out,
+                                                                      uint32_t* __restrict__ keys_out,
                                                                       uint32_t* __restrict__ vals_out, uint32_t R, int shift,
                                                                       int nbits, const uint32_t* __restrict__ digit_base,
                                                                       volatile uint32_t* status, uint32_t* ticket,
-                                                                      uint32_t* err_flag) {
+                                                                      uint32_t spin_limit, int fault) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    uint64_t* s_keys = reinterpret_cast<uint64_t*>(smem_raw);
-    uint32_t* s_vals = reinterpret_cast<uint32_t*>(smem_raw + RADIX_TILE * 8);
+    uint32_t* s_keys = reinterpret_cast<uint32_t*>(smem_raw);
+    uint32_t* s_vals = reinterpret_cast<uint32_t*>(smem_raw + RADIX_TILE * 4);
     uint32_t* s_whist = s_vals + RADIX_TILE;             // [RADIX_WARPS][256] per-warp running digit counters
     uint32_t* s_dstart = s_whist + RADIX_WARPS * 256;    // [256] block-local exclusive digit start
     uint32_t* s_gbase = s_dstart + 256;                  // [256] global base minus local start
@@ -346,21 +379,21 @@ __global__ void __launch_bounds__(RADIX_THREADS, VCR_RADIX_MINBLOCKS) radix_pass
     const uint32_t base = bid * RADIX_TILE;
     const uint32_t n = min((uint32_t)RADIX_TILE, R - base);
 
-    uint64_t key[RADIX_ITEMS];
+    uint32_t key[RADIX_ITEMS];
     uint32_t val[RADIX_ITEMS];
     uint32_t rank[RADIX_ITEMS];
 #pragma unroll
     for (int i = 0; i < RADIX_ITEMS; i++) {
         const uint32_t li = w * (32 * RADIX_ITEMS) + i * 32 + lane;
         if (li < n) { key[i] = keys_in[base + li]; val[i] = vals_in[base + li]; }
-        else { key[i] = ~0ull; val[i] = 0u; }
+        else { key[i] = ~0u; val[i] = 0u; }
     }
     uint32_t* my_hist = s_whist + w * 256;
 #pragma unroll
     for (int i = 0; i < RADIX_ITEMS; i++) {
         const uint32_t li = w * (32 * RADIX_ITEMS) + i * 32 + lane;
         const bool valid = li < n;
-        const uint32_t d = (uint32_t)(key[i] >> shift) & mask;
+        const uint32_t d = (key[i] >> shift) & mask;
         const uint32_t vmask = __ballot_sync(0xffffffffu, valid);
 #ifndef VCR_RADIX_MATCH_ANY
         // peer mask from one ballot per digit bit: constant cost, whereas match.any costs one round per distinct digit in
@@ -396,7 +429,7 @@ __global__ void __launch_bounds__(RADIX_THREADS, VCR_RADIX_MINBLOCKS) radix_pass
         }
         // Publish the block-local count as early as possible.  Flag and count share one 32-bit word, so no fence is
         // needed: a reader either sees the old word (keeps polling) or the complete new one.
-        my_status[t] = (bid == 0 ? FLAG_GLOBAL : FLAG_LOCAL) | cnt;
+        if (!(fault && bid == 0)) my_status[t] = (bid == 0 ? FLAG_GLOBAL : FLAG_LOCAL) | cnt;   // (fault: test hook, block 0 stays silent)
         // block-local exclusive scan over digits (8 warps)
         inc = cnt;
 #pragma unroll
@@ -438,7 +471,7 @@ __global__ void __launch_bounds__(RADIX_THREADS, VCR_RADIX_MINBLOCKS) radix_pass
                     if (f == FLAG_GLOBAL) found = true;
                 }
                 j -= used;
-                if (!found && used == 0 && ++spins > (1u << 26)) { atomicExch(err_flag, 1u); break; }
+                if (!found && used == 0 && ++spins > spin_limit) { atomicExch(&g_radix_timeout, 1u); break; }
             }
             my_status[t] = FLAG_GLOBAL | (excl + cnt);
         }
@@ -450,7 +483,7 @@ __global__ void __launch_bounds__(RADIX_THREADS, VCR_RADIX_MINBLOCKS) radix_pass
     for (int i = 0; i < RADIX_ITEMS; i++) {
         const uint32_t li = w * (32 * RADIX_ITEMS) + i * 32 + lane;
         if (li < n) {
-            const uint32_t d = (uint32_t)(key[i] >> shift) & mask;
+            const uint32_t d = (key[i] >> shift) & mask;
             const uint32_t slot = s_dstart[d] + my_hist[d] + rank[i];
             s_keys[slot] = key[i];
             s_vals[slot] = val[i];
@@ -458,27 +491,30 @@ __global__ void __launch_bounds__(RADIX_THREADS, VCR_RADIX_MINBLOCKS) radix_pass
     }
     __syncthreads();
     for (uint32_t sl = t; sl < n; sl += RADIX_THREADS) {
-        const uint64_t k = s_keys[sl];
-        const uint32_t d = (uint32_t)(k >> shift) & mask;
+        const uint32_t k = s_keys[sl];
+        const uint32_t d = (k >> shift) & mask;
         const uint32_t pos = s_gbase[d] + sl;
         keys_out[pos] = k;
         vals_out[pos] = s_vals[sl];
     }
 }
 
-// Stable LSD sort of n (u64 key, u32 value) pairs over key bits [0, key_bits), 8 bits per pass.  `hist` holds the digit
+// Stable LSD sort of n (u32 key, u32 value) pairs over key bits [0, key_bits), 8 bits per pass.  `hist` holds the digit
 // histogram of every pass ([npass][256], turned into exclusive offsets here); the sorted pairs end in (kA, vA), with
 // (kB, vB) as the other ping-pong buffer.  (kA, vA) may alias the input when the number of passes is even.
-static int radix_sort_run(const uint64_t* kin, const uint32_t* vin, uint64_t* kA, uint32_t* vA, uint64_t* kB, uint32_t* vB,
+static int radix_sort_run(const uint32_t* kin, const uint32_t* vin, uint32_t* kA, uint32_t* vA, uint32_t* kB, uint32_t* vB,
                           uint32_t n, int key_bits, uint32_t* hist, uint32_t* status, cudaStream_t s) {
-    // the opt-in shared-memory size is a per-device function attribute
-    static bool attr_set_dev[64] = {false};
+    // the opt-in shared-memory size is a per-device function attribute (setting it twice is harmless, so a benign race
+    // between two host threads on the atomic flag only costs a repeated call)
+    static std::atomic<bool> attr_set_dev[64];
     int dev_ = 0;
     VCR_CUDA_TRY(cudaGetDevice(&dev_));
-    if (dev_ >= 0 && dev_ < 64 && !attr_set_dev[dev_]) {
+    if (dev_ >= 0 && dev_ < 64 && !attr_set_dev[dev_].load(std::memory_order_acquire)) {
         VCR_CUDA_TRY(cudaFuncSetAttribute(radix_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, RADIX_SMEM_BYTES));
-        attr_set_dev[dev_] = true;
+        attr_set_dev[dev_].store(true, std::memory_order_release);
     }
+    if (key_bits < 1 || key_bits > 32) { vcr_set_error("radix sort: 1..32 key bits"); return 1; }
+    if (n >= (1u << 30)) { vcr_set_error("radix sort: at most 2^30 - 1 pairs (the look-back words carry flag | count in 32 bits)"); return 1; }
     const int npass = (key_bits + 7) / 8;
     const uint32_t nblocks = (n + RADIX_TILE - 1) / RADIX_TILE;
     { VcrProfScope prof(VCR_K_RADIX_HIST, s); radix_scan_hist_kernel<<<npass, 256, 0, s>>>(hist); }
@@ -489,23 +525,39 @@ static int radix_sort_run(const uint64_t* kin, const uint32_t* vin, uint64_t* kA
     uint32_t* tickets = status + (size_t)npass * nblocks * 256;
     for (int pass = 0; pass < npass; pass++) {
         const bool to_final = ((npass - 1 - pass) % 2) == 0;
-        uint64_t* kout = to_final ? kA : kB;
+        uint32_t* kout = to_final ? kA : kB;
         uint32_t* vout = to_final ? vA : vB;
         const int nbits = key_bits - 8 * pass < 8 ? key_bits - 8 * pass : 8;
         VcrProfScope prof(VCR_K_RADIX_PASS, s);
         radix_pass_kernel<<<nblocks, RADIX_THREADS, RADIX_SMEM_BYTES, s>>>(kin, vin, kout, vout, n, 8 * pass, nbits, hist + pass * 256,
                                                                            status + (size_t)pass * nblocks * 256, tickets + pass,
-                                                                           tickets + 15);
+                                                                           g_radix_spin_limit, g_radix_fault);
         VCR_LAUNCH_CHECK("radix_pass_kernel");
         kin = kout; vin = vout;
     }
     return 0;
 }
 
-// Generic entry (kNN's Morton sort): input in the *_unsorted pair, result in (point_list_keys, point_list).
+// Generic entry (kNN's Morton sort, an even number of passes): sorts (tile_keys, point_list) in place, B as ping-pong.
 int vcr_launch_radix_sort(BinningState& b, int R, int key_bits, cudaStream_t s) {
-    return radix_sort_run(b.point_list_keys_unsorted, b.point_list_unsorted, b.point_list_keys, b.point_list, b.alt_keys, b.alt_vals,
-                          (uint32_t)R, key_bits, b.sort_hist, b.sort_status, s);
+    if (((key_bits + 7) / 8) & 1) { vcr_set_error("vcr_launch_radix_sort: in-place sort needs an even number of 8-bit passes"); return 1; }
+    return radix_sort_run(b.tile_keys, b.point_list, b.tile_keys, b.point_list, b.alt_keys, b.alt_vals, (uint32_t)R, key_bits, b.sort_hist,
+                          b.sort_status, s);
+}
+
+// Move the look-back timeout flag of this device into *flag_out_device (and clear it), ordered on `s`.
+__global__ void radix_take_error_kernel(uint32_t* out) { *out = atomicExch(&g_radix_timeout, 0u); }
+int vcr_radix_take_error(uint32_t* flag_out_device, cudaStream_t s) {
+    radix_take_error_kernel<<<1, 1, 0, s>>>(flag_out_device);
+    VCR_LAUNCH_CHECK("radix_take_error_kernel");
+    return 0;
+}
+// Test hook (tests/test_rasterizer_gpu.py): with on != 0 block 0 of every radix pass publishes nothing and the spin limit
+// drops to 2000 polls, so every multi-block sort times out (and produces garbage) — the failure the flag exists to report.
+extern "C" int vcr_debug_radix_fault(int on) {
+    g_radix_fault = on ? 1 : 0;
+    g_radix_spin_limit = on ? 2000u : (1u << 26);
+    return 0;
 }
 
 // Sort ALL Gaussians by depth bits (stable, i.e. ties in index order): 4 passes over P pairs written by preprocess_kernel.
@@ -517,22 +569,24 @@ int vcr_launch_gaussian_sort(int P, GeomState& g, cudaStream_t s) {
 
 // Stable sort of the R instances (emitted in depth order by duplicate_sorted_kernel) by tile id alone: ceil(tile_bits/8)
 // passes.  Within a tile the depth order of the emission survives, which is exactly the order the reference gets from
-// sorting (tile << 32 | depth) keys.  Input in (alt_keys, alt_vals), result in (point_list_keys, point_list).
+// sorting (tile << 32 | depth) keys.  Input where vcr_launch_duplicate_sorted left it (buffer A for an even number of
+// passes, B for an odd one), result in buffer A = (tile_keys, point_list).
 int vcr_launch_tile_sort(BinningState& b, int R, int tile_bits, cudaStream_t s) {
-    return radix_sort_run(b.alt_keys, b.alt_vals, b.point_list_keys, b.point_list, b.point_list_keys_unsorted, b.point_list_unsorted,
+    const bool odd = ((tile_bits + 7) / 8) & 1;
+    return radix_sort_run(odd ? b.alt_keys : b.tile_keys, odd ? b.alt_vals : b.point_list, b.tile_keys, b.point_list, b.alt_keys, b.alt_vals,
                           (uint32_t)R, tile_bits, b.sort_hist, b.sort_status, s);
 }
 
 // ------------------------------------------------------------------------------------------------
 // Tile ranges (identifyTileRanges, rasterizer_impl.cu:116-138).
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) tile_ranges_kernel(uint32_t L, const uint64_t* __restrict__ keys, uint2* __restrict__ ranges) {
+__global__ void __launch_bounds__(256) tile_ranges_kernel(uint32_t L, const uint32_t* __restrict__ keys, uint2* __restrict__ ranges) {
     const uint32_t idx = blockIdx.x * 256u + threadIdx.x;
-    if (idx >= L) return;
-    const uint32_t cur = (uint32_t)keys[idx];          // the production keys are bare tile ids
+    if (idx >= L || g_radix_timeout) return;           // (a failed sort leaves garbage tile ids: do not index with them)
+    const uint32_t cur = keys[idx];                    // the production keys are bare tile ids
     if (idx == 0) ranges[cur].x = 0;
     else {
-        const uint32_t prev = (uint32_t)keys[idx - 1];
+        const uint32_t prev = keys[idx - 1];
         if (cur != prev) { ranges[prev].y = idx; ranges[cur].x = idx; }
     }
     if (idx == L - 1) ranges[cur].y = L;
@@ -570,7 +624,7 @@ int vcr_launch_tile_ranges(BinningState& b, ImageState& img, int R, int tiles, c
     { VcrProfScope m(VCR_K_MEMSET, s); VCR_CUDA_TRY(cudaMemsetAsync(img.ranges, 0, (size_t)tiles * sizeof(uint2), s)); }
     if (R > 0) {
         VcrProfScope prof(VCR_K_TILE_RANGES, s);
-        tile_ranges_kernel<<<((uint32_t)R + 255u) / 256u, 256, 0, s>>>((uint32_t)R, b.point_list_keys, img.ranges);
+        tile_ranges_kernel<<<((uint32_t)R + 255u) / 256u, 256, 0, s>>>((uint32_t)R, b.tile_keys, img.ranges);
         VCR_LAUNCH_CHECK("tile_ranges_kernel");
     }
     {

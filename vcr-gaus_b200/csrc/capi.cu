@@ -100,19 +100,20 @@ BinningState BinningState::carve(char* chunk, int R) {
     BinningState b;
     const size_t n = (size_t)R;
     carve_one(chunk, b.point_list, n);
-    carve_one(chunk, b.point_list_keys, n);
-    carve_one(chunk, b.point_list_unsorted, n);
-    carve_one(chunk, b.point_list_keys_unsorted, n);
+    carve_one(chunk, b.tile_keys, n);
     carve_one(chunk, b.alt_vals, n);
     carve_one(chunk, b.alt_keys, n);
     carve_one(chunk, b.sort_hist, (size_t)8 * 256);
-    carve_one(chunk, b.sort_status, (size_t)8 * radix_blocks(n) * 256 + 16);
+    carve_one(chunk, b.sort_status, (size_t)4 * radix_blocks(n) * 256 + 16);
+    carve_one(chunk, b.point_list_keys, n);
+    carve_one(chunk, b.point_list_unsorted, n);
+    carve_one(chunk, b.point_list_keys_unsorted, n);
     return b;
 }
 size_t BinningState::bytes(int R) {
     char* base = nullptr;
     BinningState b = carve(base, R);
-    return reinterpret_cast<size_t>(b.sort_status + (size_t)8 * radix_blocks((size_t)R) * 256 + 16) + 256;
+    return reinterpret_cast<size_t>(b.point_list_keys_unsorted + (size_t)R) + 256;
 }
 
 static uint32_t higher_msb(uint32_t n) {  // rasterizer_impl.cu:35-50
@@ -133,7 +134,13 @@ struct ReadBack {
     cudaEvent_t ev = nullptr;
 };
 static int read_back_begin(const uint32_t* dev, ReadBack*& rb_out, cudaStream_t s) {
-    static thread_local ReadBack rb;
+    // one pinned word block + one event per host thread AND device: an event belongs to the device that was current when it
+    // was created, so a thread that drives several GPUs needs one each (they live until the process exits)
+    static thread_local ReadBack per_device[64];
+    int d = 0;
+    VCR_CUDA_TRY(cudaGetDevice(&d));
+    if (d < 0 || d >= 64) { vcr_set_error("unsupported device index %d", d); return 1; }
+    ReadBack& rb = per_device[d];
     if (!rb.pinned) VCR_CUDA_TRY(cudaHostAlloc(reinterpret_cast<void**>(&rb.pinned), 4 * sizeof(uint32_t), cudaHostAllocDefault));
     if (!rb.ev) VCR_CUDA_TRY(cudaEventCreateWithFlags(&rb.ev, cudaEventDisableTiming));
     VCR_CUDA_TRY(cudaMemcpyAsync(rb.pinned, dev, 4 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
@@ -189,6 +196,12 @@ static int forward_front(vcr_alloc_fn geometry_buffer, vcr_alloc_fn binning_buff
     if (vcr_launch_gaussian_sort(p.P, g, s)) return 1;          // runs while the host waits for R
     if (read_back_end(rb, host)) return 1;
     if (host[1]) { vcr_set_error("Point is filtered although prefiltered is set. This shouldn't happen!"); return 1; }
+    if (host[3]) {
+        vcr_set_error("radix sort look-back timed out in an earlier call on this device: the instance lists (and every result) of that "
+                      "call are invalid");
+        return 1;
+    }
+    if (host[0] >= (1u << 30)) { vcr_set_error("%u (Gaussian, tile) instances: at most 2^30 - 1 are supported", host[0]); return 1; }
     const int R = (int)host[0];
     *num_rendered_host = R;
 
@@ -196,7 +209,10 @@ static int forward_front(vcr_alloc_fn geometry_buffer, vcr_alloc_fn binning_buff
     if (!bchunk) { vcr_set_error("binning buffer callback returned NULL"); return 1; }
     b = BinningState::carve(bchunk, R);
     const int tiles = p.gx * p.gy;
-    const int tile_bits = (int)higher_msb((uint32_t)tiles);     // the reference sorts bits [0, 32 + this), rasterizer_impl.cu:305-314
+    // bits of the largest tile id (the reference sorts bits [0, 32 + getHigherMsb(tiles)), rasterizer_impl.cu:305-314, i.e. one
+    // more bit whenever the tile count is a power of two; any bit count that covers every tile id gives the same order)
+    int tile_bits = 1;
+    while (tile_bits < 32 && ((uint32_t)(tiles - 1) >> tile_bits)) tile_bits++;
     if (R > 0) {
         if (debug_sync(debug, s, "depth sort")) return 1;
         if (vcr_launch_duplicate_sorted(p, g, b, R, tile_bits, s)) return 1;
@@ -206,6 +222,13 @@ static int forward_front(vcr_alloc_fn geometry_buffer, vcr_alloc_fn binning_buff
     }
     if (vcr_launch_tile_ranges(b, img, R, tiles, s)) return 1;
     if (debug_sync(debug, s, "tile ranges")) return 1;
+    if (debug) {                                  // debug mode reports a sort failure of THIS call before returning
+        if (vcr_radix_take_error(g.num_rendered + 3, s)) return 1;
+        uint32_t flag = 0;
+        VCR_CUDA_TRY(cudaMemcpyAsync(&flag, g.num_rendered + 3, sizeof(flag), cudaMemcpyDeviceToHost, s));
+        VCR_CUDA_TRY(cudaStreamSynchronize(s));
+        if (flag) { vcr_set_error("radix sort look-back timed out: the instance lists of this call are invalid"); return 1; }
+    }
     return 0;
 }
 

@@ -6,7 +6,7 @@
 // scene bounds (the bounds stay on the device):
 //   1. knn_bounds_kernel      scene AABB by block reduction + ordered-uint atomics
 //   2. knn_morton_kernel      30-bit Morton code per point (+ radix digit histograms)
-//   3. radix sort             the library's own u64/u32 LSD sort (binning.cu), 4 passes
+//   3. radix sort             the library's own (u32 key, u32 value) LSD sort (binning.cu), 4 passes
 //   4. knn_gather_box_kernel  gather points into Morton order (float4) + AABB per 256-point box
 //   5. knn_search_kernel      per point: seed with the +-3 Morton neighbours, then visit every box whose
 //                             AABB distance does not exceed the current third-best distance
@@ -64,7 +64,7 @@ __device__ __forceinline__ uint32_t prep_morton(uint32_t x) {
 }
 
 __global__ void __launch_bounds__(256) knn_morton_kernel(int P, const float* __restrict__ pts, const uint32_t* __restrict__ bounds,
-                                                         uint64_t* __restrict__ keys, uint32_t* __restrict__ vals,
+                                                         uint32_t* __restrict__ keys, uint32_t* __restrict__ vals,
                                                          uint32_t* __restrict__ ghist) {
     __shared__ uint32_t hist[4][256];
     for (int k = threadIdx.x; k < 4 * 256; k += 256) (&hist[0][0])[k] = 0u;
@@ -81,7 +81,7 @@ __global__ void __launch_bounds__(256) knn_morton_kernel(int P, const float* __r
             const uint32_t q = (uint32_t)fminf(fmaxf(nrm * 1023.0f, 0.f), 1023.f);
             code |= prep_morton(q) << k;
         }
-        keys[i] = (uint64_t)code;
+        keys[i] = code;
         vals[i] = (uint32_t)i;
 #pragma unroll
         for (int p = 0; p < 4; p++) atomicAdd(&hist[p][(code >> (8 * p)) & 255u], 1u);
@@ -201,7 +201,7 @@ extern "C" int vcr_dist2_knn3(int P, const float* points, float* mean_dists, cha
     knn_bounds_kernel<<<min(blocks, 148 * 8), 256, 0, s>>>(P, points, bounds);
     VCR_LAUNCH_CHECK("knn_bounds_kernel");
     VCR_CUDA_TRY(cudaMemsetAsync(b.sort_hist, 0, 8 * 256 * sizeof(uint32_t), s));
-    knn_morton_kernel<<<blocks, 256, 0, s>>>(P, points, bounds, b.point_list_keys_unsorted, b.point_list_unsorted, b.sort_hist);
+    knn_morton_kernel<<<blocks, 256, 0, s>>>(P, points, bounds, b.tile_keys, b.point_list, b.sort_hist);
     VCR_LAUNCH_CHECK("knn_morton_kernel");
     if (vcr_launch_radix_sort(b, P, 32, s)) return 1;
     knn_gather_box_kernel<<<nboxes, KNN_BOX, 0, s>>>(P, points, b.point_list, sorted, boxes);

@@ -247,7 +247,7 @@ __global__ void __launch_bounds__(256) preprocess_kernel(const FwdParams p, cons
     }
     // input of the Gaussian-level depth sort: (depth bits, index) + the digit histograms of its four passes
     if (idx < p.P) {
-        g.gs_keys[0][idx] = (uint64_t)dkey;
+        g.gs_keys[0][idx] = dkey;
         g.gs_vals[0][idx] = (uint32_t)idx;
 #pragma unroll
         for (int k = 0; k < 4; k++) atomicAdd(&s_dhist[k][(dkey >> (8 * k)) & 255u], 1u);

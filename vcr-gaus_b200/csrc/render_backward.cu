@@ -16,6 +16,7 @@
 // The formulas (including the reference's quirks) are kept term by term; only the
 // division by the final weight is replaced by a multiplication with its reciprocal.
 #include "common.cuh"
+#include <atomic>
 
 #define RB_BATCH 256
 #define RB_SPARSE_LANES 2
@@ -82,8 +83,10 @@ __global__ void __launch_bounds__(256) render_backward_kernel(
     const float* __restrict__ colors, const float* __restrict__ depths, const float* __restrict__ normals,
     const float* __restrict__ objects, const float* __restrict__ dirs, const float* __restrict__ alpha_img,
     const float* __restrict__ depth_img, const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
-    const float* __restrict__ dL_dpixels, const uint8_t* __restrict__ inside_gs, float* __restrict__ acc) {
+    const float* __restrict__ dL_dpixels, const uint8_t* __restrict__ inside_gs, float* __restrict__ acc,
+    const unsigned int* __restrict__ abort_flag) {
     extern __shared__ __align__(16) unsigned char rb_smem[];
+    if (__ldg(abort_flag)) return;      // the sort of this view failed (binning.cu): the lists are garbage, accumulate nothing
     RbStage<HAS_DIRS>* s_stage = reinterpret_cast<RbStage<HAS_DIRS>*>(rb_smem);   // [2]: double-buffered staging
     __shared__ uint32_t s_block_last;
 
@@ -329,21 +332,24 @@ __global__ void __launch_bounds__(256) render_backward_kernel(
 
 int vcr_launch_render_backward(const BwdParams& p, GeomState& g, BinningState& b, ImageState& img, cudaStream_t s) {
     { VcrProfScope m(VCR_K_MEMSET, s); VCR_CUDA_TRY(cudaMemsetAsync(p.acc, 0, (size_t)p.P * VCR_ACC_STRIDE * sizeof(float), s)); }
+    const unsigned int* abort_flag = vcr_radix_abort_flag();
+    if (!abort_flag) { vcr_set_error("cannot resolve the sort status flag on this device"); return 1; }
     VcrProfScope prof(VCR_K_RENDER_BWD, s);
     const dim3 grid(p.gx * p.gy, 1, 1);
     const float* col = p.colors_precomp ? p.colors_precomp : g.rgb;
 #define RB_ARGS img.ranges, img.tile_order, p.gx, b.point_list, p.W, p.H, p.background, g.means2D, g.xyz_view, g.conic_opacity, col, g.depths, \
-                p.normals, p.sh_objs, p.dirs, p.alpha, p.depth, img.accum_alpha, img.n_contrib, p.dL_dpix, p.inside, p.acc
+                p.normals, p.sh_objs, p.dirs, p.alpha, p.depth, img.accum_alpha, img.n_contrib, p.dL_dpix, p.inside, p.acc, abort_flag
     // the opt-in shared-memory size is a per-device function attribute
-    static bool attr_set_dev[64] = {false};
+    // (atomic flag: the forward thread and autograd's backward thread may both get here; setting the attribute twice is harmless)
+    static std::atomic<bool> attr_set_dev[64];
     int dev_ = 0;
     VCR_CUDA_TRY(cudaGetDevice(&dev_));
-    if (dev_ >= 0 && dev_ < 64 && !attr_set_dev[dev_]) {
+    if (dev_ >= 0 && dev_ < 64 && !attr_set_dev[dev_].load(std::memory_order_acquire)) {
         VCR_CUDA_TRY(cudaFuncSetAttribute(render_backward_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * sizeof(RbStage<true>))));
         VCR_CUDA_TRY(cudaFuncSetAttribute(render_backward_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * sizeof(RbStage<true>))));
         VCR_CUDA_TRY(cudaFuncSetAttribute(render_backward_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * sizeof(RbStage<false>))));
         VCR_CUDA_TRY(cudaFuncSetAttribute(render_backward_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * sizeof(RbStage<false>))));
-        attr_set_dev[dev_] = true;
+        attr_set_dev[dev_].store(true, std::memory_order_release);
     }
     if (p.dirs) {
         const size_t sm = 2 * sizeof(RbStage<true>);

@@ -50,9 +50,10 @@ __global__ void __launch_bounds__(256, 4) render_forward_kernel(
     const float* __restrict__ dirs, const float4* __restrict__ conic_opacity, const uint8_t* __restrict__ inside_gs,
     const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
     float* __restrict__ out_color, int* __restrict__ gaussian_count, float* __restrict__ important_score,
-    unsigned long long* __restrict__ pair_counters = nullptr) {
+    const unsigned int* __restrict__ abort_flag, unsigned long long* __restrict__ pair_counters = nullptr) {
     __shared__ RfStage<MODE> s_stage[2];
     unsigned int st_ke = 0, st_kc = 0, st_cand = 0;
+    if (__ldg(abort_flag)) return;      // the sort of this view failed (binning.cu): the lists are garbage, leave the outputs unwritten
 
     const int tid = threadIdx.x, lane = tid & 31;
     const uint32_t tile = __ldg(tile_order + blockIdx.x);      // blocks take tiles longest-list first
@@ -231,9 +232,11 @@ __global__ void __launch_bounds__(256, 4) render_forward_kernel(
 int vcr_launch_render_forward(const FwdParams& p, GeomState& g, BinningState& b, ImageState& img, cudaStream_t s) {
     const dim3 grid(p.gx * p.gy, 1, 1);
     const float* feat = p.colors_precomp ? p.colors_precomp : g.rgb;
+    const unsigned int* abort_flag = vcr_radix_abort_flag();
+    if (!abort_flag) { vcr_set_error("cannot resolve the sort status flag on this device"); return 1; }
     VcrProfScope prof(VCR_K_RENDER_FWD, s);
 #define RF_ARGS img.ranges, img.tile_order, p.gx, b.point_list, p.W, p.H, g.means2D, g.xyz_view, feat, g.depths, p.normals, p.sh_objs, p.dirs, \
-                g.conic_opacity, p.inside, p.background, img.accum_alpha, img.n_contrib, p.out_color, nullptr, nullptr
+                g.conic_opacity, p.inside, p.background, img.accum_alpha, img.n_contrib, p.out_color, nullptr, nullptr, abort_flag
     if (g_pair_counters) {          // instrumented run (never inside a timed region)
         if (p.dirs) {
             if (p.sh_objs) render_forward_kernel<0, true, true, true><<<grid, 256, 0, s>>>(RF_ARGS, g_pair_counters);
@@ -258,9 +261,11 @@ int vcr_launch_render_aux(int mode, const FwdParams& p, GeomState& g, BinningSta
                           int* gaussians_count, float* important_score, cudaStream_t s) {
     const dim3 grid(p.gx * p.gy, 1, 1);
     const float* feat = p.colors_precomp ? p.colors_precomp : g.rgb;
+    const unsigned int* abort_flag = vcr_radix_abort_flag();
+    if (!abort_flag) { vcr_set_error("cannot resolve the sort status flag on this device"); return 1; }
     VcrProfScope prof(VCR_K_RENDER_AUX, s);
 #define RA_ARGS img.ranges, img.tile_order, p.gx, b.point_list, p.W, p.H, g.means2D, g.xyz_view, feat, g.depths, nullptr, nullptr, nullptr, \
-                g.conic_opacity, nullptr, p.background, img.accum_alpha, img.n_contrib, p.out_color, gaussians_count, important_score
+                g.conic_opacity, nullptr, p.background, img.accum_alpha, img.n_contrib, p.out_color, gaussians_count, important_score, abort_flag
     if (mode == VCR_MODE_COUNT) render_forward_kernel<VCR_MODE_COUNT, false, false><<<grid, 256, 0, s>>>(RA_ARGS);
     else render_forward_kernel<VCR_MODE_VISI_ACC, false, false><<<grid, 256, 0, s>>>(RA_ARGS);
 #undef RA_ARGS

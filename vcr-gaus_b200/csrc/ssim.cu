@@ -8,6 +8,7 @@
 // those three maps with the same window and combines them with the pixel values.  HBM bound: 20 B/element forward,
 // 24 B/element backward.
 #include "common.cuh"
+#include <atomic>
 
 #define SSIM_R 5
 #define SSIM_T 16
@@ -122,16 +123,16 @@ __global__ void __launch_bounds__(256) ssim_backward_kernel(const int H, const i
 
 static int ssim_upload_window(cudaStream_t s) {
     // tools/loss_utils.py:47-49: exp(-(x - 5)^2 / (2 * 1.5^2)) as float32, divided by its float32 sum
-    static bool done_dev[64] = {false};
+    static std::atomic<bool> done_dev[64];    // (set after the attributes: a second thread at worst repeats the harmless calls)
     int dev = 0;
     VCR_CUDA_TRY(cudaGetDevice(&dev));
-    if (dev >= 0 && dev < 64 && done_dev[dev]) return 0;
+    if (dev >= 0 && dev < 64 && done_dev[dev].load(std::memory_order_acquire)) return 0;
     float g[2 * SSIM_R + 1], sum = 0.f;
     for (int k = 0; k <= 2 * SSIM_R; k++) { g[k] = (float)exp(-(double)((k - SSIM_R) * (k - SSIM_R)) / (2.0 * 1.5 * 1.5)); sum += g[k]; }
     for (int k = 0; k <= 2 * SSIM_R; k++) g[k] /= sum;
     VCR_CUDA_TRY(cudaMemcpyToSymbolAsync(c_ssim_w, g, sizeof(g), 0, cudaMemcpyHostToDevice, s));
     VCR_CUDA_TRY(cudaStreamSynchronize(s));          // g lives on this stack frame; once per device
-    if (dev >= 0 && dev < 64) done_dev[dev] = true;
+    if (dev >= 0 && dev < 64) done_dev[dev].store(true, std::memory_order_release);
     return 0;
 }
 
