@@ -196,10 +196,18 @@ class HotPathStepper:
     def local_gradient_checksums(self, i):
         """For the exchange self-check: this rank's OWN gradients of view i (no exchange), as float64 sums per group."""
         skip, self.skip = self.skip, "grads,stats"
+        p = self.bucket.params
+        # the plain backward: dL_dsh written by the kernel itself (no compact colour gradients), no chunk hook queuing exchanges
+        compact = p["shs"].__dict__.pop("_vcr_sh_compact", None)
+        hook = p["means3D"].__dict__.pop("_vcr_chunk_hook", None)
         try:
             self.step(i, False)
         finally:
             self.skip = skip
+            if compact is not None:
+                p["shs"]._vcr_sh_compact = compact
+            if hook is not None:
+                p["means3D"]._vcr_chunk_hook = hook
         return torch.stack([self.bucket.grad_flat[o:o + n].double().sum() for _, o, n, _ in self.bucket.layout])
 
 

@@ -226,12 +226,13 @@ def test_no_reference_cycles_per_view():
         gc.enable()
 
 
-def test_radix_timeout_is_reported_not_swallowed():
+def test_radix_timeout_is_reported_not_swallowed(tmp_path, monkeypatch):
     """The sort's bounded look-back: when it gives up, the call that contains it cannot know yet (nothing is read back after
     the sort), but it must not fault, and the next forward on the device — or the same one in debug mode — must fail loudly."""
     import vcr_native as N
     from diff_gaussian_rasterization import GaussianRasterizer
     from util import settings_from
+    monkeypatch.chdir(tmp_path)                                  # a failing debug forward writes snapshot_fw.dump into the cwd
     inp, sc, cam = make_case(20_000, 320, 240, seed=3)           # 5 radix blocks over P, > 2 over R: every pass has a look-back
     dev = torch.device("cuda")
     kw = dict(means3D=inp["means3D"].to(dev), means2D=None, opacities=inp["opacities"].to(dev), shs=inp["shs"].to(dev),

@@ -1,0 +1,31 @@
+#!/usr/bin/env bash
+# One gpurun call: GPU test suite, then the named bench runs; every step under its own timeout, logs into gpurun_out/<tag>_*.
+#   tools/gpu_batch.sh TAG [steps...]      steps: tests ubench metric ref A B refA refB
+TAG=${1:-run}; shift
+OUT=gpurun_out
+mkdir -p $OUT
+run() { # name timeout cmd...
+  local name=$1 to=$2; shift 2
+  local t0=$(date +%s)
+  timeout $to "$@" > $OUT/${TAG}_$name.out 2> $OUT/${TAG}_$name.err
+  local rc=$?
+  echo "[$name] rc=$rc $(( $(date +%s) - t0 ))s" | tee -a $OUT/${TAG}_summary.txt
+  return $rc
+}
+for step in "$@"; do
+  case $step in
+    tests)  run tests 1500 python -m pytest tests -m gpu -x -q; tail -5 $OUT/${TAG}_tests.out ;;
+    testsall) run tests 1800 python -m pytest tests -m gpu -q; tail -15 $OUT/${TAG}_tests.out ;;
+    ubench) nvcc -O3 -gencode arch=compute_100a,code=sm_100a -o $OUT/ubench_f32x2 tools/ubench_f32x2.cu && run ubench 60 $OUT/ubench_f32x2; cat $OUT/${TAG}_ubench.out ;;
+    metric) run metric 600 python bench.py --steps 30 --warmup 10; head -c 600 $OUT/${TAG}_metric.out; echo ;;
+    ref)    run ref 600 python bench.py --impl reference --steps 30 --warmup 10; head -c 600 $OUT/${TAG}_ref.out; echo ;;
+    A)      run A 300 python bench.py --config A --steps 50 --warmup 10; head -c 400 $OUT/${TAG}_A.out; echo ;;
+    refA)   run refA 300 python bench.py --config A --impl reference --steps 50 --warmup 10; head -c 400 $OUT/${TAG}_refA.out; echo ;;
+    B)      run B 600 python bench.py --config B --steps 49 --warmup 10 --no-cpu-baseline; head -c 400 $OUT/${TAG}_B.out; echo ;;
+    refB)   run refB 600 python bench.py --config B --impl reference --steps 49 --warmup 10; head -c 400 $OUT/${TAG}_refB.out; echo ;;
+    C)      run C 900 python bench.py --config C --steps 300 --warmup 20 --no-cpu-baseline; head -c 600 $OUT/${TAG}_C.out; echo ;;
+    refC)   run refC 1200 python bench.py --config C --impl reference --steps 300 --warmup 20; head -c 600 $OUT/${TAG}_refC.out; echo ;;
+    *) echo "unknown step $step" ;;
+  esac
+done
+tail -3 $OUT/${TAG}_*.err 2>/dev/null | tail -40

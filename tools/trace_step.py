@@ -9,13 +9,18 @@ import bench
 
 def main(impl):
     sys.argv = ["bench.py", "--steps", "3", "--warmup", "3", "--no-cpu-baseline", "--impl", impl]
-    args = bench.parse()
-    import vcr_view_parallel as VP
+    import bench_common as BC
+    args = BC.parse()
     dev = torch.device("cuda", 0); torch.cuda.set_device(dev)
-    vp = VP.ViewParallel()
-    scene, views = bench.build_workload(args, 0, 1)
-    bucket = bench.clone_params(scene, dev, direct=(impl == "ours"))
-    st = bench.Stepper(args, impl, bucket, views, dev, vp)
+    scene = BC.build_scene(args)
+    views = BC.build_views(args, scene, 1, list(range(args.views)))
+    if impl == "ours":
+        bench._product_paths()
+        import vcr_view_parallel as VP
+        st = bench.HotPathStepper(args, scene, views, dev, VP.ViewParallel())
+    else:
+        import bench_ref
+        st = bench_ref.HotPathStepper(args, bench_ref._import_reference(), scene, views, dev, 1)
     for i in range(4): st.step(i, False)
     torch.cuda.synchronize()
     from torch.profiler import profile, ProfilerActivity
