@@ -92,7 +92,11 @@ def test_dnormal_live_against_reference_functions_on_gpu():
     from vcr_dnormal import depth_normal_loss
     from test_dnormal_knn_gpu import make_dn_inputs
     R = pyref.load()
-    for (W, H, exp_t) in ((640, 480, 0.005), (1920, 1080, 0.5)):
+    # gradient tolerance: the reference rounds its pixel grid to float32 even for a float64 depth map
+    # (valid_x = arange(W, float32).add_(0.5) / (W - 1), tools/graphics_utils.py:114-115), i.e. ~6e-8 * W pixels of
+    # coordinate noise in a finite difference of size 1/fx: its own float64 result is ~1e-3 (rel-L2) away from the exact
+    # gradient at 1080p (measured 1.2e-3 against this kernel, which is 3e-7 from the exact value, tests/test_dnormal_knn_gpu.py)
+    for (W, H, exp_t, tol) in ((640, 480, 0.005, 1e-3), (1920, 1080, 0.5, 3e-3)):
         depth, gt, rn, mask, K = make_dn_inputs(W, H, seed=W)
         d = depth.to(DEV).requires_grad_(True)
         loss = depth_normal_loss(d, K, gt.to(DEV), rn.to(DEV), mask.to(DEV), exp_t=exp_t)
@@ -102,7 +106,7 @@ def test_dnormal_live_against_reference_functions_on_gpu():
         ref = pyref.dnormal_loss(R, est, gt.to(DEV).double(), F.normalize(rn.to(DEV).double(), dim=-1), mask.to(DEV), exp_t)
         ref.backward()
         assert abs(float(loss) - float(ref)) <= 1e-5 * max(1.0, abs(float(ref)))
-        assert rel_l2(d.grad.cpu().numpy(), d64.grad.cpu().numpy()) <= 1e-3
+        assert rel_l2(d.grad.cpu().numpy(), d64.grad.cpu().numpy()) <= tol
 
 
 @needs_pyref
