@@ -152,7 +152,7 @@ class HotPathStepper:
         means2D_densify = torch.zeros_like(p["means3D"], requires_grad=True)
         out, radii = self.GR(rs)(means3D=p["means3D"], means2D=means2D, means2D_densify=means2D_densify, shs=p["shs"],
                                  normals_precomp=normals, opacities=p["opacities"], scales=p["scales"],
-                                 rotations=p["rotations"], dirs=self.dirs, inside=self.inside)
+                                 rotations=p["rotations"], dirs=self.dirs, inside=None)
         self.bucket.zero_grad()
         normals.grad = None
         ev = self.diag_events
@@ -274,7 +274,7 @@ class TrainStepper:
         means2D = torch.zeros_like(p["xyz"], requires_grad=True)
         means2D_densify = torch.zeros_like(p["xyz"], requires_grad=True)
         out, radii = self.GR(rs)(means3D=p["xyz"], means2D=means2D, means2D_densify=means2D_densify, shs=sh, normals_precomp=normals,
-                                 opacities=opac, scales=scales, rotations=rots, dirs=self.dirs, inside=self.inside)
+                                 opacities=opac, scales=scales, rotations=rots, dirs=self.dirs, inside=None)
         sc = 1.0 / vp.world
         loss = view_loss(out, d["gt_image"], d["gt_normal"], self.K4, w_l1=BC.W_L1 * sc, w_mono=BC.W_MONO * sc, w_dn=BC.W_DN * sc, exp_t=BC.EXP_T)
         loss = loss + (BC.W_SSIM * sc) * (1.0 - ssim(out[:3], d["gt_image"]))
@@ -373,6 +373,8 @@ def main():
     views = BC.build_views(args, scene, world, view_ids)
     stepper = (TrainStepper if train else HotPathStepper)(args, scene, views, dev, vp)
 
+    if os.environ.get("VCR_RENDER_VERSION"):        # development A/B of the compositing kernels (1 = one pixel per thread)
+        N.vcr_debug_render_version(int(os.environ["VCR_RENDER_VERSION"]))
     prof = not args.no_profile and not args.densify
     # ---- device-resident timing (`value`): K steps, launch counters on, per-kernel event brackets OFF ----
     N.vcr_profile_enable(0)

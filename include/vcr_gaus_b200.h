@@ -103,7 +103,8 @@ int vcr_rasterize_forward(
     int prefiltered,
     float* out_color,
     int* radii,
-    const uint8_t* inside,
+    const uint8_t* inside,       /* u8/bool[P]: which Gaussians enter the depth / normal maps (the fork's `inside` mask); NULL = all,
+                                    what the reference wrapper substitutes for inside=None — and the fast path of the backward */
     int debug,
     int* num_rendered_host,
     void* stream);
@@ -433,6 +434,9 @@ int vcr_pair_counters(unsigned long long* counters_device);
  * produces invalid instance lists; the NEXT vcr_rasterize_forward / _count / _visi_acc on the device (or the same call when
  * debug != 0) returns an error that says so.  Process-wide; for tests only. */
 int vcr_debug_radix_fault(int on);
+/* Development A/B: 1 selects the one-pixel-per-thread compositing kernels for every call, 2 (the default) the
+ * two-pixels-per-thread ones (forward always; backward when inside == NULL).  Returns the version in force. */
+int vcr_debug_render_version(int version);
 
 /* ---- test/parity accessors: decode the opaque buffers (used by tests/, never by the product path) ---- */
 typedef struct vcr_geom_view {

@@ -251,7 +251,7 @@ int vcr_rasterize_forward(vcr_alloc_fn geometry_buffer, vcr_alloc_fn binning_buf
                           const uint8_t* inside, int debug, int* num_rendered_host, void* stream) {
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
     if (!normals_precomp) { vcr_set_error("normals_precomp is required (the reference kernel dereferences it unconditionally, forward.cu:374)"); return 1; }
-    if (!inside || !background || !out_color || !num_rendered_host) { vcr_set_error("NULL required argument"); return 1; }
+    if (!background || !out_color || !num_rendered_host) { vcr_set_error("NULL required argument"); return 1; }   // inside == NULL: all inside
     FwdParams p;
     memset(&p, 0, sizeof(p));
     p.P = P; p.D = D; p.M = M; p.W = width; p.H = height;
@@ -288,7 +288,7 @@ int vcr_rasterize_backward_chunked(int P, int D, int M, int R, const float* back
         vcr_set_error("NULL gradient output");
         return 1;
     }
-    if (!normals_precomp || !inside || !radii || !alpha || !depth) { vcr_set_error("NULL required input"); return 1; }
+    if (!normals_precomp || !radii || !alpha || !depth) { vcr_set_error("NULL required input"); return 1; }   // inside == NULL: all inside
     if (scales && ((reinterpret_cast<size_t>(rotations) | reinterpret_cast<size_t>(dL_drot)) & 15)) {
         vcr_set_error("rotations and dL_drot must be 16-byte aligned (float4 accesses)");
         return 1;

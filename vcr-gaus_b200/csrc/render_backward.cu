@@ -170,7 +170,7 @@ __global__ void __launch_bounds__(256) render_backward_kernel(
         } else {
             sg.nx = __ldg(depths + id);
         }
-        sg.id_inside = (id << 1) | (__ldg(inside_gs + id) ? 1u : 0u);
+        sg.id_inside = (id << 1) | ((inside_gs == nullptr || __ldg(inside_gs + id)) ? 1u : 0u);
         st.geo[tid] = sg;
         float o0 = 0.f, o1 = 0.f;
         if (HAS_OBJ) { o0 = __ldg(objects + 2 * (size_t)id); o1 = __ldg(objects + 2 * (size_t)id + 1); }
@@ -330,6 +330,291 @@ __global__ void __launch_bounds__(256) render_backward_kernel(
     }
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// Two pixels per thread (the production kernel when every Gaussian is `inside`, i.e. the caller passed inside = NULL — what
+// render() does, gaussian_renderer/__init__.py:103; an explicit inside mask takes the one-pixel kernel above, which keeps the
+// reference's behaviour for mixed masks term by term).
+//
+// Same tile decomposition as render_forward2_kernel: 128 threads per 16x16 tile, a thread owns (x, y) and (x, y + 1), a
+// warp a 16x4 strip.  What that buys here:
+//   * warp-uniform work (staged-record reads, candidate bookkeeping) and the 16-component warp reduction are spent once
+//     per two pixels — the two pixels' contributions to a Gaussian are added in registers before the reduction;
+//   * the per-pixel arithmetic of the two pixels runs as packed FFMA2 / FMUL2 / FADD2;
+//   * the running "accum_rec" recurrences are kept in their folded form S <- S + alpha (x - S) (the value the reference's
+//     `last_alpha * last_x + (1 - last_alpha) * accum_rec` takes at the next contributor), which needs one state variable
+//     per channel instead of three and makes a non-contributing pixel a no-op by setting its alpha to 0 — no per-variable
+//     selects.  Algebraically identical to backward.cu:556-812 (with all Gaussians inside, accum_rec2 and accum_alpha_rec
+//     are the same sequence); rounding differs at the 1e-7 level, far inside the 1e-3 gradient gate.
+// ------------------------------------------------------------------------------------------------------------------
+#define RB2_THREADS 128
+#define RB2_BATCH 128
+
+template <bool HAS_DIRS>
+struct Rb2Stage {
+    StagedGeoB geo[RB2_BATCH];
+    float4 box[RB2_BATCH];
+    float2 ex[RB2_BATCH];
+    float4 nrm[RB2_BATCH];            // normal.xyz, semantics[0]
+    float4 col[RB2_BATCH];            // rgb, semantics[1]
+    float4 xv[HAS_DIRS ? RB2_BATCH : 1];
+};
+
+__device__ __forceinline__ float2 vcr_sub2(const float2 a, const float2 b) { return vcr_add2(a, make_float2(-b.x, -b.y)); }
+
+template <bool HAS_DIRS, bool HAS_OBJ>
+__global__ void __launch_bounds__(RB2_THREADS, 4) render_backward2_kernel(
+    const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order, int gx, const uint32_t* __restrict__ point_list, int W, int H, const float* __restrict__ bg,
+    const float2* __restrict__ means2D, const float* __restrict__ xyz_view, const float4* __restrict__ conic_opacity,
+    const float* __restrict__ colors, const float* __restrict__ depths, const float* __restrict__ normals,
+    const float* __restrict__ objects, const float* __restrict__ dirs, const float* __restrict__ alpha_img,
+    const float* __restrict__ depth_img, const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
+    const float* __restrict__ dL_dpixels, float* __restrict__ acc, const unsigned int* __restrict__ abort_flag) {
+    __shared__ Rb2Stage<HAS_DIRS> s_stage[2];
+    __shared__ uint32_t s_block_last;
+    if (__ldg(abort_flag)) return;      // the sort of this view failed (binning.cu): the lists are garbage, accumulate nothing
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t tile = __ldg(tile_order + blockIdx.x);      // blocks take tiles longest-list first
+    const uint32_t tile_x = tile % (uint32_t)gx, tile_y = tile / (uint32_t)gx;
+    const uint32_t px = tile_x * VCR_TILE_X + (lane & 15);
+    const uint32_t py0 = tile_y * VCR_TILE_Y + 4 * warp + 2 * (lane >> 4), py1 = py0 + 1;
+    const bool in0 = px < (uint32_t)W && py0 < (uint32_t)H, in1 = px < (uint32_t)W && py1 < (uint32_t)H;
+    const size_t HW = (size_t)H * W;
+    const size_t pix0 = (size_t)W * py0 + px, pix1 = pix0 + (size_t)W;
+    const float pfx = (float)px;
+    const float2 npfy = make_float2(-(float)py0, -(float)py1);
+    const float strip_x0 = (float)(tile_x * VCR_TILE_X), strip_x1 = strip_x0 + (float)(VCR_TILE_X - 1);
+    const float strip_y0 = (float)(tile_y * VCR_TILE_Y + 4 * warp), strip_y1 = strip_y0 + 3.0f;
+
+    const uint2 range = ranges[tile];
+    const uint32_t lastc0 = in0 ? n_contrib[pix0] : 0u, lastc1 = in1 ? n_contrib[pix1] : 0u;
+    // Entries behind the last contributor of every pixel of the warp / block can never pass `contributor <
+    // last_contributor` (backward.cu:589-591): drop them without staging or evaluating them.
+    const uint32_t warp_last = __reduce_max_sync(0xffffffffu, max(lastc0, lastc1));
+    if (tid == 0) s_block_last = 0u;
+    __syncthreads();
+    if (lane == 0 && warp_last) atomicMax(&s_block_last, warp_last);
+    __syncthreads();
+    const uint32_t block_last = s_block_last;          // <= range.y - range.x
+    const uint32_t list_end = range.x + block_last;    // effective list: [range.x, list_end)
+    const int rounds = (int)((block_last + RB2_BATCH - 1) / RB2_BATCH);
+    int toDo = (int)block_last;
+
+    auto ld2 = [&](const float* base, float dflt) {
+        return make_float2(in0 ? __ldg(base + pix0) : dflt, in1 ? __ldg(base + pix1) : dflt);
+    };
+    const float2 T_final = ld2(final_Ts, 0.f);
+    float2 T = T_final;
+    const float2 wimg = ld2(alpha_img, 1.f);
+    const float2 inv_weight = make_float2(1.0f / wimg.x, 1.0f / wimg.y);
+    const float2 depth_final = ld2(depth_img, 1.f);
+    const float2 gC0 = ld2(dL_dpixels, 0.f), gC1 = ld2(dL_dpixels + HW, 0.f), gC2 = ld2(dL_dpixels + 2 * HW, 0.f);
+    const float2 gD = ld2(dL_dpixels + VCR_DEPTH_OFFSET * HW, 0.f);
+    const float2 gN0 = ld2(dL_dpixels + (VCR_NORMAL_OFFSET + 0) * HW, 0.f), gN1 = ld2(dL_dpixels + (VCR_NORMAL_OFFSET + 1) * HW, 0.f),
+                 gN2 = ld2(dL_dpixels + (VCR_NORMAL_OFFSET + 2) * HW, 0.f);
+    float2 gO0 = make_float2(0.f, 0.f), gO1 = gO0;
+    if (HAS_OBJ) { gO0 = ld2(dL_dpixels + (VCR_OBJECT_OFFSET + 0) * HW, 0.f); gO1 = ld2(dL_dpixels + (VCR_OBJECT_OFFSET + 1) * HW, 0.f); }
+    float2 gA = ld2(dL_dpixels + VCR_ALPHA_OFFSET * HW, 0.f);             // grows with the semantics terms (backward.cu:766)
+    float2 dirx = make_float2(0.f, 0.f), diry = dirx, dirz = make_float2(1.f, 1.f);
+    if (HAS_DIRS) { dirx = ld2(dirs, 0.f); diry = ld2(dirs + HW, 0.f); dirz = ld2(dirs + 2 * HW, 1.f); }
+    const float bgr = __ldg(bg), bgg = __ldg(bg + 1), bgb = __ldg(bg + 2);
+    const float2 bg_dot = make_float2(bgr * gC0.x + bgg * gC1.x + bgb * gC2.x, bgr * gC0.y + bgg * gC1.y + bgb * gC2.y);
+    // per-pixel constants folded once: (inv_weight * dL/dpixel) for the depth and normal channels
+    const float2 kD = vcr_mul2(inv_weight, gD);
+    const float2 kN0 = vcr_mul2(inv_weight, gN0), kN1 = vcr_mul2(inv_weight, gN1), kN2 = vcr_mul2(inv_weight, gN2);
+    const float2 nTf_bg = make_float2(-T_final.x * bg_dot.x, -T_final.y * bg_dot.y);
+
+    // folded recurrences (see the header): colour, depth, the constant 1, normal, semantics
+    const float2 Z = make_float2(0.f, 0.f);
+    float2 Sc0 = Z, Sc1 = Z, Sc2 = Z, Sd = Z, S1 = Z, Sn0 = Z, Sn1 = Z, Sn2 = Z, So0 = Z, So1 = Z;
+
+    auto stage = [&](int batch, int buf) {
+        const uint32_t progress = (uint32_t)batch * RB2_BATCH + tid;
+        if (range.x + progress >= list_end) return;
+        Rb2Stage<HAS_DIRS>& st = s_stage[buf];
+        const uint32_t id = __ldg(point_list + (list_end - progress - 1));
+        const float2 xy = __ldg(means2D + id);
+        const float4 co = __ldg(conic_opacity + id);
+        const float3 n = make_float3(__ldg(normals + 3 * (size_t)id), __ldg(normals + 3 * (size_t)id + 1),
+                                     __ldg(normals + 3 * (size_t)id + 2));
+        StagedGeoB sg;
+        sg.x = xy.x; sg.y = xy.y; sg.ca = co.x; sg.cb = co.y; sg.cc = co.z; sg.op = co.w;
+        st.box[tid] = vcr_alpha_bbox(xy, co);
+        st.ex[tid] = vcr_alpha_rowtest(co);
+        if (HAS_DIRS) {
+            const float3 xv = make_float3(__ldg(xyz_view + 3 * (size_t)id), __ldg(xyz_view + 3 * (size_t)id + 1),
+                                          __ldg(xyz_view + 3 * (size_t)id + 2));
+            sg.nx = n.x * xv.x + n.y * xv.y + n.z * xv.z;
+            st.xv[tid] = make_float4(xv.x, xv.y, xv.z, 0.f);
+        } else {
+            sg.nx = __ldg(depths + id);
+        }
+        sg.id_inside = id;
+        st.geo[tid] = sg;
+        float o0 = 0.f, o1 = 0.f;
+        if (HAS_OBJ) { o0 = __ldg(objects + 2 * (size_t)id); o1 = __ldg(objects + 2 * (size_t)id + 1); }
+        st.nrm[tid] = make_float4(n.x, n.y, n.z, o0);
+        st.col[tid] = make_float4(__ldg(colors + 3 * (size_t)id), __ldg(colors + 3 * (size_t)id + 1),
+                                  __ldg(colors + 3 * (size_t)id + 2), o1);
+    };
+
+    if (rounds > 0) stage(0, 0);
+    __syncthreads();
+    for (int i = 0; i < rounds; i++, toDo -= RB2_BATCH) {
+        const int buf = i & 1;
+        if (i + 1 < rounds) stage(i + 1, buf ^ 1);   // overlaps with the replay of batch i
+        const Rb2Stage<HAS_DIRS>& st = s_stage[buf];
+        const int cnt = min(RB2_BATCH, toDo);
+        // entry j of this batch has list position (contributor index) block_last - 1 - (i*RB2_BATCH + j)
+        const int first_pos = (int)block_last - 1 - i * RB2_BATCH;
+#pragma unroll 1
+        for (int k = 0; k < RB2_BATCH / 32; k++) {
+            if (k * 32 >= cnt) break;
+            const int jj = k * 32 + lane;
+            const float4 bx = st.box[jj];
+            bool hit = jj < cnt && (uint32_t)(first_pos - jj) < warp_last && bx.x <= strip_x1 && bx.y >= strip_x0 &&
+                       bx.z <= strip_y1 && bx.w >= strip_y0;
+            if (hit) {
+                const float4 gq = *reinterpret_cast<const float4*>(&st.geo[jj]);        // x, y, ca, cb
+                hit = vcr_strip_may_contribute_rows<4>(gq.x, gq.y, gq.z, gq.w, st.geo[jj].cc, st.ex[jj], strip_x0, strip_x1, strip_y0);
+            }
+            uint32_t m = __ballot_sync(0xffffffffu, hit);
+            while (m) {
+                const int j = k * 32 + __ffs(m) - 1;
+                m &= m - 1;
+                const uint32_t contributor = (uint32_t)(first_pos - j);
+                const float4 g0 = *reinterpret_cast<const float4*>(&st.geo[j]);        // x, y, ca, cb
+                const float4 g1 = *reinterpret_cast<const float4*>(&st.geo[j].cc);     // cc, op, nx, id
+                const float dx = g0.x - pfx;
+                const float2 dy = vcr_add2(vcr_bcast2(g0.y), npfy);
+                const float adx = __fmul_rn(g0.z, dx), nbdx = -__fmul_rn(g0.w, dx);
+                const float2 q = vcr_fma2(vcr_bcast2(adx), vcr_bcast2(dx), vcr_mul2(vcr_mul2(vcr_bcast2(g1.x), dy), dy));
+                const float2 power = vcr_fma2(q, vcr_bcast2(-0.5f), vcr_mul2(vcr_bcast2(nbdx), dy));
+                bool c0 = contributor < lastc0 && !(power.x > 0.0f);
+                bool c1 = contributor < lastc1 && !(power.y > 0.0f);
+                if (!__any_sync(0xffffffffu, c0 || c1)) continue;
+                // Fast intrinsics from here on: the backward only has to meet 1e-3 relative L2 (the forward, which must
+                // match the reference bit for bit, keeps expf and IEEE division).
+                const float2 Gr = make_float2(__expf(power.x), __expf(power.y));
+                const float2 ar = make_float2(fminf(0.99f, g1.y * Gr.x), fminf(0.99f, g1.y * Gr.y));
+                c0 = c0 && !(ar.x < 1.0f / 255.0f);
+                c1 = c1 && !(ar.y < 1.0f / 255.0f);
+                const float4 nrm = st.nrm[j];
+                float2 pd = make_float2(1.f, 1.f), ipd = pd, cdr;
+                if (HAS_DIRS) {
+                    pd = vcr_fma2(vcr_bcast2(nrm.z), dirz, vcr_fma2(vcr_bcast2(nrm.x), dirx, vcr_mul2(vcr_bcast2(nrm.y), diry)));
+                    ipd = make_float2(__fdividef(1.0f, pd.x), __fdividef(1.0f, pd.y));
+                    cdr = vcr_mul2(vcr_mul2(vcr_bcast2(g1.z), ipd), dirz);
+                } else {
+                    cdr = vcr_bcast2(g1.z);
+                }
+                c0 = c0 && !(cdr.x < 0.2f);  // == (double)c_d < 0.2, backward.cu:616
+                c1 = c1 && !(cdr.y < 0.2f);
+                const uint32_t cmask = __ballot_sync(0xffffffffu, c0 || c1);
+                if (cmask == 0u) continue;
+
+                // a pixel that does not take this Gaussian: alpha = G = 0 (and finite stand-ins where it may hold inf / NaN)
+                const float2 alpha = make_float2(c0 ? ar.x : 0.f, c1 ? ar.y : 0.f);
+                const float2 G = make_float2(c0 ? Gr.x : 0.f, c1 ? Gr.y : 0.f);
+                const float2 c_d = make_float2(c0 ? cdr.x : 0.f, c1 ? cdr.y : 0.f);
+                if (HAS_DIRS) ipd = make_float2(c0 ? ipd.x : 0.f, c1 ? ipd.y : 0.f);
+                const float2 one = make_float2(1.f, 1.f);
+                const float2 oma = vcr_sub2(one, alpha);
+                const float2 inv1ma = make_float2(__fdividef(1.0f, oma.x), __fdividef(1.0f, oma.y));
+                T = vcr_mul2(T, inv1ma);
+                const float2 aT = vcr_mul2(alpha, T);
+                const float4 col = st.col[j];
+                float2 v[16];
+                // colour (backward.cu:632-641): dL_dopa += (c - accum_rec) * dL_dpixel;  dL_dcolor += alpha T dL_dpixel
+                float2 d0 = vcr_sub2(vcr_bcast2(col.x), Sc0), d1 = vcr_sub2(vcr_bcast2(col.y), Sc1), d2 = vcr_sub2(vcr_bcast2(col.z), Sc2);
+                float2 dopa = vcr_fma2(d2, gC2, vcr_fma2(d1, gC1, vcr_mul2(d0, gC0)));
+                Sc0 = vcr_fma2(alpha, d0, Sc0); Sc1 = vcr_fma2(alpha, d1, Sc1); Sc2 = vcr_fma2(alpha, d2, Sc2);
+                v[ACC_COLOR_R] = vcr_mul2(aT, gC0); v[ACC_COLOR_R + 1] = vcr_mul2(aT, gC1); v[ACC_COLOR_R + 2] = vcr_mul2(aT, gC2);
+                // depth and normal (backward.cu:643-754); om1 = 1 - accum_rec2 = 1 - accum_alpha_rec
+                const float2 om1 = vcr_sub2(one, S1);
+                const float2 aTw = vcr_mul2(aT, inv_weight);
+                {
+                    const float2 dd = vcr_sub2(c_d, Sd);
+                    const float2 t = vcr_fma2(make_float2(-depth_final.x, -depth_final.y), om1, dd);
+                    dopa = vcr_fma2(t, kD, dopa);
+                    Sd = vcr_fma2(alpha, dd, Sd);
+                }
+                const float2 dL_dd_j = vcr_mul2(aTw, gD);
+                float2 dn0 = Z, dn1 = Z, dn2 = Z;
+                if (HAS_DIRS) {  // backward.cu:722-728
+                    const float4 xv = st.xv[j];
+                    const float2 sv = vcr_mul2(vcr_mul2(dL_dd_j, dirz), ipd);      // dL/dxyz_view = normal * sum(sv)
+                    const float2 s2 = vcr_mul2(sv, ipd);
+                    const float2 nnx = vcr_bcast2(-g1.z);
+                    dn0 = vcr_mul2(s2, vcr_fma2(pd, vcr_bcast2(xv.x), vcr_mul2(dirx, nnx)));
+                    dn1 = vcr_mul2(s2, vcr_fma2(pd, vcr_bcast2(xv.y), vcr_mul2(diry, nnx)));
+                    dn2 = vcr_mul2(s2, vcr_fma2(pd, vcr_bcast2(xv.z), vcr_mul2(dirz, nnx)));
+                    v[ACC_SV_OR_DEPTH] = sv;
+                } else {
+                    v[ACC_SV_OR_DEPTH] = dL_dd_j;
+                }
+                {
+                    // reference quirk kept: the "final normal" of the normalisation term is this Gaussian's own n (backward.cu:741-745)
+                    const float2 n0 = vcr_bcast2(nrm.x), n1 = vcr_bcast2(nrm.y), n2 = vcr_bcast2(nrm.z);
+                    const float2 e0 = vcr_sub2(n0, Sn0), e1 = vcr_sub2(n1, Sn1), e2 = vcr_sub2(n2, Sn2);
+                    const float2 nom1 = make_float2(-om1.x, -om1.y);
+                    dopa = vcr_fma2(vcr_fma2(n0, nom1, e0), kN0, dopa);
+                    dopa = vcr_fma2(vcr_fma2(n1, nom1, e1), kN1, dopa);
+                    dopa = vcr_fma2(vcr_fma2(n2, nom1, e2), kN2, dopa);
+                    Sn0 = vcr_fma2(alpha, e0, Sn0); Sn1 = vcr_fma2(alpha, e1, Sn1); Sn2 = vcr_fma2(alpha, e2, Sn2);
+                    v[ACC_NORMAL_X] = vcr_fma2(aTw, gN0, dn0); v[ACC_NORMAL_X + 1] = vcr_fma2(aTw, gN1, dn1); v[ACC_NORMAL_X + 2] = vcr_fma2(aTw, gN2, dn2);
+                }
+                float2 ex_obj1 = Z;
+                v[ACC_OBJ_0] = Z;
+                if (HAS_OBJ) {
+                    // dL_dalpha += (o - accum_rec_obj) * dL_dpixel_obj persists across Gaussians (backward.cu:766); contributing pixels only
+                    const float2 f0 = vcr_sub2(vcr_bcast2(nrm.w), So0), f1 = vcr_sub2(vcr_bcast2(col.w), So1);
+                    const float2 add = vcr_fma2(f1, gO1, vcr_mul2(f0, gO0));
+                    gA = make_float2(c0 ? gA.x + add.x : gA.x, c1 ? gA.y + add.y : gA.y);
+                    So0 = vcr_fma2(alpha, f0, So0); So1 = vcr_fma2(alpha, f1, So1);
+                    v[ACC_OBJ_0] = vcr_mul2(aT, gO0); ex_obj1 = vcr_mul2(aT, gO1);
+                }
+                dopa = vcr_fma2(om1, gA, dopa);                                   // (1 - accum_alpha_rec) * dL_dalpha
+                S1 = vcr_fma2(alpha, om1, S1);
+                dopa = vcr_fma2(inv1ma, nTf_bg, vcr_mul2(dopa, T));               // * T, + (-T_final / (1 - alpha)) * bg . dL_dpixel
+                // raw moments; the per-Gaussian factors (opacity, conic, 0.5 W) are applied once in preprocess_backward
+                const float2 bb = vcr_mul2(G, dopa);
+                const float2 bxx = vcr_mul2(bb, vcr_bcast2(dx)), byy = vcr_mul2(bb, dy);
+                v[ACC_M0] = bb; v[ACC_MX] = bxx; v[ACC_MY] = byy;
+                v[ACC_MXX] = vcr_mul2(bxx, vcr_bcast2(dx)); v[ACC_MXY] = vcr_mul2(bxx, dy); v[ACC_MYY] = vcr_mul2(byy, dy);
+                const float2 ax = vcr_fma2(byy, vcr_bcast2(g0.w), vcr_mul2(bxx, vcr_bcast2(g0.z)));
+                const float2 ay = vcr_fma2(bxx, vcr_bcast2(g0.w), vcr_mul2(byy, vcr_bcast2(g1.x)));
+                v[ACC_ABS_X] = make_float2(fabsf(ax.x), fabsf(ax.y)); v[ACC_ABS_Y] = make_float2(fabsf(ay.x), fabsf(ay.y));
+
+                // the thread's two pixels first, then the warp
+                float s[16];
+#pragma unroll
+                for (int q_ = 0; q_ < 16; q_++) s[q_] = v[q_].x + v[q_].y;
+                const float eo1 = ex_obj1.x + ex_obj1.y;
+                float* rec = acc + (size_t)__float_as_uint(g1.w) * VCR_ACC_STRIDE;
+                if (__popc(cmask) <= RB_SPARSE_LANES) {
+                    if (c0 || c1) {
+#pragma unroll
+                        for (int q_ = 0; q_ < (HAS_OBJ ? 16 : 15); q_++) atomicAdd(rec + q_, s[q_]);
+                        if (HAS_OBJ) atomicAdd(rec + ACC_OBJ_1, eo1);
+                    }
+                    continue;
+                }
+                const float red = warp_reduce16_transposed(s, lane);
+                if (lane < (HAS_OBJ ? 16 : 15)) atomicAdd(rec + lane, red);
+                if (HAS_OBJ) {
+                    const float o1 = vcr_warp_sum(eo1);
+                    if (lane == 16) atomicAdd(rec + ACC_OBJ_1, o1);
+                }
+            }
+        }
+        // one barrier per batch: publishes batch i+1 and frees buffer `buf` for batch i+2
+        __syncthreads();
+    }
+}
+
+int vcr_render_version();      // render_forward.cu
+
 int vcr_launch_render_backward(const BwdParams& p, GeomState& g, BinningState& b, ImageState& img, cudaStream_t s) {
     { VcrProfScope m(VCR_K_MEMSET, s); VCR_CUDA_TRY(cudaMemsetAsync(p.acc, 0, (size_t)p.P * VCR_ACC_STRIDE * sizeof(float), s)); }
     const unsigned int* abort_flag = vcr_radix_abort_flag();
@@ -350,6 +635,21 @@ int vcr_launch_render_backward(const BwdParams& p, GeomState& g, BinningState& b
         VCR_CUDA_TRY(cudaFuncSetAttribute(render_backward_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * sizeof(RbStage<false>))));
         VCR_CUDA_TRY(cudaFuncSetAttribute(render_backward_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * sizeof(RbStage<false>))));
         attr_set_dev[dev_].store(true, std::memory_order_release);
+    }
+    if (p.inside == nullptr && vcr_render_version() == 2) {
+        // every Gaussian inside: the two-pixels-per-thread kernel (static shared memory)
+#define RB2_ARGS img.ranges, img.tile_order, p.gx, b.point_list, p.W, p.H, p.background, g.means2D, g.xyz_view, g.conic_opacity, col, g.depths, \
+                 p.normals, p.sh_objs, p.dirs, p.alpha, p.depth, img.accum_alpha, img.n_contrib, p.dL_dpix, p.acc, abort_flag
+        if (p.dirs) {
+            if (p.sh_objs) render_backward2_kernel<true, true><<<grid, RB2_THREADS, 0, s>>>(RB2_ARGS);
+            else render_backward2_kernel<true, false><<<grid, RB2_THREADS, 0, s>>>(RB2_ARGS);
+        } else {
+            if (p.sh_objs) render_backward2_kernel<false, true><<<grid, RB2_THREADS, 0, s>>>(RB2_ARGS);
+            else render_backward2_kernel<false, false><<<grid, RB2_THREADS, 0, s>>>(RB2_ARGS);
+        }
+#undef RB2_ARGS
+        VCR_LAUNCH_CHECK("render_backward2_kernel");
+        return 0;
     }
     if (p.dirs) {
         const size_t sm = 2 * sizeof(RbStage<true>);

@@ -100,7 +100,7 @@ __global__ void __launch_bounds__(256, 4) render_forward_kernel(
             } else {
                 sg.nx = __ldg(depths + id);
             }
-            ins = __ldg(inside_gs + id) ? 1u : 0u;
+            ins = (inside_gs == nullptr || __ldg(inside_gs + id)) ? 1u : 0u;      // NULL: every Gaussian inside
             if (HAS_OBJ) { o0 = __ldg(obj + 2 * (size_t)id); o1 = __ldg(obj + 2 * (size_t)id + 1); }
             st.nrm[tid] = make_float4(n.x, n.y, n.z, o0);
         } else {
@@ -229,12 +229,236 @@ __global__ void __launch_bounds__(256, 4) render_forward_kernel(
     }
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// Two pixels per thread (the production kernel of f_count = 0).
+//
+// ncu of the one-pixel kernel above: instruction-issue bound (70 % issue-active, 3.6 % DRAM), 85 warp-instructions per
+// (warp, Gaussian) candidate, of which only the FMA chains are per-pixel work — the shared-memory reads of the staged
+// record, the candidate bookkeeping and the loop control are warp-uniform.  Here a 16x16 tile is drawn by 128 threads; a
+// thread owns the vertically adjacent pixels (x, y) and (x, y + 1), a warp a 16x4 strip.  Warp-uniform work is spent once
+// per two pixels, the number of (warp, Gaussian) candidates drops (a footprint that touches the upper 16x2 strip nearly
+// always touches the lower one), and the paired FMA chains go through the packed FFMA2 / FMUL2 / FADD2 instructions of
+// sm_100 (fma.rn.f32x2: one issue slot, two IEEE-rounded results; 1.5x the FMA throughput of scalar FFMA measured with
+// tools/ubench_f32x2.cu).  Every lane of a packed operation is rounded exactly like the scalar operation it replaces and
+// the per-pixel operation order is the reference's, so the images stay bit-identical to the reference build.
+// A pixel that does not take a Gaussian adds w = 0: fma(c, 0, acc) == acc for every finite c, which is the one assumption
+// (finite colours / normals / semantics) this formulation adds.
+// ------------------------------------------------------------------------------------------------------------------
+#define RF2_THREADS 128
+#define RF2_BATCH 128
+
+struct Rf2Stage {
+    StagedGeo geo[RF2_BATCH];
+    float4 box[RF2_BATCH];
+    float2 ex[RF2_BATCH];
+    float4 nrm[RF2_BATCH];             // normal.xyz, semantics[0]
+    float4 col[RF2_BATCH];             // rgb, semantics[1]
+};
+
+template <bool HAS_DIRS, bool HAS_OBJ, bool STATS>
+__global__ void __launch_bounds__(RF2_THREADS, 6) render_forward2_kernel(
+    const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order, int gx, const uint32_t* __restrict__ point_list, int W, int H,
+    const float2* __restrict__ means2D, const float* __restrict__ xyz_view, const float* __restrict__ features,
+    const float* __restrict__ depths, const float* __restrict__ normals, const float* __restrict__ obj,
+    const float* __restrict__ dirs, const float4* __restrict__ conic_opacity, const uint8_t* __restrict__ inside_gs,
+    const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
+    float* __restrict__ out_color, const unsigned int* __restrict__ abort_flag, unsigned long long* __restrict__ pair_counters) {
+    __shared__ Rf2Stage s_stage[2];
+    unsigned int st_ke = 0, st_kc = 0, st_cand = 0;
+    if (__ldg(abort_flag)) return;      // the sort of this view failed (binning.cu): the lists are garbage, leave the outputs unwritten
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t tile = __ldg(tile_order + blockIdx.x);      // blocks take tiles longest-list first
+    const uint32_t tile_x = tile % (uint32_t)gx, tile_y = tile / (uint32_t)gx;
+    // lanes 0-15: rows 4w, 4w+1; lanes 16-31: rows 4w+2, 4w+3 — the warp's strip is 16 columns x 4 rows
+    const uint32_t px = tile_x * VCR_TILE_X + (lane & 15);
+    const uint32_t py0 = tile_y * VCR_TILE_Y + 4 * warp + 2 * (lane >> 4), py1 = py0 + 1;
+    const bool in0 = px < (uint32_t)W && py0 < (uint32_t)H, in1 = px < (uint32_t)W && py1 < (uint32_t)H;
+    const size_t HW = (size_t)H * W;
+    const size_t pix0 = (size_t)W * py0 + px, pix1 = pix0 + (size_t)W;
+    const float pfx = (float)px;
+    const float2 npfy = make_float2(-(float)py0, -(float)py1);       // dy = g.y - pfy as g.y + (-pfy): the same rounding
+    uint32_t alive = (in0 ? 1u : 0u) | (in1 ? 2u : 0u);               // bit k: pixel k still composites
+    const float strip_x0 = (float)(tile_x * VCR_TILE_X), strip_x1 = strip_x0 + (float)(VCR_TILE_X - 1);
+    const float strip_y0 = (float)(tile_y * VCR_TILE_Y + 4 * warp), strip_y1 = strip_y0 + 3.0f;
+
+    float2 dirx = make_float2(0.f, 0.f), diry = dirx, dirz = dirx;
+    if (HAS_DIRS) {
+        if (in0) { dirx.x = __ldg(dirs + pix0); diry.x = __ldg(dirs + HW + pix0); dirz.x = __ldg(dirs + 2 * HW + pix0); }
+        if (in1) { dirx.y = __ldg(dirs + pix1); diry.y = __ldg(dirs + HW + pix1); dirz.y = __ldg(dirs + 2 * HW + pix1); }
+    }
+
+    const uint2 range = ranges[tile];
+    const int total = (int)(range.y - range.x);
+    const int rounds = (total + RF2_BATCH - 1) / RF2_BATCH;
+
+    auto stage = [&](int batch, int buf) {
+        const uint32_t pos = range.x + (uint32_t)batch * RF2_BATCH + tid;
+        if (pos >= range.y) return;
+        Rf2Stage& st = s_stage[buf];
+        const uint32_t id = __ldg(point_list + pos);
+        const float2 xy = __ldg(means2D + id);
+        const float4 co = __ldg(conic_opacity + id);
+        StagedGeo sg;
+        sg.x = xy.x; sg.y = xy.y; sg.ca = co.x; sg.cb = co.y; sg.cc = co.z; sg.op = co.w;
+        st.box[tid] = vcr_alpha_bbox(xy, co);
+        st.ex[tid] = vcr_alpha_rowtest(co);
+        float o0 = 0.f, o1 = 0.f;
+        const float3 n = make_float3(__ldg(normals + 3 * (size_t)id), __ldg(normals + 3 * (size_t)id + 1), __ldg(normals + 3 * (size_t)id + 2));
+        if (HAS_DIRS) {
+            const float3 xv = make_float3(__ldg(xyz_view + 3 * (size_t)id), __ldg(xyz_view + 3 * (size_t)id + 1),
+                                          __ldg(xyz_view + 3 * (size_t)id + 2));
+            sg.nx = n.x * xv.x + n.y * xv.y + n.z * xv.z;  // dot(n, x) of intersect(), auxiliary.h:262-271
+        } else {
+            sg.nx = __ldg(depths + id);
+        }
+        const uint32_t ins = (inside_gs == nullptr || __ldg(inside_gs + id)) ? 1u : 0u;      // NULL: every Gaussian inside
+        if (HAS_OBJ) { o0 = __ldg(obj + 2 * (size_t)id); o1 = __ldg(obj + 2 * (size_t)id + 1); }
+        st.nrm[tid] = make_float4(n.x, n.y, n.z, o0);
+        sg.id_inside = (id << 1) | ins;
+        st.geo[tid] = sg;
+        st.col[tid] = make_float4(__ldg(features + 3 * (size_t)id), __ldg(features + 3 * (size_t)id + 1),
+                                  __ldg(features + 3 * (size_t)id + 2), o1);
+    };
+
+    float2 T = make_float2(1.0f, 1.0f);
+    uint32_t last0 = 0, last1 = 0;
+    float2 C0 = make_float2(0.f, 0.f), C1 = C0, C2 = C0;
+    float2 weight = make_float2(1e-10f, 1e-10f);  // reference quirk: alpha output starts at 1e-10 (forward.cu:326)
+    float2 D = C0, N0 = C0, N1 = C0, N2 = C0, O0 = C0, O1 = C0;
+
+    if (rounds > 0) stage(0, 0);
+    __syncthreads();
+    for (int i = 0; i < rounds; i++) {
+        const int buf = i & 1;
+        if (i + 1 < rounds) stage(i + 1, buf ^ 1);   // overlaps with compositing batch i
+        const Rf2Stage& st = s_stage[buf];
+        const int cnt = min(RF2_BATCH, total - i * RF2_BATCH);
+        bool warp_done = __all_sync(0xffffffffu, alive == 0u);
+#pragma unroll 1
+        for (int k = 0; k < RF2_BATCH / 32 && !warp_done; k++) {
+            if (k * 32 >= cnt) break;
+            const int jj = k * 32 + lane;
+            const float4 bx = st.box[jj];
+            bool hit = jj < cnt && bx.x <= strip_x1 && bx.y >= strip_x0 && bx.z <= strip_y1 && bx.w >= strip_y0;
+            if (hit) {
+                const float4 gq = *reinterpret_cast<const float4*>(&st.geo[jj]);        // x, y, ca, cb
+                hit = vcr_strip_may_contribute_rows<4>(gq.x, gq.y, gq.z, gq.w, st.geo[jj].cc, st.ex[jj], strip_x0, strip_x1, strip_y0);
+            }
+            uint32_t m = __ballot_sync(0xffffffffu, hit);
+            while (m) {
+                // m is warp-uniform, so every lane passes here once per candidate: a safe place to vote
+                if (__all_sync(0xffffffffu, alive == 0u)) { warp_done = true; break; }
+                const int j = k * 32 + __ffs(m) - 1;
+                m &= m - 1;
+                if (STATS && lane == 0) st_cand++;
+                if (alive == 0u) continue;
+                if (STATS) st_ke += __popc(alive);
+                const float4 g0 = *reinterpret_cast<const float4*>(&st.geo[j]);        // x, y, ca, cb
+                const float4 g1 = *reinterpret_cast<const float4*>(&st.geo[j].cc);     // cc, op, nx, id_inside
+                const float dx = g0.x - pfx;
+                const float2 dy = vcr_add2(vcr_bcast2(g0.y), npfy);
+                // power = -0.5f*(ca*dx*dx + cc*dy*dy) - cb*dx*dy, contracted exactly like the reference build:
+                //   q = fma(fmul(ca,dx), dx, fmul(fmul(cc,dy), dy));  power = fma(q, -0.5, -fmul(fmul(cb,dx), dy))
+                const float adx = __fmul_rn(g0.z, dx), nbdx = -__fmul_rn(g0.w, dx);
+                const float2 q = vcr_fma2(vcr_bcast2(adx), vcr_bcast2(dx), vcr_mul2(vcr_mul2(vcr_bcast2(g1.x), dy), dy));
+                const float2 power = vcr_fma2(q, vcr_bcast2(-0.5f), vcr_mul2(vcr_bcast2(nbdx), dy));
+                // the reference tests depth before alpha (forward.cu:382-391); both are side-effect-free `continue`s,
+                // so alpha goes first here: most rejected pairs fail it, and it spares them the IEEE division
+                const float a0 = fminf(0.99f, g1.y * expf(power.x)), a1 = fminf(0.99f, g1.y * expf(power.y));
+                bool ok0 = (alive & 1u) && !(power.x > 0.0f) && !(a0 < 1.0f / 255.0f);
+                bool ok1 = (alive & 2u) && !(power.y > 0.0f) && !(a1 < 1.0f / 255.0f);
+                if (!(ok0 || ok1)) continue;
+                const float4 nrm = st.nrm[j];
+                float2 depth;
+                if (HAS_DIRS) {
+                    // t = nx / dot(n, dir) with the dot product in the reference's order: n.y*d.y, then n.x*d.x, then n.z*d.z
+                    const float2 pd = vcr_fma2(vcr_bcast2(nrm.z), dirz, vcr_fma2(vcr_bcast2(nrm.x), dirx, vcr_mul2(vcr_bcast2(nrm.y), diry)));
+                    depth = vcr_mul2(make_float2(__fdiv_rn(g1.z, pd.x), __fdiv_rn(g1.z, pd.y)), dirz);
+                } else {
+                    depth = vcr_bcast2(g1.z);
+                }
+                ok0 = ok0 && !(depth.x < 0.2f);  // == (double)depth <= 0.2, forward.cu:382
+                ok1 = ok1 && !(depth.y < 0.2f);
+                const float2 test_T = vcr_mul2(T, make_float2(1 - a0, 1 - a1));
+                if (ok0 && test_T.x < 0.0001f) { alive &= ~1u; ok0 = false; }
+                if (ok1 && test_T.y < 0.0001f) { alive &= ~2u; ok1 = false; }
+                if (!(ok0 || ok1)) continue;
+                const float4 col = st.col[j];
+                const uint32_t idi = __float_as_uint(g1.w);
+                const float2 w = make_float2(ok0 ? __fmul_rn(a0, T.x) : 0.f, ok1 ? __fmul_rn(a1, T.y) : 0.f);
+                C0 = vcr_fma2(vcr_bcast2(col.x), w, C0); C1 = vcr_fma2(vcr_bcast2(col.y), w, C1); C2 = vcr_fma2(vcr_bcast2(col.z), w, C2);
+                if (HAS_OBJ) { O0 = vcr_fma2(vcr_bcast2(nrm.w), w, O0); O1 = vcr_fma2(vcr_bcast2(col.w), w, O1); }
+                weight = vcr_add2(weight, w);
+                if (idi & 1u) {
+                    D = vcr_fma2(make_float2(ok0 ? depth.x : 0.f, ok1 ? depth.y : 0.f), w, D);
+                    N0 = vcr_fma2(vcr_bcast2(nrm.x), w, N0); N1 = vcr_fma2(vcr_bcast2(nrm.y), w, N1); N2 = vcr_fma2(vcr_bcast2(nrm.z), w, N2);
+                }
+                const uint32_t here = (uint32_t)(i * RF2_BATCH + j + 1);
+                if (ok0) { T.x = test_T.x; last0 = here; }
+                if (ok1) { T.y = test_T.y; last1 = here; }
+                if (STATS) st_kc += (ok0 ? 1u : 0u) + (ok1 ? 1u : 0u);
+            }
+        }
+        // one barrier per batch: publishes batch i+1, frees buffer `buf` for batch i+2, and votes on completion
+        if (__syncthreads_and(alive == 0u)) break;
+    }
+
+    if (STATS) {
+        const unsigned int ke = __reduce_add_sync(0xffffffffu, st_ke), kc = __reduce_add_sync(0xffffffffu, st_kc);
+        const unsigned int nc = __reduce_add_sync(0xffffffffu, (in0 ? last0 : 0u) + (in1 ? last1 : 0u));
+        if (lane == 0) {
+            atomicAdd(pair_counters + 0, (unsigned long long)ke); atomicAdd(pair_counters + 1, (unsigned long long)kc);
+            atomicAdd(pair_counters + 2, (unsigned long long)nc); atomicAdd(pair_counters + 3, (unsigned long long)st_cand);
+        }
+    }
+    const float bg0 = __ldg(bg), bg1 = __ldg(bg + 1), bg2 = __ldg(bg + 2);
+    auto write = [&](const size_t pix, const float Tv, const uint32_t last, const float c0, const float c1, const float c2, const float wt,
+                     const float d, const float n0, const float n1, const float n2, const float o0, const float o1) {
+        final_T[pix] = Tv;
+        n_contrib[pix] = last;
+        out_color[pix] = __fmaf_rn(Tv, bg0, c0);
+        out_color[HW + pix] = __fmaf_rn(Tv, bg1, c1);
+        out_color[2 * HW + pix] = __fmaf_rn(Tv, bg2, c2);
+        out_color[VCR_DEPTH_OFFSET * HW + pix] = d / wt;
+        out_color[VCR_ALPHA_OFFSET * HW + pix] = wt;
+        out_color[(VCR_NORMAL_OFFSET + 0) * HW + pix] = n0 / wt;
+        out_color[(VCR_NORMAL_OFFSET + 1) * HW + pix] = n1 / wt;
+        out_color[(VCR_NORMAL_OFFSET + 2) * HW + pix] = n2 / wt;
+        // the reference leaves the semantic channels at their zero initialisation when there are none
+        out_color[(VCR_OBJECT_OFFSET + 0) * HW + pix] = HAS_OBJ ? o0 : 0.f;
+        out_color[(VCR_OBJECT_OFFSET + 1) * HW + pix] = HAS_OBJ ? o1 : 0.f;
+    };
+    if (in0) write(pix0, T.x, last0, C0.x, C1.x, C2.x, weight.x, D.x, N0.x, N1.x, N2.x, O0.x, O1.x);
+    if (in1) write(pix1, T.y, last1, C0.y, C1.y, C2.y, weight.y, D.y, N0.y, N1.y, N2.y, O0.y, O1.y);
+}
+
+// vcr_debug_render_version(1) selects the one-pixel-per-thread kernels (A/B measurements, tools/); 2 (default) = two pixels.
+static int g_render_version = 2;
+extern "C" int vcr_debug_render_version(int v) { if (v == 1 || v == 2) g_render_version = v; return g_render_version; }
+int vcr_render_version() { return g_render_version; }
+
 int vcr_launch_render_forward(const FwdParams& p, GeomState& g, BinningState& b, ImageState& img, cudaStream_t s) {
     const dim3 grid(p.gx * p.gy, 1, 1);
     const float* feat = p.colors_precomp ? p.colors_precomp : g.rgb;
     const unsigned int* abort_flag = vcr_radix_abort_flag();
     if (!abort_flag) { vcr_set_error("cannot resolve the sort status flag on this device"); return 1; }
     VcrProfScope prof(VCR_K_RENDER_FWD, s);
+    if (g_render_version == 2) {
+#define RF2_ARGS img.ranges, img.tile_order, p.gx, b.point_list, p.W, p.H, g.means2D, g.xyz_view, feat, g.depths, p.normals, p.sh_objs, p.dirs, \
+                 g.conic_opacity, p.inside, p.background, img.accum_alpha, img.n_contrib, p.out_color, abort_flag, g_pair_counters
+#define RF2_LAUNCH(D_, O_)                                                                                   \
+        do {                                                                                                 \
+            if (g_pair_counters) render_forward2_kernel<D_, O_, true><<<grid, RF2_THREADS, 0, s>>>(RF2_ARGS); \
+            else render_forward2_kernel<D_, O_, false><<<grid, RF2_THREADS, 0, s>>>(RF2_ARGS);                \
+        } while (0)
+        if (p.dirs) { if (p.sh_objs) RF2_LAUNCH(true, true); else RF2_LAUNCH(true, false); }
+        else { if (p.sh_objs) RF2_LAUNCH(false, true); else RF2_LAUNCH(false, false); }
+#undef RF2_LAUNCH
+#undef RF2_ARGS
+        VCR_LAUNCH_CHECK("render_forward2_kernel");
+        return 0;
+    }
 #define RF_ARGS img.ranges, img.tile_order, p.gx, b.point_list, p.W, p.H, g.means2D, g.xyz_view, feat, g.depths, p.normals, p.sh_objs, p.dirs, \
                 g.conic_opacity, p.inside, p.background, img.accum_alpha, img.n_contrib, p.out_color, nullptr, nullptr, abort_flag
     if (g_pair_counters) {          // instrumented run (never inside a timed region)

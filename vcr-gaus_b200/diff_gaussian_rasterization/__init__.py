@@ -118,9 +118,11 @@ class _RasterizeGaussians(torch.autograd.Function):
             means3D_c, sh_c, colors_c = _f32c(means3D), _f32c(sh, True), _f32c(colors_precomp)
             normals_c, sem_c, opac_c = _f32c(normals_precomp), _f32c(semantics_precomp), _f32c(opacities)
             scales_c, rot_c, cov_c, dirs_c = _f32c(scales), _f32c(rotations, True), _f32c(cov3Ds_precomp), _f32c(dirs)
-            inside_c = inside.contiguous()
-            if inside_c.dtype != torch.bool:
-                raise RuntimeError("inside must be a bool tensor")
+            inside_c = None
+            if inside is not None:              # None = every Gaussian inside (the library's fast path; the reference passes ones)
+                inside_c = inside.contiguous()
+                if inside_c.dtype != torch.bool:
+                    raise RuntimeError("inside must be a bool tensor")
             bg, view, proj, campos = _settings_tensors(rs, device)
             M = sh_c.shape[1] if sh_c is not None and sh_c.numel() != 0 else 0
             n_host = ctypes.c_int(0)
@@ -128,7 +130,7 @@ class _RasterizeGaussians(torch.autograd.Function):
                     _n.ptr(means3D_c), _n.ptr(sh_c), _n.ptr(colors_c), _n.ptr(normals_c), _n.ptr(sem_c), _n.ptr(opac_c),
                     _n.ptr(scales_c), float(rs.scale_modifier), _n.ptr(rot_c), _n.ptr(cov_c), _n.ptr(view), _n.ptr(proj),
                     _n.ptr(dirs_c), _n.ptr(campos), float(rs.tanfovx), float(rs.tanfovy), int(bool(rs.prefiltered)),
-                    outmap.data_ptr(), radii.data_ptr(), inside_c.data_ptr(), int(bool(rs.debug)), ctypes.byref(n_host),
+                    outmap.data_ptr(), radii.data_ptr(), _n.ptr(inside_c), int(bool(rs.debug)), ctypes.byref(n_host),
                     _stream())
             if rs.debug:
                 cpu_args = cpu_deep_copy_tuple((rs.bg, means3D, colors_precomp, normals_precomp, semantics_precomp, opacities,
@@ -209,7 +211,7 @@ class _RasterizeGaussians(torch.autograd.Function):
                     binningBuffer.data_ptr(), imgBuffer.data_ptr(), grad_c.data_ptr(), g_means2D.data_ptr(),
                     g_means2D_densify.data_ptr(), g_opacity.data_ptr(), _n.ptr(g_colors), g_normals.data_ptr(),
                     _n.ptr(g_objects), g_means3D.data_ptr(), _n.ptr(g_cov3D), _n.ptr(g_sh), g_scales.data_ptr(),
-                    g_rot.data_ptr(), inside.contiguous().data_ptr(), scratch.data_ptr(), int(bool(rs.debug)), _stream())
+                    g_rot.data_ptr(), _n.ptr(inside.contiguous() if inside is not None else None), scratch.data_ptr(), int(bool(rs.debug)), _stream())
             if rs.debug:
                 cpu_args = cpu_deep_copy_tuple((rs.bg, means3D, radii, colors_precomp, normals_precomp, semantics_precomp, scales,
                                                 rotations, rs.scale_modifier, cov3Ds_precomp, rs.viewmatrix, rs.projmatrix, dirs,
@@ -369,8 +371,8 @@ class GaussianRasterizer(nn.Module):
         rotations = empty() if rotations is None else rotations
         cov3D_precomp = empty() if cov3D_precomp is None else cov3D_precomp
         dirs = empty() if dirs is None else dirs
-        if inside is None:
-            inside = torch.ones(means3D.shape[0], device=dev, dtype=torch.bool)
+        # inside=None stays None: the library treats a NULL mask as "all inside" (the reference allocates a tensor of ones per
+        # call, __init__.py:521-522) and takes its two-pixels-per-thread backward
         if raster_settings.f_count == 0:
             if normals_precomp is None:
                 # The reference kernel dereferences `normals` unconditionally (forward.cu:374): with
