@@ -348,6 +348,9 @@ __global__ void __launch_bounds__(256) render_backward_kernel(
 // ------------------------------------------------------------------------------------------------------------------
 #define RB2_THREADS 128
 #define RB2_BATCH 128
+#ifndef VCR_RB2_MINBLOCKS
+#define VCR_RB2_MINBLOCKS 5
+#endif
 
 template <bool HAS_DIRS>
 struct Rb2Stage {
@@ -362,7 +365,7 @@ struct Rb2Stage {
 __device__ __forceinline__ float2 vcr_sub2(const float2 a, const float2 b) { return vcr_add2(a, make_float2(-b.x, -b.y)); }
 
 template <bool HAS_DIRS, bool HAS_OBJ>
-__global__ void __launch_bounds__(RB2_THREADS, 4) render_backward2_kernel(
+__global__ void __launch_bounds__(RB2_THREADS, VCR_RB2_MINBLOCKS) render_backward2_kernel(
     const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order, int gx, const uint32_t* __restrict__ point_list, int W, int H, const float* __restrict__ bg,
     const float2* __restrict__ means2D, const float* __restrict__ xyz_view, const float4* __restrict__ conic_opacity,
     const float* __restrict__ colors, const float* __restrict__ depths, const float* __restrict__ normals,

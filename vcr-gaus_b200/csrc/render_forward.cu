@@ -246,6 +246,9 @@ __global__ void __launch_bounds__(256, 4) render_forward_kernel(
 // ------------------------------------------------------------------------------------------------------------------
 #define RF2_THREADS 128
 #define RF2_BATCH 128
+#ifndef VCR_RF2_MINBLOCKS
+#define VCR_RF2_MINBLOCKS 7
+#endif
 
 struct Rf2Stage {
     StagedGeo geo[RF2_BATCH];
@@ -256,7 +259,7 @@ struct Rf2Stage {
 };
 
 template <bool HAS_DIRS, bool HAS_OBJ, bool STATS>
-__global__ void __launch_bounds__(RF2_THREADS, 6) render_forward2_kernel(
+__global__ void __launch_bounds__(RF2_THREADS, VCR_RF2_MINBLOCKS) render_forward2_kernel(
     const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order, int gx, const uint32_t* __restrict__ point_list, int W, int H,
     const float2* __restrict__ means2D, const float* __restrict__ xyz_view, const float* __restrict__ features,
     const float* __restrict__ depths, const float* __restrict__ normals, const float* __restrict__ obj,
