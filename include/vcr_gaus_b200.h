@@ -414,6 +414,36 @@ int vcr_dist2_knn3(int P, const float* points /* f32[P,3] */, float* mean_dists 
 int vcr_knn_noalloc_max_points(void);
 int vcr_dist2_knn3_noalloc(int P, const float* points /* f32[P,3] */, float* mean_dists /* f32[P] */, void* stream);
 
+/* ---- the reference's compile-time variants (DGR/cuda_rasterizer/config.h:17-18, README.md:150-155) as run-time arguments ----
+ * num_dist in {0, 1} = NUM_DIST (a depth-distortion channel, forward.cu:400-412, 464-472), num_depth2 in {0, 2} = NUM_DEPTH2
+ * (the sums of NDC depth and of its square over the inside Gaussians, forward.cu:426-430, 473-476; what render() turns into
+ * `depth_var`, gaussian_renderer/__init__.py:154-158).  out_color and dL_dpix then have vcr_variant_channels() channels
+ * (OUTPUT_CHANNELS, auxiliary.h:28); both variants write from channel 10 on, as in the reference (DISTORTION_OFFSET ==
+ * DEPTH2_OFFSET), so with both set channel 10 holds the first depth sum and channel 12 stays zero.  Gradients: the depth sums
+ * reach the Gaussians through the depth only (DETACH_WEIGHT = 1, backward.cu:656-664); the distortion channel has none — in
+ * the reference as written its backward terms multiply variables that are re-declared in an inner scope and stay zero
+ * (backward.cu:489-499).  Not reproduced: with NUM_DIST = 1 the reference also stores two values per pixel behind the end
+ * of its final_T array (forward.cu:469-470 against rasterizer_impl.cu:176), over its own n_contrib.  All other arguments as
+ * vcr_rasterize_forward / vcr_rasterize_backward.  The variants run on the one-pixel-per-thread kernels. */
+int vcr_variant_channels(int num_dist, int num_depth2);
+int vcr_rasterize_forward_variant(
+    int num_dist, int num_depth2,
+    vcr_alloc_fn geometry_buffer, vcr_alloc_fn binning_buffer, vcr_alloc_fn image_buffer, void* alloc_user,
+    int P, int D, int M, const float* background, int width, int height, const float* means3D, const float* shs,
+    const float* colors_precomp, const float* normals_precomp, const float* sh_objs, const float* opacities, const float* scales,
+    float scale_modifier, const float* rotations, const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+    const float* dirs, const float* cam_pos, float tan_fovx, float tan_fovy, int prefiltered, float* out_color, int* radii,
+    const uint8_t* inside, int debug, int* num_rendered_host, void* stream);
+int vcr_rasterize_backward_variant(
+    int num_dist, int num_depth2,
+    int P, int D, int M, int R, const float* background, int width, int height, const float* means3D, const float* shs,
+    const float* colors_precomp, const float* normals_precomp, const float* sh_objs, const float* alpha, const float* depth,
+    const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
+    const float* projmatrix, const float* dirs, const float* campos, float tan_fovx, float tan_fovy, const int* radii,
+    char* geom_buffer, char* binning_buffer, char* img_buffer, const float* dL_dpix, float* dL_dmean2D, float* dL_dmean2D_densify,
+    float* dL_dopacity, float* dL_dcolor, float* dL_dnormal, float* dL_dobjects, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh,
+    float* dL_dscale, float* dL_drot, const uint8_t* inside, char* scratch, int debug, void* stream);
+
 /* ---- measurement hooks (bench.py; no counterpart in the reference, which has no per-kernel timers — SURVEY.md §5) ----
  * With profiling enabled every kernel launch of this library is bracketed by CUDA events on its own stream.
  * vcr_profile_read sums the elapsed milliseconds and the number of timed launches per kernel id since the last reset

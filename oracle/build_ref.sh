@@ -18,7 +18,7 @@
 #
 # This is test infrastructure (the parity oracle + the `--impl reference` bench arm), never the product path.
 # Variant build: NUM_DIST=1 NUM_DEPTH2=2 bash oracle/build_ref.sh builds the distortion variant of the rasterizer
-# (DGR/cuda_rasterizer/config.h:17-18) into oracle/_ref/diff_gaussian_rasterization_dist/.
+# (DGR/cuda_rasterizer/config.h:17-18) into oracle/_ref/diff_gaussian_rasterization_d${NUM_DIST:-0}_${NUM_DEPTH2:-0}/.
 set -euo pipefail
 REF=${REF:-/root/reference}
 HERE="$(cd "$(dirname "$0")" && pwd)"
@@ -118,14 +118,15 @@ if [ -n "${NUM_DIST:-}" ] || [ -n "${NUM_DEPTH2:-}" ]; then
   # distortion variant (README.md:150-155): config.h gives NUM_DIST / NUM_DEPTH2 no #ifndef guard, so the build compiles
   # against a temporary copy of cuda_rasterizer/ in which those two #define lines carry the requested values
   VAR="$OUT/obj/dgr_variant"
-  rm -rf "$VAR" && mkdir -p "$VAR" "$OUT/diff_gaussian_rasterization_dist"
+  rm -rf "$VAR" && mkdir -p "$VAR" "$OUT/diff_gaussian_rasterization_d${NUM_DIST:-0}_${NUM_DEPTH2:-0}"
   cp -r "$DGR/cuda_rasterizer" "$DGR/rasterize_points.cu" "$DGR/rasterize_points.h" "$DGR/ext.cpp" "$VAR/"
   sed -i "s/^#define NUM_DIST .*/#define NUM_DIST ${NUM_DIST:-0}/; s/^#define NUM_DEPTH2 .*/#define NUM_DEPTH2 ${NUM_DEPTH2:-0}/" "$VAR/cuda_rasterizer/config.h"
   grep -E "^#define NUM_(DIST|DEPTH2) " "$VAR/cuda_rasterizer/config.h" >&2
-  build_one diff_gaussian_rasterization_dist "$VAR" "$ARCH_DGR" "-I$GLMFIX" \
+  build_one diff_gaussian_rasterization_d${NUM_DIST:-0}_${NUM_DEPTH2:-0} "$VAR" "$ARCH_DGR" "-I$GLMFIX" \
     cuda_rasterizer/rasterizer_impl.cu cuda_rasterizer/forward.cu cuda_rasterizer/backward.cu rasterize_points.cu ext.cpp
   rm -rf "$OUT/obj"
-  echo "built: $OUT/diff_gaussian_rasterization_dist/_C.so"
+  cp "$DGR/diff_gaussian_rasterization/__init__.py" "$OUT/diff_gaussian_rasterization_d${NUM_DIST:-0}_${NUM_DEPTH2:-0}/__init__.py"
+  echo "built: $OUT/diff_gaussian_rasterization_d${NUM_DIST:-0}_${NUM_DEPTH2:-0}/_C.so"
   exit 0
 fi
 build_one diff_gaussian_rasterization "$DGR" "$ARCH_DGR" "-I$GLMFIX" \

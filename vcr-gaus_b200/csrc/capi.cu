@@ -242,7 +242,7 @@ size_t vcr_image_bytes(int width, int height) { return ImageState::bytes(width, 
 size_t vcr_binning_bytes(int num_rendered) { return BinningState::bytes(num_rendered); }
 size_t vcr_backward_scratch_bytes(int P) { return (size_t)P * VCR_ACC_STRIDE * sizeof(float) + 256; }
 
-int vcr_rasterize_forward(vcr_alloc_fn geometry_buffer, vcr_alloc_fn binning_buffer, vcr_alloc_fn image_buffer, void* alloc_user,
+static int rasterize_forward_impl(int variant, vcr_alloc_fn geometry_buffer, vcr_alloc_fn binning_buffer, vcr_alloc_fn image_buffer, void* alloc_user,
                           int P, int D, int M, const float* background, int width, int height, const float* means3D,
                           const float* shs, const float* colors_precomp, const float* normals_precomp, const float* sh_objs,
                           const float* opacities, const float* scales, float scale_modifier, const float* rotations,
@@ -259,7 +259,7 @@ int vcr_rasterize_forward(vcr_alloc_fn geometry_buffer, vcr_alloc_fn binning_buf
     p.opacities = opacities; p.scales = scales; p.scale_modifier = scale_modifier; p.rotations = rotations;
     p.cov3D_precomp = cov3D_precomp; p.viewmatrix = viewmatrix; p.projmatrix = projmatrix; p.dirs = dirs; p.cam_pos = cam_pos;
     p.background = background; p.tan_fovx = tan_fovx; p.tan_fovy = tan_fovy; p.prefiltered = prefiltered;
-    p.out_color = out_color; p.radii = radii; p.inside = inside;
+    p.out_color = out_color; p.radii = radii; p.inside = inside; p.variant = variant;
     GeomState g; BinningState b; ImageState img;
     if (forward_front(geometry_buffer, binning_buffer, image_buffer, alloc_user, p, g, b, img, debug, num_rendered_host, s)) return 1;
     if (vcr_launch_render_forward(p, g, b, img, s)) return 1;
@@ -267,7 +267,40 @@ int vcr_rasterize_forward(vcr_alloc_fn geometry_buffer, vcr_alloc_fn binning_buf
     return 0;
 }
 
-int vcr_rasterize_backward_chunked(int P, int D, int M, int R, const float* background, int width, int height, const float* means3D,
+int vcr_rasterize_forward(vcr_alloc_fn geometry_buffer, vcr_alloc_fn binning_buffer, vcr_alloc_fn image_buffer, void* alloc_user,
+                          int P, int D, int M, const float* background, int width, int height, const float* means3D,
+                          const float* shs, const float* colors_precomp, const float* normals_precomp, const float* sh_objs,
+                          const float* opacities, const float* scales, float scale_modifier, const float* rotations,
+                          const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix, const float* dirs,
+                          const float* cam_pos, float tan_fovx, float tan_fovy, int prefiltered, float* out_color, int* radii,
+                          const uint8_t* inside, int debug, int* num_rendered_host, void* stream) {
+    return rasterize_forward_impl(0, geometry_buffer, binning_buffer, image_buffer, alloc_user, P, D, M, background, width, height, means3D, shs, colors_precomp, normals_precomp, sh_objs, opacities, scales, scale_modifier, rotations, cov3D_precomp, viewmatrix, projmatrix, dirs, cam_pos, tan_fovx, tan_fovy, prefiltered, out_color, radii, inside, debug, num_rendered_host, stream);
+}
+
+static int variant_code(int num_dist, int num_depth2, int* code) {
+    if ((num_dist != 0 && num_dist != 1) || (num_depth2 != 0 && num_depth2 != 2)) {
+        vcr_set_error("NUM_DIST must be 0 or 1 and NUM_DEPTH2 0 or 2 (DGR/cuda_rasterizer/config.h:17-18), got %d / %d", num_dist, num_depth2);
+        return 1;
+    }
+    *code = (num_dist ? 1 : 0) | (num_depth2 ? 2 : 0);
+    return 0;
+}
+
+int vcr_variant_channels(int num_dist, int num_depth2) { return VCR_OUT_CH + (num_dist ? 1 : 0) + (num_depth2 ? 2 : 0); }
+
+int vcr_rasterize_forward_variant(int num_dist, int num_depth2, vcr_alloc_fn geometry_buffer, vcr_alloc_fn binning_buffer, vcr_alloc_fn image_buffer, void* alloc_user,
+                          int P, int D, int M, const float* background, int width, int height, const float* means3D,
+                          const float* shs, const float* colors_precomp, const float* normals_precomp, const float* sh_objs,
+                          const float* opacities, const float* scales, float scale_modifier, const float* rotations,
+                          const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix, const float* dirs,
+                          const float* cam_pos, float tan_fovx, float tan_fovy, int prefiltered, float* out_color, int* radii,
+                          const uint8_t* inside, int debug, int* num_rendered_host, void* stream) {
+    int code = 0;
+    if (variant_code(num_dist, num_depth2, &code)) return 1;
+    return rasterize_forward_impl(code, geometry_buffer, binning_buffer, image_buffer, alloc_user, P, D, M, background, width, height, means3D, shs, colors_precomp, normals_precomp, sh_objs, opacities, scales, scale_modifier, rotations, cov3D_precomp, viewmatrix, projmatrix, dirs, cam_pos, tan_fovx, tan_fovy, prefiltered, out_color, radii, inside, debug, num_rendered_host, stream);
+}
+
+static int rasterize_backward_impl(int variant, int P, int D, int M, int R, const float* background, int width, int height, const float* means3D,
                            const float* shs, const float* colors_precomp, const float* normals_precomp, const float* sh_objs,
                            const float* alpha, const float* depth, const float* scales, float scale_modifier,
                            const float* rotations, const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
@@ -310,7 +343,7 @@ int vcr_rasterize_backward_chunked(int P, int D, int M, int R, const float* back
     p.dL_dmean2D = dL_dmean2D; p.dL_dmean2D_densify = dL_dmean2D_densify; p.dL_dopacity = dL_dopacity; p.dL_dcolor = dL_dcolor;
     p.dL_dnormal = dL_dnormal; p.dL_dobjects = dL_dobjects; p.dL_dmean3D = dL_dmean3D; p.dL_dcov3D = dL_dcov3D; p.dL_dsh = dL_dsh;
     p.dL_dscale = dL_dscale; p.dL_drot = dL_drot; p.inside = inside;
-    p.dL_dcolor_masked = shs ? dL_dcolor_masked : nullptr;
+    p.dL_dcolor_masked = shs ? dL_dcolor_masked : nullptr; p.variant = variant;
     p.acc = reinterpret_cast<float*>(vcr_align256(reinterpret_cast<size_t>(scratch)));
     GeomState g = GeomState::carve(geom_buffer, P);
     BinningState b = BinningState::carve(binning_buffer, R);
@@ -331,6 +364,33 @@ int vcr_rasterize_backward_chunked(int P, int D, int M, int R, const float* back
     }
     if (debug_sync(debug, s, "preprocess backward")) return 1;
     return 0;
+}
+
+int vcr_rasterize_backward_chunked(int P, int D, int M, int R, const float* background, int width, int height, const float* means3D,
+                           const float* shs, const float* colors_precomp, const float* normals_precomp, const float* sh_objs,
+                           const float* alpha, const float* depth, const float* scales, float scale_modifier,
+                           const float* rotations, const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+                           const float* dirs, const float* campos, float tan_fovx, float tan_fovy, const int* radii,
+                           char* geom_buffer, char* binning_buffer, char* img_buffer, const float* dL_dpix, float* dL_dmean2D,
+                           float* dL_dmean2D_densify, float* dL_dopacity, float* dL_dcolor, float* dL_dnormal, float* dL_dobjects,
+                           float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
+                           const uint8_t* inside, char* scratch, int debug, void* stream, int n_chunks,
+                           vcr_chunk_fn chunk_enqueued, void* chunk_user, float* dL_dcolor_masked) {
+    return rasterize_backward_impl(0, P, D, M, R, background, width, height, means3D, shs, colors_precomp, normals_precomp, sh_objs, alpha, depth, scales, scale_modifier, rotations, cov3D_precomp, viewmatrix, projmatrix, dirs, campos, tan_fovx, tan_fovy, radii, geom_buffer, binning_buffer, img_buffer, dL_dpix, dL_dmean2D, dL_dmean2D_densify, dL_dopacity, dL_dcolor, dL_dnormal, dL_dobjects, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, inside, scratch, debug, stream, n_chunks, chunk_enqueued, chunk_user, dL_dcolor_masked);
+}
+
+int vcr_rasterize_backward_variant(int num_dist, int num_depth2, int P, int D, int M, int R, const float* background, int width, int height, const float* means3D,
+                           const float* shs, const float* colors_precomp, const float* normals_precomp, const float* sh_objs,
+                           const float* alpha, const float* depth, const float* scales, float scale_modifier,
+                           const float* rotations, const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+                           const float* dirs, const float* campos, float tan_fovx, float tan_fovy, const int* radii,
+                           char* geom_buffer, char* binning_buffer, char* img_buffer, const float* dL_dpix, float* dL_dmean2D,
+                           float* dL_dmean2D_densify, float* dL_dopacity, float* dL_dcolor, float* dL_dnormal, float* dL_dobjects,
+                           float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
+                           const uint8_t* inside, char* scratch, int debug, void* stream) {
+    int code = 0;
+    if (variant_code(num_dist, num_depth2, &code)) return 1;
+    return rasterize_backward_impl(code, P, D, M, R, background, width, height, means3D, shs, colors_precomp, normals_precomp, sh_objs, alpha, depth, scales, scale_modifier, rotations, cov3D_precomp, viewmatrix, projmatrix, dirs, campos, tan_fovx, tan_fovy, radii, geom_buffer, binning_buffer, img_buffer, dL_dpix, dL_dmean2D, dL_dmean2D_densify, dL_dopacity, dL_dcolor, dL_dnormal, dL_dobjects, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, inside, scratch, debug, stream, 1, nullptr, nullptr, nullptr);
 }
 
 int vcr_rasterize_backward(int P, int D, int M, int R, const float* background, int width, int height, const float* means3D,

@@ -76,7 +76,11 @@ __device__ __forceinline__ float warp_reduce16_transposed(float (&v)[16], int la
     return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 16);
 }
 
-template <bool HAS_DIRS, bool HAS_OBJ>
+// DEPTH2: the reference built with NUM_DEPTH2 = 2 (config.h:18): dL/dpixel has two more channels (sum of NDC depth and of its
+// square, DEPTH2_OFFSET = 10) whose gradient reaches the Gaussians through the depth only — DETACH_WEIGHT = 1 (auxiliary.h:32)
+// removes the opacity term (backward.cu:656-680).  The NUM_DIST = 1 channel has no gradient in the reference as written: the
+// values it would use are declared a second time inside `if (NUM_DIST) { ... }` (backward.cu:494-499) and the outer ones stay 0.
+template <bool HAS_DIRS, bool HAS_OBJ, bool DEPTH2 = false>
 __global__ void __launch_bounds__(256) render_backward_kernel(
     const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order, int gx, const uint32_t* __restrict__ point_list, int W, int H, const float* __restrict__ bg,
     const float2* __restrict__ means2D, const float* __restrict__ xyz_view, const float4* __restrict__ conic_opacity,
@@ -126,7 +130,12 @@ __global__ void __launch_bounds__(256) render_backward_kernel(
     float accum_normal_rec[3] = {0.f, 0.f, 0.f}, dL_dpixel_normal[3] = {0.f, 0.f, 0.f};
     float accum_rec_obj[2] = {0.f, 0.f}, dL_dpixel_obj[2] = {0.f, 0.f};
     float accum_alpha_rec = 0.f, dL_dalpha = 0.f;
+    float dL_dd1 = 0.f, dL_dd2 = 0.f;
     float3 dir = make_float3(0.f, 0.f, 1.f);
+    if (inside && DEPTH2) {
+        dL_dd1 = __ldg(dL_dpixels + VCR_OUT_CH * HW + pix_id);
+        dL_dd2 = __ldg(dL_dpixels + (VCR_OUT_CH + 1) * HW + pix_id);
+    }
     if (inside) {
 #pragma unroll
         for (int i = 0; i < 3; i++) dL_dpixel[i] = __ldg(dL_dpixels + i * HW + pix_id);
@@ -254,7 +263,13 @@ __global__ void __launch_bounds__(256) render_backward_kernel(
                         accum_rec2 = last_alpha + (1.f - last_alpha) * accum_rec2;  // == accum_normal_rec2[ch], same recurrence
                         dL_dopa += (((c_d - accum_depth_rec) - depth_final * (1 - accum_rec2)) * inv_weight) * dL_dpixel_depth;
                         const float aTw = aT * inv_weight;
-                        const float dL_dd_j = aTw * dL_dpixel_depth;
+                        float dL_dd_j = aTw * dL_dpixel_depth;
+                        if (DEPTH2) {        // backward.cu:656-664
+                            const float dn = (float)((100.0 * (double)c_d - 100.0 * 0.2) / ((100.0 - 0.2) * (double)c_d));
+                            const float dmax_t_dd = (float)((100.0 * 0.2) / ((100.0 - 0.2) * (double)c_d * (double)c_d));
+                            dL_dd_j += aT * dmax_t_dd * dL_dd1;
+                            dL_dd_j += 2.0f * aT * dn * dmax_t_dd * dL_dd2;
+                        }
                         float dnd[3] = {0.f, 0.f, 0.f};
                         if (HAS_DIRS) {  // backward.cu:722-728
                             const float4 xv = st.xv[j];
@@ -637,9 +652,13 @@ int vcr_launch_render_backward(const BwdParams& p, GeomState& g, BinningState& b
         VCR_CUDA_TRY(cudaFuncSetAttribute(render_backward_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * sizeof(RbStage<true>))));
         VCR_CUDA_TRY(cudaFuncSetAttribute(render_backward_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * sizeof(RbStage<false>))));
         VCR_CUDA_TRY(cudaFuncSetAttribute(render_backward_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * sizeof(RbStage<false>))));
+        VCR_CUDA_TRY(cudaFuncSetAttribute(render_backward_kernel<true, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * sizeof(RbStage<true>))));
+        VCR_CUDA_TRY(cudaFuncSetAttribute(render_backward_kernel<true, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * sizeof(RbStage<true>))));
+        VCR_CUDA_TRY(cudaFuncSetAttribute(render_backward_kernel<false, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * sizeof(RbStage<false>))));
+        VCR_CUDA_TRY(cudaFuncSetAttribute(render_backward_kernel<false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * sizeof(RbStage<false>))));
         attr_set_dev[dev_].store(true, std::memory_order_release);
     }
-    if (p.inside == nullptr && vcr_render_version() == 2) {
+    if (p.inside == nullptr && vcr_render_version() == 2 && !(p.variant & 2)) {
         // every Gaussian inside: the two-pixels-per-thread kernel (static shared memory)
 #define RB2_ARGS img.ranges, img.tile_order, p.gx, b.point_list, p.W, p.H, p.background, g.means2D, g.xyz_view, g.conic_opacity, col, g.depths, \
                  p.normals, p.sh_objs, p.dirs, p.alpha, p.depth, img.accum_alpha, img.n_contrib, p.dL_dpix, p.acc, abort_flag
@@ -652,6 +671,19 @@ int vcr_launch_render_backward(const BwdParams& p, GeomState& g, BinningState& b
         }
 #undef RB2_ARGS
         VCR_LAUNCH_CHECK("render_backward2_kernel");
+        return 0;
+    }
+    if (p.variant & 2) {
+        if (p.dirs) {
+            const size_t sm = 2 * sizeof(RbStage<true>);
+            if (p.sh_objs) render_backward_kernel<true, true, true><<<grid, 256, sm, s>>>(RB_ARGS);
+            else render_backward_kernel<true, false, true><<<grid, 256, sm, s>>>(RB_ARGS);
+        } else {
+            const size_t sm = 2 * sizeof(RbStage<false>);
+            if (p.sh_objs) render_backward_kernel<false, true, true><<<grid, 256, sm, s>>>(RB_ARGS);
+            else render_backward_kernel<false, false, true><<<grid, 256, sm, s>>>(RB_ARGS);
+        }
+        VCR_LAUNCH_CHECK("render_backward_kernel (depth2)");
         return 0;
     }
     if (p.dirs) {

@@ -42,8 +42,17 @@ struct RfStage {                       // one staging buffer
 static unsigned long long* g_pair_counters = nullptr;
 extern "C" int vcr_pair_counters(unsigned long long* counters_device) { g_pair_counters = counters_device; return 0; }
 
-template <int MODE, bool HAS_DIRS, bool HAS_OBJ, bool STATS = false>
-__global__ void __launch_bounds__(256, 4) render_forward_kernel(
+// VAR: the reference's compile-time variants (DGR/cuda_rasterizer/config.h:17-18) as a template parameter — bit 0: NUM_DIST = 1
+// (depth-distortion channel, forward.cu:400-412, 464-472), bit 1: NUM_DEPTH2 = 2 (sums of NDC depth and its square over the
+// inside Gaussians, forward.cu:426-430, 473-476).  Both write from channel 10 on (DISTORTION_OFFSET == DEPTH2_OFFSET,
+// auxiliary.h:25-26), so with both set the distortion value is overwritten, as in the reference.
+__device__ __forceinline__ float vcr_depth_ndc(const float depth) {
+    // (FAR_PLANE * depth - FAR_PLANE * NEAR_PLANE) / ((FAR_PLANE - NEAR_PLANE) * depth): the macros are double literals (auxiliary.h:30-31)
+    return (float)((100.0 * (double)depth - 100.0 * 0.2) / ((100.0 - 0.2) * (double)depth));
+}
+
+template <int MODE, bool HAS_DIRS, bool HAS_OBJ, bool STATS = false, int VAR = 0>
+__global__ void __launch_bounds__(256, VAR ? 3 : 4) render_forward_kernel(
     const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order, int gx, const uint32_t* __restrict__ point_list, int W, int H,
     const float2* __restrict__ means2D, const float* __restrict__ xyz_view, const float* __restrict__ features,
     const float* __restrict__ depths, const float* __restrict__ normals, const float* __restrict__ obj,
@@ -118,6 +127,7 @@ __global__ void __launch_bounds__(256, 4) render_forward_kernel(
     float C[3] = {0.f, 0.f, 0.f};
     float weight = 1e-10f;  // reference quirk: alpha output starts at 1e-10 (forward.cu:326)
     float D = 0.f, N[3] = {0.f, 0.f, 0.f}, O[2] = {0.f, 0.f};
+    float dist1 = 0.f, dist2 = 0.f, distortion = 0.f;       // VAR only
 
     if (rounds > 0) stage(0, 0);
     __syncthreads();
@@ -187,11 +197,20 @@ __global__ void __launch_bounds__(256, 4) render_forward_kernel(
                     C[0] += col.x * alpha * T; C[1] += col.y * alpha * T; C[2] += col.z * alpha * T;
                 } else {
                     const float w = alpha * T;
+                    if (VAR & 1) {          // distortion loss of 2DGS (forward.cu:400-412)
+                        const float dn = vcr_depth_ndc(depth);
+                        const float A = 1 - T;
+                        const float error = dn * dn * A + dist2 - 2 * dn * dist1;
+                        distortion += error * w;
+                        dist1 += dn * w;
+                        dist2 += dn * dn * w;
+                    }
                     C[0] = __fmaf_rn(col.x, w, C[0]); C[1] = __fmaf_rn(col.y, w, C[1]); C[2] = __fmaf_rn(col.z, w, C[2]);
                     if (HAS_OBJ) { O[0] = __fmaf_rn(nrm.w, w, O[0]); O[1] = __fmaf_rn(col.w, w, O[1]); }
                     weight += w;
                     if (idi & 1u) {
                         D = __fmaf_rn(depth, w, D);
+                        if (VAR & 2) { const float dn = vcr_depth_ndc(depth); dist1 += dn * w; dist2 += dn * dn * w; }
                         N[0] = __fmaf_rn(nrm.x, w, N[0]); N[1] = __fmaf_rn(nrm.y, w, N[1]); N[2] = __fmaf_rn(nrm.z, w, N[2]);
                     }
                 }
@@ -225,6 +244,9 @@ __global__ void __launch_bounds__(256, 4) render_forward_kernel(
             // the reference leaves the semantic channels at their zero initialisation when there are none
             out_color[(VCR_OBJECT_OFFSET + 0) * HW + pix_id] = HAS_OBJ ? O[0] : 0.f;
             out_color[(VCR_OBJECT_OFFSET + 1) * HW + pix_id] = HAS_OBJ ? O[1] : 0.f;
+            if (VAR & 1) out_color[VCR_OUT_CH * HW + pix_id] = (float)((double)distortion / ((double)((1 - T) * (1 - T)) + 1e-7));
+            if (VAR & 2) { out_color[VCR_OUT_CH * HW + pix_id] = dist1; out_color[(VCR_OUT_CH + 1) * HW + pix_id] = dist2; }
+            if (VAR == 3) out_color[(VCR_OUT_CH + 2) * HW + pix_id] = 0.f;     // the reference's 13th channel stays at its zero fill
         }
     }
 }
@@ -447,6 +469,22 @@ int vcr_launch_render_forward(const FwdParams& p, GeomState& g, BinningState& b,
     const unsigned int* abort_flag = vcr_radix_abort_flag();
     if (!abort_flag) { vcr_set_error("cannot resolve the sort status flag on this device"); return 1; }
     VcrProfScope prof(VCR_K_RENDER_FWD, s);
+    if (p.variant) {          // distortion / depth-variance channels: the one-pixel kernel carries the variants
+#define RFV_ARGS img.ranges, img.tile_order, p.gx, b.point_list, p.W, p.H, g.means2D, g.xyz_view, feat, g.depths, p.normals, p.sh_objs, p.dirs, \
+                 g.conic_opacity, p.inside, p.background, img.accum_alpha, img.n_contrib, p.out_color, nullptr, nullptr, abort_flag
+#define RFV_LAUNCH(V_)                                                                                              \
+        do {                                                                                                        \
+            if (p.dirs) { if (p.sh_objs) render_forward_kernel<0, true, true, false, V_><<<grid, 256, 0, s>>>(RFV_ARGS);   \
+                          else render_forward_kernel<0, true, false, false, V_><<<grid, 256, 0, s>>>(RFV_ARGS); }          \
+            else { if (p.sh_objs) render_forward_kernel<0, false, true, false, V_><<<grid, 256, 0, s>>>(RFV_ARGS);         \
+                   else render_forward_kernel<0, false, false, false, V_><<<grid, 256, 0, s>>>(RFV_ARGS); }                \
+        } while (0)
+        if (p.variant == 1) RFV_LAUNCH(1); else if (p.variant == 2) RFV_LAUNCH(2); else RFV_LAUNCH(3);
+#undef RFV_LAUNCH
+#undef RFV_ARGS
+        VCR_LAUNCH_CHECK("render_forward_kernel (variant)");
+        return 0;
+    }
     if (g_render_version == 2) {
 #define RF2_ARGS img.ranges, img.tile_order, p.gx, b.point_list, p.W, p.H, g.means2D, g.xyz_view, feat, g.depths, p.normals, p.sh_objs, p.dirs, \
                  g.conic_opacity, p.inside, p.background, img.accum_alpha, img.n_contrib, p.out_color, abort_flag, g_pair_counters

@@ -20,7 +20,22 @@ import vcr_native as _n
 _LAST_NUM_RENDERED = 0
 NUM_CHANNELS = 3
 NUM_OBJECTS = 2
-OUTPUT_CHANNELS = 3 + 1 + 3 + 1 + NUM_OBJECTS  # DGR/cuda_rasterizer/auxiliary.h:28 with NUM_DIST = NUM_DEPTH2 = 0
+NUM_DIST = 0        # DGR/cuda_rasterizer/config.h:17
+NUM_DEPTH2 = 0      # DGR/cuda_rasterizer/config.h:18
+OUTPUT_CHANNELS = 3 + 1 + 3 + 1 + NUM_OBJECTS + NUM_DIST + NUM_DEPTH2  # DGR/cuda_rasterizer/auxiliary.h:28
+
+
+def set_variant(num_dist=0, num_depth2=0):
+    """What editing NUM_DIST / NUM_DEPTH2 in cuda_rasterizer/config.h and reinstalling does for the reference
+    (README.md:150-155), as a process-wide setting: num_dist in (0, 1) adds the depth-distortion channel, num_depth2 in (0, 2)
+    the two NDC-depth sums that render() turns into `depth_var` (gaussian_renderer/__init__.py:154-158).  The output map of
+    f_count = 0 then has OUTPUT_CHANNELS = 10 + num_dist + num_depth2 channels.  Returns OUTPUT_CHANNELS."""
+    global NUM_DIST, NUM_DEPTH2, OUTPUT_CHANNELS
+    if num_dist not in (0, 1) or num_depth2 not in (0, 2):
+        raise ValueError("NUM_DIST must be 0 or 1 and NUM_DEPTH2 0 or 2")
+    NUM_DIST, NUM_DEPTH2 = int(num_dist), int(num_depth2)
+    OUTPUT_CHANNELS = int(_n.vcr_variant_channels(NUM_DIST, NUM_DEPTH2))
+    return OUTPUT_CHANNELS
 
 
 def cpu_deep_copy_tuple(input_tuple):
@@ -99,6 +114,12 @@ def rasterize_gaussians(means3D, means2D, means2D_densify, sh, colors_precomp, n
     raise ValueError(f"unknown f_count {raster_settings.f_count}")
 
 
+def _forward_call(args):
+    if NUM_DIST or NUM_DEPTH2:
+        return _n.vcr_rasterize_forward_variant(NUM_DIST, NUM_DEPTH2, *args)
+    return _n.vcr_rasterize_forward(*args)
+
+
 class _RasterizeGaussians(torch.autograd.Function):
     @staticmethod
     def forward(ctx, means3D, means2D, means2D_densify, sh, colors_precomp, normals_precomp, semantics_precomp, opacities,
@@ -138,19 +159,20 @@ class _RasterizeGaussians(torch.autograd.Function):
                                                 rs.projmatrix, dirs, rs.tanfovx, rs.tanfovy, rs.image_height, rs.image_width,
                                                 sh, rs.sh_degree, rs.campos, rs.prefiltered, inside, rs.debug))
                 try:
-                    _n.check(_n.vcr_rasterize_forward(*args), "rasterize_gaussians")
+                    _n.check(_forward_call(args), "rasterize_gaussians")
                 except Exception as ex:
                     torch.save(cpu_args, "snapshot_fw.dump")
                     print("\nAn error occured in forward. Please forward snapshot_fw.dump for debugging.")
                     raise ex
             else:
-                _n.check(_n.vcr_rasterize_forward(*args), "rasterize_gaussians")
+                _n.check(_forward_call(args), "rasterize_gaussians")
             num_rendered = n_host.value
             global _LAST_NUM_RENDERED
             _LAST_NUM_RENDERED = num_rendered  # bench.py reads this to report R
         geomBuffer, binningBuffer, imgBuffer = bufs.get("geom"), bufs.get("binning"), bufs.get("img")
         ctx.raster_settings = rs
         ctx.num_rendered = num_rendered
+        ctx.variant = (NUM_DIST, NUM_DEPTH2)
         # Optional zero-copy gradient destinations (vcr_view_parallel.GaussianBucket): a parameter may carry a
         # `_vcr_grad_out` tensor; the backward kernel then writes that gradient straight into it (every element is
         # written) and autograd adopts a view of it as `.grad` instead of allocating + accumulating.
@@ -212,7 +234,12 @@ class _RasterizeGaussians(torch.autograd.Function):
                     g_means2D_densify.data_ptr(), g_opacity.data_ptr(), _n.ptr(g_colors), g_normals.data_ptr(),
                     _n.ptr(g_objects), g_means3D.data_ptr(), _n.ptr(g_cov3D), _n.ptr(g_sh), g_scales.data_ptr(),
                     g_rot.data_ptr(), _n.ptr(inside.contiguous() if inside is not None else None), scratch.data_ptr(), int(bool(rs.debug)), _stream())
-            if rs.debug:
+            variant = getattr(ctx, "variant", (0, 0))
+            if variant != (0, 0):
+                if grad_c.shape[0] != _n.vcr_variant_channels(*variant):
+                    raise RuntimeError("gradient of the output map has the wrong number of channels for this variant")
+                _n.check(_n.vcr_rasterize_backward_variant(variant[0], variant[1], *args), "rasterize_gaussians_backward")
+            elif rs.debug:
                 cpu_args = cpu_deep_copy_tuple((rs.bg, means3D, radii, colors_precomp, normals_precomp, semantics_precomp, scales,
                                                 rotations, rs.scale_modifier, cov3Ds_precomp, rs.viewmatrix, rs.projmatrix, dirs,
                                                 rs.tanfovx, rs.tanfovy, grad_color, sh, rs.sh_degree, rs.campos, geomBuffer,

@@ -53,6 +53,10 @@ vcr_rasterize_backward = _sig(
      c_float, c_float, P_, P_, P_, P_, P_,
      P_, P_, P_, P_, P_, P_, P_, P_, P_, P_, P_, P_, P_, c_int, c_void_p])
 
+vcr_variant_channels = _sig("vcr_variant_channels", c_int, [c_int, c_int])
+vcr_rasterize_forward_variant = _sig("vcr_rasterize_forward_variant", c_int, [c_int, c_int] + list(vcr_rasterize_forward.argtypes))
+vcr_rasterize_backward_variant = _sig("vcr_rasterize_backward_variant", c_int, [c_int, c_int] + list(vcr_rasterize_backward.argtypes))
+
 CHUNK_FN = ctypes.CFUNCTYPE(None, c_void_p, c_int, c_int, c_int)   # (user, chunk, first_gaussian, n_gaussians)
 vcr_rasterize_backward_chunked = _sig(
     "vcr_rasterize_backward_chunked", c_int,
@@ -165,7 +169,7 @@ DECLARED_SYMBOLS = [
     "vcr_knn_noalloc_max_points", "vcr_dist2_knn3_noalloc", "vcr_view_loss_forward", "vcr_view_loss_backward",
     "vcr_profile_enable", "vcr_profile_kernel_count", "vcr_profile_kernel_name", "vcr_profile_read",
     "vcr_rasterize_backward_chunked", "vcr_densify_stats_accumulate", "vcr_multimem_allreduce_sum", "vcr_prologue_forward", "vcr_prologue_backward", "vcr_ssim_forward", "vcr_ssim_backward", "vcr_adam_step", "vcr_view_loss_total", "vcr_binning_reference_lists", "vcr_compact_scratch_bytes", "vcr_compact_rows", "vcr_sh_grad_from_colors", "vcr_multimem_exchange",
-    "vcr_pair_counters", "vcr_debug_radix_fault", "vcr_debug_render_version", "vcr_densify_scratch_bytes", "vcr_densify_decide", "vcr_densify_fill",
+    "vcr_variant_channels", "vcr_rasterize_forward_variant", "vcr_rasterize_backward_variant", "vcr_pair_counters", "vcr_debug_radix_fault", "vcr_debug_render_version", "vcr_densify_scratch_bytes", "vcr_densify_decide", "vcr_densify_fill",
 ]
 
 
