@@ -608,6 +608,7 @@ def scene_stats(stepper, args, clocks):
     return {"P": P, "P_visible": Pv, "R": R, "R_per_P": R / max(P, 1), "pixels": args.width * args.height,
             "tiles": ((args.width + 15) // 16) * ((args.height + 15) // 16),
             "sum_n_contrib": c[2], "K_e": c[0], "K_c": c[1], "warp_candidates": c[3],
+            "forward_longest_block_cycles": c[4], "forward_sum_block_cycles": c[5],
             "mean_contributors_per_pixel": c[1] / max(args.width * args.height, 1)}
 
 

@@ -290,6 +290,7 @@ __global__ void __launch_bounds__(RF2_THREADS, VCR_RF2_MINBLOCKS) render_forward
     float* __restrict__ out_color, const unsigned int* __restrict__ abort_flag, unsigned long long* __restrict__ pair_counters) {
     __shared__ Rf2Stage s_stage[2];
     unsigned int st_ke = 0, st_kc = 0, st_cand = 0;
+    const long long st_t0 = STATS ? clock64() : 0;
     if (__ldg(abort_flag)) return;      // the sort of this view failed (binning.cu): the lists are garbage, leave the outputs unwritten
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -435,6 +436,10 @@ __global__ void __launch_bounds__(RF2_THREADS, VCR_RF2_MINBLOCKS) render_forward
         if (lane == 0) {
             atomicAdd(pair_counters + 0, (unsigned long long)ke); atomicAdd(pair_counters + 1, (unsigned long long)kc);
             atomicAdd(pair_counters + 2, (unsigned long long)nc); atomicAdd(pair_counters + 3, (unsigned long long)st_cand);
+        }
+        if (tid == 0) {         // [4] longest block in SM cycles, [5] sum over blocks: is the kernel bound by its longest tile?
+            const unsigned long long dt = (unsigned long long)(clock64() - st_t0);
+            atomicMax(pair_counters + 4, dt); atomicAdd(pair_counters + 5, dt);
         }
     }
     const float bg0 = __ldg(bg), bg1 = __ldg(bg + 1), bg2 = __ldg(bg + 2);
