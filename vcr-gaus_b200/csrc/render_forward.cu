@@ -271,6 +271,9 @@ __global__ void __launch_bounds__(256, VAR ? 3 : 4) render_forward_kernel(
 #ifndef VCR_RF2_MINBLOCKS
 #define VCR_RF2_MINBLOCKS 7
 #endif
+#ifndef VCR_RF2_WAY
+#define VCR_RF2_WAY 2          // candidates evaluated together per loop iteration
+#endif
 
 struct Rf2Stage {
     StagedGeo geo[RF2_BATCH];
@@ -353,6 +356,62 @@ __global__ void __launch_bounds__(RF2_THREADS, VCR_RF2_MINBLOCKS) render_forward
     float2 weight = make_float2(1e-10f, 1e-10f);  // reference quirk: alpha output starts at 1e-10 (forward.cu:326)
     float2 D = C0, N0 = C0, N1 = C0, N2 = C0, O0 = C0, O1 = C0;
 
+    // One candidate in two halves. eval: everything that does not depend on the running transmittance (two shared-memory
+    // reads, the quadratic form, expf). commit: the tests against `alive` and T, and the accumulation, in list order.
+    auto eval = [&](const Rf2Stage& st, const int j, uint32_t& pos) -> float2 {
+        const float4 g0 = *reinterpret_cast<const float4*>(&st.geo[j]);        // x, y, ca, cb
+        const float2 g1 = *reinterpret_cast<const float2*>(&st.geo[j].cc);     // cc, op
+        const float dx = g0.x - pfx;
+        const float2 dy = vcr_add2(vcr_bcast2(g0.y), npfy);
+        // power = -0.5f*(ca*dx*dx + cc*dy*dy) - cb*dx*dy, contracted exactly like the reference build:
+        //   q = fma(fmul(ca,dx), dx, fmul(fmul(cc,dy), dy));  power = fma(q, -0.5, -fmul(fmul(cb,dx), dy))
+        const float adx = __fmul_rn(g0.z, dx), nbdx = -__fmul_rn(g0.w, dx);
+        const float2 q = vcr_fma2(vcr_bcast2(adx), vcr_bcast2(dx), vcr_mul2(vcr_mul2(vcr_bcast2(g1.x), dy), dy));
+        const float2 power = vcr_fma2(q, vcr_bcast2(-0.5f), vcr_mul2(vcr_bcast2(nbdx), dy));
+        // the reference tests depth before alpha (forward.cu:382-391); both are side-effect-free `continue`s,
+        // so alpha goes first here: most rejected pairs fail it, and it spares them the IEEE division
+        // power > 0 rejects the pair (forward.cu:386): two bits of `pos` carry that to commit, the alpha chain stays branch-free
+        pos = (power.x > 0.0f ? 1u : 0u) | (power.y > 0.0f ? 2u : 0u);
+        return make_float2(fminf(0.99f, g1.y * expf(power.x)), fminf(0.99f, g1.y * expf(power.y)));
+    };
+    auto commit = [&](const Rf2Stage& st, const int i, const int j, const float2 al, const uint32_t pos) {
+        const float a0 = al.x, a1 = al.y;
+        if (STATS) st_ke += __popc(alive);
+        bool ok0 = (alive & ~pos & 1u) && !(a0 < 1.0f / 255.0f);
+        bool ok1 = (alive & ~pos & 2u) && !(a1 < 1.0f / 255.0f);
+        if (!(ok0 || ok1)) return;
+        const float2 g1 = *reinterpret_cast<const float2*>(&st.geo[j].nx);     // nx, id_inside
+        const float4 nrm = st.nrm[j];
+        float2 depth;
+        if (HAS_DIRS) {
+            // t = nx / dot(n, dir) with the dot product in the reference's order: n.y*d.y, then n.x*d.x, then n.z*d.z
+            const float2 pd = vcr_fma2(vcr_bcast2(nrm.z), dirz, vcr_fma2(vcr_bcast2(nrm.x), dirx, vcr_mul2(vcr_bcast2(nrm.y), diry)));
+            depth = vcr_mul2(make_float2(__fdiv_rn(g1.x, pd.x), __fdiv_rn(g1.x, pd.y)), dirz);
+        } else {
+            depth = vcr_bcast2(g1.x);
+        }
+        ok0 = ok0 && !(depth.x < 0.2f);  // == (double)depth <= 0.2, forward.cu:382
+        ok1 = ok1 && !(depth.y < 0.2f);
+        const float2 test_T = vcr_mul2(T, make_float2(1 - a0, 1 - a1));
+        if (ok0 && test_T.x < 0.0001f) { alive &= ~1u; ok0 = false; }
+        if (ok1 && test_T.y < 0.0001f) { alive &= ~2u; ok1 = false; }
+        if (!(ok0 || ok1)) return;
+        const float4 col = st.col[j];
+        const uint32_t idi = __float_as_uint(g1.y);
+        const float2 w = make_float2(ok0 ? __fmul_rn(a0, T.x) : 0.f, ok1 ? __fmul_rn(a1, T.y) : 0.f);
+        C0 = vcr_fma2(vcr_bcast2(col.x), w, C0); C1 = vcr_fma2(vcr_bcast2(col.y), w, C1); C2 = vcr_fma2(vcr_bcast2(col.z), w, C2);
+        if (HAS_OBJ) { O0 = vcr_fma2(vcr_bcast2(nrm.w), w, O0); O1 = vcr_fma2(vcr_bcast2(col.w), w, O1); }
+        weight = vcr_add2(weight, w);
+        if (idi & 1u) {
+            D = vcr_fma2(make_float2(ok0 ? depth.x : 0.f, ok1 ? depth.y : 0.f), w, D);
+            N0 = vcr_fma2(vcr_bcast2(nrm.x), w, N0); N1 = vcr_fma2(vcr_bcast2(nrm.y), w, N1); N2 = vcr_fma2(vcr_bcast2(nrm.z), w, N2);
+        }
+        const uint32_t here = (uint32_t)(i * RF2_BATCH + j + 1);
+        if (ok0) { T.x = test_T.x; last0 = here; }
+        if (ok1) { T.y = test_T.y; last1 = here; }
+        if (STATS) st_kc += (ok0 ? 1u : 0u) + (ok1 ? 1u : 0u);
+    };
+
     if (rounds > 0) stage(0, 0);
     __syncthreads();
     for (int i = 0; i < rounds; i++) {
@@ -373,57 +432,27 @@ __global__ void __launch_bounds__(RF2_THREADS, VCR_RF2_MINBLOCKS) render_forward
             }
             uint32_t m = __ballot_sync(0xffffffffu, hit);
             while (m) {
-                // m is warp-uniform, so every lane passes here once per candidate: a safe place to vote
+                // m is warp-uniform, so every lane passes here once per candidate group: a safe place to vote
                 if (__all_sync(0xffffffffu, alive == 0u)) { warp_done = true; break; }
-                const int j = k * 32 + __ffs(m) - 1;
-                m &= m - 1;
-                if (STATS && lane == 0) st_cand++;
+                // VCR_RF2_WAY candidates per iteration: their alpha chains are independent of T and of each other, so they are
+                // issued together (the kernel is as long as its longest tile, whose four warps are latency-bound), then
+                // committed one after the other, in list order.
+                int js[VCR_RF2_WAY];
+                float2 als[VCR_RF2_WAY];
+                uint32_t pos[VCR_RF2_WAY];
+                int n = 0;
+#pragma unroll
+                for (int w = 0; w < VCR_RF2_WAY; w++) {
+                    if (m) { js[w] = k * 32 + __ffs(m) - 1; m &= m - 1; n = w + 1; }
+                    else js[w] = js[0];
+                }
+                if (STATS && lane == 0) st_cand += (unsigned int)n;
                 if (alive == 0u) continue;
-                if (STATS) st_ke += __popc(alive);
-                const float4 g0 = *reinterpret_cast<const float4*>(&st.geo[j]);        // x, y, ca, cb
-                const float4 g1 = *reinterpret_cast<const float4*>(&st.geo[j].cc);     // cc, op, nx, id_inside
-                const float dx = g0.x - pfx;
-                const float2 dy = vcr_add2(vcr_bcast2(g0.y), npfy);
-                // power = -0.5f*(ca*dx*dx + cc*dy*dy) - cb*dx*dy, contracted exactly like the reference build:
-                //   q = fma(fmul(ca,dx), dx, fmul(fmul(cc,dy), dy));  power = fma(q, -0.5, -fmul(fmul(cb,dx), dy))
-                const float adx = __fmul_rn(g0.z, dx), nbdx = -__fmul_rn(g0.w, dx);
-                const float2 q = vcr_fma2(vcr_bcast2(adx), vcr_bcast2(dx), vcr_mul2(vcr_mul2(vcr_bcast2(g1.x), dy), dy));
-                const float2 power = vcr_fma2(q, vcr_bcast2(-0.5f), vcr_mul2(vcr_bcast2(nbdx), dy));
-                // the reference tests depth before alpha (forward.cu:382-391); both are side-effect-free `continue`s,
-                // so alpha goes first here: most rejected pairs fail it, and it spares them the IEEE division
-                const float a0 = fminf(0.99f, g1.y * expf(power.x)), a1 = fminf(0.99f, g1.y * expf(power.y));
-                bool ok0 = (alive & 1u) && !(power.x > 0.0f) && !(a0 < 1.0f / 255.0f);
-                bool ok1 = (alive & 2u) && !(power.y > 0.0f) && !(a1 < 1.0f / 255.0f);
-                if (!(ok0 || ok1)) continue;
-                const float4 nrm = st.nrm[j];
-                float2 depth;
-                if (HAS_DIRS) {
-                    // t = nx / dot(n, dir) with the dot product in the reference's order: n.y*d.y, then n.x*d.x, then n.z*d.z
-                    const float2 pd = vcr_fma2(vcr_bcast2(nrm.z), dirz, vcr_fma2(vcr_bcast2(nrm.x), dirx, vcr_mul2(vcr_bcast2(nrm.y), diry)));
-                    depth = vcr_mul2(make_float2(__fdiv_rn(g1.z, pd.x), __fdiv_rn(g1.z, pd.y)), dirz);
-                } else {
-                    depth = vcr_bcast2(g1.z);
-                }
-                ok0 = ok0 && !(depth.x < 0.2f);  // == (double)depth <= 0.2, forward.cu:382
-                ok1 = ok1 && !(depth.y < 0.2f);
-                const float2 test_T = vcr_mul2(T, make_float2(1 - a0, 1 - a1));
-                if (ok0 && test_T.x < 0.0001f) { alive &= ~1u; ok0 = false; }
-                if (ok1 && test_T.y < 0.0001f) { alive &= ~2u; ok1 = false; }
-                if (!(ok0 || ok1)) continue;
-                const float4 col = st.col[j];
-                const uint32_t idi = __float_as_uint(g1.w);
-                const float2 w = make_float2(ok0 ? __fmul_rn(a0, T.x) : 0.f, ok1 ? __fmul_rn(a1, T.y) : 0.f);
-                C0 = vcr_fma2(vcr_bcast2(col.x), w, C0); C1 = vcr_fma2(vcr_bcast2(col.y), w, C1); C2 = vcr_fma2(vcr_bcast2(col.z), w, C2);
-                if (HAS_OBJ) { O0 = vcr_fma2(vcr_bcast2(nrm.w), w, O0); O1 = vcr_fma2(vcr_bcast2(col.w), w, O1); }
-                weight = vcr_add2(weight, w);
-                if (idi & 1u) {
-                    D = vcr_fma2(make_float2(ok0 ? depth.x : 0.f, ok1 ? depth.y : 0.f), w, D);
-                    N0 = vcr_fma2(vcr_bcast2(nrm.x), w, N0); N1 = vcr_fma2(vcr_bcast2(nrm.y), w, N1); N2 = vcr_fma2(vcr_bcast2(nrm.z), w, N2);
-                }
-                const uint32_t here = (uint32_t)(i * RF2_BATCH + j + 1);
-                if (ok0) { T.x = test_T.x; last0 = here; }
-                if (ok1) { T.y = test_T.y; last1 = here; }
-                if (STATS) st_kc += (ok0 ? 1u : 0u) + (ok1 ? 1u : 0u);
+#pragma unroll
+                for (int w = 0; w < VCR_RF2_WAY; w++) als[w] = eval(st, js[w], pos[w]);
+#pragma unroll
+                for (int w = 0; w < VCR_RF2_WAY; w++)
+                    if (w < n && alive != 0u) commit(st, i, js[w], als[w], pos[w]);
             }
         }
         // one barrier per batch: publishes batch i+1, frees buffer `buf` for batch i+2, and votes on completion
