@@ -590,16 +590,23 @@ def scene_stats(stepper, args, clocks):
                                        bg=v["bg"].to(dev), scale_modifier=1.0, viewmatrix=v["viewmatrix"].to(dev),
                                        projmatrix=v["projmatrix"].to(dev), sh_degree=3, campos=v["campos"].to(dev),
                                        prefiltered=False, debug=False, f_count=0)
+    def render():
+        with torch.no_grad():
+            res = GaussianRasterizer(rs)(means3D=p["means3D"].detach(), means2D=None, opacities=p["opacities"].detach(),
+                                         shs=p["shs"].detach(), normals_precomp=stepper.normals[0].detach(),
+                                         scales=p["scales"].detach(), rotations=p["rotations"].detach(), dirs=stepper.dirs)
+        torch.cuda.synchronize(dev)
+        return res
+
     counters = torch.zeros(8, dtype=torch.int64, device=dev)
     N.check(N.vcr_pair_counters(counters.data_ptr()), "pair_counters")
     try:
-        with torch.no_grad():
-            out, radii = GaussianRasterizer(rs)(means3D=p["means3D"].detach(), means2D=None, opacities=p["opacities"].detach(),
-                                                shs=p["shs"].detach(), normals_precomp=stepper.normals[0].detach(),
-                                                scales=p["scales"].detach(), rotations=p["rotations"].detach(), dirs=stepper.dirs)
-        torch.cuda.synchronize(dev)
+        out, radii = render()
     finally:
         N.check(N.vcr_pair_counters(None), "pair_counters")
+    timeline = None
+    if os.environ.get("VCR_BENCH_TIMELINE"):
+        timeline = block_timeline(render, ((args.width + 15) // 16) * ((args.height + 15) // 16), dev, os.environ["VCR_BENCH_TIMELINE"])
     N.profile_read(reset=True)
     c = counters.cpu().tolist()
     P = int(radii.numel())
@@ -609,7 +616,45 @@ def scene_stats(stepper, args, clocks):
             "tiles": ((args.width + 15) // 16) * ((args.height + 15) // 16),
             "sum_n_contrib": c[2], "K_e": c[0], "K_c": c[1], "warp_candidates": c[3],
             "forward_longest_block_cycles": c[4], "forward_sum_block_cycles": c[5],
-            "mean_contributors_per_pixel": c[1] / max(args.width * args.height, 1)}
+            "mean_contributors_per_pixel": c[1] / max(args.width * args.height, 1), "forward_block_timeline": timeline}
+
+
+def block_timeline(render, blocks, dev, path):
+    """Start / end of every block of the forward compositing kernel (vcr_debug_block_timeline): is the kernel as long as its
+    longest tile?  Two passes: the production kernel (times), then the instrumented one (candidates per warp).  Writes the raw
+    tables to `path` (.npz) and returns the summary."""
+    import numpy as np
+    import vcr_native as N
+
+    def run(instrumented):
+        buf = torch.zeros(8 * blocks, dtype=torch.int64, device=dev)
+        cnt = torch.zeros(8, dtype=torch.int64, device=dev)
+        render()
+        if instrumented:
+            N.check(N.vcr_pair_counters(cnt.data_ptr()), "pair_counters")
+        N.check(N.vcr_debug_block_timeline(buf.data_ptr()), "block_timeline")
+        try:
+            render()
+        finally:
+            N.check(N.vcr_debug_block_timeline(None), "block_timeline")
+            N.check(N.vcr_pair_counters(None), "pair_counters")
+        t = buf.cpu().numpy().reshape(blocks, 8)
+        return t
+
+    t, ti = run(False), run(True)
+    np.savez(path, plain=t, instrumented=ti)
+    t0 = int(t[:, 0].min())
+    start, end = (t[:, 0] - t0) * 1e-3, (t[:, 1] - t0) * 1e-3        # us
+    dur = end - start
+    order = np.argsort(-dur)[:8]
+    ends = np.sort(end)
+    n = len(t)
+    return {"kernel_span_us": float(end.max()), "blocks": int(n), "sum_block_us": float(dur.sum()),
+            "all_blocks_started_by_us": float(start.max()),
+            "blocks_done_at_us": {q: float(ends[min(n - 1, int(q * n))]) for q in (0.5, 0.9, 0.99, 0.999)},
+            "longest_blocks": [{"block": int(b), "tile": int(t[b, 2] >> 32), "sm": int(t[b, 2] & 0xffffffff), "list": int(t[b, 3]),
+                                "warp_candidates": [int(x) for x in ti[b, 4:8]] if b < len(ti) else None,
+                                "start_us": float(start[b]), "end_us": float(end[b])} for b in order]}
 
 
 def roofline_entry(dom, stats, args, hbm_peak, peak_src, clocks):

@@ -459,6 +459,12 @@ int vcr_profile_read(float* ms, long long* timed, long long* launches, int reset
  * contributed, [2] sum over pixels of n_contrib, [3] (warp, Gaussian) candidates after culling.  NULL switches it off.
  * Process-wide, not thread-safe; meant for bench.py outside its timed regions. */
 int vcr_pair_counters(unsigned long long* counters_device);
+/* Block timeline of the two-pixel forward compositing kernel (bench.py VCR_BENCH_TIMELINE; no counterpart in the reference).
+ * While a device array of 8 u64 per tile is registered, block b writes [8b] its start and [8b+1] its
+ * end (globaltimer, ns), [8b+2] = (tile << 32) | SM id, [8b+3] = its list length and, while vcr_pair_counters is
+ * registered too, [8b+4..7] = the candidates each of its warps evaluated.  NULL switches it off.  Process-wide, not
+ * thread-safe, never inside a timed region. */
+int vcr_debug_block_timeline(unsigned long long* timeline_device);
 /* Test hook for the sort's failure path (no counterpart in the reference, whose CUB sort cannot time out): with on != 0 every
  * multi-block radix pass is made to time out in its look-back (block 0 publishes nothing, 2000 polls).  The affected call
  * produces invalid instance lists; the NEXT vcr_rasterize_forward / _count / _visi_acc on the device (or the same call when

@@ -41,6 +41,16 @@ struct RfStage {                       // one staging buffer
 // contribute), sum(n_contrib) and the number of (warp, Gaussian) candidates.  The production instantiation has none of this.
 static unsigned long long* g_pair_counters = nullptr;
 extern "C" int vcr_pair_counters(unsigned long long* counters_device) { g_pair_counters = counters_device; return 0; }
+// Block timeline (bench.py VCR_BENCH_TIMELINE): while a device array of 8 u64 per tile is registered, every block of the
+// two-pixel forward writes [0] start, [1] end (globaltimer, ns), [2] tile << 32 | SM id, [3] list length and, in the
+// instrumented instantiation, [4..7] the candidates each warp evaluated. One uniform test per block when switched off.
+static unsigned long long* g_block_timeline = nullptr;
+extern "C" int vcr_debug_block_timeline(unsigned long long* timeline_device) { g_block_timeline = timeline_device; return 0; }
+__device__ __forceinline__ unsigned long long vcr_globaltimer() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
 
 // VAR: the reference's compile-time variants (DGR/cuda_rasterizer/config.h:17-18) as a template parameter — bit 0: NUM_DIST = 1
 // (depth-distortion channel, forward.cu:400-412, 464-472), bit 1: NUM_DEPTH2 = 2 (sums of NDC depth and its square over the
@@ -290,8 +300,10 @@ __global__ void __launch_bounds__(RF2_THREADS, VCR_RF2_MINBLOCKS) render_forward
     const float* __restrict__ depths, const float* __restrict__ normals, const float* __restrict__ obj,
     const float* __restrict__ dirs, const float4* __restrict__ conic_opacity, const uint8_t* __restrict__ inside_gs,
     const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
-    float* __restrict__ out_color, const unsigned int* __restrict__ abort_flag, unsigned long long* __restrict__ pair_counters) {
+    float* __restrict__ out_color, const unsigned int* __restrict__ abort_flag, unsigned long long* __restrict__ pair_counters,
+    unsigned long long* __restrict__ timeline) {
     __shared__ Rf2Stage s_stage[2];
+    if (timeline && threadIdx.x == 0) timeline[8 * (size_t)blockIdx.x] = vcr_globaltimer();
     unsigned int st_ke = 0, st_kc = 0, st_cand = 0;
     const long long st_t0 = STATS ? clock64() : 0;
     if (__ldg(abort_flag)) return;      // the sort of this view failed (binning.cu): the lists are garbage, leave the outputs unwritten
@@ -490,6 +502,18 @@ __global__ void __launch_bounds__(RF2_THREADS, VCR_RF2_MINBLOCKS) render_forward
     };
     if (in0) write(pix0, T.x, last0, C0.x, C1.x, C2.x, weight.x, D.x, N0.x, N1.x, N2.x, O0.x, O1.x);
     if (in1) write(pix1, T.y, last1, C0.y, C1.y, C2.y, weight.y, D.y, N0.y, N1.y, N2.y, O0.y, O1.y);
+    if (timeline) {
+        __syncthreads();
+        unsigned long long* rec = timeline + 8 * (size_t)blockIdx.x;
+        if (tid == 0) {
+            unsigned int smid;
+            asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+            rec[1] = vcr_globaltimer();
+            rec[2] = ((unsigned long long)tile << 32) | smid;
+            rec[3] = (unsigned long long)(uint32_t)total;
+        }
+        if (STATS && lane == 0) rec[4 + warp] = st_cand;       // (warp, Gaussian) candidates after culling, per warp
+    }
 }
 
 // vcr_debug_render_version(1) selects the one-pixel-per-thread kernels (A/B measurements, tools/); 2 (default) = two pixels.
@@ -521,7 +545,7 @@ int vcr_launch_render_forward(const FwdParams& p, GeomState& g, BinningState& b,
     }
     if (g_render_version == 2) {
 #define RF2_ARGS img.ranges, img.tile_order, p.gx, b.point_list, p.W, p.H, g.means2D, g.xyz_view, feat, g.depths, p.normals, p.sh_objs, p.dirs, \
-                 g.conic_opacity, p.inside, p.background, img.accum_alpha, img.n_contrib, p.out_color, abort_flag, g_pair_counters
+                 g.conic_opacity, p.inside, p.background, img.accum_alpha, img.n_contrib, p.out_color, abort_flag, g_pair_counters, g_block_timeline
 #define RF2_LAUNCH(D_, O_)                                                                                   \
         do {                                                                                                 \
             if (g_pair_counters) render_forward2_kernel<D_, O_, true><<<grid, RF2_THREADS, 0, s>>>(RF2_ARGS); \

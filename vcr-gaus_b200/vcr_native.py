@@ -125,6 +125,7 @@ vcr_dist2_knn3_noalloc = _sig("vcr_dist2_knn3_noalloc", c_int, [c_int, P_, P_, c
 
 
 vcr_pair_counters = _sig("vcr_pair_counters", c_int, [P_])
+vcr_debug_block_timeline = _sig("vcr_debug_block_timeline", c_int, [P_])
 vcr_debug_radix_fault = _sig("vcr_debug_radix_fault", c_int, [c_int])
 vcr_debug_render_version = _sig("vcr_debug_render_version", c_int, [c_int])
 vcr_profile_enable = _sig("vcr_profile_enable", c_int, [c_int])
@@ -169,7 +170,7 @@ DECLARED_SYMBOLS = [
     "vcr_knn_noalloc_max_points", "vcr_dist2_knn3_noalloc", "vcr_view_loss_forward", "vcr_view_loss_backward",
     "vcr_profile_enable", "vcr_profile_kernel_count", "vcr_profile_kernel_name", "vcr_profile_read",
     "vcr_rasterize_backward_chunked", "vcr_densify_stats_accumulate", "vcr_multimem_allreduce_sum", "vcr_prologue_forward", "vcr_prologue_backward", "vcr_ssim_forward", "vcr_ssim_backward", "vcr_adam_step", "vcr_view_loss_total", "vcr_binning_reference_lists", "vcr_compact_scratch_bytes", "vcr_compact_rows", "vcr_sh_grad_from_colors", "vcr_multimem_exchange",
-    "vcr_variant_channels", "vcr_rasterize_forward_variant", "vcr_rasterize_backward_variant", "vcr_pair_counters", "vcr_debug_radix_fault", "vcr_debug_render_version", "vcr_densify_scratch_bytes", "vcr_densify_decide", "vcr_densify_fill",
+    "vcr_variant_channels", "vcr_rasterize_forward_variant", "vcr_rasterize_backward_variant", "vcr_pair_counters", "vcr_debug_block_timeline", "vcr_debug_radix_fault", "vcr_debug_render_version", "vcr_densify_scratch_bytes", "vcr_densify_decide", "vcr_densify_fill",
 ]
 
 
