@@ -372,6 +372,9 @@ struct Rb2Stage {
     StagedGeoB geo[RB2_BATCH];
     float4 box[RB2_BATCH];
     float2 ex[RB2_BATCH];
+#if VCR_QUAD
+    float exc[RB2_BATCH];             // 1 / conic.z for the column tests
+#endif
     float4 nrm[RB2_BATCH];            // normal.xyz, semantics[0]
     float4 col[RB2_BATCH];            // rgb, semantics[1]
     float4 xv[HAS_DIRS ? RB2_BATCH : 1];
@@ -394,15 +397,26 @@ __global__ void __launch_bounds__(RB2_THREADS, VCR_RB2_MINBLOCKS) render_backwar
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t tile = __ldg(tile_order + blockIdx.x);      // blocks take tiles longest-list first
     const uint32_t tile_x = tile % (uint32_t)gx, tile_y = tile / (uint32_t)gx;
+#if VCR_QUAD
+    // warp w owns the 8x8 quadrant (w & 1, w >> 1) of the tile; lane l the pixels (l & 7, 2 (l >> 3)) and the one below
+    const uint32_t strip_c = tile_x * VCR_TILE_X + 8 * (warp & 1), strip_r = tile_y * VCR_TILE_Y + 8 * (warp >> 1);
+    const uint32_t px = strip_c + (lane & 7);
+    const uint32_t py0 = strip_r + 2 * (lane >> 3), py1 = py0 + 1;
+#else
     const uint32_t px = tile_x * VCR_TILE_X + (lane & 15);
     const uint32_t py0 = tile_y * VCR_TILE_Y + 4 * warp + 2 * (lane >> 4), py1 = py0 + 1;
+#endif
     const bool in0 = px < (uint32_t)W && py0 < (uint32_t)H, in1 = px < (uint32_t)W && py1 < (uint32_t)H;
     const size_t HW = (size_t)H * W;
     const size_t pix0 = (size_t)W * py0 + px, pix1 = pix0 + (size_t)W;
     const float pfx = (float)px;
     const float2 npfy = make_float2(-(float)py0, -(float)py1);
+#if VCR_QUAD
+    const float strip_x0 = (float)strip_c, strip_x1 = strip_x0 + 7.0f, strip_y0 = (float)strip_r, strip_y1 = strip_y0 + 7.0f;
+#else
     const float strip_x0 = (float)(tile_x * VCR_TILE_X), strip_x1 = strip_x0 + (float)(VCR_TILE_X - 1);
     const float strip_y0 = (float)(tile_y * VCR_TILE_Y + 4 * warp), strip_y1 = strip_y0 + 3.0f;
+#endif
 
     const uint2 range = ranges[tile];
     const uint32_t lastc0 = in0 ? n_contrib[pix0] : 0u, lastc1 = in1 ? n_contrib[pix1] : 0u;
@@ -459,6 +473,9 @@ __global__ void __launch_bounds__(RB2_THREADS, VCR_RB2_MINBLOCKS) render_backwar
         sg.x = xy.x; sg.y = xy.y; sg.ca = co.x; sg.cb = co.y; sg.cc = co.z; sg.op = co.w;
         st.box[tid] = vcr_alpha_bbox(xy, co);
         st.ex[tid] = vcr_alpha_rowtest(co);
+#if VCR_QUAD
+        st.exc[tid] = 1.0f / co.z;      // only read where ex says the conic is sound
+#endif
         if (HAS_DIRS) {
             const float3 xv = make_float3(__ldg(xyz_view + 3 * (size_t)id), __ldg(xyz_view + 3 * (size_t)id + 1),
                                           __ldg(xyz_view + 3 * (size_t)id + 2));
@@ -494,7 +511,11 @@ __global__ void __launch_bounds__(RB2_THREADS, VCR_RB2_MINBLOCKS) render_backwar
                        bx.z <= strip_y1 && bx.w >= strip_y0;
             if (hit) {
                 const float4 gq = *reinterpret_cast<const float4*>(&st.geo[jj]);        // x, y, ca, cb
+                #if VCR_QUAD
+                hit = vcr_rect_may_contribute(gq.x, gq.y, gq.z, gq.w, st.geo[jj].cc, st.ex[jj], st.exc[jj], strip_x0, strip_x1, strip_y0, strip_y1);
+#else
                 hit = vcr_strip_may_contribute_rows<4>(gq.x, gq.y, gq.z, gq.w, st.geo[jj].cc, st.ex[jj], strip_x0, strip_x1, strip_y0);
+#endif
             }
             uint32_t m = __ballot_sync(0xffffffffu, hit);
             while (m) {
