@@ -26,6 +26,10 @@ for step in "$@"; do
         $CMD > $OUT/${TAG}_plain.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:render_ -s 30 -c 2 -f -o $OUT/${TAG}_render $CMD > $OUT/${TAG}_ncu.log 2>&1
         echo "[ncu_render] rc=$?" | tee -a $OUT/${TAG}_summary.txt; tail -3 $OUT/${TAG}_ncu.log
         unset VCR_BENCH_WARMUP_FLOOR ;;
+    launches) # per-launch durations of two steady-state steps (after the same command ran clean)
+        CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-full-step --no-profile"
+        $CMD > $OUT/${TAG}_plain.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $OUT/${TAG}_launch_list.csv $CMD > $OUT/${TAG}_ncu_list.log 2>&1
+        echo "[launches] rc=$?" | tee -a $OUT/${TAG}_summary.txt ;;
     ref)    run ref 600 python bench.py --impl reference --steps 30 --warmup 10; head -c 600 $OUT/${TAG}_ref.out; echo ;;
     A)      run A 300 python bench.py --config A --steps 50 --warmup 10; head -c 400 $OUT/${TAG}_A.out; echo ;;
     refA)   run refA 300 python bench.py --config A --impl reference --steps 50 --warmup 10; head -c 400 $OUT/${TAG}_refA.out; echo ;;
