@@ -627,7 +627,7 @@ def block_timeline(render, blocks, dev, path):
     import vcr_native as N
 
     def run(instrumented):
-        buf = torch.zeros(8 * blocks, dtype=torch.int64, device=dev)
+        buf = torch.zeros(16 * blocks, dtype=torch.int64, device=dev)
         cnt = torch.zeros(8, dtype=torch.int64, device=dev)
         render()
         if instrumented:
@@ -638,7 +638,7 @@ def block_timeline(render, blocks, dev, path):
         finally:
             N.check(N.vcr_debug_block_timeline(None), "block_timeline")
             N.check(N.vcr_pair_counters(None), "pair_counters")
-        t = buf.cpu().numpy().reshape(blocks, 8)
+        t = buf.cpu().numpy().reshape(blocks, 16)
         return t
 
     t, ti = run(False), run(True)

@@ -460,9 +460,10 @@ int vcr_profile_read(float* ms, long long* timed, long long* launches, int reset
  * Process-wide, not thread-safe; meant for bench.py outside its timed regions. */
 int vcr_pair_counters(unsigned long long* counters_device);
 /* Block timeline of the two-pixel forward compositing kernel (bench.py VCR_BENCH_TIMELINE; no counterpart in the reference).
- * While a device array of 8 u64 per tile is registered, block b writes [8b] its start and [8b+1] its
- * end (globaltimer, ns), [8b+2] = (tile << 32) | SM id, [8b+3] = its list length and, while vcr_pair_counters is
- * registered too, [8b+4..7] = the candidates each of its warps evaluated.  NULL switches it off.  Process-wide, not
+ * While a device array of 16 u64 per tile is registered, block b writes at 16b: [0] its start and [1] its end
+ * (globaltimer, ns), [2] = (tile << 32) | SM id, [3] = its list length and, while vcr_pair_counters is registered too,
+ * [4..7] = the candidates each of its warps evaluated, [8..11] = the cycles each warp waited at the per-batch barrier,
+ * [12] = the block's cycles.  NULL switches it off.  Process-wide, not
  * thread-safe, never inside a timed region. */
 int vcr_debug_block_timeline(unsigned long long* timeline_device);
 /* Test hook for the sort's failure path (no counterpart in the reference, whose CUB sort cannot time out): with on != 0 every

@@ -41,9 +41,9 @@ struct RfStage {                       // one staging buffer
 // contribute), sum(n_contrib) and the number of (warp, Gaussian) candidates.  The production instantiation has none of this.
 static unsigned long long* g_pair_counters = nullptr;
 extern "C" int vcr_pair_counters(unsigned long long* counters_device) { g_pair_counters = counters_device; return 0; }
-// Block timeline (bench.py VCR_BENCH_TIMELINE): while a device array of 8 u64 per tile is registered, every block of the
+// Block timeline (bench.py VCR_BENCH_TIMELINE): while a device array of 16 u64 per tile is registered, every block of the
 // two-pixel forward writes [0] start, [1] end (globaltimer, ns), [2] tile << 32 | SM id, [3] list length and, in the
-// instrumented instantiation, [4..7] the candidates each warp evaluated. One uniform test per block when switched off.
+// instrumented instantiation, [4..7] the candidates each warp evaluated, [8..11] the cycles each warp waited at the per-batch barrier, [12] the block's cycles. One uniform test per block when switched off.
 static unsigned long long* g_block_timeline = nullptr;
 extern "C" int vcr_debug_block_timeline(unsigned long long* timeline_device) { g_block_timeline = timeline_device; return 0; }
 __device__ __forceinline__ unsigned long long vcr_globaltimer() {
@@ -306,8 +306,9 @@ __global__ void __launch_bounds__(RF2_THREADS, VCR_RF2_MINBLOCKS) render_forward
     float* __restrict__ out_color, const unsigned int* __restrict__ abort_flag, unsigned long long* __restrict__ pair_counters,
     unsigned long long* __restrict__ timeline) {
     __shared__ Rf2Stage s_stage[2];
-    if (timeline && threadIdx.x == 0) timeline[8 * (size_t)blockIdx.x] = vcr_globaltimer();
+    if (timeline && threadIdx.x == 0) timeline[16 * (size_t)blockIdx.x] = vcr_globaltimer();
     unsigned int st_ke = 0, st_kc = 0, st_cand = 0;
+    long long st_wait = 0;             // cycles this warp spent at the per-batch barrier (instrumented runs)
     const long long st_t0 = STATS ? clock64() : 0;
     if (__ldg(abort_flag)) return;      // the sort of this view failed (binning.cu): the lists are garbage, leave the outputs unwritten
 
@@ -401,7 +402,8 @@ __global__ void __launch_bounds__(RF2_THREADS, VCR_RF2_MINBLOCKS) render_forward
         // so alpha goes first here: most rejected pairs fail it, and it spares them the IEEE division
         // power > 0 rejects the pair (forward.cu:386): two bits of `pos` carry that to commit, the alpha chain stays branch-free
         pos = (power.x > 0.0f ? 1u : 0u) | (power.y > 0.0f ? 2u : 0u);
-        return make_float2(fminf(0.99f, g1.y * expf(power.x)), fminf(0.99f, g1.y * expf(power.y)));
+        const float2 e = vcr_expf2(power);                      // == expf on both lanes, exhaustively (tools/expf2_check.cu)
+        return make_float2(fminf(0.99f, g1.y * e.x), fminf(0.99f, g1.y * e.y));
     };
     auto commit = [&](const Rf2Stage& st, const int i, const int j, const float2 al, const uint32_t pos) {
         const float a0 = al.x, a1 = al.y;
@@ -489,7 +491,10 @@ __global__ void __launch_bounds__(RF2_THREADS, VCR_RF2_MINBLOCKS) render_forward
             }
         }
         // one barrier per batch: publishes batch i+1, frees buffer `buf` for batch i+2, and votes on completion
-        if (__syncthreads_and(alive == 0u)) break;
+        const long long st_b0 = STATS ? clock64() : 0;
+        const bool all_done = __syncthreads_and(alive == 0u);
+        if (STATS) st_wait += clock64() - st_b0;
+        if (all_done) break;
     }
 
     if (STATS) {
@@ -525,7 +530,7 @@ __global__ void __launch_bounds__(RF2_THREADS, VCR_RF2_MINBLOCKS) render_forward
     if (in1) write(pix1, T.y, last1, C0.y, C1.y, C2.y, weight.y, D.y, N0.y, N1.y, N2.y, O0.y, O1.y);
     if (timeline) {
         __syncthreads();
-        unsigned long long* rec = timeline + 8 * (size_t)blockIdx.x;
+        unsigned long long* rec = timeline + 16 * (size_t)blockIdx.x;
         if (tid == 0) {
             unsigned int smid;
             asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
@@ -533,7 +538,11 @@ __global__ void __launch_bounds__(RF2_THREADS, VCR_RF2_MINBLOCKS) render_forward
             rec[2] = ((unsigned long long)tile << 32) | smid;
             rec[3] = (unsigned long long)(uint32_t)total;
         }
-        if (STATS && lane == 0) rec[4 + warp] = st_cand;       // (warp, Gaussian) candidates after culling, per warp
+        if (STATS && lane == 0) {
+            rec[4 + warp] = st_cand;                           // (warp, Gaussian) candidates after culling, per warp
+            rec[8 + warp] = (unsigned long long)st_wait;       // cycles at the per-batch barrier, per warp
+            if (warp == 0) rec[12] = (unsigned long long)(clock64() - st_t0);
+        }
     }
 }
 
