@@ -278,6 +278,14 @@ __global__ void __launch_bounds__(256, VAR ? 3 : 4) render_forward_kernel(
 // ------------------------------------------------------------------------------------------------------------------
 #define RF2_THREADS 128
 #define RF2_BATCH 128
+#ifndef VCR_RING
+#define VCR_RING 1            // 1: the staging buffer is a ring of 32-entry chunks with per-chunk ready flags (no block barrier)
+#endif
+#define RF2_CHUNKS 8                      // ring length in chunks
+#ifndef VCR_RING_AHEAD
+#define VCR_RING_AHEAD 4                  // a warp stages a chunk before consuming if the ring is less than this far ahead of it
+#endif
+#define RF2_SLOTS (VCR_RING ? 32 * RF2_CHUNKS : RF2_BATCH)
 #ifndef VCR_RF2_MINBLOCKS
 #define VCR_RF2_MINBLOCKS 7
 #endif
@@ -286,14 +294,14 @@ __global__ void __launch_bounds__(256, VAR ? 3 : 4) render_forward_kernel(
 #endif
 
 struct Rf2Stage {
-    StagedGeo geo[RF2_BATCH];
-    float4 box[RF2_BATCH];
-    float2 ex[RF2_BATCH];
+    StagedGeo geo[RF2_SLOTS];
+    float4 box[RF2_SLOTS];
+    float2 ex[RF2_SLOTS];
 #if VCR_QUAD
-    float exc[RF2_BATCH];              // 1 / conic.z for the column tests
+    float exc[RF2_SLOTS];              // 1 / conic.z for the column tests
 #endif
-    float4 nrm[RF2_BATCH];             // normal.xyz, semantics[0]
-    float4 col[RF2_BATCH];             // rgb, semantics[1]
+    float4 nrm[RF2_SLOTS];             // normal.xyz, semantics[0]
+    float4 col[RF2_SLOTS];             // rgb, semantics[1]
 };
 
 template <bool HAS_DIRS, bool HAS_OBJ, bool STATS>
@@ -305,7 +313,7 @@ __global__ void __launch_bounds__(RF2_THREADS, VCR_RF2_MINBLOCKS) render_forward
     const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
     float* __restrict__ out_color, const unsigned int* __restrict__ abort_flag, unsigned long long* __restrict__ pair_counters,
     unsigned long long* __restrict__ timeline) {
-    __shared__ Rf2Stage s_stage[2];
+    __shared__ Rf2Stage s_stage[VCR_RING ? 1 : 2];
     if (timeline && threadIdx.x == 0) timeline[16 * (size_t)blockIdx.x] = vcr_globaltimer();
     unsigned int st_ke = 0, st_kc = 0, st_cand = 0;
     long long st_wait = 0;             // cycles this warp spent at the per-batch barrier (instrumented runs)
@@ -348,10 +356,8 @@ __global__ void __launch_bounds__(RF2_THREADS, VCR_RF2_MINBLOCKS) render_forward
     const int total = (int)(range.y - range.x);
     const int rounds = (total + RF2_BATCH - 1) / RF2_BATCH;
 
-    auto stage = [&](int batch, int buf) {
-        const uint32_t pos = range.x + (uint32_t)batch * RF2_BATCH + tid;
+    auto stage_one = [&](const uint32_t pos, Rf2Stage& st, const int tid) {      // list entry `pos` into slot `tid`
         if (pos >= range.y) return;
-        Rf2Stage& st = s_stage[buf];
         const uint32_t id = __ldg(point_list + pos);
         const float2 xy = __ldg(means2D + id);
         const float4 co = __ldg(conic_opacity + id);
@@ -405,7 +411,7 @@ __global__ void __launch_bounds__(RF2_THREADS, VCR_RF2_MINBLOCKS) render_forward
         const float2 e = vcr_expf2(power);                      // == expf on both lanes, exhaustively (tools/expf2_check.cu)
         return make_float2(fminf(0.99f, g1.y * e.x), fminf(0.99f, g1.y * e.y));
     };
-    auto commit = [&](const Rf2Stage& st, const int i, const int j, const float2 al, const uint32_t pos) {
+    auto commit = [&](const Rf2Stage& st, const int list_base, const int j, const float2 al, const uint32_t pos) {
         const float a0 = al.x, a1 = al.y;
         if (STATS) st_ke += __popc(alive);
         bool ok0 = (alive & ~pos & 1u) && !(a0 < 1.0f / 255.0f);
@@ -437,58 +443,134 @@ __global__ void __launch_bounds__(RF2_THREADS, VCR_RF2_MINBLOCKS) render_forward
             D = vcr_fma2(make_float2(ok0 ? depth.x : 0.f, ok1 ? depth.y : 0.f), w, D);
             N0 = vcr_fma2(vcr_bcast2(nrm.x), w, N0); N1 = vcr_fma2(vcr_bcast2(nrm.y), w, N1); N2 = vcr_fma2(vcr_bcast2(nrm.z), w, N2);
         }
-        const uint32_t here = (uint32_t)(i * RF2_BATCH + j + 1);
+        const uint32_t here = (uint32_t)(list_base + j + 1);       // list position + 1 of the entry in slot j
         if (ok0) { T.x = test_T.x; last0 = here; }
         if (ok1) { T.y = test_T.y; last1 = here; }
         if (STATS) st_kc += (ok0 ? 1u : 0u) + (ok1 ? 1u : 0u);
     };
 
-    if (rounds > 0) stage(0, 0);
+    // One chunk of 32 staged entries, slots slot0 .. slot0+31 of `st`, the first n of them valid; list_base + slot = list
+    // position.  Footprint culling on the lanes, then the surviving candidates one pair at a time.  Returns true when every
+    // pixel of the warp has finished.
+    auto consume = [&](const Rf2Stage& st, const int slot0, const int n, const int list_base) -> bool {
+        const int jj = slot0 + lane;
+        const float4 bx = st.box[jj];
+        bool hit = lane < n && bx.x <= strip_x1 && bx.y >= strip_x0 && bx.z <= strip_y1 && bx.w >= strip_y0;
+        if (hit) {
+            const float4 gq = *reinterpret_cast<const float4*>(&st.geo[jj]);        // x, y, ca, cb
+#if VCR_QUAD
+            hit = vcr_rect_may_contribute(gq.x, gq.y, gq.z, gq.w, st.geo[jj].cc, st.ex[jj], st.exc[jj], strip_x0, strip_x1, strip_y0, strip_y1);
+#else
+            hit = vcr_strip_may_contribute_rows<4>(gq.x, gq.y, gq.z, gq.w, st.geo[jj].cc, st.ex[jj], strip_x0, strip_x1, strip_y0);
+#endif
+        }
+        uint32_t m = __ballot_sync(0xffffffffu, hit);
+        while (m) {
+            // m is warp-uniform, so every lane passes here once per candidate group: a safe place to vote
+            if (__all_sync(0xffffffffu, alive == 0u)) return true;
+            // VCR_RF2_WAY candidates per iteration: their alpha chains are independent of T and of each other, so they are
+            // issued together (the kernel is as long as its longest tile, whose four warps are latency-bound), then
+            // committed one after the other, in list order.
+            int js[VCR_RF2_WAY];
+            float2 als[VCR_RF2_WAY];
+            uint32_t pos[VCR_RF2_WAY];
+            int nc = 0;
+#pragma unroll
+            for (int w = 0; w < VCR_RF2_WAY; w++) {
+                if (m) { js[w] = slot0 + __ffs(m) - 1; m &= m - 1; nc = w + 1; }
+                else js[w] = js[0];
+            }
+            if (STATS && lane == 0) st_cand += (unsigned int)nc;
+            if (alive == 0u) continue;
+#pragma unroll
+            for (int w = 0; w < VCR_RF2_WAY; w++) als[w] = eval(st, js[w], pos[w]);
+#pragma unroll
+            for (int w = 0; w < VCR_RF2_WAY; w++)
+                if (w < nc && alive != 0u) commit(st, list_base, js[w], als[w], pos[w]);
+        }
+        return false;
+    };
+
+#if VCR_RING
+    // Ring of RF2_CHUNKS chunks of 32 entries, shared by the four warps, no block barrier: chunk c lives in slots
+    // 32 (c mod RF2_CHUNKS) .., is staged by whichever warp claims it (s_next, compare-and-swap) and published through
+    // s_ready[c mod RF2_CHUNKS] = c + 1; a slot may be overwritten once every warp has left the chunk that was there
+    // (s_tail).  A warp that finds its next chunk missing stages chunks itself, so the warps that are ahead do the staging
+    // and the warp with the most candidates — the one that decides when the block ends — finds its chunks ready.
+    __shared__ uint32_t s_ready[RF2_CHUNKS];
+    __shared__ uint32_t s_tail[RF2_THREADS / 32];    // chunks each warp has finished with; 0xffffffff once it has left the loop
+    __shared__ uint32_t s_next;                      // first chunk nobody has claimed
+    if (tid < RF2_CHUNKS) s_ready[tid] = 0u;
+    if (tid < RF2_THREADS / 32) s_tail[tid] = 0u;
+    if (tid == 0) s_next = 0u;
+    __syncthreads();
+    {
+        Rf2Stage& st = s_stage[0];
+        volatile uint32_t* v_ready = s_ready;
+        volatile uint32_t* v_tail = s_tail;
+        volatile uint32_t* v_next = &s_next;
+        const uint32_t nchunks = ((uint32_t)total + 31u) >> 5;
+        // stage the first unclaimed chunk if it lies below `limit` and its slots are free; false if there was nothing to do
+        auto try_stage = [&](const uint32_t limit) -> bool {
+            const uint32_t c = *v_next;
+            if (c >= limit) return false;
+            const uint32_t behind = min(min(v_tail[0], v_tail[1]), min(v_tail[2], v_tail[3]));
+            if (c >= RF2_CHUNKS && c - RF2_CHUNKS >= behind) return false;
+            uint32_t got = c + 1u;
+            if (lane == 0) got = atomicCAS(&s_next, c, c + 1u);
+            got = __shfl_sync(0xffffffffu, got, 0);
+            if (got == c) {
+                stage_one(range.x + 32u * c + lane, st, (int)((32u * c + lane) % RF2_SLOTS));
+                __threadfence_block();
+                __syncwarp();
+                if (lane == 0) v_ready[c % RF2_CHUNKS] = c + 1u;
+            }
+            return true;
+        };
+        for (uint32_t my = 0; my < nchunks; my++) {
+            if (__all_sync(0xffffffffu, alive == 0u)) break;
+            try_stage(min(nchunks, my + VCR_RING_AHEAD));            // keep the ring ahead of the warps that lead
+            const long long st_b0 = STATS ? clock64() : 0;
+            uint32_t spins = 0;
+            while (v_ready[my % RF2_CHUNKS] != my + 1u) {
+                if (!try_stage(nchunks)) {
+                    __nanosleep(32);
+                    // never reached unless the protocol is broken: leave through the error flag of the sort (reported by the
+                    // next call) instead of hanging the device
+                    if (++spins > (1u << 22)) { atomicExch(const_cast<unsigned int*>(abort_flag), 1u); break; }
+                }
+            }
+            if (spins > (1u << 22)) break;
+            __threadfence_block();
+            if (STATS) st_wait += clock64() - st_b0;
+            const bool done = consume(st, (int)((32u * my) % RF2_SLOTS), min(32, total - (int)(32u * my)), (int)(32u * my - (32u * my) % RF2_SLOTS));
+            __threadfence_block();
+            __syncwarp();
+            if (done) break;
+            if (lane == 0) v_tail[warp] = my + 1u;
+        }
+        if (lane == 0) v_tail[warp] = 0xffffffffu;
+        // A warp that has finished keeps staging for the others (they would otherwise pay the load latency of every chunk
+        // themselves — in the longest tiles one warp is often the only one left for most of the list).
+        for (uint32_t spins = 0; spins < (1u << 22); ) {
+            if (*v_next >= nchunks) break;                                                              // everything is staged
+            if ((v_tail[0] & v_tail[1] & v_tail[2] & v_tail[3]) == 0xffffffffu) break;                  // nobody is left to read it
+            if (!try_stage(nchunks)) { __nanosleep(64); spins++; }
+        }
+    }
+#else
+    if (rounds > 0) stage_one(range.x + tid, s_stage[0], tid);
     __syncthreads();
     for (int i = 0; i < rounds; i++) {
         const int buf = i & 1;
-        if (i + 1 < rounds) stage(i + 1, buf ^ 1);   // overlaps with compositing batch i
+        if (i + 1 < rounds) stage_one(range.x + (uint32_t)(i + 1) * RF2_BATCH + tid, s_stage[buf ^ 1], tid);   // overlaps with compositing batch i
         const Rf2Stage& st = s_stage[buf];
         const int cnt = min(RF2_BATCH, total - i * RF2_BATCH);
         bool warp_done = __all_sync(0xffffffffu, alive == 0u);
 #pragma unroll 1
         for (int k = 0; k < RF2_BATCH / 32 && !warp_done; k++) {
             if (k * 32 >= cnt) break;
-            const int jj = k * 32 + lane;
-            const float4 bx = st.box[jj];
-            bool hit = jj < cnt && bx.x <= strip_x1 && bx.y >= strip_x0 && bx.z <= strip_y1 && bx.w >= strip_y0;
-            if (hit) {
-                const float4 gq = *reinterpret_cast<const float4*>(&st.geo[jj]);        // x, y, ca, cb
-                #if VCR_QUAD
-                hit = vcr_rect_may_contribute(gq.x, gq.y, gq.z, gq.w, st.geo[jj].cc, st.ex[jj], st.exc[jj], strip_x0, strip_x1, strip_y0, strip_y1);
-#else
-                hit = vcr_strip_may_contribute_rows<4>(gq.x, gq.y, gq.z, gq.w, st.geo[jj].cc, st.ex[jj], strip_x0, strip_x1, strip_y0);
-#endif
-            }
-            uint32_t m = __ballot_sync(0xffffffffu, hit);
-            while (m) {
-                // m is warp-uniform, so every lane passes here once per candidate group: a safe place to vote
-                if (__all_sync(0xffffffffu, alive == 0u)) { warp_done = true; break; }
-                // VCR_RF2_WAY candidates per iteration: their alpha chains are independent of T and of each other, so they are
-                // issued together (the kernel is as long as its longest tile, whose four warps are latency-bound), then
-                // committed one after the other, in list order.
-                int js[VCR_RF2_WAY];
-                float2 als[VCR_RF2_WAY];
-                uint32_t pos[VCR_RF2_WAY];
-                int n = 0;
-#pragma unroll
-                for (int w = 0; w < VCR_RF2_WAY; w++) {
-                    if (m) { js[w] = k * 32 + __ffs(m) - 1; m &= m - 1; n = w + 1; }
-                    else js[w] = js[0];
-                }
-                if (STATS && lane == 0) st_cand += (unsigned int)n;
-                if (alive == 0u) continue;
-#pragma unroll
-                for (int w = 0; w < VCR_RF2_WAY; w++) als[w] = eval(st, js[w], pos[w]);
-#pragma unroll
-                for (int w = 0; w < VCR_RF2_WAY; w++)
-                    if (w < n && alive != 0u) commit(st, i, js[w], als[w], pos[w]);
-            }
+            warp_done = consume(st, k * 32, cnt - k * 32, i * RF2_BATCH);
         }
         // one barrier per batch: publishes batch i+1, frees buffer `buf` for batch i+2, and votes on completion
         const long long st_b0 = STATS ? clock64() : 0;
@@ -496,6 +578,7 @@ __global__ void __launch_bounds__(RF2_THREADS, VCR_RF2_MINBLOCKS) render_forward
         if (STATS) st_wait += clock64() - st_b0;
         if (all_done) break;
     }
+#endif
 
     if (STATS) {
         const unsigned int ke = __reduce_add_sync(0xffffffffu, st_ke), kc = __reduce_add_sync(0xffffffffu, st_kc);
