@@ -363,21 +363,29 @@ __global__ void __launch_bounds__(256) render_backward_kernel(
 // ------------------------------------------------------------------------------------------------------------------
 #define RB2_THREADS 128
 #define RB2_BATCH 128
+#ifndef VCR_RING_B
+#define VCR_RING_B 1          // 1: staging buffer as a ring of 32-entry chunks with ready flags, no block barrier (see render_forward.cu)
+#endif
+#define RB2_CHUNKS 8
+#define RB2_SLOTS (VCR_RING_B ? 32 * RB2_CHUNKS : RB2_BATCH)
+#ifndef VCR_RING_B_AHEAD
+#define VCR_RING_B_AHEAD 4
+#endif
 #ifndef VCR_RB2_MINBLOCKS
 #define VCR_RB2_MINBLOCKS 5
 #endif
 
 template <bool HAS_DIRS>
 struct Rb2Stage {
-    StagedGeoB geo[RB2_BATCH];
-    float4 box[RB2_BATCH];
-    float2 ex[RB2_BATCH];
+    StagedGeoB geo[RB2_SLOTS];
+    float4 box[RB2_SLOTS];
+    float2 ex[RB2_SLOTS];
 #if VCR_QUAD
-    float exc[RB2_BATCH];             // 1 / conic.z for the column tests
+    float exc[RB2_SLOTS];             // 1 / conic.z for the column tests
 #endif
-    float4 nrm[RB2_BATCH];            // normal.xyz, semantics[0]
-    float4 col[RB2_BATCH];            // rgb, semantics[1]
-    float4 xv[HAS_DIRS ? RB2_BATCH : 1];
+    float4 nrm[RB2_SLOTS];            // normal.xyz, semantics[0]
+    float4 col[RB2_SLOTS];            // rgb, semantics[1]
+    float4 xv[HAS_DIRS ? RB2_SLOTS : 1];
 };
 
 __device__ __forceinline__ float2 vcr_sub2(const float2 a, const float2 b) { return vcr_add2(a, make_float2(-b.x, -b.y)); }
@@ -390,7 +398,7 @@ __global__ void __launch_bounds__(RB2_THREADS, VCR_RB2_MINBLOCKS) render_backwar
     const float* __restrict__ objects, const float* __restrict__ dirs, const float* __restrict__ alpha_img,
     const float* __restrict__ depth_img, const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
     const float* __restrict__ dL_dpixels, float* __restrict__ acc, const unsigned int* __restrict__ abort_flag) {
-    __shared__ Rb2Stage<HAS_DIRS> s_stage[2];
+    __shared__ Rb2Stage<HAS_DIRS> s_stage[VCR_RING_B ? 1 : 2];
     __shared__ uint32_t s_block_last;
     if (__ldg(abort_flag)) return;      // the sort of this view failed (binning.cu): the lists are garbage, accumulate nothing
 
@@ -460,10 +468,8 @@ __global__ void __launch_bounds__(RB2_THREADS, VCR_RB2_MINBLOCKS) render_backwar
     const float2 Z = make_float2(0.f, 0.f);
     float2 Sc0 = Z, Sc1 = Z, Sc2 = Z, Sd = Z, S1 = Z, Sn0 = Z, Sn1 = Z, Sn2 = Z, So0 = Z, So1 = Z;
 
-    auto stage = [&](int batch, int buf) {
-        const uint32_t progress = (uint32_t)batch * RB2_BATCH + tid;
+    auto stage_one = [&](const uint32_t progress, Rb2Stage<HAS_DIRS>& st, const int tid) {    // entry `progress` of the reversed list into slot `tid`
         if (range.x + progress >= list_end) return;
-        Rb2Stage<HAS_DIRS>& st = s_stage[buf];
         const uint32_t id = __ldg(point_list + (list_end - progress - 1));
         const float2 xy = __ldg(means2D + id);
         const float4 co = __ldg(conic_opacity + id);
@@ -493,11 +499,218 @@ __global__ void __launch_bounds__(RB2_THREADS, VCR_RB2_MINBLOCKS) render_backwar
                                   __ldg(colors + 3 * (size_t)id + 2), o1);
     };
 
-    if (rounds > 0) stage(0, 0);
+    // One chunk of 32 staged entries, slots slot0 .. slot0+31 of `st`, the first n valid; the entry in slot j is contributor
+    // cbase - j of the tile's list.  Footprint culling on the lanes, then the surviving candidates one at a time.
+    auto consume = [&](const Rb2Stage<HAS_DIRS>& st, const int slot0, const int n, const int cbase) {
+        const int jj = slot0 + lane;
+        const float4 bx = st.box[jj];
+        bool hit = lane < n && (uint32_t)(cbase - jj) < warp_last && bx.x <= strip_x1 && bx.y >= strip_x0 &&
+                   bx.z <= strip_y1 && bx.w >= strip_y0;
+        if (hit) {
+            const float4 gq = *reinterpret_cast<const float4*>(&st.geo[jj]);        // x, y, ca, cb
+            #if VCR_QUAD
+            hit = vcr_rect_may_contribute(gq.x, gq.y, gq.z, gq.w, st.geo[jj].cc, st.ex[jj], st.exc[jj], strip_x0, strip_x1, strip_y0, strip_y1);
+#else
+            hit = vcr_strip_may_contribute_rows<4>(gq.x, gq.y, gq.z, gq.w, st.geo[jj].cc, st.ex[jj], strip_x0, strip_x1, strip_y0);
+#endif
+        }
+        uint32_t m = __ballot_sync(0xffffffffu, hit);
+        while (m) {
+            const int j = slot0 + __ffs(m) - 1;
+            m &= m - 1;
+            const uint32_t contributor = (uint32_t)(cbase - j);
+            const float4 g0 = *reinterpret_cast<const float4*>(&st.geo[j]);        // x, y, ca, cb
+            const float4 g1 = *reinterpret_cast<const float4*>(&st.geo[j].cc);     // cc, op, nx, id
+            const float dx = g0.x - pfx;
+            const float2 dy = vcr_add2(vcr_bcast2(g0.y), npfy);
+            const float adx = __fmul_rn(g0.z, dx), nbdx = -__fmul_rn(g0.w, dx);
+            const float2 q = vcr_fma2(vcr_bcast2(adx), vcr_bcast2(dx), vcr_mul2(vcr_mul2(vcr_bcast2(g1.x), dy), dy));
+            const float2 power = vcr_fma2(q, vcr_bcast2(-0.5f), vcr_mul2(vcr_bcast2(nbdx), dy));
+            bool c0 = contributor < lastc0 && !(power.x > 0.0f);
+            bool c1 = contributor < lastc1 && !(power.y > 0.0f);
+            if (!__any_sync(0xffffffffu, c0 || c1)) continue;
+            // Fast intrinsics from here on: the backward only has to meet 1e-3 relative L2 (the forward, which must
+            // match the reference bit for bit, keeps expf and IEEE division).
+            const float2 Gr = make_float2(__expf(power.x), __expf(power.y));
+            const float2 ar = make_float2(fminf(0.99f, g1.y * Gr.x), fminf(0.99f, g1.y * Gr.y));
+            c0 = c0 && !(ar.x < 1.0f / 255.0f);
+            c1 = c1 && !(ar.y < 1.0f / 255.0f);
+            const float4 nrm = st.nrm[j];
+            float2 pd = make_float2(1.f, 1.f), ipd = pd, cdr;
+            if (HAS_DIRS) {
+                pd = vcr_fma2(vcr_bcast2(nrm.z), dirz, vcr_fma2(vcr_bcast2(nrm.x), dirx, vcr_mul2(vcr_bcast2(nrm.y), diry)));
+                ipd = make_float2(__fdividef(1.0f, pd.x), __fdividef(1.0f, pd.y));
+                cdr = vcr_mul2(vcr_mul2(vcr_bcast2(g1.z), ipd), dirz);
+            } else {
+                cdr = vcr_bcast2(g1.z);
+            }
+            c0 = c0 && !(cdr.x < 0.2f);  // == (double)c_d < 0.2, backward.cu:616
+            c1 = c1 && !(cdr.y < 0.2f);
+            const uint32_t cmask = __ballot_sync(0xffffffffu, c0 || c1);
+            if (cmask == 0u) continue;
+
+            // a pixel that does not take this Gaussian: alpha = G = 0 (and finite stand-ins where it may hold inf / NaN)
+            const float2 alpha = make_float2(c0 ? ar.x : 0.f, c1 ? ar.y : 0.f);
+            const float2 G = make_float2(c0 ? Gr.x : 0.f, c1 ? Gr.y : 0.f);
+            const float2 c_d = make_float2(c0 ? cdr.x : 0.f, c1 ? cdr.y : 0.f);
+            if (HAS_DIRS) ipd = make_float2(c0 ? ipd.x : 0.f, c1 ? ipd.y : 0.f);
+            const float2 one = make_float2(1.f, 1.f);
+            const float2 oma = vcr_sub2(one, alpha);
+            const float2 inv1ma = make_float2(__fdividef(1.0f, oma.x), __fdividef(1.0f, oma.y));
+            T = vcr_mul2(T, inv1ma);
+            const float2 aT = vcr_mul2(alpha, T);
+            const float4 col = st.col[j];
+            float2 v[16];
+            // colour (backward.cu:632-641): dL_dopa += (c - accum_rec) * dL_dpixel;  dL_dcolor += alpha T dL_dpixel
+            float2 d0 = vcr_sub2(vcr_bcast2(col.x), Sc0), d1 = vcr_sub2(vcr_bcast2(col.y), Sc1), d2 = vcr_sub2(vcr_bcast2(col.z), Sc2);
+            float2 dopa = vcr_fma2(d2, gC2, vcr_fma2(d1, gC1, vcr_mul2(d0, gC0)));
+            Sc0 = vcr_fma2(alpha, d0, Sc0); Sc1 = vcr_fma2(alpha, d1, Sc1); Sc2 = vcr_fma2(alpha, d2, Sc2);
+            v[ACC_COLOR_R] = vcr_mul2(aT, gC0); v[ACC_COLOR_R + 1] = vcr_mul2(aT, gC1); v[ACC_COLOR_R + 2] = vcr_mul2(aT, gC2);
+            // depth and normal (backward.cu:643-754); om1 = 1 - accum_rec2 = 1 - accum_alpha_rec
+            const float2 om1 = vcr_sub2(one, S1);
+            const float2 aTw = vcr_mul2(aT, inv_weight);
+            {
+                const float2 dd = vcr_sub2(c_d, Sd);
+                const float2 t = vcr_fma2(make_float2(-depth_final.x, -depth_final.y), om1, dd);
+                dopa = vcr_fma2(t, kD, dopa);
+                Sd = vcr_fma2(alpha, dd, Sd);
+            }
+            const float2 dL_dd_j = vcr_mul2(aTw, gD);
+            float2 dn0 = Z, dn1 = Z, dn2 = Z;
+            if (HAS_DIRS) {  // backward.cu:722-728
+                const float4 xv = st.xv[j];
+                const float2 sv = vcr_mul2(vcr_mul2(dL_dd_j, dirz), ipd);      // dL/dxyz_view = normal * sum(sv)
+                const float2 s2 = vcr_mul2(sv, ipd);
+                const float2 nnx = vcr_bcast2(-g1.z);
+                dn0 = vcr_mul2(s2, vcr_fma2(pd, vcr_bcast2(xv.x), vcr_mul2(dirx, nnx)));
+                dn1 = vcr_mul2(s2, vcr_fma2(pd, vcr_bcast2(xv.y), vcr_mul2(diry, nnx)));
+                dn2 = vcr_mul2(s2, vcr_fma2(pd, vcr_bcast2(xv.z), vcr_mul2(dirz, nnx)));
+                v[ACC_SV_OR_DEPTH] = sv;
+            } else {
+                v[ACC_SV_OR_DEPTH] = dL_dd_j;
+            }
+            {
+                // reference quirk kept: the "final normal" of the normalisation term is this Gaussian's own n (backward.cu:741-745)
+                const float2 n0 = vcr_bcast2(nrm.x), n1 = vcr_bcast2(nrm.y), n2 = vcr_bcast2(nrm.z);
+                const float2 e0 = vcr_sub2(n0, Sn0), e1 = vcr_sub2(n1, Sn1), e2 = vcr_sub2(n2, Sn2);
+                const float2 nom1 = make_float2(-om1.x, -om1.y);
+                dopa = vcr_fma2(vcr_fma2(n0, nom1, e0), kN0, dopa);
+                dopa = vcr_fma2(vcr_fma2(n1, nom1, e1), kN1, dopa);
+                dopa = vcr_fma2(vcr_fma2(n2, nom1, e2), kN2, dopa);
+                Sn0 = vcr_fma2(alpha, e0, Sn0); Sn1 = vcr_fma2(alpha, e1, Sn1); Sn2 = vcr_fma2(alpha, e2, Sn2);
+                v[ACC_NORMAL_X] = vcr_fma2(aTw, gN0, dn0); v[ACC_NORMAL_X + 1] = vcr_fma2(aTw, gN1, dn1); v[ACC_NORMAL_X + 2] = vcr_fma2(aTw, gN2, dn2);
+            }
+            float2 ex_obj1 = Z;
+            v[ACC_OBJ_0] = Z;
+            if (HAS_OBJ) {
+                // dL_dalpha += (o - accum_rec_obj) * dL_dpixel_obj persists across Gaussians (backward.cu:766); contributing pixels only
+                const float2 f0 = vcr_sub2(vcr_bcast2(nrm.w), So0), f1 = vcr_sub2(vcr_bcast2(col.w), So1);
+                const float2 add = vcr_fma2(f1, gO1, vcr_mul2(f0, gO0));
+                gA = make_float2(c0 ? gA.x + add.x : gA.x, c1 ? gA.y + add.y : gA.y);
+                So0 = vcr_fma2(alpha, f0, So0); So1 = vcr_fma2(alpha, f1, So1);
+                v[ACC_OBJ_0] = vcr_mul2(aT, gO0); ex_obj1 = vcr_mul2(aT, gO1);
+            }
+            dopa = vcr_fma2(om1, gA, dopa);                                   // (1 - accum_alpha_rec) * dL_dalpha
+            S1 = vcr_fma2(alpha, om1, S1);
+            dopa = vcr_fma2(inv1ma, nTf_bg, vcr_mul2(dopa, T));               // * T, + (-T_final / (1 - alpha)) * bg . dL_dpixel
+            // raw moments; the per-Gaussian factors (opacity, conic, 0.5 W) are applied once in preprocess_backward
+            const float2 bb = vcr_mul2(G, dopa);
+            const float2 bxx = vcr_mul2(bb, vcr_bcast2(dx)), byy = vcr_mul2(bb, dy);
+            v[ACC_M0] = bb; v[ACC_MX] = bxx; v[ACC_MY] = byy;
+            v[ACC_MXX] = vcr_mul2(bxx, vcr_bcast2(dx)); v[ACC_MXY] = vcr_mul2(bxx, dy); v[ACC_MYY] = vcr_mul2(byy, dy);
+            const float2 ax = vcr_fma2(byy, vcr_bcast2(g0.w), vcr_mul2(bxx, vcr_bcast2(g0.z)));
+            const float2 ay = vcr_fma2(bxx, vcr_bcast2(g0.w), vcr_mul2(byy, vcr_bcast2(g1.x)));
+            v[ACC_ABS_X] = make_float2(fabsf(ax.x), fabsf(ax.y)); v[ACC_ABS_Y] = make_float2(fabsf(ay.x), fabsf(ay.y));
+
+            // the thread's two pixels first, then the warp
+            float s[16];
+#pragma unroll
+            for (int q_ = 0; q_ < 16; q_++) s[q_] = v[q_].x + v[q_].y;
+            const float eo1 = ex_obj1.x + ex_obj1.y;
+            float* rec = acc + (size_t)__float_as_uint(g1.w) * VCR_ACC_STRIDE;
+            if (__popc(cmask) <= RB_SPARSE_LANES) {
+                if (c0 || c1) {
+#pragma unroll
+                    for (int q_ = 0; q_ < (HAS_OBJ ? 16 : 15); q_++) atomicAdd(rec + q_, s[q_]);
+                    if (HAS_OBJ) atomicAdd(rec + ACC_OBJ_1, eo1);
+                }
+                continue;
+            }
+            const float red = warp_reduce16_transposed(s, lane);
+            if (lane < (HAS_OBJ ? 16 : 15)) atomicAdd(rec + lane, red);
+            if (HAS_OBJ) {
+                const float o1 = vcr_warp_sum(eo1);
+                if (lane == 16) atomicAdd(rec + ACC_OBJ_1, o1);
+            }
+        }
+    };
+
+#if VCR_RING_B
+    // Ring protocol of render_forward2_kernel: chunk c of the reversed list in slots 32 (c mod RB2_CHUNKS) .., staged by the
+    // warp that claims it, published through s_ready, slots reused once every warp has left the chunk that was there.  A warp
+    // starts at the first chunk that holds a contributor below its warp_last; until then it only stages.
+    __shared__ uint32_t s_ready[RB2_CHUNKS];
+    __shared__ uint32_t s_tail[RB2_THREADS / 32];
+    __shared__ uint32_t s_next;
+    const uint32_t nchunks = (block_last + 31u) >> 5;
+    const uint32_t first_chunk = warp_last ? (block_last - warp_last) >> 5 : nchunks;      // chunks before it hold nothing for this warp
+    if (tid < RB2_CHUNKS) s_ready[tid] = 0u;
+    if (lane == 0) s_tail[warp] = first_chunk;
+    if (tid == 0) s_next = 0u;
+    __syncthreads();
+    {
+        Rb2Stage<HAS_DIRS>& st = s_stage[0];
+        volatile uint32_t* v_ready = s_ready;
+        volatile uint32_t* v_tail = s_tail;
+        volatile uint32_t* v_next = &s_next;
+        auto try_stage = [&](const uint32_t limit) -> bool {
+            const uint32_t c = *v_next;
+            if (c >= limit) return false;
+            const uint32_t behind = min(min(v_tail[0], v_tail[1]), min(v_tail[2], v_tail[3]));
+            if (c >= RB2_CHUNKS && c - RB2_CHUNKS >= behind) return false;
+            uint32_t got = c + 1u;
+            if (lane == 0) got = atomicCAS(&s_next, c, c + 1u);
+            got = __shfl_sync(0xffffffffu, got, 0);
+            if (got == c) {
+                stage_one(32u * c + lane, st, (int)((32u * c + lane) % RB2_SLOTS));
+                __threadfence_block();
+                __syncwarp();
+                if (lane == 0) v_ready[c % RB2_CHUNKS] = c + 1u;
+            }
+            return true;
+        };
+        bool broken = false;
+        for (uint32_t my = first_chunk; my < nchunks && !broken; my++) {
+            try_stage(min(nchunks, my + VCR_RING_B_AHEAD));
+            uint32_t spins = 0;
+            while (v_ready[my % RB2_CHUNKS] != my + 1u) {
+                if (!try_stage(nchunks)) {
+                    __nanosleep(32);
+                    // never reached unless the protocol is broken: leave through the error flag of the sort instead of hanging
+                    if (++spins > (1u << 22)) { atomicExch(const_cast<unsigned int*>(abort_flag), 1u); broken = true; break; }
+                }
+            }
+            if (broken) break;
+            __threadfence_block();
+            const int slot0 = (int)((32u * my) % RB2_SLOTS);
+            consume(st, slot0, min(32, (int)(block_last - 32u * my)), (int)block_last - 1 - (int)(32u * my) + slot0);
+            __threadfence_block();
+            __syncwarp();
+            if (lane == 0) v_tail[warp] = my + 1u;
+        }
+        if (lane == 0) v_tail[warp] = 0xffffffffu;
+        for (uint32_t spins = 0; spins < (1u << 22); ) {        // finished (or nothing to do): keep staging for the others
+            if (*v_next >= nchunks) break;
+            if ((v_tail[0] & v_tail[1] & v_tail[2] & v_tail[3]) == 0xffffffffu) break;
+            if (!try_stage(nchunks)) { __nanosleep(64); spins++; }
+        }
+    }
+#else
+    if (rounds > 0) stage_one((uint32_t)tid, s_stage[0], tid);
     __syncthreads();
     for (int i = 0; i < rounds; i++, toDo -= RB2_BATCH) {
         const int buf = i & 1;
-        if (i + 1 < rounds) stage(i + 1, buf ^ 1);   // overlaps with the replay of batch i
+        if (i + 1 < rounds) stage_one((uint32_t)(i + 1) * RB2_BATCH + tid, s_stage[buf ^ 1], tid);   // overlaps with the replay of batch i
         const Rb2Stage<HAS_DIRS>& st = s_stage[buf];
         const int cnt = min(RB2_BATCH, toDo);
         // entry j of this batch has list position (contributor index) block_last - 1 - (i*RB2_BATCH + j)
@@ -505,151 +718,12 @@ __global__ void __launch_bounds__(RB2_THREADS, VCR_RB2_MINBLOCKS) render_backwar
 #pragma unroll 1
         for (int k = 0; k < RB2_BATCH / 32; k++) {
             if (k * 32 >= cnt) break;
-            const int jj = k * 32 + lane;
-            const float4 bx = st.box[jj];
-            bool hit = jj < cnt && (uint32_t)(first_pos - jj) < warp_last && bx.x <= strip_x1 && bx.y >= strip_x0 &&
-                       bx.z <= strip_y1 && bx.w >= strip_y0;
-            if (hit) {
-                const float4 gq = *reinterpret_cast<const float4*>(&st.geo[jj]);        // x, y, ca, cb
-                #if VCR_QUAD
-                hit = vcr_rect_may_contribute(gq.x, gq.y, gq.z, gq.w, st.geo[jj].cc, st.ex[jj], st.exc[jj], strip_x0, strip_x1, strip_y0, strip_y1);
-#else
-                hit = vcr_strip_may_contribute_rows<4>(gq.x, gq.y, gq.z, gq.w, st.geo[jj].cc, st.ex[jj], strip_x0, strip_x1, strip_y0);
-#endif
-            }
-            uint32_t m = __ballot_sync(0xffffffffu, hit);
-            while (m) {
-                const int j = k * 32 + __ffs(m) - 1;
-                m &= m - 1;
-                const uint32_t contributor = (uint32_t)(first_pos - j);
-                const float4 g0 = *reinterpret_cast<const float4*>(&st.geo[j]);        // x, y, ca, cb
-                const float4 g1 = *reinterpret_cast<const float4*>(&st.geo[j].cc);     // cc, op, nx, id
-                const float dx = g0.x - pfx;
-                const float2 dy = vcr_add2(vcr_bcast2(g0.y), npfy);
-                const float adx = __fmul_rn(g0.z, dx), nbdx = -__fmul_rn(g0.w, dx);
-                const float2 q = vcr_fma2(vcr_bcast2(adx), vcr_bcast2(dx), vcr_mul2(vcr_mul2(vcr_bcast2(g1.x), dy), dy));
-                const float2 power = vcr_fma2(q, vcr_bcast2(-0.5f), vcr_mul2(vcr_bcast2(nbdx), dy));
-                bool c0 = contributor < lastc0 && !(power.x > 0.0f);
-                bool c1 = contributor < lastc1 && !(power.y > 0.0f);
-                if (!__any_sync(0xffffffffu, c0 || c1)) continue;
-                // Fast intrinsics from here on: the backward only has to meet 1e-3 relative L2 (the forward, which must
-                // match the reference bit for bit, keeps expf and IEEE division).
-                const float2 Gr = make_float2(__expf(power.x), __expf(power.y));
-                const float2 ar = make_float2(fminf(0.99f, g1.y * Gr.x), fminf(0.99f, g1.y * Gr.y));
-                c0 = c0 && !(ar.x < 1.0f / 255.0f);
-                c1 = c1 && !(ar.y < 1.0f / 255.0f);
-                const float4 nrm = st.nrm[j];
-                float2 pd = make_float2(1.f, 1.f), ipd = pd, cdr;
-                if (HAS_DIRS) {
-                    pd = vcr_fma2(vcr_bcast2(nrm.z), dirz, vcr_fma2(vcr_bcast2(nrm.x), dirx, vcr_mul2(vcr_bcast2(nrm.y), diry)));
-                    ipd = make_float2(__fdividef(1.0f, pd.x), __fdividef(1.0f, pd.y));
-                    cdr = vcr_mul2(vcr_mul2(vcr_bcast2(g1.z), ipd), dirz);
-                } else {
-                    cdr = vcr_bcast2(g1.z);
-                }
-                c0 = c0 && !(cdr.x < 0.2f);  // == (double)c_d < 0.2, backward.cu:616
-                c1 = c1 && !(cdr.y < 0.2f);
-                const uint32_t cmask = __ballot_sync(0xffffffffu, c0 || c1);
-                if (cmask == 0u) continue;
-
-                // a pixel that does not take this Gaussian: alpha = G = 0 (and finite stand-ins where it may hold inf / NaN)
-                const float2 alpha = make_float2(c0 ? ar.x : 0.f, c1 ? ar.y : 0.f);
-                const float2 G = make_float2(c0 ? Gr.x : 0.f, c1 ? Gr.y : 0.f);
-                const float2 c_d = make_float2(c0 ? cdr.x : 0.f, c1 ? cdr.y : 0.f);
-                if (HAS_DIRS) ipd = make_float2(c0 ? ipd.x : 0.f, c1 ? ipd.y : 0.f);
-                const float2 one = make_float2(1.f, 1.f);
-                const float2 oma = vcr_sub2(one, alpha);
-                const float2 inv1ma = make_float2(__fdividef(1.0f, oma.x), __fdividef(1.0f, oma.y));
-                T = vcr_mul2(T, inv1ma);
-                const float2 aT = vcr_mul2(alpha, T);
-                const float4 col = st.col[j];
-                float2 v[16];
-                // colour (backward.cu:632-641): dL_dopa += (c - accum_rec) * dL_dpixel;  dL_dcolor += alpha T dL_dpixel
-                float2 d0 = vcr_sub2(vcr_bcast2(col.x), Sc0), d1 = vcr_sub2(vcr_bcast2(col.y), Sc1), d2 = vcr_sub2(vcr_bcast2(col.z), Sc2);
-                float2 dopa = vcr_fma2(d2, gC2, vcr_fma2(d1, gC1, vcr_mul2(d0, gC0)));
-                Sc0 = vcr_fma2(alpha, d0, Sc0); Sc1 = vcr_fma2(alpha, d1, Sc1); Sc2 = vcr_fma2(alpha, d2, Sc2);
-                v[ACC_COLOR_R] = vcr_mul2(aT, gC0); v[ACC_COLOR_R + 1] = vcr_mul2(aT, gC1); v[ACC_COLOR_R + 2] = vcr_mul2(aT, gC2);
-                // depth and normal (backward.cu:643-754); om1 = 1 - accum_rec2 = 1 - accum_alpha_rec
-                const float2 om1 = vcr_sub2(one, S1);
-                const float2 aTw = vcr_mul2(aT, inv_weight);
-                {
-                    const float2 dd = vcr_sub2(c_d, Sd);
-                    const float2 t = vcr_fma2(make_float2(-depth_final.x, -depth_final.y), om1, dd);
-                    dopa = vcr_fma2(t, kD, dopa);
-                    Sd = vcr_fma2(alpha, dd, Sd);
-                }
-                const float2 dL_dd_j = vcr_mul2(aTw, gD);
-                float2 dn0 = Z, dn1 = Z, dn2 = Z;
-                if (HAS_DIRS) {  // backward.cu:722-728
-                    const float4 xv = st.xv[j];
-                    const float2 sv = vcr_mul2(vcr_mul2(dL_dd_j, dirz), ipd);      // dL/dxyz_view = normal * sum(sv)
-                    const float2 s2 = vcr_mul2(sv, ipd);
-                    const float2 nnx = vcr_bcast2(-g1.z);
-                    dn0 = vcr_mul2(s2, vcr_fma2(pd, vcr_bcast2(xv.x), vcr_mul2(dirx, nnx)));
-                    dn1 = vcr_mul2(s2, vcr_fma2(pd, vcr_bcast2(xv.y), vcr_mul2(diry, nnx)));
-                    dn2 = vcr_mul2(s2, vcr_fma2(pd, vcr_bcast2(xv.z), vcr_mul2(dirz, nnx)));
-                    v[ACC_SV_OR_DEPTH] = sv;
-                } else {
-                    v[ACC_SV_OR_DEPTH] = dL_dd_j;
-                }
-                {
-                    // reference quirk kept: the "final normal" of the normalisation term is this Gaussian's own n (backward.cu:741-745)
-                    const float2 n0 = vcr_bcast2(nrm.x), n1 = vcr_bcast2(nrm.y), n2 = vcr_bcast2(nrm.z);
-                    const float2 e0 = vcr_sub2(n0, Sn0), e1 = vcr_sub2(n1, Sn1), e2 = vcr_sub2(n2, Sn2);
-                    const float2 nom1 = make_float2(-om1.x, -om1.y);
-                    dopa = vcr_fma2(vcr_fma2(n0, nom1, e0), kN0, dopa);
-                    dopa = vcr_fma2(vcr_fma2(n1, nom1, e1), kN1, dopa);
-                    dopa = vcr_fma2(vcr_fma2(n2, nom1, e2), kN2, dopa);
-                    Sn0 = vcr_fma2(alpha, e0, Sn0); Sn1 = vcr_fma2(alpha, e1, Sn1); Sn2 = vcr_fma2(alpha, e2, Sn2);
-                    v[ACC_NORMAL_X] = vcr_fma2(aTw, gN0, dn0); v[ACC_NORMAL_X + 1] = vcr_fma2(aTw, gN1, dn1); v[ACC_NORMAL_X + 2] = vcr_fma2(aTw, gN2, dn2);
-                }
-                float2 ex_obj1 = Z;
-                v[ACC_OBJ_0] = Z;
-                if (HAS_OBJ) {
-                    // dL_dalpha += (o - accum_rec_obj) * dL_dpixel_obj persists across Gaussians (backward.cu:766); contributing pixels only
-                    const float2 f0 = vcr_sub2(vcr_bcast2(nrm.w), So0), f1 = vcr_sub2(vcr_bcast2(col.w), So1);
-                    const float2 add = vcr_fma2(f1, gO1, vcr_mul2(f0, gO0));
-                    gA = make_float2(c0 ? gA.x + add.x : gA.x, c1 ? gA.y + add.y : gA.y);
-                    So0 = vcr_fma2(alpha, f0, So0); So1 = vcr_fma2(alpha, f1, So1);
-                    v[ACC_OBJ_0] = vcr_mul2(aT, gO0); ex_obj1 = vcr_mul2(aT, gO1);
-                }
-                dopa = vcr_fma2(om1, gA, dopa);                                   // (1 - accum_alpha_rec) * dL_dalpha
-                S1 = vcr_fma2(alpha, om1, S1);
-                dopa = vcr_fma2(inv1ma, nTf_bg, vcr_mul2(dopa, T));               // * T, + (-T_final / (1 - alpha)) * bg . dL_dpixel
-                // raw moments; the per-Gaussian factors (opacity, conic, 0.5 W) are applied once in preprocess_backward
-                const float2 bb = vcr_mul2(G, dopa);
-                const float2 bxx = vcr_mul2(bb, vcr_bcast2(dx)), byy = vcr_mul2(bb, dy);
-                v[ACC_M0] = bb; v[ACC_MX] = bxx; v[ACC_MY] = byy;
-                v[ACC_MXX] = vcr_mul2(bxx, vcr_bcast2(dx)); v[ACC_MXY] = vcr_mul2(bxx, dy); v[ACC_MYY] = vcr_mul2(byy, dy);
-                const float2 ax = vcr_fma2(byy, vcr_bcast2(g0.w), vcr_mul2(bxx, vcr_bcast2(g0.z)));
-                const float2 ay = vcr_fma2(bxx, vcr_bcast2(g0.w), vcr_mul2(byy, vcr_bcast2(g1.x)));
-                v[ACC_ABS_X] = make_float2(fabsf(ax.x), fabsf(ax.y)); v[ACC_ABS_Y] = make_float2(fabsf(ay.x), fabsf(ay.y));
-
-                // the thread's two pixels first, then the warp
-                float s[16];
-#pragma unroll
-                for (int q_ = 0; q_ < 16; q_++) s[q_] = v[q_].x + v[q_].y;
-                const float eo1 = ex_obj1.x + ex_obj1.y;
-                float* rec = acc + (size_t)__float_as_uint(g1.w) * VCR_ACC_STRIDE;
-                if (__popc(cmask) <= RB_SPARSE_LANES) {
-                    if (c0 || c1) {
-#pragma unroll
-                        for (int q_ = 0; q_ < (HAS_OBJ ? 16 : 15); q_++) atomicAdd(rec + q_, s[q_]);
-                        if (HAS_OBJ) atomicAdd(rec + ACC_OBJ_1, eo1);
-                    }
-                    continue;
-                }
-                const float red = warp_reduce16_transposed(s, lane);
-                if (lane < (HAS_OBJ ? 16 : 15)) atomicAdd(rec + lane, red);
-                if (HAS_OBJ) {
-                    const float o1 = vcr_warp_sum(eo1);
-                    if (lane == 16) atomicAdd(rec + ACC_OBJ_1, o1);
-                }
-            }
+            consume(st, k * 32, cnt - k * 32, first_pos);
         }
         // one barrier per batch: publishes batch i+1 and frees buffer `buf` for batch i+2
         __syncthreads();
     }
+#endif
 }
 
 int vcr_render_version();      // render_forward.cu
