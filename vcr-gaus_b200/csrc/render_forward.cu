@@ -283,7 +283,7 @@ __global__ void __launch_bounds__(256, VAR ? 3 : 4) render_forward_kernel(
 #endif
 #define RF2_CHUNKS 8                      // ring length in chunks
 #ifndef VCR_RING_AHEAD
-#define VCR_RING_AHEAD 4                  // a warp stages a chunk before consuming if the ring is less than this far ahead of it
+#define VCR_RING_AHEAD 2                  // a warp stages a chunk before consuming if the ring is less than this far ahead of it
 #endif
 #define RF2_SLOTS (VCR_RING ? 32 * RF2_CHUNKS : RF2_BATCH)
 #ifndef VCR_RF2_MINBLOCKS
