@@ -26,6 +26,12 @@ for step in "$@"; do
         $CMD > $OUT/${TAG}_plain.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:render_ -s 30 -c 2 -f -o $OUT/${TAG}_render $CMD > $OUT/${TAG}_ncu.log 2>&1
         echo "[ncu_render] rc=$?" | tee -a $OUT/${TAG}_summary.txt; tail -3 $OUT/${TAG}_ncu.log
         unset VCR_BENCH_WARMUP_FLOOR ;;
+    ncu_small) # ncu --set full of the HBM-side kernels in steady state (after the same command ran clean)
+        export VCR_BENCH_WARMUP_FLOOR=20
+        CMD="python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-full-step --no-profile"
+        $CMD > $OUT/${TAG}_plain.log 2>&1 && ncu --set full --clock-control none --import-source on -k "regex:radix_pass|duplicate_sorted|preprocess|view_loss_backward|tile_order|scan_block" -s 60 -c 14 -f -o $OUT/${TAG}_small $CMD > $OUT/${TAG}_ncu.log 2>&1
+        echo "[ncu_small] rc=$?" | tee -a $OUT/${TAG}_summary.txt; tail -3 $OUT/${TAG}_ncu.log
+        unset VCR_BENCH_WARMUP_FLOOR ;;
     launches) # per-launch durations of two steady-state steps (after the same command ran clean)
         CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-full-step --no-profile"
         $CMD > $OUT/${TAG}_plain.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $OUT/${TAG}_launch_list.csv $CMD > $OUT/${TAG}_ncu_list.log 2>&1

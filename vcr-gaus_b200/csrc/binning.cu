@@ -258,8 +258,9 @@ __global__ void __launch_bounds__(256) duplicate_sorted_kernel(int P, int gx, in
         keys_out[base + k] = tile;
         vals_out[base + k] = s_gid[lo];
         for (int p = 0; p < npass; p++) {
-            const int nb = min(8, tile_bits - 8 * p);
-            atomicAdd(&hist[p][(tile >> (8 * p)) & ((1u << nb) - 1u)], 1u);
+            int sh, nb;
+            vcr_radix_pass_bits(tile_bits, p, sh, nb);             // the digit widths vcr_launch_tile_sort uses
+            atomicAdd(&hist[p][(tile >> sh) & ((1u << nb) - 1u)], 1u);
         }
     }
     __syncthreads();
@@ -354,6 +355,7 @@ __global__ void __launch_bounds__(256) radix_scan_hist_kernel(uint32_t* __restri
 static uint32_t g_radix_spin_limit = 1u << 26;      // vcr_debug_radix_fault() lowers it and silences block 0
 static int g_radix_fault = 0;
 
+template <int NB>      // ballots per item in the ranking: >= the digit width of the pass
 __global__ void __launch_bounds__(RADIX_THREADS, VCR_RADIX_MINBLOCKS) radix_pass_kernel(const uint32_t* __restrict__ keys_in,
                                                                       const uint32_t* __restrict__ vals_in,
                                                                       uint32_t* __restrict__ keys_out,
@@ -401,7 +403,7 @@ __global__ void __launch_bounds__(RADIX_THREADS, VCR_RADIX_MINBLOCKS) radix_pass
         // put ~30 distinct digits into a warp (89 us against 62 for the low tile byte)
         uint32_t peers = vmask;
 #pragma unroll
-        for (int b = 0; b < 8; b++) {
+        for (int b = 0; b < NB; b++) {
             const uint32_t bit = (d >> b) & 1u;
             const uint32_t m = __ballot_sync(0xffffffffu, bit != 0u);
             peers &= bit ? m : ~m;
@@ -452,7 +454,10 @@ __global__ void __launch_bounds__(RADIX_THREADS, VCR_RADIX_MINBLOCKS) radix_pass
             // Walk back over the predecessors' words, RB_LOOK of them in flight at a time: when all blocks of a pass are
             // resident at once (the P-sized depth sort: a few hundred blocks) block i has to look ~i/2 blocks back, and
             // one dependent L2 round trip per block made that walk the longest thing in the kernel.
-            constexpr int RB_LOOK = 8;
+#ifndef VCR_RADIX_LOOK
+#define VCR_RADIX_LOOK 4
+#endif
+            constexpr int RB_LOOK = VCR_RADIX_LOOK;
             int j = (int)bid - 1;
             uint32_t spins = 0;
             bool found = false;
@@ -502,15 +507,26 @@ __global__ void __launch_bounds__(RADIX_THREADS, VCR_RADIX_MINBLOCKS) radix_pass
 // Stable LSD sort of n (u32 key, u32 value) pairs over key bits [0, key_bits), 8 bits per pass.  `hist` holds the digit
 // histogram of every pass ([npass][256], turned into exclusive offsets here); the sorted pairs end in (kA, vA), with
 // (kB, vB) as the other ping-pong buffer.  (kA, vA) may alias the input when the number of passes is even.
+template <int NB>
+static void radix_pass_launch(uint32_t nblocks, cudaStream_t s, const uint32_t* kin, const uint32_t* vin, uint32_t* kout, uint32_t* vout, uint32_t n,
+                              int shift, int nbits, const uint32_t* digit_base, uint32_t* status, uint32_t* ticket) {
+    radix_pass_kernel<NB><<<nblocks, RADIX_THREADS, RADIX_SMEM_BYTES, s>>>(kin, vin, kout, vout, n, shift, nbits, digit_base, status, ticket,
+                                                                           g_radix_spin_limit, g_radix_fault);
+}
+// `balanced`: ceil(bits/8) passes of (almost) equal width (vcr_radix_pass_bits) instead of 8-bit digits and a remainder
 static int radix_sort_run(const uint32_t* kin, const uint32_t* vin, uint32_t* kA, uint32_t* vA, uint32_t* kB, uint32_t* vB,
-                          uint32_t n, int key_bits, uint32_t* hist, uint32_t* status, cudaStream_t s) {
+                          uint32_t n, int key_bits, uint32_t* hist, uint32_t* status, cudaStream_t s, bool balanced = false) {
     // the opt-in shared-memory size is a per-device function attribute (setting it twice is harmless, so a benign race
     // between two host threads on the atomic flag only costs a repeated call)
     static std::atomic<bool> attr_set_dev[64];
     int dev_ = 0;
     VCR_CUDA_TRY(cudaGetDevice(&dev_));
     if (dev_ >= 0 && dev_ < 64 && !attr_set_dev[dev_].load(std::memory_order_acquire)) {
-        VCR_CUDA_TRY(cudaFuncSetAttribute(radix_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, RADIX_SMEM_BYTES));
+        VCR_CUDA_TRY(cudaFuncSetAttribute(radix_pass_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, RADIX_SMEM_BYTES));
+        VCR_CUDA_TRY(cudaFuncSetAttribute(radix_pass_kernel<7>, cudaFuncAttributeMaxDynamicSharedMemorySize, RADIX_SMEM_BYTES));
+        VCR_CUDA_TRY(cudaFuncSetAttribute(radix_pass_kernel<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, RADIX_SMEM_BYTES));
+        VCR_CUDA_TRY(cudaFuncSetAttribute(radix_pass_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, RADIX_SMEM_BYTES));
+        VCR_CUDA_TRY(cudaFuncSetAttribute(radix_pass_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, RADIX_SMEM_BYTES));
         attr_set_dev[dev_].store(true, std::memory_order_release);
     }
     if (key_bits < 1 || key_bits > 32) { vcr_set_error("radix sort: 1..32 key bits"); return 1; }
@@ -527,11 +543,15 @@ static int radix_sort_run(const uint32_t* kin, const uint32_t* vin, uint32_t* kA
         const bool to_final = ((npass - 1 - pass) % 2) == 0;
         uint32_t* kout = to_final ? kA : kB;
         uint32_t* vout = to_final ? vA : vB;
-        const int nbits = key_bits - 8 * pass < 8 ? key_bits - 8 * pass : 8;
+        int shift = 8 * pass, nbits = key_bits - 8 * pass < 8 ? key_bits - 8 * pass : 8;
+        if (balanced) vcr_radix_pass_bits(key_bits, pass, shift, nbits);
         VcrProfScope prof(VCR_K_RADIX_PASS, s);
-        radix_pass_kernel<<<nblocks, RADIX_THREADS, RADIX_SMEM_BYTES, s>>>(kin, vin, kout, vout, n, 8 * pass, nbits, hist + pass * 256,
-                                                                           status + (size_t)pass * nblocks * 256, tickets + pass,
-                                                                           g_radix_spin_limit, g_radix_fault);
+        uint32_t* st_ = status + (size_t)pass * nblocks * 256;
+        if (nbits <= 4) radix_pass_launch<4>(nblocks, s, kin, vin, kout, vout, n, shift, nbits, hist + pass * 256, st_, tickets + pass);
+        else if (nbits == 5) radix_pass_launch<5>(nblocks, s, kin, vin, kout, vout, n, shift, nbits, hist + pass * 256, st_, tickets + pass);
+        else if (nbits == 6) radix_pass_launch<6>(nblocks, s, kin, vin, kout, vout, n, shift, nbits, hist + pass * 256, st_, tickets + pass);
+        else if (nbits == 7) radix_pass_launch<7>(nblocks, s, kin, vin, kout, vout, n, shift, nbits, hist + pass * 256, st_, tickets + pass);
+        else radix_pass_launch<8>(nblocks, s, kin, vin, kout, vout, n, shift, nbits, hist + pass * 256, st_, tickets + pass);
         VCR_LAUNCH_CHECK("radix_pass_kernel");
         kin = kout; vin = vout;
     }
@@ -574,7 +594,7 @@ int vcr_launch_gaussian_sort(int P, GeomState& g, cudaStream_t s) {
 int vcr_launch_tile_sort(BinningState& b, int R, int tile_bits, cudaStream_t s) {
     const bool odd = ((tile_bits + 7) / 8) & 1;
     return radix_sort_run(odd ? b.alt_keys : b.tile_keys, odd ? b.alt_vals : b.point_list, b.tile_keys, b.point_list, b.alt_keys, b.alt_vals,
-                          (uint32_t)R, tile_bits, b.sort_hist, b.sort_status, s);
+                          (uint32_t)R, tile_bits, b.sort_hist, b.sort_status, s, true);
 }
 
 // ------------------------------------------------------------------------------------------------
