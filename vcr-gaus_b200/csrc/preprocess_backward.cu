@@ -201,6 +201,40 @@ __device__ __forceinline__ void preprocess_backward_body(const BwdParams& p, con
                 gsh[3 * k] = bk * gg[0]; gsh[3 * k + 1] = bk * gg[1]; gsh[3 * k + 2] = bk * gg[2];
             }
         }
+        if (M == 16) {
+            // Colour is linear in the coefficients, so d colour / d dir . gg = sum_k (d basis_k / d dir) t_k with
+            // t_k = gg . sh[k]: one dot product per coefficient instead of the three per-channel polynomials, and the row is
+            // read as twelve 16-byte loads (the per-channel form issued 45 scalar loads 192 bytes apart across the warp:
+            // 32 lines per request, the L1 pipe was the limit of this kernel).
+            const float4* sh4 = reinterpret_cast<const float4*>(sh);
+            float t[16];
+#pragma unroll
+            for (int q = 0; q < 4; q++) {           // floats 12q .. 12q+11 = coefficients 4q .. 4q+3
+                const float4 a0 = __ldg(sh4 + 3 * q), a1 = __ldg(sh4 + 3 * q + 1), a2 = __ldg(sh4 + 3 * q + 2);
+                t[4 * q + 0] = a0.x * gg[0] + a0.y * gg[1] + a0.z * gg[2];
+                t[4 * q + 1] = a0.w * gg[0] + a1.x * gg[1] + a1.y * gg[2];
+                t[4 * q + 2] = a1.z * gg[0] + a1.w * gg[1] + a2.x * gg[2];
+                t[4 * q + 3] = a2.y * gg[0] + a2.z * gg[1] + a2.w * gg[2];
+            }
+            if (D > 0) {
+                ddx = -kC1 * t[3]; ddy = -kC1 * t[1]; ddz = kC1 * t[2];
+                if (D > 1) {
+                    ddx += kC2[0] * y * t[4] + kC2[2] * 2.f * -x * t[6] + kC2[3] * z * t[7] + kC2[4] * 2.f * x * t[8];
+                    ddy += kC2[0] * x * t[4] + kC2[1] * z * t[5] + kC2[2] * 2.f * -y * t[6] + kC2[4] * 2.f * -y * t[8];
+                    ddz += kC2[1] * y * t[5] + kC2[2] * 2.f * 2.f * z * t[6] + kC2[3] * x * t[7];
+                    if (D > 2) {
+                        ddx += kC3[0] * t[9] * 3.f * 2.f * xy + kC3[1] * t[10] * yz + kC3[2] * t[11] * -2.f * xy +
+                               kC3[3] * t[12] * -3.f * 2.f * xz + kC3[4] * t[13] * (-3.f * xx + 4.f * zz - yy) +
+                               kC3[5] * t[14] * 2.f * xz + kC3[6] * t[15] * 3.f * (xx - yy);
+                        ddy += kC3[0] * t[9] * 3.f * (xx - yy) + kC3[1] * t[10] * xz + kC3[2] * t[11] * (-3.f * yy + 4.f * zz - xx) +
+                               kC3[3] * t[12] * -3.f * 2.f * yz + kC3[4] * t[13] * -2.f * xy + kC3[5] * t[14] * -2.f * yz +
+                               kC3[6] * t[15] * -3.f * 2.f * xy;
+                        ddz += kC3[1] * t[10] * xy + kC3[2] * t[11] * 4.f * 2.f * yz + kC3[3] * t[12] * 3.f * (2.f * zz - xx - yy) +
+                               kC3[4] * t[13] * 4.f * 2.f * xz + kC3[5] * t[14] * (xx - yy);
+                    }
+                }
+            }
+        } else {
 #pragma unroll
         for (int ch = 0; ch < 3; ch++) {
 #define S(k) __ldg(sh + (k) * 3 + ch)
@@ -225,6 +259,7 @@ __device__ __forceinline__ void preprocess_backward_body(const BwdParams& p, con
             }
 #undef S
             ddx += dx_ * gg[ch]; ddy += dy_ * gg[ch]; ddz += dz_ * gg[ch];
+        }
         }
         // dnormvdv (auxiliary.h:102-113)
         const float sum2 = dox * dox + doy * doy + doz * doz;
