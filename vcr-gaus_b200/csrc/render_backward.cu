@@ -568,14 +568,13 @@ __global__ void __launch_bounds__(RB2_THREADS, VCR_RB2_MINBLOCKS) render_backwar
             v[ACC_COLOR_R] = vcr_mul2(aT, gC0); v[ACC_COLOR_R + 1] = vcr_mul2(aT, gC1); v[ACC_COLOR_R + 2] = vcr_mul2(aT, gC2);
             // depth and normal (backward.cu:643-754); om1 = 1 - accum_rec2 = 1 - accum_alpha_rec
             const float2 om1 = vcr_sub2(one, S1);
-            const float2 aTw = vcr_mul2(aT, inv_weight);
             {
                 const float2 dd = vcr_sub2(c_d, Sd);
                 const float2 t = vcr_fma2(make_float2(-depth_final.x, -depth_final.y), om1, dd);
                 dopa = vcr_fma2(t, kD, dopa);
                 Sd = vcr_fma2(alpha, dd, Sd);
             }
-            const float2 dL_dd_j = vcr_mul2(aTw, gD);
+            const float2 dL_dd_j = vcr_mul2(aT, kD);          // alpha T / weight * dL/ddepth, with kD = dL/ddepth / weight folded per pixel
             float2 dn0 = Z, dn1 = Z, dn2 = Z;
             if (HAS_DIRS) {  // backward.cu:722-728
                 const float4 xv = st.xv[j];
@@ -598,7 +597,7 @@ __global__ void __launch_bounds__(RB2_THREADS, VCR_RB2_MINBLOCKS) render_backwar
                 dopa = vcr_fma2(vcr_fma2(n1, nom1, e1), kN1, dopa);
                 dopa = vcr_fma2(vcr_fma2(n2, nom1, e2), kN2, dopa);
                 Sn0 = vcr_fma2(alpha, e0, Sn0); Sn1 = vcr_fma2(alpha, e1, Sn1); Sn2 = vcr_fma2(alpha, e2, Sn2);
-                v[ACC_NORMAL_X] = vcr_fma2(aTw, gN0, dn0); v[ACC_NORMAL_X + 1] = vcr_fma2(aTw, gN1, dn1); v[ACC_NORMAL_X + 2] = vcr_fma2(aTw, gN2, dn2);
+                v[ACC_NORMAL_X] = vcr_fma2(aT, kN0, dn0); v[ACC_NORMAL_X + 1] = vcr_fma2(aT, kN1, dn1); v[ACC_NORMAL_X + 2] = vcr_fma2(aT, kN2, dn2);
             }
             float2 ex_obj1 = Z;
             v[ACC_OBJ_0] = Z;
