@@ -236,30 +236,30 @@ __device__ __forceinline__ void preprocess_backward_body(const BwdParams& p, con
             }
         } else {
 #pragma unroll
-        for (int ch = 0; ch < 3; ch++) {
+            for (int ch = 0; ch < 3; ch++) {
 #define S(k) __ldg(sh + (k) * 3 + ch)
-            float dx_ = 0.f, dy_ = 0.f, dz_ = 0.f;
-            if (D > 0) {
-                dx_ = -kC1 * S(3); dy_ = -kC1 * S(1); dz_ = kC1 * S(2);
-                if (D > 1) {
-                    dx_ += kC2[0] * y * S(4) + kC2[2] * 2.f * -x * S(6) + kC2[3] * z * S(7) + kC2[4] * 2.f * x * S(8);
-                    dy_ += kC2[0] * x * S(4) + kC2[1] * z * S(5) + kC2[2] * 2.f * -y * S(6) + kC2[4] * 2.f * -y * S(8);
-                    dz_ += kC2[1] * y * S(5) + kC2[2] * 2.f * 2.f * z * S(6) + kC2[3] * x * S(7);
-                    if (D > 2) {
-                        dx_ += kC3[0] * S(9) * 3.f * 2.f * xy + kC3[1] * S(10) * yz + kC3[2] * S(11) * -2.f * xy +
-                               kC3[3] * S(12) * -3.f * 2.f * xz + kC3[4] * S(13) * (-3.f * xx + 4.f * zz - yy) +
-                               kC3[5] * S(14) * 2.f * xz + kC3[6] * S(15) * 3.f * (xx - yy);
-                        dy_ += kC3[0] * S(9) * 3.f * (xx - yy) + kC3[1] * S(10) * xz + kC3[2] * S(11) * (-3.f * yy + 4.f * zz - xx) +
-                               kC3[3] * S(12) * -3.f * 2.f * yz + kC3[4] * S(13) * -2.f * xy + kC3[5] * S(14) * -2.f * yz +
-                               kC3[6] * S(15) * -3.f * 2.f * xy;
-                        dz_ += kC3[1] * S(10) * xy + kC3[2] * S(11) * 4.f * 2.f * yz + kC3[3] * S(12) * 3.f * (2.f * zz - xx - yy) +
-                               kC3[4] * S(13) * 4.f * 2.f * xz + kC3[5] * S(14) * (xx - yy);
+                float dx_ = 0.f, dy_ = 0.f, dz_ = 0.f;
+                if (D > 0) {
+                    dx_ = -kC1 * S(3); dy_ = -kC1 * S(1); dz_ = kC1 * S(2);
+                    if (D > 1) {
+                        dx_ += kC2[0] * y * S(4) + kC2[2] * 2.f * -x * S(6) + kC2[3] * z * S(7) + kC2[4] * 2.f * x * S(8);
+                        dy_ += kC2[0] * x * S(4) + kC2[1] * z * S(5) + kC2[2] * 2.f * -y * S(6) + kC2[4] * 2.f * -y * S(8);
+                        dz_ += kC2[1] * y * S(5) + kC2[2] * 2.f * 2.f * z * S(6) + kC2[3] * x * S(7);
+                        if (D > 2) {
+                            dx_ += kC3[0] * S(9) * 3.f * 2.f * xy + kC3[1] * S(10) * yz + kC3[2] * S(11) * -2.f * xy +
+                                   kC3[3] * S(12) * -3.f * 2.f * xz + kC3[4] * S(13) * (-3.f * xx + 4.f * zz - yy) +
+                                   kC3[5] * S(14) * 2.f * xz + kC3[6] * S(15) * 3.f * (xx - yy);
+                            dy_ += kC3[0] * S(9) * 3.f * (xx - yy) + kC3[1] * S(10) * xz + kC3[2] * S(11) * (-3.f * yy + 4.f * zz - xx) +
+                                   kC3[3] * S(12) * -3.f * 2.f * yz + kC3[4] * S(13) * -2.f * xy + kC3[5] * S(14) * -2.f * yz +
+                                   kC3[6] * S(15) * -3.f * 2.f * xy;
+                            dz_ += kC3[1] * S(10) * xy + kC3[2] * S(11) * 4.f * 2.f * yz + kC3[3] * S(12) * 3.f * (2.f * zz - xx - yy) +
+                                   kC3[4] * S(13) * 4.f * 2.f * xz + kC3[5] * S(14) * (xx - yy);
+                        }
                     }
                 }
-            }
 #undef S
-            ddx += dx_ * gg[ch]; ddy += dy_ * gg[ch]; ddz += dz_ * gg[ch];
-        }
+                ddx += dx_ * gg[ch]; ddy += dy_ * gg[ch]; ddz += dz_ * gg[ch];
+            }
         }
         // dnormvdv (auxiliary.h:102-113)
         const float sum2 = dox * dox + doy * doy + doz * doz;

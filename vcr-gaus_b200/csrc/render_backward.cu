@@ -515,9 +515,15 @@ __global__ void __launch_bounds__(RB2_THREADS, VCR_RB2_MINBLOCKS) render_backwar
 #endif
         }
         uint32_t m = __ballot_sync(0xffffffffu, hit);
-        while (m) {
-            const int j = slot0 + __ffs(m) - 1;
-            m &= m - 1;
+        // One candidate in two halves, like the forward: eval() is everything that does not depend on the running
+        // transmittance and the recurrences (exponent, alpha, depth along the ray, the tests) and ends in the warp's vote;
+        // process() replays the pixel's state and accumulates.  (Issuing the evals of two candidates together, which pays in
+        // the forward, costs registers here: 877 us against 836.)
+        struct Ev { float2 Gr, ipd; bool c0, c1; uint32_t cmask; };      // the rest is cheap to redo in process()
+        auto eval = [&](const int j) -> Ev {
+            Ev e;
+            e.cmask = 0u; e.c0 = false; e.c1 = false;
+            e.Gr = e.ipd = make_float2(0.f, 0.f);
             const uint32_t contributor = (uint32_t)(cbase - j);
             const float4 g0 = *reinterpret_cast<const float4*>(&st.geo[j]);        // x, y, ca, cb
             const float4 g1 = *reinterpret_cast<const float4*>(&st.geo[j].cc);     // cc, op, nx, id
@@ -528,26 +534,43 @@ __global__ void __launch_bounds__(RB2_THREADS, VCR_RB2_MINBLOCKS) render_backwar
             const float2 power = vcr_fma2(q, vcr_bcast2(-0.5f), vcr_mul2(vcr_bcast2(nbdx), dy));
             bool c0 = contributor < lastc0 && !(power.x > 0.0f);
             bool c1 = contributor < lastc1 && !(power.y > 0.0f);
-            if (!__any_sync(0xffffffffu, c0 || c1)) continue;
+            if (!__any_sync(0xffffffffu, c0 || c1)) return e;
             // Fast intrinsics from here on: the backward only has to meet 1e-3 relative L2 (the forward, which must
             // match the reference bit for bit, keeps expf and IEEE division).
-            const float2 Gr = make_float2(__expf(power.x), __expf(power.y));
-            const float2 ar = make_float2(fminf(0.99f, g1.y * Gr.x), fminf(0.99f, g1.y * Gr.y));
+            e.Gr = make_float2(__expf(power.x), __expf(power.y));
+            const float2 ar = make_float2(fminf(0.99f, g1.y * e.Gr.x), fminf(0.99f, g1.y * e.Gr.y));
             c0 = c0 && !(ar.x < 1.0f / 255.0f);
             c1 = c1 && !(ar.y < 1.0f / 255.0f);
             const float4 nrm = st.nrm[j];
-            float2 pd = make_float2(1.f, 1.f), ipd = pd, cdr;
+            float2 pd = make_float2(1.f, 1.f), cdr; e.ipd = pd;
             if (HAS_DIRS) {
-                pd = vcr_fma2(vcr_bcast2(nrm.z), dirz, vcr_fma2(vcr_bcast2(nrm.x), dirx, vcr_mul2(vcr_bcast2(nrm.y), diry)));
-                ipd = make_float2(__fdividef(1.0f, pd.x), __fdividef(1.0f, pd.y));
-                cdr = vcr_mul2(vcr_mul2(vcr_bcast2(g1.z), ipd), dirz);
+            pd = vcr_fma2(vcr_bcast2(nrm.z), dirz, vcr_fma2(vcr_bcast2(nrm.x), dirx, vcr_mul2(vcr_bcast2(nrm.y), diry)));
+            e.ipd = make_float2(__fdividef(1.0f, pd.x), __fdividef(1.0f, pd.y));
+            cdr = vcr_mul2(vcr_mul2(vcr_bcast2(g1.z), e.ipd), dirz);
             } else {
-                cdr = vcr_bcast2(g1.z);
+            cdr = vcr_bcast2(g1.z);
             }
             c0 = c0 && !(cdr.x < 0.2f);  // == (double)c_d < 0.2, backward.cu:616
             c1 = c1 && !(cdr.y < 0.2f);
-            const uint32_t cmask = __ballot_sync(0xffffffffu, c0 || c1);
-            if (cmask == 0u) continue;
+            e.c0 = c0; e.c1 = c1;
+            e.cmask = __ballot_sync(0xffffffffu, c0 || c1);
+            return e;
+        };
+        auto process = [&](const int j, const Ev& e) {
+            const float4 g0 = *reinterpret_cast<const float4*>(&st.geo[j]);        // x, y, ca, cb
+            const float4 g1 = *reinterpret_cast<const float4*>(&st.geo[j].cc);     // cc, op, nx, id
+            const float4 nrm = st.nrm[j];
+            const float dx = g0.x - pfx;
+            const float2 dy = vcr_add2(vcr_bcast2(g0.y), npfy);
+            const bool c0 = e.c0, c1 = e.c1;
+            const uint32_t cmask = e.cmask;
+            const float2 Gr = e.Gr;
+            const float2 ar = make_float2(fminf(0.99f, g1.y * Gr.x), fminf(0.99f, g1.y * Gr.y));
+            float2 ipd = e.ipd, pd = make_float2(1.f, 1.f), cdr = vcr_bcast2(g1.z);
+            if (HAS_DIRS) {
+                pd = vcr_fma2(vcr_bcast2(nrm.z), dirz, vcr_fma2(vcr_bcast2(nrm.x), dirx, vcr_mul2(vcr_bcast2(nrm.y), diry)));
+                cdr = vcr_mul2(vcr_mul2(vcr_bcast2(g1.z), ipd), dirz);
+            }
 
             // a pixel that does not take this Gaussian: alpha = G = 0 (and finite stand-ins where it may hold inf / NaN)
             const float2 alpha = make_float2(c0 ? ar.x : 0.f, c1 ? ar.y : 0.f);
@@ -569,45 +592,45 @@ __global__ void __launch_bounds__(RB2_THREADS, VCR_RB2_MINBLOCKS) render_backwar
             // depth and normal (backward.cu:643-754); om1 = 1 - accum_rec2 = 1 - accum_alpha_rec
             const float2 om1 = vcr_sub2(one, S1);
             {
-                const float2 dd = vcr_sub2(c_d, Sd);
-                const float2 t = vcr_fma2(make_float2(-depth_final.x, -depth_final.y), om1, dd);
-                dopa = vcr_fma2(t, kD, dopa);
-                Sd = vcr_fma2(alpha, dd, Sd);
+            const float2 dd = vcr_sub2(c_d, Sd);
+            const float2 t = vcr_fma2(make_float2(-depth_final.x, -depth_final.y), om1, dd);
+            dopa = vcr_fma2(t, kD, dopa);
+            Sd = vcr_fma2(alpha, dd, Sd);
             }
             const float2 dL_dd_j = vcr_mul2(aT, kD);          // alpha T / weight * dL/ddepth, with kD = dL/ddepth / weight folded per pixel
             float2 dn0 = Z, dn1 = Z, dn2 = Z;
             if (HAS_DIRS) {  // backward.cu:722-728
-                const float4 xv = st.xv[j];
-                const float2 sv = vcr_mul2(vcr_mul2(dL_dd_j, dirz), ipd);      // dL/dxyz_view = normal * sum(sv)
-                const float2 s2 = vcr_mul2(sv, ipd);
-                const float2 nnx = vcr_bcast2(-g1.z);
-                dn0 = vcr_mul2(s2, vcr_fma2(pd, vcr_bcast2(xv.x), vcr_mul2(dirx, nnx)));
-                dn1 = vcr_mul2(s2, vcr_fma2(pd, vcr_bcast2(xv.y), vcr_mul2(diry, nnx)));
-                dn2 = vcr_mul2(s2, vcr_fma2(pd, vcr_bcast2(xv.z), vcr_mul2(dirz, nnx)));
-                v[ACC_SV_OR_DEPTH] = sv;
+            const float4 xv = st.xv[j];
+            const float2 sv = vcr_mul2(vcr_mul2(dL_dd_j, dirz), ipd);      // dL/dxyz_view = normal * sum(sv)
+            const float2 s2 = vcr_mul2(sv, ipd);
+            const float2 nnx = vcr_bcast2(-g1.z);
+            dn0 = vcr_mul2(s2, vcr_fma2(pd, vcr_bcast2(xv.x), vcr_mul2(dirx, nnx)));
+            dn1 = vcr_mul2(s2, vcr_fma2(pd, vcr_bcast2(xv.y), vcr_mul2(diry, nnx)));
+            dn2 = vcr_mul2(s2, vcr_fma2(pd, vcr_bcast2(xv.z), vcr_mul2(dirz, nnx)));
+            v[ACC_SV_OR_DEPTH] = sv;
             } else {
-                v[ACC_SV_OR_DEPTH] = dL_dd_j;
+            v[ACC_SV_OR_DEPTH] = dL_dd_j;
             }
             {
-                // reference quirk kept: the "final normal" of the normalisation term is this Gaussian's own n (backward.cu:741-745)
-                const float2 n0 = vcr_bcast2(nrm.x), n1 = vcr_bcast2(nrm.y), n2 = vcr_bcast2(nrm.z);
-                const float2 e0 = vcr_sub2(n0, Sn0), e1 = vcr_sub2(n1, Sn1), e2 = vcr_sub2(n2, Sn2);
-                const float2 nom1 = make_float2(-om1.x, -om1.y);
-                dopa = vcr_fma2(vcr_fma2(n0, nom1, e0), kN0, dopa);
-                dopa = vcr_fma2(vcr_fma2(n1, nom1, e1), kN1, dopa);
-                dopa = vcr_fma2(vcr_fma2(n2, nom1, e2), kN2, dopa);
-                Sn0 = vcr_fma2(alpha, e0, Sn0); Sn1 = vcr_fma2(alpha, e1, Sn1); Sn2 = vcr_fma2(alpha, e2, Sn2);
-                v[ACC_NORMAL_X] = vcr_fma2(aT, kN0, dn0); v[ACC_NORMAL_X + 1] = vcr_fma2(aT, kN1, dn1); v[ACC_NORMAL_X + 2] = vcr_fma2(aT, kN2, dn2);
+            // reference quirk kept: the "final normal" of the normalisation term is this Gaussian's own n (backward.cu:741-745)
+            const float2 n0 = vcr_bcast2(nrm.x), n1 = vcr_bcast2(nrm.y), n2 = vcr_bcast2(nrm.z);
+            const float2 e0 = vcr_sub2(n0, Sn0), e1 = vcr_sub2(n1, Sn1), e2 = vcr_sub2(n2, Sn2);
+            const float2 nom1 = make_float2(-om1.x, -om1.y);
+            dopa = vcr_fma2(vcr_fma2(n0, nom1, e0), kN0, dopa);
+            dopa = vcr_fma2(vcr_fma2(n1, nom1, e1), kN1, dopa);
+            dopa = vcr_fma2(vcr_fma2(n2, nom1, e2), kN2, dopa);
+            Sn0 = vcr_fma2(alpha, e0, Sn0); Sn1 = vcr_fma2(alpha, e1, Sn1); Sn2 = vcr_fma2(alpha, e2, Sn2);
+            v[ACC_NORMAL_X] = vcr_fma2(aT, kN0, dn0); v[ACC_NORMAL_X + 1] = vcr_fma2(aT, kN1, dn1); v[ACC_NORMAL_X + 2] = vcr_fma2(aT, kN2, dn2);
             }
             float2 ex_obj1 = Z;
             v[ACC_OBJ_0] = Z;
             if (HAS_OBJ) {
-                // dL_dalpha += (o - accum_rec_obj) * dL_dpixel_obj persists across Gaussians (backward.cu:766); contributing pixels only
-                const float2 f0 = vcr_sub2(vcr_bcast2(nrm.w), So0), f1 = vcr_sub2(vcr_bcast2(col.w), So1);
-                const float2 add = vcr_fma2(f1, gO1, vcr_mul2(f0, gO0));
-                gA = make_float2(c0 ? gA.x + add.x : gA.x, c1 ? gA.y + add.y : gA.y);
-                So0 = vcr_fma2(alpha, f0, So0); So1 = vcr_fma2(alpha, f1, So1);
-                v[ACC_OBJ_0] = vcr_mul2(aT, gO0); ex_obj1 = vcr_mul2(aT, gO1);
+            // dL_dalpha += (o - accum_rec_obj) * dL_dpixel_obj persists across Gaussians (backward.cu:766); contributing pixels only
+            const float2 f0 = vcr_sub2(vcr_bcast2(nrm.w), So0), f1 = vcr_sub2(vcr_bcast2(col.w), So1);
+            const float2 add = vcr_fma2(f1, gO1, vcr_mul2(f0, gO0));
+            gA = make_float2(c0 ? gA.x + add.x : gA.x, c1 ? gA.y + add.y : gA.y);
+            So0 = vcr_fma2(alpha, f0, So0); So1 = vcr_fma2(alpha, f1, So1);
+            v[ACC_OBJ_0] = vcr_mul2(aT, gO0); ex_obj1 = vcr_mul2(aT, gO1);
             }
             dopa = vcr_fma2(om1, gA, dopa);                                   // (1 - accum_alpha_rec) * dL_dalpha
             S1 = vcr_fma2(alpha, om1, S1);
@@ -628,19 +651,25 @@ __global__ void __launch_bounds__(RB2_THREADS, VCR_RB2_MINBLOCKS) render_backwar
             const float eo1 = ex_obj1.x + ex_obj1.y;
             float* rec = acc + (size_t)__float_as_uint(g1.w) * VCR_ACC_STRIDE;
             if (__popc(cmask) <= RB_SPARSE_LANES) {
-                if (c0 || c1) {
+            if (c0 || c1) {
 #pragma unroll
-                    for (int q_ = 0; q_ < (HAS_OBJ ? 16 : 15); q_++) atomicAdd(rec + q_, s[q_]);
-                    if (HAS_OBJ) atomicAdd(rec + ACC_OBJ_1, eo1);
-                }
-                continue;
+                for (int q_ = 0; q_ < (HAS_OBJ ? 16 : 15); q_++) atomicAdd(rec + q_, s[q_]);
+                if (HAS_OBJ) atomicAdd(rec + ACC_OBJ_1, eo1);
+            }
+            return;
             }
             const float red = warp_reduce16_transposed(s, lane);
             if (lane < (HAS_OBJ ? 16 : 15)) atomicAdd(rec + lane, red);
             if (HAS_OBJ) {
-                const float o1 = vcr_warp_sum(eo1);
-                if (lane == 16) atomicAdd(rec + ACC_OBJ_1, o1);
+            const float o1 = vcr_warp_sum(eo1);
+            if (lane == 16) atomicAdd(rec + ACC_OBJ_1, o1);
             }
+        };
+        while (m) {
+            const int ja = slot0 + __ffs(m) - 1;
+            m &= m - 1;
+            const Ev ea = eval(ja);
+            if (ea.cmask) process(ja, ea);
         }
     };
 
