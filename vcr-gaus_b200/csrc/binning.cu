@@ -601,15 +601,28 @@ int vcr_launch_tile_sort(BinningState& b, int R, int tile_bits, cudaStream_t s) 
 // Tile ranges (identifyTileRanges, rasterizer_impl.cu:116-138).
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) tile_ranges_kernel(uint32_t L, const uint32_t* __restrict__ keys, uint2* __restrict__ ranges) {
-    const uint32_t idx = blockIdx.x * 256u + threadIdx.x;
+    // four consecutive keys per thread (one 16-byte load) and the key before them
+    const uint32_t idx = 4u * (blockIdx.x * 256u + threadIdx.x);
     if (idx >= L || g_radix_timeout) return;           // (a failed sort leaves garbage tile ids: do not index with them)
-    const uint32_t cur = keys[idx];                    // the production keys are bare tile ids
-    if (idx == 0) ranges[cur].x = 0;
-    else {
-        const uint32_t prev = keys[idx - 1];
-        if (cur != prev) { ranges[prev].y = idx; ranges[cur].x = idx; }
+    uint32_t k[4];                                     // the production keys are bare tile ids
+    if (idx + 4u <= L) {
+        const uint4 q = *reinterpret_cast<const uint4*>(keys + idx);
+        k[0] = q.x; k[1] = q.y; k[2] = q.z; k[3] = q.w;
+    } else {
+#pragma unroll
+        for (int e = 0; e < 4; e++) k[e] = idx + e < L ? keys[idx + e] : 0u;
     }
-    if (idx == L - 1) ranges[cur].y = L;
+    uint32_t prev = idx ? keys[idx - 1] : 0u;
+#pragma unroll
+    for (int e = 0; e < 4; e++) {
+        const uint32_t i = idx + e;
+        if (i >= L) break;
+        const uint32_t cur = k[e];
+        if (i == 0) ranges[cur].x = 0;
+        else if (cur != prev) { ranges[prev].y = i; ranges[cur].x = i; }
+        if (i == L - 1) ranges[cur].y = L;
+        prev = cur;
+    }
 }
 
 // Block schedule for the compositing kernels: tile ids ordered by list length, longest first (coarse: by
@@ -644,7 +657,7 @@ int vcr_launch_tile_ranges(BinningState& b, ImageState& img, int R, int tiles, c
     { VcrProfScope m(VCR_K_MEMSET, s); VCR_CUDA_TRY(cudaMemsetAsync(img.ranges, 0, (size_t)tiles * sizeof(uint2), s)); }
     if (R > 0) {
         VcrProfScope prof(VCR_K_TILE_RANGES, s);
-        tile_ranges_kernel<<<((uint32_t)R + 255u) / 256u, 256, 0, s>>>((uint32_t)R, b.tile_keys, img.ranges);
+        tile_ranges_kernel<<<((uint32_t)R + 1023u) / 1024u, 256, 0, s>>>((uint32_t)R, b.tile_keys, img.ranges);
         VCR_LAUNCH_CHECK("tile_ranges_kernel");
     }
     {

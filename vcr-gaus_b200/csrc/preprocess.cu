@@ -165,7 +165,10 @@ __device__ float3 sh_to_rgb_generic(int deg, int M, const float3 pos, const floa
     return make_float3(res[0], res[1], res[2]);
 }
 
-__global__ void __launch_bounds__(256) preprocess_kernel(const FwdParams p, const GeomState g) {
+#ifndef VCR_PRE_MINBLOCKS
+#define VCR_PRE_MINBLOCKS 3
+#endif
+__global__ void __launch_bounds__(256, VCR_PRE_MINBLOCKS) preprocess_kernel(const FwdParams p, const GeomState g) {
     const int idx = blockIdx.x * 256 + threadIdx.x;
     __shared__ float sV[16], sP[16];
     __shared__ uint32_t warp_tiles[8];
