@@ -197,7 +197,7 @@ static int forward_front(vcr_alloc_fn geometry_buffer, vcr_alloc_fn binning_buff
     if (read_back_end(rb, host)) return 1;
     if (host[1]) { vcr_set_error("Point is filtered although prefiltered is set. This shouldn't happen!"); return 1; }
     if (host[3]) {
-        vcr_set_error("radix sort look-back timed out in an earlier call on this device: the instance lists (and every result) of that "
+        vcr_set_error("radix sort look-back timed out in an earlier call on this device (or a staging-ring wait of its compositing kernels): the instance lists (and every result) of that "
                       "call are invalid");
         return 1;
     }

@@ -715,7 +715,7 @@ __global__ void __launch_bounds__(RB2_THREADS, VCR_RB2_MINBLOCKS) render_backwar
                 if (!try_stage(nchunks)) {
                     __nanosleep(32);
                     // never reached unless the protocol is broken: leave through the error flag of the sort instead of hanging
-                    if (++spins > (1u << 22)) { atomicExch(const_cast<unsigned int*>(abort_flag), 1u); broken = true; break; }
+                    if (++spins > (VCR_RING_SPIN_LIMIT)) { atomicExch(const_cast<unsigned int*>(abort_flag), 1u); broken = true; break; }
                 }
             }
             if (broken) break;
@@ -727,7 +727,7 @@ __global__ void __launch_bounds__(RB2_THREADS, VCR_RB2_MINBLOCKS) render_backwar
             if (lane == 0) v_tail[warp] = my + 1u;
         }
         if (lane == 0) v_tail[warp] = 0xffffffffu;
-        for (uint32_t spins = 0; spins < (1u << 22); ) {        // finished (or nothing to do): keep staging for the others
+        for (uint32_t spins = 0; spins < (VCR_RING_SPIN_LIMIT); ) {        // finished (or nothing to do): keep staging for the others
             if (*v_next >= nchunks) break;
             if ((v_tail[0] & v_tail[1] & v_tail[2] & v_tail[3]) == 0xffffffffu) break;
             if (!try_stage(nchunks)) { __nanosleep(64); spins++; }

@@ -537,10 +537,10 @@ __global__ void __launch_bounds__(RF2_THREADS, VCR_RF2_MINBLOCKS) render_forward
                     __nanosleep(32);
                     // never reached unless the protocol is broken: leave through the error flag of the sort (reported by the
                     // next call) instead of hanging the device
-                    if (++spins > (1u << 22)) { atomicExch(const_cast<unsigned int*>(abort_flag), 1u); break; }
+                    if (++spins > (VCR_RING_SPIN_LIMIT)) { atomicExch(const_cast<unsigned int*>(abort_flag), 1u); break; }
                 }
             }
-            if (spins > (1u << 22)) break;
+            if (spins > (VCR_RING_SPIN_LIMIT)) break;
             __threadfence_block();
             if (STATS) st_wait += clock64() - st_b0;
             const bool done = consume(st, (int)((32u * my) % RF2_SLOTS), min(32, total - (int)(32u * my)), (int)(32u * my - (32u * my) % RF2_SLOTS));
@@ -552,7 +552,7 @@ __global__ void __launch_bounds__(RF2_THREADS, VCR_RF2_MINBLOCKS) render_forward
         if (lane == 0) v_tail[warp] = 0xffffffffu;
         // A warp that has finished keeps staging for the others (they would otherwise pay the load latency of every chunk
         // themselves — in the longest tiles one warp is often the only one left for most of the list).
-        for (uint32_t spins = 0; spins < (1u << 22); ) {
+        for (uint32_t spins = 0; spins < (VCR_RING_SPIN_LIMIT); ) {
             if (*v_next >= nchunks) break;                                                              // everything is staged
             if ((v_tail[0] & v_tail[1] & v_tail[2] & v_tail[3]) == 0xffffffffu) break;                  // nobody is left to read it
             if (!try_stage(nchunks)) { __nanosleep(64); spins++; }
