@@ -46,7 +46,37 @@ def test_ab_at_bench_size():
     _check_ab(inp, 1920, 1080, False)
 
 
-def _check_ab(inp, W, H, use_sem):
+# Shapes that stress the two-pixel kernels' 8x8 quadrants and their staging ring (chunks claimed by the warps, no block barrier):
+# widths / heights that are not multiples of 8 or 2 (ragged quadrants, a second pixel outside the image), images smaller than
+# a tile and than a quadrant, and opaque large Gaussians in front (every pixel saturates after a few entries of lists that are
+# thousands long: the warps of a tile finish at different chunks and go on staging for the others).
+# Last column: gate on the gradients' relative L2.  The second scene (opacity 0.999, scales x 8: Gaussians as large as the
+# image, every alpha clamped at 0.99) is badly conditioned for everybody — two runs of the REFERENCE differ by 3.6e-4 in
+# dL_dmeans3D from the order of its float atomics alone (tools/ab_noise.py), this library's two-pixel and one-pixel backward by
+# 1.1e-3 and 1.4e-3 from the reference and by 3.6e-4 from each other — so it is gated at 3e-3; its images are still compared
+# bit for bit.
+RING_CASES = [
+    (50_000, 333, 251, 4.0, 0.99, 20, 1e-3),
+    (20_000, 517, 299, 8.0, 0.999, 21, 3e-3),
+    (500, 17, 9, 1.0, None, 22, 1e-3),
+    (300, 5, 3, 2.0, 0.9, 23, 1e-3),
+    (40_000, 2, 700, 3.0, None, 24, 1e-3),
+    (250_000, 640, 360, 3.0, 0.98, 25, 1e-3),
+]
+
+
+@pytest.mark.parametrize("P,W,H,scale,opacity,seed,gtol", RING_CASES)
+def test_ab_ragged_and_saturating_scenes(P, W, H, scale, opacity, seed, gtol):
+    if ref_ab.load() is None:
+        pytest.skip("oracle/_ref reference extension not built / not loadable here")
+    inp, sc, cam = make_case(P, W, H, seed=seed, use_dirs=True, use_sem=(seed % 2 == 1), sh_degree=3)
+    inp["scales"] = inp["scales"] * scale
+    if opacity is not None:
+        inp["opacities"] = torch.full_like(inp["opacities"], opacity)
+    _check_ab(inp, W, H, seed % 2 == 1, gtol)
+
+
+def _check_ab(inp, W, H, use_sem, gtol=1e-3):
     ref = ref_ab.RefRun(inp)
     run = CudaRun(inp)
     rd, cd = ref.decode(), run.decode()
@@ -80,9 +110,9 @@ def _check_ab(inp, W, H, use_sem):
     for k in ("dL_dmeans3D", "dL_dmeans2D", "dL_dmeans2D_densify", "dL_dsh", "dL_dnormals", "dL_dopacity", "dL_dscales",
               "dL_drotations"):
         e = rel_l2(cb[k], rb[k])
-        assert e <= 1e-3, f"{k}: relative L2 error {e}"
+        assert e <= gtol, f"{k}: relative L2 error {e}"
     if use_sem:
-        assert rel_l2(cb["dL_dobjects"], rb["dL_dobjects"]) <= 1e-3
+        assert rel_l2(cb["dL_dobjects"], rb["dL_dobjects"]) <= gtol
 
 
 def test_ab_knn():
