@@ -261,3 +261,17 @@ def test_radix_timeout_is_reported_not_swallowed(tmp_path, monkeypatch):
     finally:
         N.vcr_debug_radix_fault(0)
     assert torch.equal(forward(), good)
+
+
+def test_packed_expf_is_the_library_expf_for_every_argument():
+    """render_forward2_kernel evaluates expf for its two pixels with packed FMAs (vcr_expf2, csrc/common.cuh); the images stay
+    bit-identical to the reference build only if that is expf for every input.  tools/expf2_check.cu compares the two over all
+    2^32 arguments on both lanes (built by __graft_entry__.build(); about two seconds on a B200)."""
+    import os
+    import subprocess
+    exe = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools", "bin", "expf2_check")
+    if not os.path.exists(exe):
+        pytest.skip("tools/bin/expf2_check not built (run __graft_entry__.build())")
+    res = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0 and " 0 mismatching arguments" in res.stdout, res.stdout + res.stderr
+
