@@ -77,6 +77,21 @@ def measure_view_costs(args, bucket, views, dev):
     return costs
 
 
+def unpack_u8(u8):
+    """uint8 ground truth -> the float image u8 / 255, by the library's kernel, on the current (copy) stream."""
+    import vcr_native as N
+    out = torch.empty(u8.shape, dtype=torch.float32, device=u8.device)
+    N.check(N.vcr_unpack_u8(u8.data_ptr(), out.data_ptr(), u8.numel(), torch.cuda.current_stream(u8.device).cuda_stream), "unpack_u8")
+    return out
+
+
+def wire_unpack(vp):
+    """Wire format of the ground-truth image in the e2e region: float32 on one GPU (the copy hides behind the step, an unpack
+    kernel only adds work), uint8 + vcr_unpack_u8 when several ranks share the host's memory system.  VCR_BENCH_WIRE overrides."""
+    w = os.environ.get("VCR_BENCH_WIRE", "u8" if vp.world > 1 else "f32")
+    return unpack_u8 if w == "u8" else None
+
+
 def clone_params(scene, dev, vp):
     """Rasterizer-input parameters + flat gradient bucket.  With a ViewParallel layer at N > 1 the bucket is placed in
     symmetric memory so that the gradient exchange can go through the NVSwitch multicast kernel (VCR_BENCH_TRANSPORT=nccl
@@ -106,7 +121,7 @@ class HotPathStepper:
         self.args, self.dev, self.vp = args, dev, vp
         self.bucket = bucket = clone_params(scene, dev, vp)
         self.views = views
-        self.feed = BC.ViewFeeder(views, dev, extra=("dL_dout",) if args.step_kind == "raster" else ())
+        self.feed = BC.ViewFeeder(views, dev, extra=("dL_dout",) if args.step_kind == "raster" else (), u8_image=wire_unpack(vp))
         P = bucket.P
         self.inside = torch.ones(P, dtype=torch.bool, device=dev)
         self.xyz_gradient_accum = torch.zeros((P, 1), device=dev)
@@ -223,7 +238,7 @@ class TrainStepper:
         from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
         self.GRS, self.GR, self.VP = GaussianRasterizationSettings, GaussianRasterizer, VP
         self.args, self.dev, self.vp = args, dev, vp
-        self.feed = BC.ViewFeeder(views, dev)
+        self.feed = BC.ViewFeeder(views, dev, u8_image=wire_unpack(vp))
         self.views = views
         raw = {k: v.to(dev) for k, v in BC.raw_parameters(scene).items()}
         store = None
@@ -433,7 +448,9 @@ def main():
                       "view_sharding": "cost-balanced (balanced_view_table)" if balanced else "every world-th camera",
                       "verified": exchange_check} if world > 1 else None),
         "e2e": {"value": e2e_vps, "unit": "views/s", "h2d_bytes_per_step": stepper.feed.h2d_bytes, "d2h_bytes_per_step": stepper.d2h_bytes,
-                "ms_per_step": ms_e2e / args.steps},
+                "ms_per_step": ms_e2e / args.steps,
+                "wire": ("ground-truth image as uint8 (its file format), unpacked to u8/255 on the copy stream" if stepper.feed.u8_image
+                         else "ground-truth image f32") + "; ground-truth normal, camera block f32"},
     }
     if hasattr(stepper, "P_history"):
         out["gaussians_after_each_densification"] = stepper.P_history

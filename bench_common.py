@@ -118,9 +118,12 @@ def build_views(args, scene, world, view_ids, light=False):
         if not light:
             g = torch.Generator().manual_seed(10_000 + gid)
             H, W = args.height, args.width
-            gt_image = torch.rand((3, H, W), generator=g)
+            # 8-bit ground truth, as image files hold it; the float image both arms train on is u8 / 255 (what the
+            # reference's loader computes, utils/general_utils.py PILtoTorch)
+            gt_u8 = torch.randint(0, 256, (3, H, W), generator=g, dtype=torch.uint8)
+            gt_image = gt_u8.to(torch.float32) / 255.0
             gt_normal = F.normalize(torch.randn((H, W, 3), generator=g) * 0.4 + torch.tensor([0.0, 0.0, -1.0]), dim=-1)
-            view.update(gt_image=gt_image.contiguous(), gt_normal=gt_normal.contiguous())
+            view.update(gt_image=gt_image.contiguous(), gt_image_u8=gt_u8.contiguous(), gt_normal=gt_normal.contiguous())
             if args.step_kind == "raster":
                 view.update(dL_dout=torch.randn((10, H, W), generator=g).contiguous())
         views.append(view)
@@ -266,18 +269,29 @@ class ViewFeeder:
     (`value`) or copied every step from pinned host memory on a side stream, one view ahead of the compute stream (`e2e`;
     the copies stay inside the timed region, they are only overlapped).  Used identically by both arms."""
 
-    def __init__(self, views, dev, extra=()):
-        self.dev, self.n = dev, len(views)
+    def __init__(self, views, dev, extra=(), u8_image=None):
+        """u8_image: None, or a function (uint8 device tensor) -> float32 device tensor run on the current stream.  With it the
+        ground-truth image crosses the bus as the 8-bit image it is (6.2 MB at 1080p instead of 24.9 MB) and becomes u8 / 255
+        on the device, on the copy stream — checked here to be bit-identical to the float image of the other wire format."""
+        self.dev, self.n, self.u8_image = dev, len(views), u8_image
         self.host, self.devv = [], []
         for v in views:
             inp = v["inp"]
-            h = dict(gt_image=v["gt_image"].pin_memory(), gt_normal=v["gt_normal"].pin_memory(),
+            h = dict(gt_normal=v["gt_normal"].pin_memory(),
                      cam=torch.cat([inp["viewmatrix"].reshape(-1), inp["projmatrix"].reshape(-1), inp["campos"].reshape(-1),
                                     inp["bg"].reshape(-1)]).pin_memory())
+            if u8_image:
+                h["gt_image_u8"] = v["gt_image_u8"].pin_memory()
+            else:
+                h["gt_image"] = v["gt_image"].pin_memory()
             for name in extra:
                 h[name] = v[name].pin_memory()
             self.host.append(h)
-            self.devv.append({k: t.to(dev) for k, t in h.items()})
+            d = {k: t.to(dev) for k, t in h.items()}
+            if u8_image:
+                d["gt_image"] = u8_image(d.pop("gt_image_u8"))
+                assert torch.equal(d["gt_image"].cpu(), v["gt_image"]), "u8 / 255 on the device differs from the loader's float image"
+            self.devv.append(d)
         self.h2d_bytes = sum(t.numel() * t.element_size() for t in self.host[0].values())
         self.copy_stream = torch.cuda.Stream(device=dev)
         self._prefetched = None
@@ -286,6 +300,8 @@ class ViewFeeder:
         k = i % self.n
         with torch.cuda.stream(self.copy_stream):
             d = {name: t.to(self.dev, non_blocking=True) for name, t in self.host[k].items()}
+            if self.u8_image:
+                d["gt_image"] = self.u8_image(d.pop("gt_image_u8"))
             ev = torch.cuda.Event()
             ev.record(self.copy_stream)
         for t in d.values():                      # keep the tensors alive on the compute stream's timeline

@@ -225,6 +225,10 @@ int vcr_binning_reference_lists(int P, int R, int width, int height, const int* 
 /* *loss (device f32) = w_l1*s0/(3N) + w_mono*(s1+s2)/N + w_dn*(s3+s4)/s5 (last term 0 when s5 == 0) from the sums of
  * vcr_view_loss_forward, N = width*height: one launch instead of a dozen single-element PyTorch launches. */
 int vcr_view_loss_total(const float* sums, int width, int height, float w_l1, float w_mono, float w_dn, float* loss, void* stream);
+/* dst[i] = (float)src[i] / 255 for n 8-bit samples (IEEE division: the float image the reference's loader forms,
+ * utils/general_utils.py PILtoTorch), so that ground-truth images can cross the bus in their file format.  No counterpart in
+ * the reference (it keeps float images on the device).  src and dst 16-byte aligned. */
+int vcr_unpack_u8(const uint8_t* src, float* dst, long long n, void* stream);
 
 /* Everything render() computes per Gaussian before it calls the rasterizer, fused:
  *   opacities = sigmoid(opacity_raw), scales = exp(scaling_raw), rotations = normalize(rotation_raw),

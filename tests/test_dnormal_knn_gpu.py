@@ -158,3 +158,18 @@ def test_fused_view_loss_matches_the_pytorch_composition(W, H, use_mask):
         e = rel_l2(o32.grad[sl].cpu().numpy(), o.grad[sl].cpu().numpy())
         assert e <= 1e-3, f"{name}: relative L2 error {e}"
     assert float(o32.grad[7:].abs().max()) == 0.0
+
+
+def test_unpack_u8_is_the_loaders_float_image():
+    """vcr_unpack_u8 (ground truth crosses the bus as 8-bit): (float)u8 / 255 with IEEE division, i.e. bit-identical to
+    torch.from_numpy(np.array(image)) / 255.0 of the reference's loader (utils/general_utils.py PILtoTorch); sizes that are
+    and are not multiples of the 16 samples a thread converts."""
+    import vcr_native as N
+    for n in (16 * 1000, 3 * 1080 * 1920, 16 * 7 + 5, 1):
+        u8 = torch.randint(0, 256, (n,), dtype=torch.uint8, generator=torch.Generator().manual_seed(n))
+        want = u8.to(torch.float32) / 255.0
+        d = u8.cuda()
+        out = torch.empty(n, dtype=torch.float32, device="cuda")
+        N.check(N.vcr_unpack_u8(d.data_ptr(), out.data_ptr(), n, torch.cuda.current_stream().cuda_stream), "unpack_u8")
+        assert torch.equal(out.cpu(), want)
+

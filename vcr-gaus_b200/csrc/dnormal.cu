@@ -407,3 +407,28 @@ int vcr_dnormal_backward(const float* depth, const float* gt_normal, const float
 }
 
 }  // extern "C"
+
+// Ground-truth images cross the bus as the 8-bit images they are; dst = (float)src / 255 (IEEE division: the value the reference's
+// loader computes, utils/general_utils.py PILtoTorch).  Sixteen pixels per thread.
+__global__ void __launch_bounds__(256) unpack_u8_kernel(const uint8_t* __restrict__ src, float* __restrict__ dst, const long long n) {
+    const long long i = 16ll * ((long long)blockIdx.x * 256 + threadIdx.x);
+    if (i + 16 <= n) {
+        const uint4 q = __ldg(reinterpret_cast<const uint4*>(src + i));
+        const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+            reinterpret_cast<float4*>(dst + i)[k] = make_float4(__fdiv_rn((float)(w[k] & 255u), 255.0f), __fdiv_rn((float)((w[k] >> 8) & 255u), 255.0f),
+                                                                __fdiv_rn((float)((w[k] >> 16) & 255u), 255.0f), __fdiv_rn((float)(w[k] >> 24), 255.0f));
+    } else {
+        for (long long j = i; j < n; j++) dst[j] = __fdiv_rn((float)src[j], 255.0f);
+    }
+}
+extern "C" int vcr_unpack_u8(const uint8_t* src, float* dst, long long n, void* stream) {
+    if (n <= 0) return 0;
+    if ((reinterpret_cast<uintptr_t>(src) & 15) || (reinterpret_cast<uintptr_t>(dst) & 15)) { vcr_set_error("vcr_unpack_u8: src and dst must be 16-byte aligned"); return 1; }
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const long long threads = (n + 15) / 16;
+    unpack_u8_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(src, dst, n);
+    VCR_LAUNCH_CHECK("unpack_u8_kernel");
+    return 0;
+}

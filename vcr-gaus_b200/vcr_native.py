@@ -72,6 +72,7 @@ vcr_prologue_backward = _sig("vcr_prologue_backward", c_int, [c_int, c_int] + [P
 
 vcr_binning_reference_lists = _sig("vcr_binning_reference_lists", c_int, [c_int, c_int, c_int, c_int, P_, P_, P_, c_void_p])
 vcr_view_loss_total = _sig("vcr_view_loss_total", c_int, [P_, c_int, c_int, c_float, c_float, c_float, P_, c_void_p])
+vcr_unpack_u8 = _sig("vcr_unpack_u8", c_int, [P_, P_, ctypes.c_longlong, c_void_p])
 vcr_ssim_forward = _sig("vcr_ssim_forward", c_int, [c_int, c_int, c_int, P_, P_, P_, P_, c_void_p])
 vcr_ssim_backward = _sig("vcr_ssim_backward", c_int, [c_int, c_int, c_int, P_, P_, P_, P_, P_, c_void_p])
 
@@ -169,7 +170,7 @@ DECLARED_SYMBOLS = [
     "vcr_knn_scratch_bytes", "vcr_dist2_knn3", "vcr_geom_layout", "vcr_binning_layout", "vcr_image_layout",
     "vcr_knn_noalloc_max_points", "vcr_dist2_knn3_noalloc", "vcr_view_loss_forward", "vcr_view_loss_backward",
     "vcr_profile_enable", "vcr_profile_kernel_count", "vcr_profile_kernel_name", "vcr_profile_read",
-    "vcr_rasterize_backward_chunked", "vcr_densify_stats_accumulate", "vcr_multimem_allreduce_sum", "vcr_prologue_forward", "vcr_prologue_backward", "vcr_ssim_forward", "vcr_ssim_backward", "vcr_adam_step", "vcr_view_loss_total", "vcr_binning_reference_lists", "vcr_compact_scratch_bytes", "vcr_compact_rows", "vcr_sh_grad_from_colors", "vcr_multimem_exchange",
+    "vcr_rasterize_backward_chunked", "vcr_densify_stats_accumulate", "vcr_multimem_allreduce_sum", "vcr_prologue_forward", "vcr_prologue_backward", "vcr_ssim_forward", "vcr_ssim_backward", "vcr_adam_step", "vcr_view_loss_total", "vcr_unpack_u8", "vcr_binning_reference_lists", "vcr_compact_scratch_bytes", "vcr_compact_rows", "vcr_sh_grad_from_colors", "vcr_multimem_exchange",
     "vcr_variant_channels", "vcr_rasterize_forward_variant", "vcr_rasterize_backward_variant", "vcr_pair_counters", "vcr_debug_block_timeline", "vcr_debug_radix_fault", "vcr_debug_render_version", "vcr_densify_scratch_bytes", "vcr_densify_decide", "vcr_densify_fill",
 ]
 
