@@ -366,7 +366,9 @@ __global__ void __launch_bounds__(256) render_backward_kernel(
 #ifndef VCR_RING_B
 #define VCR_RING_B 1          // 1: staging buffer as a ring of 32-entry chunks with ready flags, no block barrier (see render_forward.cu)
 #endif
+#ifndef RB2_CHUNKS
 #define RB2_CHUNKS 8
+#endif
 #define RB2_SLOTS (VCR_RING_B ? 32 * RB2_CHUNKS : RB2_BATCH)
 #ifndef VCR_RING_B_AHEAD
 #define VCR_RING_B_AHEAD 4

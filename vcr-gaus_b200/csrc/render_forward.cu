@@ -281,7 +281,9 @@ __global__ void __launch_bounds__(256, VAR ? 3 : 4) render_forward_kernel(
 #ifndef VCR_RING
 #define VCR_RING 1            // 1: the staging buffer is a ring of 32-entry chunks with per-chunk ready flags (no block barrier)
 #endif
+#ifndef RF2_CHUNKS
 #define RF2_CHUNKS 8                      // ring length in chunks
+#endif
 #ifndef VCR_RING_AHEAD
 #define VCR_RING_AHEAD 2                  // a warp stages a chunk before consuming if the ring is less than this far ahead of it
 #endif
