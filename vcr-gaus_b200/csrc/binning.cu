@@ -209,6 +209,7 @@ __global__ void __launch_bounds__(256) duplicate_sorted_kernel(int P, int gx, in
     __shared__ uint32_t incl[256];
     __shared__ uint32_t s_gid[256];
     __shared__ int s_x0[256], s_y0[256], s_w[256];
+    __shared__ float s_iw[256];                     // 1 / rectangle width
     __shared__ uint32_t warp_tot[8];
     __shared__ uint32_t hist[4][256];
     const int t = threadIdx.x, lane = t & 31, w = t >> 5;
@@ -240,7 +241,7 @@ __global__ void __launch_bounds__(256) duplicate_sorted_kernel(int P, int gx, in
     for (int k = 0; k < 8; k++) wex += (k < w) ? warp_tot[k] : 0u;
     inc += wex;
     incl[t] = inc;
-    s_gid[t] = gid; s_x0[t] = x0; s_y0[t] = y0; s_w[t] = rw;
+    s_gid[t] = gid; s_x0[t] = x0; s_y0[t] = y0; s_w[t] = rw; s_iw[t] = rw > 0 ? 1.0f / (float)rw : 0.f;
     const uint32_t base = sorted_sums[blockIdx.x];
     __syncthreads();
     const uint32_t total = incl[255];
@@ -252,8 +253,14 @@ __global__ void __launch_bounds__(256) duplicate_sorted_kernel(int P, int gx, in
         }
         const uint32_t local = k - (lo ? incl[lo - 1] : 0u);
         const int wdt = s_w[lo];
-        const int y = s_y0[lo] + (int)(local / (uint32_t)wdt);
-        const int x = s_x0[lo] + (int)(local % (uint32_t)wdt);
+        // row = local / width.  (local + 0.5) * (1 / width) in FP32 has the same integer part as the exact quotient while
+        // local < 2^22: the quotient's fraction lies in [0.5/w, 1 - 0.5/w] and the two roundings move it by < local * 2^-23 / w.
+        // Rectangles of 2^22 tiles and more (a 32k x 32k image covered by one Gaussian) take the integer division.
+        uint32_t row;
+        if (local < (1u << 22)) row = (uint32_t)(((float)local + 0.5f) * s_iw[lo]);
+        else row = local / (uint32_t)wdt;
+        const int y = s_y0[lo] + (int)row;
+        const int x = s_x0[lo] + (int)(local - row * (uint32_t)wdt);
         const uint32_t tile = (uint32_t)(y * gx + x);
         keys_out[base + k] = tile;
         vals_out[base + k] = s_gid[lo];
