@@ -715,7 +715,7 @@ __global__ void __launch_bounds__(RB2_THREADS, VCR_RB2_MINBLOCKS) render_backwar
             uint32_t spins = 0;
             while (v_ready[my % RB2_CHUNKS] != my + 1u) {
                 if (!try_stage(nchunks)) {
-                    __nanosleep(32);
+                    __nanosleep(VCR_RING_NAP);
                     // never reached unless the protocol is broken: leave through the error flag of the sort instead of hanging
                     if (++spins > (VCR_RING_SPIN_LIMIT)) { atomicExch(const_cast<unsigned int*>(abort_flag), 1u); broken = true; break; }
                 }
@@ -732,7 +732,7 @@ __global__ void __launch_bounds__(RB2_THREADS, VCR_RB2_MINBLOCKS) render_backwar
         for (uint32_t spins = 0; spins < (VCR_RING_SPIN_LIMIT); ) {        // finished (or nothing to do): keep staging for the others
             if (*v_next >= nchunks) break;
             if ((v_tail[0] & v_tail[1] & v_tail[2] & v_tail[3]) == 0xffffffffu) break;
-            if (!try_stage(nchunks)) { __nanosleep(64); spins++; }
+            if (!try_stage(nchunks)) { __nanosleep(2 * VCR_RING_NAP); spins++; }
         }
     }
 #else

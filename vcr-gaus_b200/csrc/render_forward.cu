@@ -536,7 +536,7 @@ __global__ void __launch_bounds__(RF2_THREADS, VCR_RF2_MINBLOCKS) render_forward
             uint32_t spins = 0;
             while (v_ready[my % RF2_CHUNKS] != my + 1u) {
                 if (!try_stage(nchunks)) {
-                    __nanosleep(32);
+                    __nanosleep(VCR_RING_NAP);
                     // never reached unless the protocol is broken: leave through the error flag of the sort (reported by the
                     // next call) instead of hanging the device
                     if (++spins > (VCR_RING_SPIN_LIMIT)) { atomicExch(const_cast<unsigned int*>(abort_flag), 1u); break; }
@@ -557,7 +557,7 @@ __global__ void __launch_bounds__(RF2_THREADS, VCR_RF2_MINBLOCKS) render_forward
         for (uint32_t spins = 0; spins < (VCR_RING_SPIN_LIMIT); ) {
             if (*v_next >= nchunks) break;                                                              // everything is staged
             if ((v_tail[0] & v_tail[1] & v_tail[2] & v_tail[3]) == 0xffffffffu) break;                  // nobody is left to read it
-            if (!try_stage(nchunks)) { __nanosleep(64); spins++; }
+            if (!try_stage(nchunks)) { __nanosleep(2 * VCR_RING_NAP); spins++; }
         }
     }
 #else
