@@ -319,8 +319,11 @@ __device__ __forceinline__ void preprocess_backward_body(const BwdParams& p, con
     }
 }
 
+#ifndef VCR_PB_MINBLOCKS
+#define VCR_PB_MINBLOCKS 4
+#endif
 template <bool COOP>
-__global__ void __launch_bounds__(256, 4) preprocess_backward_kernel(const BwdParams p, const GeomState g, const int first_block) {
+__global__ void __launch_bounds__(256, VCR_PB_MINBLOCKS) preprocess_backward_kernel(const BwdParams p, const GeomState g, const int first_block) {
     const int block = first_block + (int)blockIdx.x;        // a launch covers blocks [first_block, first_block + gridDim.x)
     const int idx = block * 256 + threadIdx.x;
     __shared__ float V[16], Pm[16];

@@ -19,7 +19,9 @@
 #include <atomic>
 
 #define RB_BATCH 256
+#ifndef RB_SPARSE_LANES
 #define RB_SPARSE_LANES 2
+#endif
 
 struct __align__(16) StagedGeoB {
     float x, y, ca, cb;
